@@ -1,0 +1,438 @@
+// K3/K4: BatchNorm2d(track_running_stats=False) + ReLU (+ MaxPool2d(2,2))
+// forward and backward as fused NHWC bf16 kernels.  Reference modules:
+// /root/reference/part1/model.py:15-16 (MaxPool2d), :24 (BatchNorm2d, batch statistics in
+// train AND eval), :25 (ReLU).  Three ATen ops per direction in the reference; here
+//   forward : one pass   raw conv output -> normalised, rectified, (pooled) activation
+//   backward: two passes (per-channel sums, then dx), recomputing the normalised value,
+//             the ReLU mask and the pool argmax from the saved raw conv output instead
+//             of storing masks / indices.
+// Per-channel sums of the forward come from the conv epilogue (conv_fprop.cu) or from
+// ddpb_channel_stats below (stand-alone variant, also the oracle in the unit tests).
+#include "common.cuh"
+
+namespace ddpb {
+
+constexpr int kBnThreads = 256;
+
+struct BnGeom {
+  int N, H, W, C;   // pre-pool geometry
+  int pool;         // 1: 2x2/2 max-pool follows the ReLU
+  float eps;
+};
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
+  uint4 u;
+  u.x = pack_bf16x2(v[0], v[1]);
+  u.y = pack_bf16x2(v[2], v[3]);
+  u.z = pack_bf16x2(v[4], v[5]);
+  u.w = pack_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
+// scale/shift per channel in shared memory: y = x*scale + shift.
+__device__ __forceinline__ void bn_coeffs_to_smem(const float* __restrict__ stats, const float* __restrict__ gamma,
+                                                  const float* __restrict__ beta, int C, float count, float eps,
+                                                  float* s_scale, float* s_shift, float* s_mean, float* s_rstd) {
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float mean = stats[c] / count;
+    float var = stats[C + c] / count - mean * mean;   // biased variance, as nn.BatchNorm2d normalises
+    var = fmaxf(var, 0.f);
+    const float rstd = rsqrtf(var + eps);
+    const float sc = gamma[c] * rstd;
+    s_scale[c] = sc;
+    s_shift[c] = beta[c] - mean * sc;
+    if (s_mean) {
+      s_mean[c] = mean;
+      s_rstd[c] = rstd;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// stand-alone per-channel sum / sum of squares (accumulates into stats[2][C])
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBnThreads)
+channel_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ stats, long long P, int C) {
+  extern __shared__ float s_acc[];  // [2][C]
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) s_acc[c] = 0.f;
+  __syncthreads();
+  const int groups = C / 8;
+  const long long items = P * groups;
+  float a1[8], a2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a1[j] = a2[j] = 0.f;
+  int my_group = -1;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < items; i += stride) {
+    const int g = static_cast<int>(i % groups);
+    if (g != my_group) {
+      if (my_group >= 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          atomicAdd(&s_acc[my_group * 8 + j], a1[j]);
+          atomicAdd(&s_acc[C + my_group * 8 + j], a2[j]);
+          a1[j] = a2[j] = 0.f;
+        }
+      }
+      my_group = g;
+    }
+    float v[8];
+    load8(x + i * 8, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      a1[j] += v[j];
+      a2[j] += v[j] * v[j];
+    }
+  }
+  if (my_group >= 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&s_acc[my_group * 8 + j], a1[j]);
+      atomicAdd(&s_acc[C + my_group * 8 + j], a2[j]);
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) atomicAdd(&stats[c], s_acc[c]);
+}
+
+// ------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBnThreads)
+bn_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
+                        const float* __restrict__ gamma, const float* __restrict__ beta,
+                        __nv_bfloat16* __restrict__ y, float* __restrict__ saved /* [2][C] mean, rstd */,
+                        BnGeom g) {
+  extern __shared__ float s_coef[];  // scale[C], shift[C], mean[C], rstd[C]
+  float* s_scale = s_coef;
+  float* s_shift = s_coef + g.C;
+  float* s_mean = s_coef + 2 * g.C;
+  float* s_rstd = s_coef + 3 * g.C;
+  const float count = static_cast<float>(static_cast<long long>(g.N) * g.H * g.W);
+  bn_coeffs_to_smem(stats, gamma, beta, g.C, count, g.eps, s_scale, s_shift, s_mean, s_rstd);
+  __syncthreads();
+  if (blockIdx.x == 0 && saved != nullptr) {
+    for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
+      saved[c] = s_mean[c];
+      saved[g.C + c] = s_rstd[c];
+    }
+  }
+  const int groups = g.C / 8;
+  const int Ho = g.pool ? g.H / 2 : g.H, Wo = g.pool ? g.W / 2 : g.W;
+  const long long items = static_cast<long long>(g.N) * Ho * Wo * groups;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < items; i += stride) {
+    const int cg = static_cast<int>(i % groups);
+    const long long opix = i / groups;
+    float sc[8], sh[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = s_scale[cg * 8 + j];
+      sh[j] = s_shift[cg * 8 + j];
+    }
+    float out[8];
+    if (!g.pool) {
+      float v[8];
+      load8(x + opix * g.C + cg * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) out[j] = fmaxf(fmaf(v[j], sc[j], sh[j]), 0.f);
+    } else {
+      const int wo = static_cast<int>(opix % Wo);
+      const long long t = opix / Wo;
+      const int ho = static_cast<int>(t % Ho);
+      const long long n = t / Ho;
+      const long long base = ((n * g.H + 2 * ho) * g.W + 2 * wo);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) out[j] = 0.f;   // ReLU floor
+#pragma unroll
+      for (int d = 0; d < 4; ++d) {
+        const long long ipix = base + (d >> 1) * g.W + (d & 1);
+        float v[8];
+        load8(x + ipix * g.C + cg * 8, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) out[j] = fmaxf(out[j], fmaf(v[j], sc[j], sh[j]));
+      }
+    }
+    store8(y + opix * g.C + cg * 8, out);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward, pass 1: sums[0][c] = sum g, sums[1][c] = sum g*xhat, where g is dy routed back
+// through the pool (first maximum wins, like ATen) and the ReLU mask.
+// Block 0 also clears the conv-bias gradient slot that pass 2 accumulates into.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void routed_grad(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                            const BnGeom& g, long long ipix_n, int h, int w, int cg,
+                                            const float (&sc)[8], const float (&sh)[8], const float (&xv)[8],
+                                            float (&gr)[8]) {
+  // gradient reaching pre-pool position (n,h,w) for the 8 channels of group cg
+  if (!g.pool) {
+    float d[8];
+    load8(dy + ((ipix_n * g.H + h) * g.W + w) * g.C + cg * 8, d);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) gr[j] = (fmaf(xv[j], sc[j], sh[j]) > 0.f) ? d[j] : 0.f;
+    return;
+  }
+  const int Ho = g.H / 2, Wo = g.W / 2;
+  const int ho = h >> 1, wo = w >> 1;
+  const int me = ((h & 1) << 1) | (w & 1);
+  float d[8];
+  load8(dy + ((ipix_n * Ho + ho) * Wo + wo) * g.C + cg * 8, d);
+  float best[8];
+  int arg[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    best[j] = 0.f;   // a window whose maximum is <= 0 passes no gradient (ReLU)
+    arg[j] = -1;
+  }
+  const long long base = (ipix_n * g.H + 2 * ho) * g.W + 2 * wo;
+#pragma unroll
+  for (int dd = 0; dd < 4; ++dd) {
+    float v[8];
+    if (dd == me) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = xv[j];
+    } else {
+      load8(x + (base + (dd >> 1) * g.W + (dd & 1)) * g.C + cg * 8, v);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float z = fmaf(v[j], sc[j], sh[j]);
+      if (z > best[j]) {
+        best[j] = z;
+        arg[j] = dd;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) gr[j] = (arg[j] == me) ? d[j] : 0.f;
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                     const float* __restrict__ saved, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, float* __restrict__ sums /* [2][C] accumulated */,
+                     float* __restrict__ dbias_clear /* [C] or null */, BnGeom g) {
+  extern __shared__ float s_mem[];  // scale[C], shift[C], mean[C], rstd[C], acc[2][C]
+  float* s_scale = s_mem;
+  float* s_shift = s_mem + g.C;
+  float* s_mean = s_mem + 2 * g.C;
+  float* s_rstd = s_mem + 3 * g.C;
+  float* s_acc = s_mem + 4 * g.C;
+  for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
+    const float mean = saved[c], rstd = saved[g.C + c];
+    const float sc = gamma[c] * rstd;
+    s_scale[c] = sc;
+    s_shift[c] = beta[c] - mean * sc;
+    s_mean[c] = mean;
+    s_rstd[c] = rstd;
+    s_acc[c] = 0.f;
+    s_acc[g.C + c] = 0.f;
+    if (blockIdx.x == 0 && dbias_clear != nullptr) dbias_clear[c] = 0.f;
+  }
+  __syncthreads();
+  const int groups = g.C / 8;
+  const long long items = static_cast<long long>(g.N) * g.H * g.W * groups;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  float a1[8], a2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a1[j] = a2[j] = 0.f;
+  int my_group = -1;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < items; i += stride) {
+    const int cg = static_cast<int>(i % groups);
+    const long long pix = i / groups;
+    if (cg != my_group) {
+      if (my_group >= 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          atomicAdd(&s_acc[my_group * 8 + j], a1[j]);
+          atomicAdd(&s_acc[g.C + my_group * 8 + j], a2[j]);
+          a1[j] = a2[j] = 0.f;
+        }
+      }
+      my_group = cg;
+    }
+    const int w = static_cast<int>(pix % g.W);
+    const long long t = pix / g.W;
+    const int h = static_cast<int>(t % g.H);
+    const long long n = t / g.H;
+    float sc[8], sh[8], xv[8], gr[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = s_scale[cg * 8 + j];
+      sh[j] = s_shift[cg * 8 + j];
+    }
+    load8(x + pix * g.C + cg * 8, xv);
+    routed_grad(x, dy, g, n, h, w, cg, sc, sh, xv, gr);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float xhat = (xv[j] - s_mean[cg * 8 + j]) * s_rstd[cg * 8 + j];
+      a1[j] += gr[j];
+      a2[j] += gr[j] * xhat;
+    }
+  }
+  if (my_group >= 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&s_acc[my_group * 8 + j], a1[j]);
+      atomicAdd(&s_acc[g.C + my_group * 8 + j], a2[j]);
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * g.C; c += blockDim.x) atomicAdd(&sums[c], s_acc[c]);
+}
+
+// ------------------------------------------------------------------------------------------
+// backward, pass 2: dx = gamma*rstd*(g - mean(g) - xhat*mean(g*xhat)); block 0 publishes
+// dgamma = sum g*xhat and dbeta = sum g; every block adds its share of sum(dx) to dbias.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                    const float* __restrict__ saved, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, const float* __restrict__ sums,
+                    __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                    float* __restrict__ dbias, BnGeom g) {
+  extern __shared__ float s_mem[];  // scale, shift, mean, rstd, mg, mgx, acc : 7*C
+  float* s_scale = s_mem;
+  float* s_shift = s_mem + g.C;
+  float* s_mean = s_mem + 2 * g.C;
+  float* s_rstd = s_mem + 3 * g.C;
+  float* s_mg = s_mem + 4 * g.C;
+  float* s_mgx = s_mem + 5 * g.C;
+  float* s_acc = s_mem + 6 * g.C;
+  const float inv_count = 1.f / static_cast<float>(static_cast<long long>(g.N) * g.H * g.W);
+  for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
+    const float mean = saved[c], rstd = saved[g.C + c];
+    const float sc = gamma[c] * rstd;
+    s_scale[c] = sc;
+    s_shift[c] = beta[c] - mean * sc;
+    s_mean[c] = mean;
+    s_rstd[c] = rstd;
+    s_mg[c] = sums[c] * inv_count;
+    s_mgx[c] = sums[g.C + c] * inv_count;
+    s_acc[c] = 0.f;
+    if (blockIdx.x == 0) {
+      if (dbeta) dbeta[c] = sums[c];
+      if (dgamma) dgamma[c] = sums[g.C + c];
+    }
+  }
+  __syncthreads();
+  const int groups = g.C / 8;
+  const long long items = static_cast<long long>(g.N) * g.H * g.W * groups;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  float ab[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) ab[j] = 0.f;
+  int my_group = -1;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < items; i += stride) {
+    const int cg = static_cast<int>(i % groups);
+    const long long pix = i / groups;
+    if (cg != my_group) {
+      if (my_group >= 0 && dbias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          atomicAdd(&s_acc[my_group * 8 + j], ab[j]);
+          ab[j] = 0.f;
+        }
+      }
+      my_group = cg;
+    }
+    const int w = static_cast<int>(pix % g.W);
+    const long long t = pix / g.W;
+    const int h = static_cast<int>(t % g.H);
+    const long long n = t / g.H;
+    float sc[8], sh[8], xv[8], gr[8], o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = s_scale[cg * 8 + j];
+      sh[j] = s_shift[cg * 8 + j];
+    }
+    load8(x + pix * g.C + cg * 8, xv);
+    routed_grad(x, dy, g, n, h, w, cg, sc, sh, xv, gr);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = cg * 8 + j;
+      const float xhat = (xv[j] - s_mean[c]) * s_rstd[c];
+      o[j] = sc[j] * (gr[j] - s_mg[c] - xhat * s_mgx[c]);
+      ab[j] += o[j];
+    }
+    store8(dx + pix * g.C + cg * 8, o);
+  }
+  if (dbias != nullptr) {
+    if (my_group >= 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) atomicAdd(&s_acc[my_group * 8 + j], ab[j]);
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < g.C; c += blockDim.x) atomicAdd(&dbias[c], s_acc[c]);
+  }
+}
+
+static int bn_grid(long long items) {
+  long long blocks = (items + kBnThreads - 1) / kBnThreads;
+  const long long cap = 4LL * sm_count();
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+#define DDPB_BN_CHECK_GEOM(name)                                                                   \
+  DDPB_REQUIRE(C > 0 && C % 8 == 0 && C <= 2048, name ": C must be a multiple of 8, <= 2048 (got %d)", C); \
+  DDPB_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), name ": pooling needs even H, W (got %dx%d)", H, W)
+
+// stats[2][C] += (sum x, sum x^2) over the P rows of x[P][C] (bf16).
+extern "C" int ddpb_channel_stats(const void* x, float* stats, long long P, int C, cudaStream_t stream) {
+  DDPB_REQUIRE(C > 0 && C % 8 == 0 && C <= 2048, "channel_stats: bad C %d", C);
+  const long long items = P * (C / 8);
+  channel_stats_kernel<<<bn_grid(items), kBnThreads, 2 * C * sizeof(float), stream>>>(
+      static_cast<const __nv_bfloat16*>(x), stats, P, C);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// y = maxpool2x2?(relu(batchnorm(x)));  x: [N*H*W][C] bf16 raw conv output, stats: [2][C]
+// sums over those rows, saved: [2][C] receives (mean, rstd) for the backward pass.
+extern "C" int ddpb_bn_relu_pool_fwd(const void* x, const float* stats, const float* gamma, const float* beta,
+                                     void* y, float* saved, int N, int H, int W, int C, int pool, float eps,
+                                     cudaStream_t stream) {
+  DDPB_BN_CHECK_GEOM("bn_relu_pool_fwd");
+  BnGeom g{N, H, W, C, pool, eps};
+  const long long items = static_cast<long long>(N) * (pool ? H / 2 : H) * (pool ? W / 2 : W) * (C / 8);
+  bn_relu_pool_fwd_kernel<<<bn_grid(items), kBnThreads, 4 * C * sizeof(float), stream>>>(
+      static_cast<const __nv_bfloat16*>(x), stats, gamma, beta, static_cast<__nv_bfloat16*>(y), saved, g);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Backward of the fused block.  dy: gradient w.r.t. the (pooled) output, bf16.
+// sums: [2][C] fp32 scratch that MUST be zero on entry (pass 1 accumulates into it).
+// dx: [N*H*W][C] bf16 gradient w.r.t. the raw conv output.  dgamma/dbeta/dbias: fp32 [C]
+// (dbias may be null; it is cleared by pass 1 and accumulated by pass 2).
+extern "C" int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float* saved, const float* gamma,
+                                     const float* beta, float* sums, void* dx, float* dgamma, float* dbeta,
+                                     float* dbias, int N, int H, int W, int C, int pool, float eps,
+                                     cudaStream_t stream) {
+  DDPB_BN_CHECK_GEOM("bn_relu_pool_bwd");
+  BnGeom g{N, H, W, C, pool, eps};
+  const long long items = static_cast<long long>(N) * H * W * (C / 8);
+  const int grid = bn_grid(items);
+  bn_bwd_reduce_kernel<<<grid, kBnThreads, 6 * C * sizeof(float), stream>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), saved, gamma, beta, sums,
+      dbias, g);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  bn_bwd_apply_kernel<<<grid, kBnThreads, 7 * C * sizeof(float), stream>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), saved, gamma, beta, sums,
+      static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, dbias, g);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,323 @@
+// K6: convolution weight gradient (reference op O3, produced by autograd
+// for the nn.Conv2d at /root/reference/part1/model.py:18-23) on tcgen05 tensor cores.
+//
+//   dW[k][tap][c] = sum over pixels p of dY[p][k] * X[p shifted by tap][c]
+//
+// GEMM view per filter tap: M = C_out (128 per CTA), N = C_in (64 or 128 per CTA),
+// reduction over the N*H*W pixels.  Both operands are stored pixel-major with the
+// channel contiguous, i.e. they are "MN-major" for this GEMM, which tcgen05.mma
+// consumes directly (a_major = b_major = 1): no transposes are materialised.
+//   A = dY  : 2-D TMA boxes of (64 channels, 64 pixels)
+//   B = X   : 4-D TMA boxes (64 ch, W, bh, bn) shifted by the tap offset, halo zero-filled
+// Each box is 64 rows of 128 bytes with SWIZZLE_128B; a 128-wide M (or N) is two boxes
+// LBO = 8 KB apart, and 8-pixel groups are SBO = 1 KB apart.
+//
+// The pixel reduction is split over gridDim.y CTAs; partial tiles go to a scratch
+// buffer [split][C_out][taps*C_in] that ddpb_wgrad_reduce sums in a fixed order
+// (deterministic, unlike atomics).  With one split the tile is written straight to
+// its final place (for the training engine: the flat gradient arena).
+#include "common.cuh"
+
+namespace ddpb {
+
+constexpr int kWgThreads = 192;
+constexpr int kWgPix = 64;                    // pixels per pipeline stage
+constexpr int kWgBoxBytes = kWgPix * 128;     // one (64 ch x 64 px) box = 8 KB
+
+template <int BLOCK_N>
+struct WgradCfg {
+  static constexpr int kStages = 4;
+  static constexpr int kABytes = 2 * kWgBoxBytes;                 // M = 128 channels of dY
+  static constexpr int kBBytes = (BLOCK_N / 64) * kWgBoxBytes;    // N channels of X
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 256;
+};
+
+struct WgradParams {
+  float* out;          // final gradient or scratch (see out_split_stride)
+  long long out_split_stride;  // elements between splits (0 when gridDim.y == 1)
+  int out_ld;          // row stride of `out` in elements (taps * C_in)
+  int P;               // pixels
+  int C_in, C_out;
+  int taps;
+  int m_tiles, n_tiles;
+  int bh, bn, hblocks;  // 64-pixel box geometry of X
+  int dup_m;            // C_out == 64: both halves of M read the same 64 channels
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kWgThreads)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x,
+                  const WgradParams p) {
+  using Cfg = WgradCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tiles = smem;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + Cfg::kStages;
+  uint64_t* tmem_full_bar = bars + 2 * Cfg::kStages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * Cfg::kStages + 1);
+
+  const int warp = threadIdx.x >> 5;
+  // blockIdx.x -> (tap, m_tile, n_tile)
+  int t = blockIdx.x;
+  const int n_tile = t % p.n_tiles;
+  t /= p.n_tiles;
+  const int m_tile = t % p.m_tiles;
+  const int tap = t / p.m_tiles;
+  const int split = blockIdx.y, splits = gridDim.y;
+  const int pix_blocks = (p.P + kWgPix - 1) / kWgPix;
+  const int pb_begin = static_cast<int>(static_cast<long long>(pix_blocks) * split / splits);
+  const int pb_end = static_cast<int>(static_cast<long long>(pix_blocks) * (split + 1) / splits);
+  const int num_k = pb_end - pb_begin;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmap_dy);
+    tma_prefetch_desc(&tmap_x);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      for (int i = 0; i < Cfg::kStages; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], 1);
+      }
+      mbar_init(tmem_full_bar, 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_ptr_smem, BLOCK_N);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int dr = 0, ds = 0;
+      if (p.taps == 9) {
+        dr = tap / 3 - 1;
+        ds = tap % 3 - 1;
+      }
+      const int k0 = m_tile * 128;
+      const int k1 = p.dup_m ? k0 : k0 + 64;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int pb = pb_begin; pb < pb_end; ++pb) {
+        const int n_img = (pb / p.hblocks) * p.bn;
+        const int h0 = (pb % p.hblocks) * p.bh;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* a_dst = tiles + stage * Cfg::kStageBytes;
+        uint8_t* b_dst = a_dst + Cfg::kABytes;
+        mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+        tma_load_2d(a_dst, &tmap_dy, &full_bar[stage], k0, pb * kWgPix);
+        tma_load_2d(a_dst + kWgBoxBytes, &tmap_dy, &full_bar[stage], k1, pb * kWgPix);
+#pragma unroll
+        for (int j = 0; j < BLOCK_N / 64; ++j)
+          tma_load_4d(b_dst + j * kWgBoxBytes, &tmap_x, &full_bar[stage], n_tile * BLOCK_N + j * 64, ds,
+                      h0 + dr, n_img);
+        if (++stage == Cfg::kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BLOCK_N, 1, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int k = 0; k < num_k; ++k) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(tiles + stage * Cfg::kStageBytes);
+        const uint32_t b_addr = a_addr + Cfg::kABytes;
+#pragma unroll
+        for (int kk = 0; kk < kWgPix / 16; ++kk) {
+          // 16 pixels = 16 rows of 128 bytes further down the box
+          const uint64_t adesc = make_smem_desc_sw128(a_addr + kk * 16 * 128, kWgBoxBytes, 1024);
+          const uint64_t bdesc = make_smem_desc_sw128(b_addr + kk * 16 * 128, kWgBoxBytes, 1024);
+          umma_f16(tmem_base, adesc, bdesc, idesc, (k | kk) != 0);
+        }
+        umma_commit(&empty_bar[stage]);
+        if (++stage == Cfg::kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tmem_full_bar);
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane_id();       // output channel within the M tile
+    const int k_ch = m_tile * 128 + row;
+    const bool valid = p.dup_m ? (row < 64) : (k_ch < p.C_out);
+    float* out_row = p.out + static_cast<long long>(split) * p.out_split_stride +
+                     static_cast<long long>(k_ch) * p.out_ld + tap * p.C_in + n_tile * BLOCK_N;
+    if (num_k > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+#pragma unroll 1
+    for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
+      uint32_t raw[32];
+      if (num_k > 0) {
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + chunk * 32, raw);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) raw[j] = 0u;
+      }
+      if (valid) {
+        uint4* dst = reinterpret_cast<uint4*>(out_row + chunk * 32);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dst[j] = make_uint4(raw[4 * j], raw[4 * j + 1], raw[4 * j + 2], raw[4 * j + 3]);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BLOCK_N);
+  }
+}
+
+// out[r][c] = sum_s ws[s][r][c] for c < cols_valid; fixed summation order.
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out, int splits,
+                                    long long split_stride, int rows, int cols_valid, int ws_ld, int out_ld) {
+  const long long total = static_cast<long long>(rows) * cols_valid;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / cols_valid), c = static_cast<int>(i - static_cast<long long>(r) * cols_valid);
+    const float* src = ws + static_cast<long long>(r) * ws_ld + c;
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += src[s * split_stride];
+    out[static_cast<long long>(r) * out_ld + c] = acc;
+  }
+}
+
+template <int BLOCK_N>
+static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
+                        cudaStream_t stream) {
+  using Cfg = WgradCfg<BLOCK_N>;
+  static bool configured = false;
+  if (!configured) {
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BLOCK_N>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  dim3 grid(p.taps * p.m_tiles * p.n_tiles, splits);
+  conv_wgrad_kernel<BLOCK_N><<<grid, kWgThreads, Cfg::kSmemBytes, stream>>>(tdy, tx, p);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+// Number of pixel splits the launcher will use for this shape (so callers can size scratch).
+extern "C" int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps) {
+  const int P = N * H * W;
+  const int block_n = (C_in % 128 == 0) ? 128 : 64;
+  const int m_tiles = (C_out + 127) / 128;
+  const int tiles = taps * m_tiles * (C_in / block_n);
+  const int pix_blocks = (P + kWgPix - 1) / kWgPix;
+  int target = 2 * sm_count();
+  if (target <= 0) target = 296;
+  int splits = (target + tiles - 1) / tiles;
+  // keep at least 8 pipeline steps (512 pixels) per CTA so the prologue amortises
+  int max_splits = pix_blocks / 8;
+  if (max_splits < 1) max_splits = 1;
+  if (splits > max_splits) splits = max_splits;
+  if (splits > 256) splits = 256;
+  if (splits < 1) splits = 1;
+  return splits;
+}
+
+// Scratch floats needed by ddpb_conv_wgrad for this shape (0 if it writes dw directly).
+extern "C" long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps) {
+  const int splits = ddpb_conv_wgrad_splits(N, H, W, C_in, C_out, taps);
+  const long long rows = (C_out < 128) ? 128 : C_out;   // dup_m tiles still own 128 rows of scratch
+  return (splits > 1 || C_out < 128) ? static_cast<long long>(splits) * rows * taps * C_in : 0;
+}
+
+// Shared implementation: `scratch` may be any device buffer of at least
+// ddpb_conv_wgrad_scratch_elems floats.
+static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, int N, int H, int W, int C_in,
+                      int C_out, int taps, int dw_cols_valid, int dw_ld, cudaStream_t stream) {
+  DDPB_REQUIRE(taps == 1 || taps == 9, "conv_wgrad: taps must be 1 or 9 (got %d)", taps);
+  DDPB_REQUIRE(C_in % 64 == 0 && C_in > 0, "conv_wgrad: C_in must be a multiple of 64 (got %d)", C_in);
+  DDPB_REQUIRE(C_out == 64 || C_out % 128 == 0, "conv_wgrad: C_out must be 64 or a multiple of 128 (got %d)",
+               C_out);
+  int bh, bn, hblocks;
+  DDPB_REQUIRE(pixel_box(H, W, kWgPix, &bh, &bn, &hblocks),
+               "conv_wgrad: unsupported spatial size %dx%d for 64-pixel boxes", H, W);
+  const int block_n = (C_in % 128 == 0) ? 128 : 64;
+  const int splits = ddpb_conv_wgrad_splits(N, H, W, C_in, C_out, taps);
+  const bool direct = (splits == 1 && C_out >= 128 && dw_cols_valid == taps * C_in && dw_ld == taps * C_in);
+  DDPB_REQUIRE(direct || scratch != nullptr, "conv_wgrad: this shape needs scratch memory");
+
+  CUtensorMap tdy, tx;
+  {
+    uint64_t dims[2] = {(uint64_t)C_out, (uint64_t)N * H * W};
+    uint64_t strides[1] = {(uint64_t)C_out * 2};
+    uint32_t box[2] = {64, (uint32_t)kWgPix};
+    if (encode_tmap(&tdy, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dy, dims, strides, box,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B))
+      return 3;
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)C_in, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t strides[3] = {(uint64_t)C_in * 2, (uint64_t)W * C_in * 2, (uint64_t)H * W * C_in * 2};
+    uint32_t box[4] = {64, (uint32_t)W, (uint32_t)bh, (uint32_t)bn};
+    if (encode_tmap(&tx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x, dims, strides, box,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B))
+      return 3;
+  }
+  WgradParams p;
+  p.P = N * H * W;
+  p.C_in = C_in;
+  p.C_out = C_out;
+  p.taps = taps;
+  p.m_tiles = (C_out + 127) / 128;
+  p.n_tiles = C_in / block_n;
+  p.bh = bh;
+  p.bn = bn;
+  p.hblocks = hblocks;
+  p.dup_m = (C_out == 64);
+  p.out_ld = taps * C_in;
+  const long long rows = (C_out < 128) ? 128 : C_out;
+  if (direct) {
+    p.out = dw;
+    p.out_split_stride = 0;
+  } else {
+    p.out = scratch;
+    p.out_split_stride = rows * taps * C_in;
+  }
+  int rc = (block_n == 128) ? launch_wgrad<128>(tdy, tx, p, splits, stream)
+                            : launch_wgrad<64>(tdy, tx, p, splits, stream);
+  if (rc) return rc;
+  if (!direct) {
+    const long long total = static_cast<long long>(C_out) * dw_cols_valid;
+    int blocks = static_cast<int>((total + 255) / 256);
+    if (blocks > 4 * 148) blocks = 4 * 148;
+    wgrad_reduce_kernel<<<blocks, 256, 0, stream>>>(scratch, dw, splits, p.out_split_stride, C_out,
+                                                    dw_cols_valid, taps * C_in, dw_ld);
+    DDPB_CHECK_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+// dy: [N*H*W][C_out] bf16; x: [N][H][W][C_in] bf16; dw: fp32 [C_out][dw_ld], of which the
+// first dw_cols_valid (<= taps*C_in) columns of every row are written.  scratch: device
+// buffer of ddpb_conv_wgrad_scratch_elems() floats (may be null when that is 0).
+extern "C" int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* scratch, int N, int H, int W,
+                               int C_in, int C_out, int taps, int dw_cols_valid, int dw_ld,
+                               cudaStream_t stream) {
+  return wgrad_impl(dy, x, dw, scratch, N, H, W, C_in, C_out, taps, dw_cols_valid, dw_ld, stream);
+}

@@ -1,0 +1,208 @@
+"""Tensor-level wrappers over the sm_100a kernels (one function per extern "C" entry point).
+
+Shapes follow the kernels' native layout: activations are NHWC bf16 stored as
+``[N*H*W, C]`` matrices; conv filters are ``[C_out, taps*C_in]`` bf16.  Each wrapper names
+the reference op it replaces.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _native as nat
+
+BN_EPS = 1e-5  # nn.BatchNorm2d default, /root/reference/part1/model.py:24
+
+
+def _s(stream):
+    return nat.stream_ptr(stream)
+
+
+def conv_fprop(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, N: int, H: int, W: int, C_in: int,
+               C_out: int, taps: int = 9, *, out: torch.Tensor | None = None, stats: torch.Tensor | None = None,
+               block_n: int = 0, stream=None) -> torch.Tensor:
+    """O1 (and O2 when fed dY and the rotated filters): y[P,C_out] = conv3x3(x) (+bias).
+
+    ``stats`` (fp32 [2, C_out]) is accumulated with per-channel sum / sum of squares of y.
+    """
+    nat.require_cuda(x, w)
+    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    assert x.numel() == N * H * W * C_in and w.numel() == C_out * taps * C_in
+    if out is None:
+        out = torch.empty(N * H * W, C_out, dtype=torch.bfloat16, device=x.device)
+    rc = nat.load().ddpb_conv_fprop(nat.ptr(x), nat.ptr(w), nat.ptr(bias), nat.ptr(out), nat.ptr(stats), N, H, W,
+                                    C_in, C_out, taps, block_n, _s(stream))
+    nat.check(rc, "ddpb_conv_fprop")
+    return out
+
+
+def conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps=9) -> int:
+    return int(nat.load().ddpb_conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps))
+
+
+def conv_wgrad_splits(N, H, W, C_in, C_out, taps=9) -> int:
+    return int(nat.load().ddpb_conv_wgrad_splits(N, H, W, C_in, C_out, taps))
+
+
+def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, N: int, H: int, W: int, C_in: int, C_out: int, taps: int = 9, *,
+               out: torch.Tensor | None = None, cols_valid: int | None = None, out_ld: int | None = None,
+               scratch: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """O3: dW[C_out, taps*C_in] (fp32) = sum over pixels of dy^T * shifted x."""
+    nat.require_cuda(dy, x)
+    assert dy.dtype == torch.bfloat16 and x.dtype == torch.bfloat16
+    cols_valid = taps * C_in if cols_valid is None else cols_valid
+    out_ld = cols_valid if out_ld is None else out_ld
+    if out is None:
+        out = torch.empty(C_out, out_ld, dtype=torch.float32, device=x.device)
+    need = conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps)
+    if need and (scratch is None or scratch.numel() < need):
+        scratch = torch.empty(need, dtype=torch.float32, device=x.device)
+    rc = nat.load().ddpb_conv_wgrad(nat.ptr(dy), nat.ptr(x), nat.ptr(out), nat.ptr(scratch), N, H, W, C_in, C_out,
+                                    taps, cols_valid, out_ld, _s(stream))
+    nat.check(rc, "ddpb_conv_wgrad")
+    return out
+
+
+def channel_stats(x: torch.Tensor, C_: int, *, stats: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    nat.require_cuda(x)
+    if stats is None:
+        stats = torch.zeros(2, C_, dtype=torch.float32, device=x.device)
+    rc = nat.load().ddpb_channel_stats(nat.ptr(x), nat.ptr(stats), x.numel() // C_, C_, _s(stream))
+    nat.check(rc, "ddpb_channel_stats")
+    return stats
+
+
+def bn_relu_pool_fwd(x, stats, gamma, beta, N, H, W, C_, pool: bool, *, out=None, saved=None, eps=BN_EPS,
+                     stream=None):
+    """O4+O6+O7 forward.  Returns (y, saved[2,C] = mean, rstd)."""
+    nat.require_cuda(x, stats, gamma, beta)
+    Po = N * (H // 2 if pool else H) * (W // 2 if pool else W)
+    if out is None:
+        out = torch.empty(Po, C_, dtype=torch.bfloat16, device=x.device)
+    if saved is None:
+        saved = torch.empty(2, C_, dtype=torch.float32, device=x.device)
+    rc = nat.load().ddpb_bn_relu_pool_fwd(nat.ptr(x), nat.ptr(stats), nat.ptr(gamma), nat.ptr(beta), nat.ptr(out),
+                                          nat.ptr(saved), N, H, W, C_, int(pool), eps, _s(stream))
+    nat.check(rc, "ddpb_bn_relu_pool_fwd")
+    return out, saved
+
+
+def bn_relu_pool_bwd(x, dy, saved, gamma, beta, N, H, W, C_, pool: bool, *, sums=None, dx=None, dgamma=None,
+                     dbeta=None, dbias=None, eps=BN_EPS, stream=None):
+    """O5+O6+O7 backward.  ``sums`` (fp32 [2,C]) must be zero on entry."""
+    nat.require_cuda(x, dy, saved, gamma, beta)
+    dev = x.device
+    if sums is None:
+        sums = torch.zeros(2, C_, dtype=torch.float32, device=dev)
+    if dx is None:
+        dx = torch.empty(N * H * W, C_, dtype=torch.bfloat16, device=dev)
+    if dgamma is None:
+        dgamma = torch.empty(C_, dtype=torch.float32, device=dev)
+    if dbeta is None:
+        dbeta = torch.empty(C_, dtype=torch.float32, device=dev)
+    rc = nat.load().ddpb_bn_relu_pool_bwd(nat.ptr(x), nat.ptr(dy), nat.ptr(saved), nat.ptr(gamma), nat.ptr(beta),
+                                          nat.ptr(sums), nat.ptr(dx), nat.ptr(dgamma), nat.ptr(dbeta),
+                                          nat.ptr(dbias), N, H, W, C_, int(pool), eps, _s(stream))
+    nat.check(rc, "ddpb_bn_relu_pool_bwd")
+    return dx, dgamma, dbeta
+
+
+def fc_ce_fwd(x, w, b, labels, *, logits=None, row_loss=None, dlogits=None, row_correct=None, loss=None,
+              correct=None, stream=None):
+    """O9+O10(+O15) forward: logits, mean CE loss, dlogits, correct count."""
+    nat.require_cuda(x, w, b, labels)
+    assert labels.dtype == torch.int64 and x.dtype == torch.bfloat16
+    B, F = x.shape
+    K = w.shape[0]
+    dev = x.device
+    if row_loss is None:
+        row_loss = torch.empty(B, dtype=torch.float32, device=dev)
+    rc = nat.load().ddpb_fc_ce_fwd(nat.ptr(x), nat.ptr(w), nat.ptr(b), nat.ptr(labels), nat.ptr(logits),
+                                   nat.ptr(row_loss), nat.ptr(dlogits), nat.ptr(row_correct), nat.ptr(loss),
+                                   nat.ptr(correct), B, F, K, _s(stream))
+    nat.check(rc, "ddpb_fc_ce_fwd")
+    return row_loss
+
+
+def fc_bwd(x, w, dlogits, *, dw=None, db=None, dx=None, want_dx=True, stream=None):
+    nat.require_cuda(x, w, dlogits)
+    B, F = x.shape
+    K = w.shape[0]
+    dev = x.device
+    if dw is None:
+        dw = torch.empty(K, F, dtype=torch.float32, device=dev)
+    if db is None:
+        db = torch.empty(K, dtype=torch.float32, device=dev)
+    if dx is None and want_dx:
+        dx = torch.empty(B, F, dtype=torch.bfloat16, device=dev)
+    rc = nat.load().ddpb_fc_bwd(nat.ptr(x), nat.ptr(w), nat.ptr(dlogits), nat.ptr(dw), nat.ptr(db), nat.ptr(dx), B, F,
+                                K, _s(stream))
+    nat.check(rc, "ddpb_fc_bwd")
+    return dw, db, dx
+
+
+def sgd_step(p, g, m, lr, momentum, weight_decay, grad_scale=1.0, *, stream=None):
+    """O11+O12 over flat fp32 arenas, in place."""
+    nat.require_cuda(p, g, m)
+    assert p.dtype == g.dtype == m.dtype == torch.float32 and p.numel() == g.numel() == m.numel()
+    rc = nat.load().ddpb_sgd_step(nat.ptr(p), nat.ptr(g), nat.ptr(m), p.numel(), lr, momentum, weight_decay,
+                                  grad_scale, _s(stream))
+    nat.check(rc, "ddpb_sgd_step")
+
+
+class PackPlan:
+    """Pre-marshalled argument arrays for ddpb_pack_weights (built once per model)."""
+
+    def __init__(self, layers):
+        """layers: list of dict(master, fprop, dgrad|None, K, C, taps, fprop_ld, flat)."""
+        n = len(layers)
+        self.n = n
+        self._keep = layers
+        VP = C.c_void_p * n
+        IA = C.c_int * n
+        self.master = VP(*[l["master"].data_ptr() for l in layers])
+        self.fprop = VP(*[l["fprop"].data_ptr() for l in layers])
+        self.dgrad = VP(*[(l["dgrad"].data_ptr() if l["dgrad"] is not None else None) for l in layers])
+        self.K = IA(*[l["K"] for l in layers])
+        self.C = IA(*[l["C"] for l in layers])
+        self.taps = IA(*[l["taps"] for l in layers])
+        self.ld = IA(*[l["fprop_ld"] for l in layers])
+        self.flat = IA(*[int(l["flat"]) for l in layers])
+
+    def run(self, stream=None):
+        rc = nat.load().ddpb_pack_weights(self.n, self.master, self.fprop, self.dgrad, self.K, self.C, self.taps,
+                                          self.ld, self.flat, _s(stream))
+        nat.check(rc, "ddpb_pack_weights")
+
+
+def first_layer_operand_f32(x_nchw: torch.Tensor, *, out=None, stream=None) -> torch.Tensor:
+    """O16 tail + im2col for layer 0 from a normalised fp32 NCHW batch."""
+    nat.require_cuda(x_nchw)
+    assert x_nchw.dtype == torch.float32 and x_nchw.is_contiguous() and x_nchw.shape[1] == 3
+    N, _, H, W = x_nchw.shape
+    if out is None:
+        out = torch.empty(N * H * W, 64, dtype=torch.bfloat16, device=x_nchw.device)
+    rc = nat.load().ddpb_first_layer_operand_f32(nat.ptr(x_nchw), nat.ptr(out), N, H, W, _s(stream))
+    nat.check(rc, "ddpb_first_layer_operand_f32")
+    return out
+
+
+_MEAN3 = (C.c_float * 3)(125.3 / 255.0, 123.0 / 255.0, 113.9 / 255.0)  # part1/main.py:20
+_STD3 = (C.c_float * 3)(63.0 / 255.0, 62.1 / 255.0, 66.7 / 255.0)      # part1/main.py:21
+
+
+def first_layer_operand_u8(x_nhwc_u8: torch.Tensor, aug: torch.Tensor | None = None, *, out=None, pad: int = 4,
+                           stream=None) -> torch.Tensor:
+    """O16: crop/flip/normalise raw uint8 NHWC pixels and emit the layer-0 GEMM operand."""
+    nat.require_cuda(x_nhwc_u8)
+    assert x_nhwc_u8.dtype == torch.uint8 and x_nhwc_u8.is_contiguous() and x_nhwc_u8.shape[-1] == 3
+    N, H, W, _ = x_nhwc_u8.shape
+    if aug is not None:
+        assert aug.dtype == torch.int8 and aug.shape == (N, 4) and aug.is_cuda
+    if out is None:
+        out = torch.empty(N * H * W, 64, dtype=torch.bfloat16, device=x_nhwc_u8.device)
+    rc = nat.load().ddpb_first_layer_operand_u8(nat.ptr(x_nhwc_u8), nat.ptr(aug), nat.ptr(out), N, H, W, _MEAN3,
+                                                _STD3, pad, _s(stream))
+    nat.check(rc, "ddpb_first_layer_operand_u8")
+    return out

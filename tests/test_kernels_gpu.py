@@ -1,0 +1,203 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 restatement of the same op
+(ddpb200.ops.reference, built from the modules of /root/reference/part1/model.py).
+
+Inputs are rounded to bf16 first, so both sides see identical operands; the remaining
+difference is accumulation order and the bf16 rounding of outputs.
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from ddpb200.ops import kernels as K
+from ddpb200.ops import reference as R
+
+DEV = "cuda"
+
+# (N, H, W, C_in, C_out): every spatial size VGG-11 sees on CIFAR plus partial tiles
+CONV_SHAPES = [
+    (4, 32, 32, 64, 64),
+    (4, 16, 16, 64, 128),
+    (8, 8, 8, 128, 256),
+    (3, 8, 8, 128, 128),      # N not a multiple of the box's image count
+    (32, 4, 4, 256, 512),
+    (64, 2, 2, 512, 512),
+    (37, 2, 2, 512, 512),     # ragged last tile
+]
+
+
+def _rel_err(a, b):
+    return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-12)).item()
+
+
+@pytest.fixture(autouse=True)
+def _no_tf32():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(0)
+    yield
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES)
+def test_conv_fprop_bias_stats(shape):
+    N, H, W, Ci, Co = shape
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
+    b = torch.randn(Co, device=DEV)
+    stats = torch.zeros(2, Co, device=DEV)
+    y = K.conv_fprop(x, w, b, N, H, W, Ci, Co, stats=stats)
+    torch.cuda.synchronize()
+    ref = R.conv_fprop(x, w, b, N, H, W, Ci, Co)
+    assert _rel_err(y, ref) < 1e-2
+    ref_stats = R.channel_stats(y)   # statistics are of the stored (rounded) tensor
+    assert torch.allclose(stats, ref_stats, rtol=2e-3, atol=1e-2 * (N * H * W) ** 0.5)
+
+
+@pytest.mark.parametrize("block_n", [64, 128, 256])
+def test_conv_fprop_block_n(block_n):
+    N, H, W, Ci, Co = 8, 8, 8, 128, 256
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
+    y = K.conv_fprop(x, w, None, N, H, W, Ci, Co, block_n=block_n)
+    assert _rel_err(y, R.conv_fprop(x, w, None, N, H, W, Ci, Co)) < 1e-2
+
+
+def test_conv_fprop_single_tap_first_layer():
+    N, H, W = 8, 32, 32
+    img = torch.randn(N, 3, H, W, device=DEV)
+    op = K.first_layer_operand_f32(img)
+    ref_op = R.first_layer_operand(img).bfloat16()
+    assert torch.equal(op, ref_op)
+    w27 = torch.randn(64, 27, device=DEV) / 27 ** 0.5
+    w = torch.zeros(64, 64, device=DEV)
+    w[:, :27] = w27
+    w = w.bfloat16()
+    y = K.conv_fprop(op, w, None, N, H, W, 64, 64, taps=1)
+    # oracle: the actual 3-channel convolution
+    w_oihw = w[:, :27].float().reshape(64, 3, 3, 3).permute(0, 3, 1, 2)
+    ref = torch.nn.functional.conv2d(img.bfloat16().float(), w_oihw, padding=1)
+    assert _rel_err(y, R.nchw_to_nhwc2d(ref)) < 1e-2
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES[1:])
+def test_conv_dgrad_via_rotated_filters(shape):
+    N, H, W, Ci, Co = shape
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Co) ** 0.5).bfloat16()
+    wd = R.rotate_filters_for_dgrad(w, Co, Ci)
+    dx = K.conv_fprop(dy, wd, None, N, H, W, Co, Ci)
+    assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES + [(64, 32, 32, 64, 128)])
+def test_conv_wgrad(shape):
+    N, H, W, Ci, Co = shape
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    dw = K.conv_wgrad(dy, x, N, H, W, Ci, Co)
+    ref = R.conv_wgrad(dy, x, N, H, W, Ci, Co)
+    assert _rel_err(dw, ref) < 2e-3   # fp32 output: only the summation order differs
+
+
+def test_conv_wgrad_first_layer_compact():
+    N, H, W = 16, 32, 32
+    op = R.first_layer_operand(torch.randn(N, 3, H, W, device=DEV)).bfloat16()
+    dy = torch.randn(N * H * W, 64, device=DEV).bfloat16()
+    dw = K.conv_wgrad(dy, op, N, H, W, 64, 64, taps=1, cols_valid=27, out_ld=27)
+    ref = R.conv_wgrad(dy, op, N, H, W, 64, 64, taps=1)[:, :27]
+    assert dw.shape == (64, 27)
+    assert _rel_err(dw, ref) < 2e-3
+
+
+@pytest.mark.parametrize("pool", [False, True])
+@pytest.mark.parametrize("geom", [(8, 32, 32, 64), (8, 8, 8, 256), (16, 2, 2, 512)])
+def test_bn_relu_pool_fwd_bwd(geom, pool):
+    N, H, W, C = geom
+    x = (torch.randn(N * H * W, C, device=DEV) * 1.5 + 0.3).bfloat16()
+    gamma = torch.rand(C, device=DEV) + 0.5
+    beta = torch.randn(C, device=DEV) * 0.2
+    stats = K.channel_stats(x, C)
+    assert torch.allclose(stats, R.channel_stats(x), rtol=1e-4, atol=1e-2)
+    y, saved = K.bn_relu_pool_fwd(x, stats, gamma, beta, N, H, W, C, pool)
+    ref_y = R.bn_relu_pool_fwd(x, gamma, beta, N, H, W, pool)
+    assert _rel_err(y, ref_y) < 1e-2
+    Po = y.shape[0]
+    dy = torch.randn(Po, C, device=DEV).bfloat16()
+    dbias = torch.full((C,), 7.0, device=DEV)
+    dx, dgamma, dbeta = K.bn_relu_pool_bwd(x, dy, saved, gamma, beta, N, H, W, C, pool, dbias=dbias)
+    rdx, rdg, rdb = R.bn_relu_pool_bwd(x, dy, gamma, beta, N, H, W, pool)
+    assert _rel_err(dx, rdx) < 2e-2
+    assert _rel_err(dgamma, rdg) < 5e-3
+    assert _rel_err(dbeta, rdb) < 5e-3
+    # conv-bias gradient = column sums of dx: mathematically zero (SURVEY.md §2.5 numerics note)
+    assert dbias.abs().max().item() < 1e-2 * dy.float().abs().sum(0).max().item()
+
+
+@pytest.mark.parametrize("B", [32, 256, 85])
+def test_fc_cross_entropy_fwd_bwd(B):
+    F_, Kc = 512, 10
+    x = torch.randn(B, F_, device=DEV).bfloat16()
+    w = torch.randn(Kc, F_, device=DEV) / F_ ** 0.5
+    b = torch.randn(Kc, device=DEV) * 0.1
+    labels = torch.randint(0, Kc, (B,), device=DEV)
+    logits = torch.empty(B, Kc, device=DEV)
+    dlogits = torch.empty(B, Kc, device=DEV)
+    row_correct = torch.empty(B, dtype=torch.int32, device=DEV)
+    loss = torch.zeros((), device=DEV)
+    correct = torch.zeros((), dtype=torch.int32, device=DEV)
+    K.fc_ce_fwd(x, w, b, labels, logits=logits, dlogits=dlogits, row_correct=row_correct, loss=loss,
+                correct=correct)
+    rl, rloss, rdl, rc = R.fc_ce(x, w, b, labels)
+    assert torch.allclose(logits, rl, rtol=1e-4, atol=1e-4)
+    assert abs(loss.item() - rloss.item()) < 1e-4
+    assert torch.allclose(dlogits, rdl, rtol=1e-3, atol=1e-6)
+    assert correct.item() == rc.item()
+    dw, db, dx = K.fc_bwd(x, w, dlogits)
+    rdw, rdb, rdx = R.fc_bwd(x, w, rdl)
+    assert torch.allclose(dw, rdw, rtol=1e-3, atol=1e-5)
+    assert torch.allclose(db, rdb, rtol=1e-3, atol=1e-6)
+    assert _rel_err(dx, rdx) < 1e-2
+
+
+def test_sgd_matches_torch_optim():
+    n = 1_000_003
+    p = torch.randn(n + 1, device=DEV)[:n + 1 - (n + 1) % 4]
+    n = p.numel()
+    p0 = p.clone()
+    ref_p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.SGD([ref_p], lr=0.1, momentum=0.9, weight_decay=1e-4)
+    m = torch.zeros_like(p)
+    for _ in range(3):
+        g = torch.randn(n, device=DEV)
+        ref_p.grad = g.clone()
+        opt.step()
+        K.sgd_step(p, g, m, 0.1, 0.9, 1e-4)
+    assert torch.allclose(p, ref_p.data, rtol=1e-5, atol=1e-6)
+
+
+def test_pack_weights_layouts():
+    Kc, Cc = 128, 64
+    master = torch.randn(Kc, 9, Cc, device=DEV)
+    fprop = torch.empty(Kc, 9 * Cc, dtype=torch.bfloat16, device=DEV)
+    dgrad = torch.empty(Cc, 9 * Kc, dtype=torch.bfloat16, device=DEV)
+    m0 = torch.randn(64, 27, device=DEV)
+    f0 = torch.full((64, 64), 5.0, dtype=torch.bfloat16, device=DEV)
+    plan = K.PackPlan([
+        dict(master=m0, fprop=f0, dgrad=None, K=64, C=3, taps=9, fprop_ld=64, flat=1),
+        dict(master=master, fprop=fprop, dgrad=dgrad, K=Kc, C=Cc, taps=9, fprop_ld=9 * Cc, flat=0),
+    ])
+    plan.run()
+    assert torch.equal(fprop, master.reshape(Kc, -1).bfloat16())
+    assert torch.equal(dgrad, R.rotate_filters_for_dgrad(master.bfloat16(), Kc, Cc))
+    assert torch.equal(f0[:, :27], m0.bfloat16()) and f0[:, 27:].abs().max().item() == 0
+
+
+def test_first_layer_operand_u8_augmentation():
+    N = 16
+    raw = torch.randint(0, 256, (N, 32, 32, 3), dtype=torch.uint8, device=DEV)
+    aug = torch.stack([torch.randint(0, 9, (N,)), torch.randint(0, 9, (N,)), torch.randint(0, 2, (N,)),
+                       torch.zeros(N, dtype=torch.long)], 1).to(torch.int8).to(DEV)
+    for a in (None, aug):
+        op = K.first_layer_operand_u8(raw, a)
+        ref = R.first_layer_operand(R.augment_normalize_u8(raw, a)).bfloat16()
+        assert (op.float() - ref.float()).abs().max().item() < 2e-2
