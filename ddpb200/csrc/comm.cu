@@ -1,0 +1,365 @@
+// K10-K14: gradient synchronisation over NVLink peer memory, no NCCL.
+//
+// Every rank owns one "symmetric" buffer: [signal pad | gradient arena], allocated so
+// that all peers can map it (CUDA IPC or torch symmetric memory, see
+// ddpb200/parallel/comm.py) and optionally bound to an NVLS multicast address.
+// The kernels below replace the reference's collectives:
+//
+//   part2b  dist.all_reduce(grad, SUM); grad /= W  per parameter
+//           (/root/reference/part2/part2b/main.py:97-103)        -> allreduce_avg_kernel
+//   part3   DDP's bucketed all-reduce (/root/reference/part3/main.py:174)
+//                                                                  -> same kernel, per bucket,
+//                                                                     on a side stream
+//   part2a  gather -> mean on rank 0 -> scatter
+//           (/root/reference/part2/part2a/main.py:97-115)         -> reduce_root_bcast_kernel
+//   DDP constructor's parameter broadcast (C7)                    -> broadcast_kernel
+//
+// All of them are ONE launch that (1) waits for every peer, (2) moves/reduces data with
+// P2P loads/stores (or multimem.ld_reduce / multimem.st through the switch), scaling by
+// 1/W on the fly, (3) waits again and (4) optionally applies the SGD update to the whole
+// range, so "all-reduce + divide + optimizer step" is a single kernel.
+//
+// allreduce is a two-shot reduce-scatter + all-gather done IN PLACE: rank r reduces only
+// slice r (reading it from every peer) and writes the average back into slice r of every
+// peer.  Nobody else touches slice r in between, so no staging copy is needed, and all
+// ranks end up with bitwise identical gradients (they all receive rank r's result).
+#include "common.cuh"
+
+namespace ddpb {
+
+constexpr int kMaxRanks = 8;
+constexpr int kSignalPadBytes = 64 * 1024;          // 16384 flags: 2048 slots x 8 ranks
+constexpr int kCommThreads = 512;
+
+struct CommCtx {
+  float* buf[kMaxRanks];   // peer-mapped base of each rank's symmetric buffer (after the signal pad)
+  uint32_t* sig[kMaxRanks];
+  float* mc;               // multicast alias of buf (null: not available)
+  int rank, world;
+};
+
+struct SgdArgs {
+  float* p;   // parameter arena (local), null = no fused update
+  float* m;   // momentum arena (local)
+  float lr, mu, wd;
+};
+
+#ifndef DDPB_COMM_TIMEOUT_NS
+#define DDPB_COMM_TIMEOUT_NS 60000000000ull
+#endif
+
+__device__ __forceinline__ uint32_t cas_release_sys(uint32_t* addr, uint32_t cmp, uint32_t val) {
+  uint32_t old;
+  asm volatile("atom.cas.release.sys.global.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
+  return old;
+}
+__device__ __forceinline__ uint32_t cas_acquire_sys(uint32_t* addr, uint32_t cmp, uint32_t val) {
+  uint32_t old;
+  asm volatile("atom.cas.acquire.sys.global.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
+  return old;
+}
+
+// Cross-GPU barrier for one CTA: thread p signals peer p and waits for peer p's signal.
+// Flags toggle 0 -> 1 -> 0, so the pad needs no reset between launches or graph replays.
+__device__ __forceinline__ void peer_barrier(const CommCtx& c, int slot) {
+  __syncthreads();
+  if (threadIdx.x < c.world) {
+    const int peer = threadIdx.x;
+    __threadfence_system();
+    uint32_t* theirs = c.sig[peer] + slot * kMaxRanks + c.rank;
+    uint32_t* mine = c.sig[c.rank] + slot * kMaxRanks + peer;
+    const unsigned long long t0 = global_timer_ns();
+    uint32_t spins = 0;
+    while (cas_release_sys(theirs, 0u, 1u) != 0u) {
+      if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_COMM_TIMEOUT_NS) {
+        printf("ddpb200: rank %d timed out signalling rank %d (slot %d)\n", c.rank, peer, slot);
+        __trap();
+      }
+    }
+    while (cas_acquire_sys(mine, 1u, 0u) != 1u) {
+      if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_COMM_TIMEOUT_NS) {
+        printf("ddpb200: rank %d timed out waiting for rank %d (slot %d)\n", c.rank, peer, slot);
+        __trap();
+      }
+    }
+    __threadfence_system();
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 ld_sys(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_sys(float* p, const float4& v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ float4 mc_ld_reduce(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st(float* p, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ void sgd_range(const CommCtx& c, const SgdArgs& s, long long off, long long n4) {
+  const float* g = c.buf[c.rank] + off;
+  float* p = s.p + off;
+  float* m = s.m + off;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+    const float4 gv = ld_sys(g + 4 * i);   // peers wrote this: do not trust L1
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    float4 mv = reinterpret_cast<float4*>(m)[i];
+    float4 gg;
+    gg.x = fmaf(s.wd, pv.x, gv.x);
+    gg.y = fmaf(s.wd, pv.y, gv.y);
+    gg.z = fmaf(s.wd, pv.z, gv.z);
+    gg.w = fmaf(s.wd, pv.w, gv.w);
+    mv.x = fmaf(s.mu, mv.x, gg.x);
+    mv.y = fmaf(s.mu, mv.y, gg.y);
+    mv.z = fmaf(s.mu, mv.z, gg.z);
+    mv.w = fmaf(s.mu, mv.w, gg.w);
+    pv.x = fmaf(-s.lr, mv.x, pv.x);
+    pv.y = fmaf(-s.lr, mv.y, pv.y);
+    pv.z = fmaf(-s.lr, mv.z, pv.z);
+    pv.w = fmaf(-s.lr, mv.w, pv.w);
+    reinterpret_cast<float4*>(p)[i] = pv;
+    reinterpret_cast<float4*>(m)[i] = mv;
+  }
+}
+
+// kMc: use the NVLS multicast address (in-switch reduction and broadcast).
+template <bool kMc>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_avg_kernel(const CommCtx c, long long off, long long n4, int slot_base, SgdArgs sgd) {
+  const int slot = slot_base + blockIdx.x;
+  peer_barrier(c, slot);  // every rank's gradients for this range are complete
+  const float inv_w = 1.f / static_cast<float>(c.world);
+  const long long lo = n4 * c.rank / c.world, hi = n4 * (c.rank + 1) / c.world;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = lo + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
+    const long long e = off + 4 * i;
+    float4 acc;
+    if (kMc) {
+      acc = mc_ld_reduce(c.mc + e);
+    } else {
+      acc = ld_sys(c.buf[0] + e);
+      for (int r = 1; r < c.world; ++r) {   // fixed order: identical rounding on every rank
+        const float4 v = ld_sys(c.buf[r] + e);
+        acc.x += v.x;
+        acc.y += v.y;
+        acc.z += v.z;
+        acc.w += v.w;
+      }
+    }
+    acc.x *= inv_w;
+    acc.y *= inv_w;
+    acc.z *= inv_w;
+    acc.w *= inv_w;
+    if (kMc) {
+      mc_st(c.mc + e, acc);
+    } else {
+      for (int r = 0; r < c.world; ++r) st_sys(c.buf[r] + e, acc);
+    }
+  }
+  peer_barrier(c, slot);  // every slice has landed everywhere
+  if (sgd.p != nullptr) sgd_range(c, sgd, off, n4);
+}
+
+// part2a: the root pulls every rank's gradients, averages, pushes the mean to everyone.
+template <bool kMc>
+__global__ void __launch_bounds__(kCommThreads)
+reduce_root_bcast_kernel(const CommCtx c, long long off, long long n4, int slot_base, int root, SgdArgs sgd) {
+  const int slot = slot_base + blockIdx.x;
+  peer_barrier(c, slot);
+  if (c.rank == root) {
+    const float inv_w = 1.f / static_cast<float>(c.world);
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+      const long long e = off + 4 * i;
+      float4 acc = ld_sys(c.buf[0] + e);
+      for (int r = 1; r < c.world; ++r) {
+        const float4 v = ld_sys(c.buf[r] + e);
+        acc.x += v.x;
+        acc.y += v.y;
+        acc.z += v.z;
+        acc.w += v.w;
+      }
+      acc.x *= inv_w;
+      acc.y *= inv_w;
+      acc.z *= inv_w;
+      acc.w *= inv_w;
+      if (kMc) {
+        mc_st(c.mc + e, acc);
+      } else {
+        for (int r = 0; r < c.world; ++r) st_sys(c.buf[r] + e, acc);
+      }
+    }
+  }
+  peer_barrier(c, slot);
+  if (sgd.p != nullptr) sgd_range(c, sgd, off, n4);
+}
+
+// Root's range is copied into every peer's buffer.
+template <bool kMc>
+__global__ void __launch_bounds__(kCommThreads)
+broadcast_kernel(const CommCtx c, long long off, long long n4, int slot_base, int root) {
+  const int slot = slot_base + blockIdx.x;
+  peer_barrier(c, slot);
+  if (c.rank == root) {
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+      const long long e = off + 4 * i;
+      const float4 v = *reinterpret_cast<const float4*>(c.buf[root] + e);
+      if (kMc) {
+        mc_st(c.mc + e, v);
+      } else {
+        for (int r = 0; r < c.world; ++r)
+          if (r != root) st_sys(c.buf[r] + e, v);
+      }
+    }
+  }
+  peer_barrier(c, slot);
+}
+
+__global__ void __launch_bounds__(kCommThreads) barrier_kernel(const CommCtx c, int slot_base) {
+  peer_barrier(c, slot_base + blockIdx.x);
+}
+
+static int fill_ctx(CommCtx* c, const void* const* bufs, const void* mc, int rank, int world) {
+  DDPB_REQUIRE(world >= 1 && world <= kMaxRanks, "comm: world size must be 1..%d (got %d)", kMaxRanks, world);
+  DDPB_REQUIRE(rank >= 0 && rank < world, "comm: bad rank %d for world %d", rank, world);
+  for (int r = 0; r < kMaxRanks; ++r) {
+    c->buf[r] = nullptr;
+    c->sig[r] = nullptr;
+  }
+  for (int r = 0; r < world; ++r) {
+    DDPB_REQUIRE(bufs[r] != nullptr, "comm: peer %d buffer not mapped", r);
+    uint8_t* base = static_cast<uint8_t*>(const_cast<void*>(bufs[r]));
+    c->sig[r] = reinterpret_cast<uint32_t*>(base);
+    c->buf[r] = reinterpret_cast<float*>(base + kSignalPadBytes);
+  }
+  c->mc = (mc != nullptr)
+              ? reinterpret_cast<float*>(static_cast<uint8_t*>(const_cast<void*>(mc)) + kSignalPadBytes)
+              : nullptr;
+  c->rank = rank;
+  c->world = world;
+  return 0;
+}
+
+static int check_range(long long off, long long n, int blocks, int slot_base) {
+  DDPB_REQUIRE(off >= 0 && off % 4 == 0 && n >= 0 && n % 4 == 0,
+               "comm: offset/count must be multiples of 4 floats (got %lld/%lld)", off, n);
+  DDPB_REQUIRE(blocks >= 1 && slot_base >= 0 && (slot_base + blocks) * kMaxRanks * 4 <= kSignalPadBytes,
+               "comm: %d blocks from slot %d do not fit the signal pad", blocks, slot_base);
+  return 0;
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+extern "C" int ddpb_comm_signal_pad_bytes() { return kSignalPadBytes; }
+extern "C" int ddpb_comm_max_ranks() { return kMaxRanks; }
+
+// bufs: `world` base pointers of the symmetric buffers as mapped in THIS process
+// (bufs[rank] is the local one); mc: multicast mapping of the same buffer or null.
+// off/n: range inside the gradient arena in floats.  p/m: local parameter and momentum
+// arenas for the fused SGD step (null = only synchronise).  use_mc selects NVLS.
+extern "C" int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int rank, int world, long long off,
+                                  long long n, int blocks, int slot_base, int use_mc, float* p, float* m, float lr,
+                                  float momentum, float weight_decay, cudaStream_t stream) {
+  CommCtx c;
+  if (int rc = fill_ctx(&c, bufs, mc, rank, world)) return rc;
+  if (int rc = check_range(off, n, blocks, slot_base)) return rc;
+  DDPB_REQUIRE(!use_mc || c.mc != nullptr, "comm: multicast requested but no multicast mapping");
+  SgdArgs s{p, m, lr, momentum, weight_decay};
+  if (use_mc)
+    allreduce_avg_kernel<true><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, s);
+  else
+    allreduce_avg_kernel<false><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, s);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ddpb_reduce_root_bcast(const void* const* bufs, const void* mc, int rank, int world, int root,
+                                      long long off, long long n, int blocks, int slot_base, int use_mc, float* p,
+                                      float* m, float lr, float momentum, float weight_decay, cudaStream_t stream) {
+  CommCtx c;
+  if (int rc = fill_ctx(&c, bufs, mc, rank, world)) return rc;
+  if (int rc = check_range(off, n, blocks, slot_base)) return rc;
+  DDPB_REQUIRE(root >= 0 && root < world, "comm: bad root %d", root);
+  DDPB_REQUIRE(!use_mc || c.mc != nullptr, "comm: multicast requested but no multicast mapping");
+  SgdArgs s{p, m, lr, momentum, weight_decay};
+  if (use_mc)
+    reduce_root_bcast_kernel<true><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, root, s);
+  else
+    reduce_root_bcast_kernel<false><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, root, s);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ddpb_broadcast(const void* const* bufs, const void* mc, int rank, int world, int root, long long off,
+                              long long n, int blocks, int slot_base, int use_mc, cudaStream_t stream) {
+  CommCtx c;
+  if (int rc = fill_ctx(&c, bufs, mc, rank, world)) return rc;
+  if (int rc = check_range(off, n, blocks, slot_base)) return rc;
+  DDPB_REQUIRE(root >= 0 && root < world, "comm: bad root %d", root);
+  DDPB_REQUIRE(!use_mc || c.mc != nullptr, "comm: multicast requested but no multicast mapping");
+  if (use_mc)
+    broadcast_kernel<true><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, root);
+  else
+    broadcast_kernel<false><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, root);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ddpb_peer_barrier(const void* const* bufs, int rank, int world, int blocks, int slot_base,
+                                 cudaStream_t stream) {
+  CommCtx c;
+  if (int rc = fill_ctx(&c, bufs, nullptr, rank, world)) return rc;
+  if (int rc = check_range(0, 0, blocks, slot_base)) return rc;
+  barrier_kernel<<<blocks, kCommThreads, 0, stream>>>(c, slot_base);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---- CUDA IPC bootstrap (used when torch symmetric memory is unavailable) ----------------
+// Rank-local allocation whose handle is shipped to the peers through the rendezvous store
+// (the same TCPStore the reference uses for its process group, part2/part2b/main.py:56-58).
+extern "C" int ddpb_ipc_alloc(long long bytes, void** ptr, void* handle64) {
+  DDPB_CHECK_CUDA(cudaMalloc(ptr, static_cast<size_t>(bytes)));
+  DDPB_CHECK_CUDA(cudaMemset(*ptr, 0, static_cast<size_t>(bytes)));
+  cudaIpcMemHandle_t h;
+  DDPB_CHECK_CUDA(cudaIpcGetMemHandle(&h, *ptr));
+  static_assert(sizeof(h) == 64, "IPC handle size");
+  memcpy(handle64, &h, sizeof(h));
+  return 0;
+}
+extern "C" int ddpb_ipc_open(const void* handle64, void** ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  DDPB_CHECK_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+extern "C" int ddpb_ipc_close(void* ptr) {
+  DDPB_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+extern "C" int ddpb_ipc_free(void* ptr) {
+  DDPB_CHECK_CUDA(cudaFree(ptr));
+  return 0;
+}
