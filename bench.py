@@ -1,0 +1,343 @@
+"""Headline benchmark: VGG-11 on CIFAR-10-shaped data, images/s and ms/iteration (max over ranks).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--mode ddp|allreduce|gather_scatter|single] [--scaling weak|strong]
+
+Metric and configs are BASELINE.json's.  The default is the flagship config: part3-style
+(bucketed, overlapped) data parallel with per-GPU batch 256 -- weak scaling, i.e. at N=1
+this is the reference's part1 step (batch 256), at N=8 the global batch is 2048.
+``--scaling strong`` keeps the global batch at 256 (per-GPU 256/N), the setting of the
+reference's report.  For N>1 launch under torchrun (the driver does); a bare
+``python bench.py --gpus N`` re-executes itself under torchrun.
+
+Two numbers per run:
+  value  device time of K steps (CUDA events, barrier + synchronize on both sides, max over
+         ranks) with the batch already on the device;
+  e2e    the same K steps through the public API from pinned host memory: every step copies
+         its uint8 images + labels host->device and reads the loss back device->host.
+
+``--impl reference`` runs the UNMODIFIED reference scripts copied to baseline/_ref
+(baseline/install_reference.py) through their own ``train_model`` / ``DDP`` code path on
+cuda + NCCL, on synthetic data of the same shape, timed the same way.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib.util
+import json
+import os
+import subprocess
+import sys
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+PUBLISHED_IMAGES_PER_S = {1: 138.0, 2: 256 / 0.86, 3: 256 / 0.76, 4: 385.5}  # BASELINE.md §1 (part1 / DDP rows)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--mode", choices=["ddp", "allreduce", "gather_scatter", "single"], default="ddp")
+    ap.add_argument("--scaling", choices=["weak", "strong"], default="weak")
+    ap.add_argument("--per-gpu-batch", type=int, default=256)
+    ap.add_argument("--granularity", choices=["fused", "param"], default="fused")
+    ap.add_argument("--no-multicast", action="store_true")
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--comm-blocks", type=int, default=None)
+    ap.add_argument("--symm-backend", default=None)
+    return ap.parse_args()
+
+
+def env_rank():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+
+
+def maybe_reexec_under_torchrun(a):
+    if a.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        port = 29500 + (os.getpid() % 2000)
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={a.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(port), str(Path(__file__).resolve()), *sys.argv[1:]]
+        raise SystemExit(subprocess.call(cmd))
+
+
+def emit(obj):
+    print(json.dumps(obj), flush=True)
+
+
+def synthetic_host_batches(n_batches, batch, seed, pinned=True):
+    import torch
+
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for _ in range(n_batches):
+        img = torch.randint(0, 256, (batch, 32, 32, 3), dtype=torch.uint8, generator=g)
+        lab = torch.randint(0, 10, (batch,), dtype=torch.int64, generator=g)
+        aug = torch.stack([torch.randint(0, 9, (batch,), generator=g), torch.randint(0, 9, (batch,), generator=g),
+                           torch.randint(0, 2, (batch,), generator=g), torch.zeros(batch, dtype=torch.int64)],
+                          1).to(torch.int8)
+        if pinned:
+            img, lab, aug = img.pin_memory(), lab.pin_memory(), aug.pin_memory()
+        out.append((img, lab, aug))
+    return out
+
+
+# =========================================================================================
+# our arm
+# =========================================================================================
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+
+    import ddpb200
+    from ddpb200.utils.timing import ClockSampler, max_over_ranks
+
+    rank, local_rank, world = env_rank()
+    assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}"
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    per_gpu = a.per_gpu_batch if a.scaling == "weak" else max(1, 256 // world)
+    global_batch = per_gpu * world
+    mode = a.mode if world > 1 else "single"
+
+    torch.manual_seed(89395)
+    model = ddpb200.VGG11().to(device)
+    trainer = ddpb200.Trainer(model, mode=mode, batch_size=per_gpu, lr=0.1, momentum=0.9, weight_decay=1e-4,
+                              rank=rank, world_size=world, granularity=a.granularity,
+                              use_multicast=False if a.no_multicast else "auto", use_graph=not a.no_graph,
+                              comm_blocks=a.comm_blocks, symm_backend=a.symm_backend)
+    n_rot = 8
+    host = synthetic_host_batches(n_rot, per_gpu, seed=1234 + rank)
+    dev_batches = [(i.to(device), l.to(device), g.to(device)) for i, l, g in host]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    def timed(batches, k, readback):
+        barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        s.record()
+        last = None
+        for it in range(k):
+            img, lab, aug = batches[it % n_rot]
+            loss = trainer.step(img, lab, aug)
+            if readback:
+                last = loss.item()      # device -> host read of the step's result, every step
+        e.record()
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        return s.elapsed_time(e), wall, last
+
+    for it in range(max(a.warmup, 3)):
+        img, lab, aug = dev_batches[it % n_rot]
+        trainer.step(img, lab, aug)
+    first_loss = float(trainer.engine.loss.item())
+    with ClockSampler(local_rank) as clocks:
+        dev_ms, _, _ = timed(dev_batches, a.steps, readback=False)
+    # end to end from pinned host memory (a few extra warm-up steps for the copy path)
+    for it in range(3):
+        img, lab, aug = host[it % n_rot]
+        trainer.step(img, lab, aug).item()
+    e2e_dev_ms, e2e_wall_ms, last_loss = timed(host, a.steps, readback=True)
+
+    dev_ms = max_over_ranks(dev_ms, device)
+    e2e_ms = max_over_ranks(max(e2e_dev_ms, e2e_wall_ms), device)
+    if rank == 0:
+        ms_step = dev_ms / a.steps
+        value = global_batch / (ms_step * 1e-3)
+        e2e_value = global_batch / (e2e_ms / a.steps * 1e-3)
+        eng = trainer.engine
+        act_mb = sum(t.numel() * 2 for ts in (eng.conv_out, eng.act, eng.dconv, eng.dact) for t in ts) / 1e6
+        ws_mb = act_mb + eng.operand0.numel() * 2 / 1e6 + 3 * eng.arena.numel * 4 / 1e6
+        pub = PUBLISHED_IMAGES_PER_S.get(world)
+        par = "single" if world == 1 else {"ddp": "dp", "allreduce": "dp-allreduce", "gather_scatter": "dp-gather-scatter"}[mode]
+        emit({
+            "metric": "VGG-11 CIFAR-10 images/sec (ms/iter max over ranks)", "value": round(value, 1),
+            "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": a.scaling,
+            "vs_baseline": round(value / pub, 2) if pub else None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
+            "config": {"model": "VGG-11 (3x32x32, 10 classes, BatchNorm batch stats)", "global_batch": global_batch,
+                       "per_gpu_batch": per_gpu, "seq_len": None, "parallelism": f"{par}{world}", "mode": mode,
+                       "optimizer": "SGD lr=0.1 momentum=0.9 wd=1e-4 (inside the timed step)",
+                       "sync": None if world == 1 else {"backend": trainer.symm.backend, "multicast": trainer.use_mc,
+                                                       "granularity": a.granularity, "buckets_floats": [b.numel for b in trainer.buckets] if mode == "ddp" else None},
+                       "cuda_graph": not a.no_graph,
+                       "l2": f"no explicit flush: working set {ws_mb:.0f} MB/step > 126 MB L2; inputs rotate over {n_rot} device batches",
+                       "baseline_ref": "BASELINE.md §1: published CPU/Gloo images/s for this worker count"},
+            "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "ms_per_step": round(e2e_ms / a.steps, 4),
+                    "h2d_bytes_per_step": world * sum(t.numel() * t.element_size() for t in host[0]),
+                    "d2h_bytes_per_step": world * 4, "api": "ddpb200.Trainer.step(pinned uint8 NHWC, labels, aug) + loss.item()"},
+            "gpu_launches": trainer.kernel_launches_per_step() * a.steps,
+            "gpu_launches_per_step": trainer.kernel_launches_per_step(),
+            "clocks": clocks.summary(),
+            "loss_first": first_loss, "loss_last": last_loss,
+        })
+    trainer.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# =========================================================================================
+# reference arm: the unmodified scripts from baseline/_ref, their own train_model
+# =========================================================================================
+def find_reference():
+    for cand in (ROOT / "baseline" / "_ref", Path("/root/reference")):
+        if (cand / "part1" / "main.py").exists() and (cand / "part3" / "main.py").exists():
+            return cand
+    return None
+
+
+def import_reference_main(ref_root: Path, part: str):
+    d = ref_root / part
+    sys.path.insert(0, str(d))          # the script does `import model as mdl`
+    sys.modules.pop("model", None)
+    spec = importlib.util.spec_from_file_location(f"ref_{part.replace('/', '_')}_main", d / "main.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+class TimedLoader:
+    """Feeds the reference's train_model (which iterates ``enumerate(train_loader)``) W+K
+    normalised fp32 CPU batches from pinned memory -- what its DataLoader(pin_memory=True)
+    yields -- and brackets batches W..W+K-1 with barrier + synchronize + CUDA events."""
+
+    def __init__(self, batches, warmup, steps, barrier):
+        self.batches, self.warmup, self.steps, self.barrier = batches, warmup, steps, barrier
+        self.start = self.end = None
+        self.wall0 = self.wall_ms = None
+
+    def __len__(self):
+        return self.warmup + self.steps
+
+    def __iter__(self):
+        import torch
+
+        for i in range(self.warmup + self.steps):
+            if i == self.warmup:
+                self.barrier()
+                self.start = torch.cuda.Event(enable_timing=True)
+                self.wall0 = time.perf_counter()
+                self.start.record()
+            yield self.batches[i % len(self.batches)]
+        self.end = torch.cuda.Event(enable_timing=True)
+        self.end.record()
+        self.barrier()
+        self.wall_ms = (time.perf_counter() - self.wall0) * 1e3
+
+
+def run_reference(a):
+    ref_root = find_reference()
+    if ref_root is None:
+        emit({"impl": "reference", "unavailable": "reference scripts not found under baseline/_ref or /root/reference "
+                                                  "(pip cannot install them: no setup.py/pyproject.toml)"})
+        return
+    try:
+        import torch
+        import torch.distributed as dist
+        import torchvision  # noqa: F401  (the reference imports it at module level)
+    except Exception as e:  # noqa: BLE001
+        emit({"impl": "reference", "unavailable": f"import failed: {e}"})
+        return
+    from ddpb200.ops.reference import CIFAR_MEAN, CIFAR_STD
+    from ddpb200.utils.timing import ClockSampler, max_over_ranks
+
+    rank, local_rank, world = env_rank()
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    per_gpu = a.per_gpu_batch if a.scaling == "weak" else max(1, 256 // world)
+    global_batch = per_gpu * world
+    part = "part1" if world == 1 else {"ddp": "part3", "allreduce": "part2/part2b", "single": "part3",
+                                       "gather_scatter": "part2/part2a"}[a.mode]
+    if part == "part2/part2a":
+        emit({"impl": "reference", "unavailable": "part2/part2a/main.py has a syntax error at line 70 as committed"})
+        return
+    # get_rank() is evaluated when the module's parse_arguments runs, not at import: importing is safe
+    ref = import_reference_main(ref_root, part)
+    ref.device = str(device)                      # the scripts read this module global (main.py:15)
+    if world > 1:
+        ref.init_distributed_setup(os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"], rank, world, "nccl")
+    import random
+
+    import numpy as np
+
+    random.seed(ref.seed)
+    torch.manual_seed(ref.seed)
+    np.random.seed(ref.seed)
+    criterion = torch.nn.CrossEntropyLoss().to(device)
+    model = ref.mdl.VGG11()
+    model.to(device)
+    net = model
+    if part == "part3":
+        net = ref.DDP(model)
+    optimizer = ref.optim.SGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0001)
+
+    mean, std = CIFAR_MEAN.view(1, 3, 1, 1), CIFAR_STD.view(1, 3, 1, 1)
+    host = []
+    for img, lab, _ in synthetic_host_batches(8, per_gpu, seed=1234 + rank, pinned=False):
+        x = ((img.permute(0, 3, 1, 2).float() / 255.0 - mean) / std).contiguous().pin_memory()
+        host.append((x, lab.pin_memory()))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    warm = max(a.warmup, 3)
+    loader = TimedLoader(host, warm, a.steps, barrier)
+    import contextlib
+    import io
+
+    sink = io.StringIO()
+    with ClockSampler(local_rank) as clocks, contextlib.redirect_stdout(sink):
+        if part == "part1" or part == "part3":
+            ref.train_model(net, loader, optimizer, criterion, 0)
+        else:
+            ref.train_model(net, rank, world, loader, optimizer, criterion, 0)
+    dev_ms = loader.start.elapsed_time(loader.end)
+    ms = max_over_ranks(max(dev_ms, loader.wall_ms), device)
+    if rank == 0:
+        ms_step = ms / a.steps
+        value = global_batch / (ms_step * 1e-3)
+        pub = PUBLISHED_IMAGES_PER_S.get(world)
+        emit({
+            "metric": "VGG-11 CIFAR-10 images/sec (ms/iter max over ranks)", "value": round(value, 1),
+            "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": warm, "ms_per_step": round(ms_step, 4),
+            "higher_is_better": True, "scaling": a.scaling, "vs_baseline": round(value / pub, 2) if pub else None,
+            "dtype": "fp32 (cuDNN TF32 convolutions, torch defaults)", "data": "synthetic", "impl": "reference",
+            "config": {"model": "VGG-11 (reference model.py, unmodified)", "global_batch": global_batch,
+                       "per_gpu_batch": per_gpu, "seq_len": None, "parallelism": f"{'single' if world == 1 else 'dp'}{world}",
+                       "script": f"baseline/_ref/{part}/main.py train_model()", "backend": None if world == 1 else "nccl",
+                       "l2": "no explicit flush; inputs rotate over 8 pinned host batches"},
+            "e2e": {"value": round(value, 1), "unit": "images/s", "ms_per_step": round(ms_step, 4),
+                    "h2d_bytes_per_step": world * sum(t.numel() * t.element_size() for t in host[0]),
+                    "d2h_bytes_per_step": world * 4,
+                    "note": "the reference's loop copies each batch host->device and calls loss.item() itself, "
+                            "so its only number is end to end"},
+            "gpu_launches": 0, "clocks": clocks.summary(),
+        })
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    maybe_reexec_under_torchrun(a)
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

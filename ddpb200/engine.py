@@ -1,0 +1,324 @@
+"""Execution engine: runs a ddpb200 VGG on one B200 with the hand-written kernels.
+
+The reference executes ``model(data)``, ``criterion``, ``loss.backward()`` and
+``optimizer.step()`` as ~100 separate ATen calls per iteration
+(/root/reference/part1/main.py:71-77).  Here the whole iteration is a fixed launch
+sequence over preallocated NHWC bf16 buffers:
+
+    input prep -> [conv fprop(+stats) -> BN/ReLU/pool] x L -> FC+CE
+               -> FC bwd -> [BN bwd -> wgrad -> dgrad] x L -> gradient sync + SGD -> repack
+
+Design points:
+  * parameters, gradients and momentum each live in ONE flat fp32 arena; ``param.data`` and
+    ``param.grad`` are views into them, so the torch-facing API and the 34-key state_dict
+    are unchanged while sync/SGD kernels see contiguous ranges ("bucket" = arena slice);
+  * conv filters are stored channels_last, i.e. physically [C_out][3][3][C_in], which is
+    the GEMM operand order -- the repack to bf16 is an elementwise cast;
+  * gradients are written by the kernels (no zero_grad pass needed);
+  * the sequence is captured once into a CUDA graph and replayed.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.nn as nn
+
+from .ops import kernels as K
+
+ALIGN = 32  # arena alignment of every parameter, in floats (128 bytes)
+
+
+# ---------------------------------------------------------------------------------------
+# flat arenas
+# ---------------------------------------------------------------------------------------
+class ParamArena:
+    """Re-homes a module's parameters (and their grads) into flat fp32 arenas."""
+
+    def __init__(self, params: list[nn.Parameter], device: torch.device, grad_storage: torch.Tensor | None = None):
+        self.params = params
+        self.offsets: list[int] = []
+        off = 0
+        for p in params:
+            self.offsets.append(off)
+            off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
+        self.numel = off
+        self.master = torch.zeros(off, dtype=torch.float32, device=device)
+        self.momentum = torch.zeros(off, dtype=torch.float32, device=device)
+        if grad_storage is None:
+            grad_storage = torch.zeros(off, dtype=torch.float32, device=device)
+        assert grad_storage.numel() >= off and grad_storage.dtype == torch.float32
+        self.grad = grad_storage[:off]
+        for p, o in zip(params, self.offsets):
+            view = self._view(self.master, p, o)
+            view.copy_(p.data)
+            p.data = view
+            p.grad = self._view(self.grad, p, o)
+
+    @staticmethod
+    def _view(flat: torch.Tensor, p: torch.Tensor, off: int) -> torch.Tensor:
+        n = p.numel()
+        if p.dim() == 4:  # conv filter (K,C,R,S): keep it physically [K][R][S][C]
+            k, c, r, s = p.shape
+            return flat[off:off + n].view(k, r, s, c).permute(0, 3, 1, 2)
+        return flat[off:off + n].view(p.shape)
+
+    def flat_master(self, idx: int) -> torch.Tensor:
+        o = self.offsets[idx]
+        return self.master[o:o + self.params[idx].numel()]
+
+    def flat_grad(self, idx: int) -> torch.Tensor:
+        o = self.offsets[idx]
+        return self.grad[o:o + self.params[idx].numel()]
+
+    def range_of(self, first_idx: int, last_idx: int) -> tuple[int, int]:
+        """(offset, count) in floats covering parameters first_idx..last_idx inclusive, padding included."""
+        lo = self.offsets[first_idx]
+        hi = self.offsets[last_idx + 1] if last_idx + 1 < len(self.offsets) else self.numel
+        return lo, hi - lo
+
+
+@dataclass
+class _Layer:
+    H: int
+    W: int
+    c_in: int       # real input channels
+    c_in_eff: int   # GEMM K per tap (64 for the first layer's gathered operand)
+    c_out: int
+    taps: int
+    pool: bool
+    p_w: int        # indices into the parameter list
+    p_b: int
+    p_g: int
+    p_beta: int
+
+
+class VGGEngine:
+    """Owns buffers + launch sequences for one model instance on one device."""
+
+    def __init__(self, model, max_batch: int, grad_storage: torch.Tensor | None = None, image_hw: int = 32):
+        self.model = model
+        params = list(model.parameters())
+        self.device = params[0].device
+        assert self.device.type == "cuda", "VGGEngine needs the model on a CUDA device"
+        self.max_batch = max_batch
+        self.arena = ParamArena(params, self.device, grad_storage)
+        index = {id(p): i for i, p in enumerate(params)}
+        dev = self.device
+
+        self.layers: list[_Layer] = []
+        hw = image_hw
+        for bi, blk in enumerate(model.conv_blocks()):
+            first = bi == 0
+            self.layers.append(_Layer(hw, hw, blk.c_in, 64 if first else blk.c_in, blk.c_out, 1 if first else 9,
+                                      blk.pool, index[id(blk.conv.weight)], index[id(blk.conv.bias)],
+                                      index[id(blk.bn.weight)], index[id(blk.bn.bias)]))
+            if first:
+                assert blk.c_in == 3 and blk.c_out % 64 == 0
+            if blk.pool:
+                hw //= 2
+        assert hw == 1, "feature map must be 1x1 before the classifier"
+        self.p_fcw, self.p_fcb = index[id(model.fc1.weight)], index[id(model.fc1.bias)]
+        self.feat = model.fc1.in_features
+        self.classes = model.fc1.out_features
+
+        B = max_batch
+        bf = dict(dtype=torch.bfloat16, device=dev)
+        f32 = dict(dtype=torch.float32, device=dev)
+        # --- activations and their gradients
+        self.operand0 = torch.empty(B * image_hw * image_hw, 64, **bf)
+        self.conv_out, self.act, self.dconv, self.dact = [], [], [], []
+        for L in self.layers:
+            P = B * L.H * L.W
+            Po = P // 4 if L.pool else P
+            self.conv_out.append(torch.empty(P, L.c_out, **bf))
+            self.act.append(torch.empty(Po, L.c_out, **bf))
+            self.dconv.append(torch.empty(P, L.c_out, **bf))
+            self.dact.append(torch.empty(Po, L.c_out, **bf))
+        # --- per-channel statistics: one arena so a single memset clears all of it
+        csum = sum(2 * L.c_out for L in self.layers)
+        self.stat_arena = torch.zeros(2 * csum, **f32)
+        self.stats, self.bsums, self.saved = [], [], []
+        o = 0
+        for L in self.layers:
+            self.stats.append(self.stat_arena[o:o + 2 * L.c_out])
+            o += 2 * L.c_out
+        for L in self.layers:
+            self.bsums.append(self.stat_arena[o:o + 2 * L.c_out])
+            o += 2 * L.c_out
+            self.saved.append(torch.empty(2 * L.c_out, **f32))
+        # --- packed bf16 filters
+        self.w_f, self.w_d = [], []
+        pack = []
+        for li, L in enumerate(self.layers):
+            ld = 64 if li == 0 else 9 * L.c_in
+            wf = torch.zeros(L.c_out, ld, **bf)
+            wd = None if li == 0 else torch.empty(L.c_in, 9 * L.c_out, **bf)
+            self.w_f.append(wf)
+            self.w_d.append(wd)
+            pack.append(dict(master=self.arena.flat_master(L.p_w), fprop=wf, dgrad=wd, K=L.c_out, C=L.c_in, taps=9,
+                             fprop_ld=ld, flat=li == 0))
+        self.pack_plan = K.PackPlan(pack)
+        # --- classifier / loss
+        self.labels = torch.zeros(B, dtype=torch.int64, device=dev)
+        self.logits = torch.empty(B, self.classes, **f32)
+        self.dlogits = torch.empty(B, self.classes, **f32)
+        self.row_loss = torch.empty(B, **f32)
+        self.row_correct = torch.empty(B, dtype=torch.int32, device=dev)
+        self.loss = torch.zeros((), **f32)
+        self.correct = torch.zeros((), dtype=torch.int32, device=dev)
+        # --- wgrad split-K scratch, shared by all layers (launches are stream ordered)
+        need = 1
+        for li, L in enumerate(self.layers):
+            need = max(need, K.conv_wgrad_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps))
+        self.wgrad_scratch = torch.empty(need, **f32)
+        self.image_hw = image_hw
+        self.repack()
+        _register_engine(self)
+
+    # -- pieces ---------------------------------------------------------------------------------
+    def repack(self, stream=None):
+        """fp32 master filters -> bf16 fprop / dgrad operand layouts (after every update)."""
+        self.pack_plan.run(stream)
+
+    def load_input_f32(self, x_nchw: torch.Tensor):
+        K.first_layer_operand_f32(x_nchw.contiguous(), out=self.operand0)
+
+    def load_input_u8(self, x_nhwc: torch.Tensor, aug: torch.Tensor | None):
+        K.first_layer_operand_u8(x_nhwc, aug, out=self.operand0)
+
+    def forward(self, N: int, with_loss: bool, want_dlogits: bool = True):
+        """operand0[:N*H*W] -> logits[:N] (and loss / dlogits / correct when with_loss)."""
+        a = self.arena
+        self.stat_arena.zero_()
+        x = self.operand0
+        for li, L in enumerate(self.layers):
+            K.conv_fprop(x, self.w_f[li], a.flat_master(L.p_b), N, L.H, L.W, L.c_in_eff, L.c_out, L.taps,
+                         out=self.conv_out[li], stats=self.stats[li])
+            K.bn_relu_pool_fwd(self.conv_out[li], self.stats[li], a.flat_master(L.p_g), a.flat_master(L.p_beta), N,
+                               L.H, L.W, L.c_out, L.pool, out=self.act[li], saved=self.saved[li])
+            x = self.act[li]
+        feat = x[:N]
+        if with_loss:
+            K.fc_ce_fwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), a.flat_master(self.p_fcb),
+                        self.labels[:N], logits=self.logits, row_loss=self.row_loss,
+                        dlogits=self.dlogits if want_dlogits else None, row_correct=self.row_correct, loss=self.loss,
+                        correct=self.correct)
+        else:
+            # logits only: labels are not read meaningfully, loss outputs are discarded
+            K.fc_ce_fwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), a.flat_master(self.p_fcb),
+                        self.labels[:N], logits=self.logits, row_loss=self.row_loss)
+
+    def backward(self, N: int, after_layer=None):
+        """dlogits[:N] -> every gradient in the arena.  ``after_layer(li)`` is called once layer
+        li's gradients (and everything after it, classifier included) are enqueued -- the hook the
+        bucketed reducer uses to start a bucket while the rest of backward still runs."""
+        a = self.arena
+        last = len(self.layers) - 1
+        feat = self.act[last][:N]
+        K.fc_bwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), self.dlogits[:N],
+                 dw=a.flat_grad(self.p_fcw), db=a.flat_grad(self.p_fcb), dx=self.dact[last])
+        for li in range(last, -1, -1):
+            L = self.layers[li]
+            x_in = self.operand0 if li == 0 else self.act[li - 1]
+            K.bn_relu_pool_bwd(self.conv_out[li], self.dact[li], self.saved[li], a.flat_master(L.p_g),
+                               a.flat_master(L.p_beta), N, L.H, L.W, L.c_out, L.pool, sums=self.bsums[li],
+                               dx=self.dconv[li], dgamma=a.flat_grad(L.p_g), dbeta=a.flat_grad(L.p_beta),
+                               dbias=a.flat_grad(L.p_b))
+            cols = 9 * L.c_in
+            K.conv_wgrad(self.dconv[li], x_in, N, L.H, L.W, L.c_in_eff, L.c_out, L.taps, out=a.flat_grad(L.p_w),
+                         cols_valid=cols, out_ld=cols, scratch=self.wgrad_scratch)
+            if li > 0:
+                K.conv_fprop(self.dconv[li], self.w_d[li], None, N, L.H, L.W, L.c_out, L.c_in, 9,
+                             out=self.dact[li - 1])
+            if after_layer is not None:
+                after_layer(li)
+
+    def sgd(self, lr: float, momentum: float, weight_decay: float, grad_scale: float = 1.0):
+        a = self.arena
+        K.sgd_step(a.master, a.grad, a.momentum, lr, momentum, weight_decay, grad_scale)
+
+    def launches_per_train_step(self, splits_reduce: bool = True) -> int:
+        """How many of OUR kernels one fwd+bwd enqueues (excluding sync/SGD/repack/input prep)."""
+        n = 0
+        B = self.max_batch
+        for li, L in enumerate(self.layers):
+            n += 2                  # fprop, bn fwd
+            n += 2                  # bn bwd (two passes)
+            n += 1                  # wgrad
+            if K.conv_wgrad_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps):
+                n += 1              # split-K reduce
+            if li > 0:
+                n += 1              # dgrad
+        return n + 2 + 1            # fc fwd + loss reduce, fc bwd
+
+
+# ---------------------------------------------------------------------------------------
+# nn.Module integration: model(x) on CUDA, differentiable through one autograd node
+# ---------------------------------------------------------------------------------------
+class _EngineFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, model, *params):
+        eng: VGGEngine = model._engine
+        N = x.shape[0]
+        eng.load_input_f32(x.float())
+        eng.forward(N, with_loss=False)
+        ctx.eng, ctx.N = eng, N
+        return eng.logits[:N].clone()
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        eng, N = ctx.eng, ctx.N
+        eng.dlogits[:N].copy_(dlogits)
+        eng.backward(N)
+        # gradients were written straight into param.grad (arena views); nothing to hand to autograd
+        return (None, None) + (None,) * len(eng.arena.params)
+
+
+_ENGINES: "weakref.WeakValueDictionary[int, VGGEngine]" = None  # storage data_ptr -> engine
+
+
+def _register_engine(eng: "VGGEngine") -> None:
+    global _ENGINES
+    import weakref
+
+    if _ENGINES is None:
+        _ENGINES = weakref.WeakValueDictionary()
+    _ENGINES[eng.arena.master.data_ptr()] = eng
+
+
+def engine_of_parameter(p: torch.Tensor):
+    """The engine whose master arena holds ``p`` (None if p is an ordinary tensor)."""
+    if _ENGINES is None:
+        return None
+    for base, eng in list(_ENGINES.items()):
+        n = eng.arena.master.numel() * 4
+        if base <= p.data_ptr() < base + n:
+            return eng
+    return None
+
+
+def get_engine(model, batch: int, grad_storage: torch.Tensor | None = None) -> VGGEngine:
+    eng = model._engine
+    if eng is None or eng.max_batch < batch:
+        if eng is not None and grad_storage is None:
+            grad_storage = None
+        eng = VGGEngine(model, batch, grad_storage)
+        model._engine = eng
+    return eng
+
+
+def engine_forward(model, x: torch.Tensor) -> torch.Tensor:
+    if x.dim() != 4 or x.shape[1] != 3:
+        raise ValueError(f"expected a [N,3,H,W] batch, got {tuple(x.shape)}")
+    eng = get_engine(model, x.shape[0])
+    for p, o in zip(eng.arena.params, eng.arena.offsets):
+        if p.grad is None:  # a stock optimizer's zero_grad(set_to_none=True) detached it
+            p.grad = ParamArena._view(eng.arena.grad, p, o)
+    if torch.is_grad_enabled() and any(p.requires_grad for p in eng.arena.params):
+        eng.repack()  # parameters may have been updated by any optimizer since the last call
+        return _EngineFn.apply(x, model, *eng.arena.params)
+    eng.repack()
+    eng.load_input_f32(x.float())
+    eng.forward(x.shape[0], with_loss=False)
+    return eng.logits[:x.shape[0]].clone()

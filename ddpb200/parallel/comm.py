@@ -1,0 +1,226 @@
+"""Process-group bootstrap and the symmetric (peer-mapped) gradient buffer.
+
+Reference: ``init_distributed_setup`` sets MASTER_ADDR/MASTER_PORT and calls
+``dist.init_process_group('gloo', rank, world_size)``
+(/root/reference/part2/part2b/main.py:52-58); every collective then goes through Gloo/TCP.
+Here the process group (NCCL on GPUs, Gloo on CPU) is used for bootstrap only: ranks
+exchange memory handles through it once, map each other's gradient arenas over
+NVLink, and from then on the sync kernels in csrc/comm.cu read and write peer memory
+directly -- no NCCL call on the hot path.
+
+Two ways to obtain a peer-mapped buffer, tried in this order:
+  1. torch symmetric memory (CUDA VMM allocation; also yields an NVLS multicast address
+     when the fabric supports it, which enables the multimem.* kernel variants);
+  2. plain CUDA IPC handles (cudaMalloc + cudaIpcGetMemHandle) shipped through the store.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import datetime
+import os
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _native as nat
+
+c_void, c_int, c_ll, c_float = C.c_void_p, C.c_int, C.c_longlong, C.c_float
+
+nat.register_optional("ddpb_comm_signal_pad_bytes", [])
+nat.register_optional("ddpb_comm_max_ranks", [])
+nat.register_optional("ddpb_allreduce_avg", [c_void, c_void, c_int, c_int, c_ll, c_ll, c_int, c_int, c_int, c_void,
+                                             c_void, c_float, c_float, c_float, c_void])
+nat.register_optional("ddpb_reduce_root_bcast", [c_void, c_void, c_int, c_int, c_int, c_ll, c_ll, c_int, c_int, c_int,
+                                                 c_void, c_void, c_float, c_float, c_float, c_void])
+nat.register_optional("ddpb_broadcast", [c_void, c_void, c_int, c_int, c_int, c_ll, c_ll, c_int, c_int, c_int,
+                                         c_void])
+nat.register_optional("ddpb_peer_barrier", [c_void, c_int, c_int, c_int, c_int, c_void])
+nat.register_optional("ddpb_ipc_alloc", [c_ll, C.POINTER(c_void), c_void])
+nat.register_optional("ddpb_ipc_open", [c_void, C.POINTER(c_void)])
+nat.register_optional("ddpb_ipc_close", [c_void])
+nat.register_optional("ddpb_ipc_free", [c_void])
+
+SIGNAL_PAD_BYTES = 64 * 1024
+MAX_RANKS = 8
+
+
+def init_distributed_setup(master_ip: str, master_port: str, rank: int, world_size: int,
+                           backend: str | None = None, device: torch.device | None = None) -> None:
+    """Same contract as the reference (part2b/main.py:52-58); backend defaults to NCCL when the
+    rank has a GPU and to Gloo otherwise."""
+    os.environ["MASTER_ADDR"] = str(master_ip)
+    os.environ["MASTER_PORT"] = str(master_port)
+    if backend is None:
+        backend = "nccl" if torch.cuda.is_available() else "gloo"
+    kwargs = {}
+    if backend == "nccl" and device is not None:
+        kwargs["device_id"] = device
+    dist.init_process_group(backend, rank=rank, world_size=world_size,
+                            timeout=datetime.timedelta(seconds=600), **kwargs)
+
+
+def test_distributed_setup() -> None:
+    """The reference's start-up banner (part2b/main.py:42-49), same four lines."""
+    print(f"Is initialized: {dist.is_initialized()}")
+    print(f"Backend: {dist.get_backend()}")
+    print(f"World size: {dist.get_world_size()}")
+    print(f"Rank: {dist.get_rank()}\n")
+
+
+class SymmetricBuffer:
+    """[signal pad | payload floats] on every rank, mapped into every peer.
+
+    ``payload`` is this rank's fp32 tensor (used as the gradient arena); ``ptrs`` holds the
+    base address of every rank's buffer in this process' address space.
+    """
+
+    def __init__(self, payload_floats: int, device: torch.device, group=None, prefer: str | None = None):
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(self.group)
+        self.world = dist.get_world_size(self.group)
+        if self.world > MAX_RANKS:
+            raise RuntimeError(f"peer-memory sync supports up to {MAX_RANKS} ranks on one NVSwitch domain")
+        self.device = device
+        self.payload_floats = payload_floats
+        self.bytes = SIGNAL_PAD_BYTES + payload_floats * 4
+        self.multicast_ptr = 0
+        self.backend = None
+        self._hdl = None
+        self._ipc_opened: list[int] = []
+        self._ipc_local = 0
+        prefer = prefer or os.environ.get("DDPB_SYMM_BACKEND", "auto")
+        errors = []
+        for name in (["symm_mem", "ipc"] if prefer == "auto" else [prefer]):
+            try:
+                getattr(self, "_init_" + name)()
+                self.backend = name
+                break
+            except Exception as e:  # noqa: BLE001 - report every backend's failure below
+                errors.append(f"{name}: {type(e).__name__}: {e}")
+            # all ranks must agree on the backend: a failure anywhere means everybody moves on
+        if self.backend is None:
+            raise RuntimeError("no peer-memory backend available: " + " | ".join(errors))
+        self._ptr_array = (C.c_void_p * MAX_RANKS)(*(self.ptrs + [None] * (MAX_RANKS - self.world)))
+        self.payload.zero_()
+        torch.cuda.synchronize(device)
+        dist.barrier(self.group)
+
+    # -- backends ---------------------------------------------------------------------------------
+    def _agree(self, ok: bool, what: str) -> None:
+        flag = torch.tensor([1 if ok else 0], device=self.device if dist.get_backend(self.group) == "nccl" else "cpu")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 0:
+            raise RuntimeError(f"{what} failed on at least one rank")
+
+    def _init_symm_mem(self) -> None:
+        ok, err = True, None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            raw = symm_mem.empty(self.bytes // 4, dtype=torch.float32, device=self.device)
+        except Exception as e:  # noqa: BLE001
+            ok, err = False, e
+        self._agree(ok, "symmetric allocation")
+        if err is not None:
+            raise err
+        try:
+            hdl = symm_mem.rendezvous(raw, self.group)
+        except Exception as e:  # noqa: BLE001
+            ok, err = False, e
+        self._agree(ok, "symmetric rendezvous")
+        if err is not None:
+            raise err
+        self._hdl = hdl
+        self._raw = raw
+        raw.zero_()
+        self.ptrs = [int(p) for p in hdl.buffer_ptrs]
+        try:
+            self.multicast_ptr = int(hdl.multicast_ptr or 0)
+        except Exception:  # noqa: BLE001
+            self.multicast_ptr = 0
+        self.payload = raw[SIGNAL_PAD_BYTES // 4:]
+
+    def _init_ipc(self) -> None:
+        lib = nat.load()
+        ptr = C.c_void_p()
+        handle = (C.c_char * 64)()
+        with torch.cuda.device(self.device):
+            nat.check(lib.ddpb_ipc_alloc(self.bytes, C.byref(ptr), handle), "ddpb_ipc_alloc")
+        self._ipc_local = ptr.value
+        handles: list = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle.raw), group=self.group)
+        self.ptrs = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self.ptrs.append(self._ipc_local)
+                continue
+            p = C.c_void_p()
+            buf = (C.c_char * 64).from_buffer_copy(h)
+            with torch.cuda.device(self.device):
+                nat.check(lib.ddpb_ipc_open(buf, C.byref(p)), "ddpb_ipc_open")
+            self._ipc_opened.append(p.value)
+            self.ptrs.append(p.value)
+        self.payload = _tensor_from_ptr(self._ipc_local + SIGNAL_PAD_BYTES, self.payload_floats, self.device, self)
+
+    # -- kernels -----------------------------------------------------------------------------------
+    @property
+    def has_multicast(self) -> bool:
+        return self.multicast_ptr != 0
+
+    def _mc(self, use_mc: bool):
+        return C.c_void_p(self.multicast_ptr) if (use_mc and self.multicast_ptr) else None
+
+    def allreduce_avg(self, off: int, n: int, *, blocks: int, slot_base: int = 0, use_mc: bool = False, sgd=None,
+                      stream=None) -> None:
+        """grad[off:off+n] <- mean over ranks, in place on every rank; optional fused SGD.
+        sgd = (param_arena, momentum_arena, lr, momentum, weight_decay) or None."""
+        p, m, lr, mu, wd = sgd if sgd is not None else (None, None, 0.0, 0.0, 0.0)
+        rc = nat.load().ddpb_allreduce_avg(self._ptr_array, self._mc(use_mc), self.rank, self.world, off, n, blocks,
+                                           slot_base, int(bool(use_mc and self.multicast_ptr)), nat.ptr(p), nat.ptr(m),
+                                           lr, mu, wd, nat.stream_ptr(stream))
+        nat.check(rc, "ddpb_allreduce_avg")
+
+    def reduce_root_bcast(self, off: int, n: int, *, root: int = 0, blocks: int, slot_base: int = 0,
+                          use_mc: bool = False, sgd=None, stream=None) -> None:
+        p, m, lr, mu, wd = sgd if sgd is not None else (None, None, 0.0, 0.0, 0.0)
+        rc = nat.load().ddpb_reduce_root_bcast(self._ptr_array, self._mc(use_mc), self.rank, self.world, root, off, n,
+                                               blocks, slot_base, int(bool(use_mc and self.multicast_ptr)), nat.ptr(p),
+                                               nat.ptr(m), lr, mu, wd, nat.stream_ptr(stream))
+        nat.check(rc, "ddpb_reduce_root_bcast")
+
+    def broadcast(self, off: int, n: int, *, root: int = 0, blocks: int = 32, slot_base: int = 0,
+                  use_mc: bool = False, stream=None) -> None:
+        rc = nat.load().ddpb_broadcast(self._ptr_array, self._mc(use_mc), self.rank, self.world, root, off, n, blocks,
+                                       slot_base, int(bool(use_mc and self.multicast_ptr)), nat.stream_ptr(stream))
+        nat.check(rc, "ddpb_broadcast")
+
+    def barrier(self, *, blocks: int = 1, slot_base: int = 0, stream=None) -> None:
+        rc = nat.load().ddpb_peer_barrier(self._ptr_array, self.rank, self.world, blocks, slot_base,
+                                          nat.stream_ptr(stream))
+        nat.check(rc, "ddpb_peer_barrier")
+
+    def close(self) -> None:
+        if self.backend == "ipc" and self._ipc_local:
+            torch.cuda.synchronize(self.device)
+            dist.barrier(self.group)
+            lib = nat.load()
+            for p in self._ipc_opened:
+                lib.ddpb_ipc_close(C.c_void_p(p))
+            dist.barrier(self.group)
+            lib.ddpb_ipc_free(C.c_void_p(self._ipc_local))
+            self._ipc_local = 0
+            self._ipc_opened = []
+
+
+class _CudaArrayHolder:
+    """Exposes a raw device pointer through __cuda_array_interface__ so torch can wrap it."""
+
+    def __init__(self, ptr: int, n_floats: int, owner):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 3,
+                                         "strides": None}
+        self._owner = owner
+
+
+def _tensor_from_ptr(ptr: int, n_floats: int, device: torch.device, owner) -> torch.Tensor:
+    with torch.cuda.device(device):
+        return torch.as_tensor(_CudaArrayHolder(ptr, n_floats, owner), device=device)

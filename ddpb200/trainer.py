@@ -1,0 +1,302 @@
+"""Trainer: one object that performs the reference's training iteration in any of its four modes.
+
+The reference spells the iteration out in ``train_model``: ``zero_grad`` -> forward ->
+loss -> backward -> [sync] -> ``optimizer.step()`` (/root/reference/part1/main.py:71-77,
+part2/part2a/main.py:137-144, part2/part2b/main.py:125-132, part3/main.py:116-122).
+``Trainer.step(data, target)`` is that whole sequence:
+
+  mode            reference      gradient sync here
+  'single'        part1          none
+  'gather_scatter' part2a        reduce-to-root + broadcast kernel
+  'allreduce'     part2b         in-place two-shot all-reduce kernel (per parameter or fused)
+  'ddp'           part3          same kernel per bucket, on a side stream, started as soon as
+                                 the bucket's last gradient is enqueued (overlaps backward)
+
+On CUDA the iteration is a CUDA graph over the hand-written kernels (engine.py,
+csrc/*.cu) and the sync kernels also apply the SGD update to their range; on CPU it
+runs the stock torch modules with the restatements in parallel/sync.py over Gloo.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+from .parallel import sync as S
+
+MODES = ("single", "gather_scatter", "allreduce", "ddp")
+
+
+class Trainer:
+    def __init__(self, model, mode: str = "single", batch_size: int = 256, lr: float = 0.1, momentum: float = 0.9,
+                 weight_decay: float = 1e-4, rank: int = 0, world_size: int = 1, granularity: str = "fused",
+                 use_multicast: bool | str = "auto", use_graph: bool = True, comm_blocks: int | None = None,
+                 first_bucket_bytes: int = S.MIB, bucket_bytes: int = 25 * S.MIB, symm_backend: str | None = None,
+                 fuse_sgd: bool = True):
+        if mode not in MODES:
+            raise ValueError(f"mode must be one of {MODES}")
+        if granularity not in ("fused", "param"):
+            raise ValueError("granularity must be 'fused' or 'param'")
+        self.model, self.mode = model, mode
+        self.batch_size = batch_size
+        self.lr, self.momentum, self.weight_decay = lr, momentum, weight_decay
+        self.rank, self.world = rank, world_size
+        self.granularity = granularity
+        self.use_graph = use_graph
+        self.fuse_sgd = fuse_sgd
+        self.device = next(model.parameters()).device
+        self.distributed = world_size > 1 and mode != "single"
+        self.iteration = 0
+        self._graphs: dict[str, torch.cuda.CUDAGraph] = {}
+        self.groups = S.param_groups_of(model)
+        self.buckets = S.plan_buckets(self.groups, first_bucket_bytes, bucket_bytes)
+        if self.device.type == "cuda":
+            self._init_cuda(use_multicast, comm_blocks, symm_backend)
+        else:
+            self._init_cpu()
+
+    # =====================================================================================
+    # CUDA path
+    # =====================================================================================
+    def _init_cuda(self, use_multicast, comm_blocks, symm_backend):
+        from .engine import VGGEngine
+        from .parallel.comm import SymmetricBuffer
+
+        torch.cuda.set_device(self.device)
+        n_params = sum((p.numel() + 31) // 32 * 32 for p in self.model.parameters())
+        self.symm = None
+        grad_storage = None
+        if self.distributed:
+            self.symm = SymmetricBuffer(n_params, self.device, prefer=symm_backend)
+            grad_storage = self.symm.payload
+        self.engine = VGGEngine(self.model, self.batch_size, grad_storage)
+        self.model._engine = self.engine
+        if use_multicast == "auto":
+            use_multicast = bool(self.symm is not None and self.symm.has_multicast)
+        self.use_mc = bool(use_multicast and self.symm is not None and self.symm.has_multicast)
+        sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+        # part3 reductions share the GPU with backward: a slice of the SMs; 2a/2b own the GPU
+        self.comm_blocks = comm_blocks if comm_blocks is not None else (32 if self.mode == "ddp" else min(sms, 128))
+        self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1) if self.mode == "ddp" else None
+        B = self.batch_size
+        hw = self.engine.image_hw
+        self.in_u8 = torch.zeros(B, hw, hw, 3, dtype=torch.uint8, device=self.device)
+        self.in_aug = torch.zeros(B, 4, dtype=torch.int8, device=self.device)
+        self.in_f32 = torch.zeros(B, 3, hw, hw, dtype=torch.float32, device=self.device)
+        self._capture_stream = torch.cuda.Stream(device=self.device)
+        if self.distributed and self.mode == "ddp":
+            self._broadcast_parameters()
+
+    def _broadcast_parameters(self):
+        """DDP's constructor-time parameter broadcast from rank 0, via the arena."""
+        a = self.engine.arena
+        a.grad.copy_(a.master)
+        torch.cuda.synchronize(self.device)
+        self.symm.broadcast(0, a.numel, root=0, blocks=self.comm_blocks, use_mc=self.use_mc)
+        torch.cuda.synchronize(self.device)
+        a.master.copy_(a.grad)
+        a.grad.zero_()
+        self.engine.repack()
+        torch.cuda.synchronize(self.device)
+
+    def _sgd_args(self):
+        a = self.engine.arena
+        return (a.master, a.momentum, self.lr, self.momentum, self.weight_decay)
+
+    def _sync_range(self, off, n, slot_base, stream=None):
+        sgd = self._sgd_args() if self.fuse_sgd else None
+        if self.mode == "gather_scatter":
+            self.symm.reduce_root_bcast(off, n, root=0, blocks=self.comm_blocks, slot_base=slot_base,
+                                        use_mc=self.use_mc, sgd=sgd, stream=stream)
+        else:
+            self.symm.allreduce_avg(off, n, blocks=self.comm_blocks, slot_base=slot_base, use_mc=self.use_mc, sgd=sgd,
+                                    stream=stream)
+
+    def _enqueue_iteration(self, kind: str, with_aug: bool, B: int | None = None):
+        """Everything between 'inputs are on the device' and 'parameters are updated'."""
+        eng, a = self.engine, self.engine.arena
+        B = self.batch_size if B is None else B
+        if kind == "u8":
+            eng.load_input_u8(self.in_u8[:B], self.in_aug[:B] if with_aug else None)
+        else:
+            eng.load_input_f32(self.in_f32[:B])
+        eng.forward(B, with_loss=True)
+        if not self.distributed:
+            eng.backward(B)
+            eng.sgd(self.lr, self.momentum, self.weight_decay)
+        elif self.mode == "ddp":
+            main = torch.cuda.current_stream()
+            ready = {b.ready_after_group: bi for bi, b in enumerate(self.buckets)}
+
+            def after_layer(li):
+                bi = ready.get(li)
+                if bi is None:
+                    return
+                b = self.buckets[bi]
+                off, n = a.range_of(b.first_param, b.last_param)
+                ev = torch.cuda.Event()
+                ev.record(main)
+                self.comm_stream.wait_event(ev)
+                with torch.cuda.stream(self.comm_stream):
+                    self._sync_range(off, n, slot_base=bi * self.comm_blocks)
+
+            eng.backward(B, after_layer=after_layer)
+            done = torch.cuda.Event()
+            done.record(self.comm_stream)
+            main.wait_event(done)
+            if not self.fuse_sgd:
+                eng.sgd(self.lr, self.momentum, self.weight_decay)
+        else:
+            eng.backward(B)
+            if self.granularity == "param":
+                # one launch per parameter tensor, like the reference's python loop
+                for i in range(len(a.params)):
+                    off, n = a.range_of(i, i)
+                    self._sync_range(off, n, slot_base=0)
+            else:
+                self._sync_range(0, a.numel, slot_base=0)
+            if not self.fuse_sgd:
+                eng.sgd(self.lr, self.momentum, self.weight_decay)
+        eng.repack()
+
+    def _stage_inputs(self, data: torch.Tensor, target: torch.Tensor, aug):
+        eng = self.engine
+        N = data.shape[0]
+        if N > self.batch_size or N < 1:
+            raise ValueError(f"Trainer was built for batches of up to {self.batch_size}, got {N}")
+        if data.dtype == torch.uint8:
+            self.in_u8[:N].copy_(data, non_blocking=True)
+            if aug is not None:
+                self.in_aug[:N].copy_(aug, non_blocking=True)
+            kind = "u8"
+        else:
+            self.in_f32[:N].copy_(data, non_blocking=True)
+            kind = "f32"
+        eng.labels[:N].copy_(target, non_blocking=True)
+        return kind
+
+    def step(self, data: torch.Tensor, target: torch.Tensor, aug: torch.Tensor | None = None) -> torch.Tensor:
+        """One training iteration.  ``data`` is either raw uint8 NHWC pixels (plus optional
+        per-image crop/flip parameters ``aug``) or a normalised fp32 NCHW batch, on the host
+        (ideally pinned) or on the device.  Returns the mean loss as a 0-d device tensor that is
+        overwritten by the next call."""
+        if self.device.type != "cuda":
+            return self._step_cpu(data, target)
+        kind = self._stage_inputs(data, target, aug)
+        with_aug = aug is not None
+        key = f"{kind}:{int(with_aug)}"
+        N = data.shape[0]
+        if not self.use_graph or N != self.batch_size:
+            # ragged last batch of an epoch (or graphs disabled): plain launches
+            self._enqueue_iteration(kind, with_aug, N)
+        else:
+            g = self._graphs.get(key)
+            if g is None:
+                g = self._capture(key, kind, with_aug)
+            else:
+                g.replay()
+        self.iteration += 1
+        return self.engine.loss
+
+    def _capture(self, key, kind, with_aug):
+        # The first call runs eagerly (it also performs one-time kernel attribute set-up) and
+        # IS the iteration; the graph is captured afterwards from a snapshot-free sequence: the
+        # capture itself executes nothing.
+        self._enqueue_iteration(kind, with_aug)
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=self._capture_stream):
+            self._enqueue_iteration(kind, with_aug)
+        self._graphs[key] = g
+        return g
+
+    def evaluate(self, data: torch.Tensor, target: torch.Tensor):
+        """Forward + loss + top-1 count for one batch (any size up to batch_size); BatchNorm uses
+        batch statistics here too, as the reference's model does in eval mode
+        (track_running_stats=False, model.py:24).  Returns (mean loss, number correct) tensors."""
+        if self.device.type != "cuda":
+            return self._evaluate_cpu(data, target)
+        eng = self.engine
+        N = data.shape[0]
+        if N > self.batch_size:
+            raise ValueError("evaluation batch larger than the engine was sized for")
+        if data.dtype == torch.uint8:
+            self.in_u8[:N].copy_(data, non_blocking=True)
+            eng.labels[:N].copy_(target, non_blocking=True)
+            from .ops import kernels as K
+
+            K.first_layer_operand_u8(self.in_u8[:N], None, out=eng.operand0)
+        else:
+            self.in_f32[:N].copy_(data, non_blocking=True)
+            eng.labels[:N].copy_(target, non_blocking=True)
+            from .ops import kernels as K
+
+            K.first_layer_operand_f32(self.in_f32[:N], out=eng.operand0)
+        eng.forward(N, with_loss=True, want_dlogits=False)
+        return eng.loss.clone(), eng.correct.clone()
+
+    def kernel_launches_per_step(self) -> int:
+        """Number of ddpb200 kernels one ``step`` enqueues (for bench.py's gpu_launches)."""
+        if self.device.type != "cuda":
+            return 0
+        n = 1 + self.engine.launches_per_train_step() + 1  # input prep ... repack
+        if not self.distributed:
+            n += 1
+        elif self.mode == "ddp":
+            n += len(self.buckets) + (0 if self.fuse_sgd else 1)
+        else:
+            n += (len(self.engine.arena.params) if self.granularity == "param" else 1) + (0 if self.fuse_sgd else 1)
+        return n
+
+    def close(self):
+        if getattr(self, "symm", None) is not None:
+            self._graphs.clear()
+            self.symm.close()
+            self.symm = None
+
+    # =====================================================================================
+    # CPU path (stock modules + torch.distributed): plumbing tests and the oracle
+    # =====================================================================================
+    def _init_cpu(self):
+        self.optimizer = torch.optim.SGD(self.model.parameters(), lr=self.lr, momentum=self.momentum,
+                                         weight_decay=self.weight_decay)
+        self.reducer = None
+        if self.distributed and self.mode == "ddp":
+            for p in self.model.parameters():  # constructor-time broadcast, as DDP does
+                dist.broadcast(p.data, src=0)
+            self.reducer = S.HostBucketReducer(self.model, self.world)
+            self.buckets = self.reducer.buckets
+
+    @staticmethod
+    def _to_float_batch(data: torch.Tensor) -> torch.Tensor:
+        if data.dtype == torch.uint8:
+            from .ops.reference import augment_normalize_u8
+
+            return augment_normalize_u8(data, None)
+        return data
+
+    def _step_cpu(self, data, target):
+        data = self._to_float_batch(data)
+        self.optimizer.zero_grad()
+        loss = F.cross_entropy(self.model(data), target)
+        loss.backward()
+        if self.distributed:
+            if self.mode == "gather_scatter":
+                S.sync_gradients_gather_scatter(self.model, self.rank, self.world)
+            elif self.mode == "allreduce":
+                S.sync_gradients_allreduce(self.model, self.world)
+            else:
+                self.reducer.finalize()
+        self.optimizer.step()
+        self.iteration += 1
+        return loss.detach()
+
+    def _evaluate_cpu(self, data, target):
+        data = self._to_float_batch(data)
+        with torch.no_grad():
+            if self.reducer is not None:
+                self.reducer.enabled = False
+            out = self.model(data)
+            if self.reducer is not None:
+                self.reducer.enabled = True
+            return F.cross_entropy(out, target), out.argmax(1).eq(target).sum()
