@@ -66,8 +66,26 @@ def maybe_reexec_under_torchrun(a):
         raise SystemExit(subprocess.call(cmd))
 
 
+_JSON_FD = None
+
+
+def isolate_stdout():
+    """Only the result line may appear on stdout: libraries (NCCL prints its version there)
+    are redirected to stderr, the JSON goes to the saved descriptor."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
 def emit(obj):
-    print(json.dumps(obj), flush=True)
+    line = json.dumps(obj) + "\n"
+    if _JSON_FD is None:
+        sys.stdout.write(line)
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, line.encode())
 
 
 def synthetic_host_batches(n_batches, batch, seed, pinned=True):
@@ -333,6 +351,7 @@ def run_reference(a):
 def main():
     a = parse()
     maybe_reexec_under_torchrun(a)
+    isolate_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:

