@@ -67,14 +67,16 @@ def main():
         stats = torch.zeros(2, Co, device=dev)
         y = torch.empty(P, Co, dtype=torch.bfloat16, device=dev)
         flops = 2.0 * P * Co * taps * Cin_eff
-        t = timeit(lambda: K.conv_fprop(x, w, bias, N, H, W, Cin_eff, Co, taps, out=y, stats=stats), flush=flush)
+        fs = torch.empty(max(1, K.conv_fprop_scratch_elems(N, H, W, Cin_eff, Co, taps)), device=dev)
+        t = timeit(lambda: K.conv_fprop(x, w, bias, N, H, W, Cin_eff, Co, taps, out=y, stats=stats, scratch=fs),
+                   flush=flush)
         rows.append(dict(layer=li, op="fprop", us=t, tflops=flops / t / 1e6))
         tot["fprop"] += t
         dy = torch.randn(P, Co, device=dev).bfloat16()
         if li > 0:
-            wd = torch.randn(Ci, 9 * Co, device=dev).bfloat16()
             dx = torch.empty(P, Ci, dtype=torch.bfloat16, device=dev)
-            t = timeit(lambda: K.conv_fprop(dy, wd, None, N, H, W, Co, Ci, 9, out=dx), flush=flush)
+            ds_ = torch.empty(max(1, K.conv_fprop_scratch_elems(N, H, W, Co, Ci, 9)), device=dev)
+            t = timeit(lambda: K.conv_dgrad(dy, w, N, H, W, Ci, Co, out=dx, scratch=ds_), flush=flush)
             rows.append(dict(layer=li, op="dgrad", us=t, tflops=flops / t / 1e6))
             tot["dgrad"] += t
         cols = 27 if li == 0 else taps * Cin_eff

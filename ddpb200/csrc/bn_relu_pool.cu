@@ -163,212 +163,231 @@ bn_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __rest
 }
 
 // ------------------------------------------------------------------------------------------
-// backward, pass 1: sums[0][c] = sum g, sums[1][c] = sum g*xhat, where g is dy routed back
-// through the pool (first maximum wins, like ATen) and the ReLU mask.
-// Block 0 also clears the conv-bias gradient slot that pass 2 accumulates into.
+// backward.  Work item = one OUTPUT position (a 2x2 window when pooling) x 8 channels, so
+// every input element is loaded exactly once per pass and the pool argmax is found once
+// per window (first maximum wins, like ATen; a window whose maximum is <= 0 passes nothing).
+//   pass 1: sums[0][c] = sum g, sums[1][c] = sum g*xhat   (g = dy routed through pool+ReLU)
+//           block 0 also clears the conv-bias gradient slot that pass 2 accumulates into.
+//   pass 2: dx = gamma*rstd*(g - mean(g) - xhat*mean(g*xhat)); block 0 publishes
+//           dgamma = sum g*xhat, dbeta = sum g; every block adds its share of sum(dx) to dbias.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void routed_grad(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
-                                            const BnGeom& g, long long ipix_n, int h, int w, int cg,
-                                            const float (&sc)[8], const float (&sh)[8], const float (&xv)[8],
-                                            float (&gr)[8]) {
-  // gradient reaching pre-pool position (n,h,w) for the 8 channels of group cg
+struct BwdItem {
+  long long ipix[4];   // input pixel index of the window positions (only [0] without pooling)
+  long long opix;
+  int cg;
+};
+
+__device__ __forceinline__ BwdItem bwd_item(const BnGeom& g, long long i, int groups) {
+  BwdItem it;
+  it.cg = static_cast<int>(i % groups);
+  it.opix = i / groups;
   if (!g.pool) {
-    float d[8];
-    load8(dy + ((ipix_n * g.H + h) * g.W + w) * g.C + cg * 8, d);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) gr[j] = (fmaf(xv[j], sc[j], sh[j]) > 0.f) ? d[j] : 0.f;
-    return;
+    it.ipix[0] = it.opix;
+    return it;
   }
-  const int Ho = g.H / 2, Wo = g.W / 2;
-  const int ho = h >> 1, wo = w >> 1;
-  const int me = ((h & 1) << 1) | (w & 1);
-  float d[8];
-  load8(dy + ((ipix_n * Ho + ho) * Wo + wo) * g.C + cg * 8, d);
-  float best[8];
-  int arg[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    best[j] = 0.f;   // a window whose maximum is <= 0 passes no gradient (ReLU)
-    arg[j] = -1;
-  }
-  const long long base = (ipix_n * g.H + 2 * ho) * g.W + 2 * wo;
-#pragma unroll
-  for (int dd = 0; dd < 4; ++dd) {
-    float v[8];
-    if (dd == me) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = xv[j];
-    } else {
-      load8(x + (base + (dd >> 1) * g.W + (dd & 1)) * g.C + cg * 8, v);
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float z = fmaf(v[j], sc[j], sh[j]);
-      if (z > best[j]) {
-        best[j] = z;
-        arg[j] = dd;
-      }
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) gr[j] = (arg[j] == me) ? d[j] : 0.f;
+  const int Ho = g.H >> 1, Wo = g.W >> 1;
+  const int wo = static_cast<int>(it.opix % Wo);
+  const long long t = it.opix / Wo;
+  const int ho = static_cast<int>(t % Ho);
+  const long long n = t / Ho;
+  const long long base = (n * g.H + 2 * ho) * g.W + 2 * wo;
+  it.ipix[0] = base;
+  it.ipix[1] = base + 1;
+  it.ipix[2] = base + g.W;
+  it.ipix[3] = base + g.W + 1;
+  return it;
 }
 
-__global__ void __launch_bounds__(kBnThreads)
+// Adds v (one value per lane; lanes l and l+groups hold the same channel) into dst[...] with
+// as few shared-memory atomics as possible.
+__device__ __forceinline__ void group_accumulate(float* dst, float v, int groups, int cg, int j) {
+  for (int off = 16; off >= groups; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  if (groups >= 32 || static_cast<int>(lane_id()) < groups) atomicAdd(&dst[cg * 8 + j], v);
+}
+
+// element j (0..7) of a packed row of 8 bf16
+__device__ __forceinline__ float bf16_at(const uint4& u, int j) {
+  const uint32_t w = (j < 2) ? u.x : (j < 4) ? u.y : (j < 6) ? u.z : u.w;
+  return __uint_as_float((j & 1) ? (w & 0xffff0000u) : (w << 16));
+}
+__device__ __forceinline__ uint4 ldg16(const __nv_bfloat16* p) { return *reinterpret_cast<const uint4*>(p); }
+
+// Pass 1.  sums[0][c] += sum g ; sums[1][c] += sum g*x (RAW x: pass 2 turns it into
+// sum g*xhat = rstd*(sum g*x - mean*sum g), which keeps mean/rstd out of this loop's registers).
+template <bool kPool>
+__global__ void __launch_bounds__(kBnThreads, 3)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                      const float* __restrict__ saved, const float* __restrict__ gamma,
                      const float* __restrict__ beta, float* __restrict__ sums /* [2][C] accumulated */,
                      float* __restrict__ dbias_clear /* [C] or null */, BnGeom g) {
-  extern __shared__ float s_mem[];  // scale[C], shift[C], mean[C], rstd[C], acc[2][C]
+  extern __shared__ float s_mem[];  // scale[C], shift[C], acc[2][C]
   float* s_scale = s_mem;
   float* s_shift = s_mem + g.C;
-  float* s_mean = s_mem + 2 * g.C;
-  float* s_rstd = s_mem + 3 * g.C;
-  float* s_acc = s_mem + 4 * g.C;
+  float* s_acc = s_mem + 2 * g.C;
   for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
     const float mean = saved[c], rstd = saved[g.C + c];
     const float sc = gamma[c] * rstd;
     s_scale[c] = sc;
     s_shift[c] = beta[c] - mean * sc;
-    s_mean[c] = mean;
-    s_rstd[c] = rstd;
     s_acc[c] = 0.f;
     s_acc[g.C + c] = 0.f;
     if (blockIdx.x == 0 && dbias_clear != nullptr) dbias_clear[c] = 0.f;
   }
   __syncthreads();
   const int groups = g.C / 8;
-  const long long items = static_cast<long long>(g.N) * g.H * g.W * groups;
+  const long long out_pix = static_cast<long long>(g.N) * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
+  const long long items = out_pix * groups;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  float a1[8], a2[8];
+  // blockDim.x is a multiple of `groups` (host checks), so a thread keeps its channel group
+  const int cg = static_cast<int>((blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) % groups);
+  float sc[8], sh[8], a1[8], a2[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) a1[j] = a2[j] = 0.f;
-  int my_group = -1;
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = s_scale[cg * 8 + j];
+    sh[j] = s_shift[cg * 8 + j];
+    a1[j] = a2[j] = 0.f;
+  }
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < items; i += stride) {
-    const int cg = static_cast<int>(i % groups);
-    const long long pix = i / groups;
-    if (cg != my_group) {
-      if (my_group >= 0) {
+    const BwdItem it = bwd_item(g, i, groups);
+    const uint4 d = ldg16(dy + it.opix * g.C + cg * 8);
+    if (!kPool) {
+      const uint4 v = ldg16(x + it.ipix[0] * g.C + cg * 8);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          atomicAdd(&s_acc[my_group * 8 + j], a1[j]);
-          atomicAdd(&s_acc[g.C + my_group * 8 + j], a2[j]);
-          a1[j] = a2[j] = 0.f;
-        }
+      for (int j = 0; j < 8; ++j) {
+        const float xv = bf16_at(v, j);
+        const float gr = (fmaf(xv, sc[j], sh[j]) > 0.f) ? bf16_at(d, j) : 0.f;
+        a1[j] += gr;
+        a2[j] = fmaf(gr, xv, a2[j]);
       }
-      my_group = cg;
-    }
-    const int w = static_cast<int>(pix % g.W);
-    const long long t = pix / g.W;
-    const int h = static_cast<int>(t % g.H);
-    const long long n = t / g.H;
-    float sc[8], sh[8], xv[8], gr[8];
+    } else {
+      uint4 v[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      sc[j] = s_scale[cg * 8 + j];
-      sh[j] = s_shift[cg * 8 + j];
-    }
-    load8(x + pix * g.C + cg * 8, xv);
-    routed_grad(x, dy, g, n, h, w, cg, sc, sh, xv, gr);
+      for (int q = 0; q < 4; ++q) v[q] = ldg16(x + it.ipix[q] * g.C + cg * 8);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float xhat = (xv[j] - s_mean[cg * 8 + j]) * s_rstd[cg * 8 + j];
-      a1[j] += gr[j];
-      a2[j] += gr[j] * xhat;
+      for (int j = 0; j < 8; ++j) {
+        float best = 0.f, xa = 0.f;
+        bool hit = false;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float xv = bf16_at(v[q], j);
+          const float z = fmaf(xv, sc[j], sh[j]);
+          if (z > best) {
+            best = z;
+            xa = xv;
+            hit = true;
+          }
+        }
+        const float gr = hit ? bf16_at(d, j) : 0.f;
+        a1[j] += gr;
+        a2[j] = fmaf(gr, xa, a2[j]);
+      }
     }
   }
-  if (my_group >= 0) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&s_acc[my_group * 8 + j], a1[j]);
-      atomicAdd(&s_acc[g.C + my_group * 8 + j], a2[j]);
-    }
+  for (int j = 0; j < 8; ++j) {
+    group_accumulate(s_acc, a1[j], groups, cg, j);
+    group_accumulate(s_acc + g.C, a2[j], groups, cg, j);
   }
   __syncthreads();
   for (int c = threadIdx.x; c < 2 * g.C; c += blockDim.x) atomicAdd(&sums[c], s_acc[c]);
 }
 
-// ------------------------------------------------------------------------------------------
-// backward, pass 2: dx = gamma*rstd*(g - mean(g) - xhat*mean(g*xhat)); block 0 publishes
-// dgamma = sum g*xhat and dbeta = sum g; every block adds its share of sum(dx) to dbias.
-// ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBnThreads)
+// Pass 2.  With A = -scale*rstd*mean(g*xhat) and Bc = -scale*mean(g) - A*mean:
+//   dx = scale*g + A*x + Bc     (one fma chain per element, four coefficient vectors)
+template <bool kPool>
+__global__ void __launch_bounds__(kBnThreads, 2)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                     const float* __restrict__ saved, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ sums,
                     __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
                     float* __restrict__ dbias, BnGeom g) {
-  extern __shared__ float s_mem[];  // scale, shift, mean, rstd, mg, mgx, acc : 7*C
+  extern __shared__ float s_mem[];  // scale, shift, A, Bc, acc : 5*C
   float* s_scale = s_mem;
   float* s_shift = s_mem + g.C;
-  float* s_mean = s_mem + 2 * g.C;
-  float* s_rstd = s_mem + 3 * g.C;
-  float* s_mg = s_mem + 4 * g.C;
-  float* s_mgx = s_mem + 5 * g.C;
-  float* s_acc = s_mem + 6 * g.C;
+  float* s_A = s_mem + 2 * g.C;
+  float* s_B = s_mem + 3 * g.C;
+  float* s_acc = s_mem + 4 * g.C;
   const float inv_count = 1.f / static_cast<float>(static_cast<long long>(g.N) * g.H * g.W);
   for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
     const float mean = saved[c], rstd = saved[g.C + c];
     const float sc = gamma[c] * rstd;
+    const float sum_g = sums[c];
+    const float sum_gxhat = rstd * (sums[g.C + c] - mean * sum_g);
+    const float A = -sc * rstd * sum_gxhat * inv_count;
     s_scale[c] = sc;
     s_shift[c] = beta[c] - mean * sc;
-    s_mean[c] = mean;
-    s_rstd[c] = rstd;
-    s_mg[c] = sums[c] * inv_count;
-    s_mgx[c] = sums[g.C + c] * inv_count;
+    s_A[c] = A;
+    s_B[c] = -sc * sum_g * inv_count - A * mean;
     s_acc[c] = 0.f;
     if (blockIdx.x == 0) {
-      if (dbeta) dbeta[c] = sums[c];
-      if (dgamma) dgamma[c] = sums[g.C + c];
+      if (dbeta) dbeta[c] = sum_g;
+      if (dgamma) dgamma[c] = sum_gxhat;
     }
   }
   __syncthreads();
   const int groups = g.C / 8;
-  const long long items = static_cast<long long>(g.N) * g.H * g.W * groups;
+  const long long out_pix = static_cast<long long>(g.N) * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
+  const long long items = out_pix * groups;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  float ab[8];
+  const int cg = static_cast<int>((blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) % groups);
+  float sc[8], sh[8], cA[8], cB[8], ab[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) ab[j] = 0.f;
-  int my_group = -1;
+  for (int j = 0; j < 8; ++j) {
+    const int c = cg * 8 + j;
+    sc[j] = s_scale[c];
+    sh[j] = s_shift[c];
+    cA[j] = s_A[c];
+    cB[j] = s_B[c];
+    ab[j] = 0.f;
+  }
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < items; i += stride) {
-    const int cg = static_cast<int>(i % groups);
-    const long long pix = i / groups;
-    if (cg != my_group) {
-      if (my_group >= 0 && dbias != nullptr) {
+    const BwdItem it = bwd_item(g, i, groups);
+    const uint4 d = ldg16(dy + it.opix * g.C + cg * 8);
+    if (!kPool) {
+      const uint4 v = ldg16(x + it.ipix[0] * g.C + cg * 8);
+      float o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          atomicAdd(&s_acc[my_group * 8 + j], ab[j]);
-          ab[j] = 0.f;
+      for (int j = 0; j < 8; ++j) {
+        const float xv = bf16_at(v, j);
+        const float gr = (fmaf(xv, sc[j], sh[j]) > 0.f) ? bf16_at(d, j) : 0.f;
+        o[j] = fmaf(sc[j], gr, fmaf(cA[j], xv, cB[j]));
+        ab[j] += o[j];
+      }
+      store8(dx + it.ipix[0] * g.C + cg * 8, o);
+    } else {
+      uint4 v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) v[q] = ldg16(x + it.ipix[q] * g.C + cg * 8);
+      int arg[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float best = 0.f;
+        arg[j] = -1;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float z = fmaf(bf16_at(v[q], j), sc[j], sh[j]);
+          if (z > best) {
+            best = z;
+            arg[j] = q;
+          }
         }
       }
-      my_group = cg;
-    }
-    const int w = static_cast<int>(pix % g.W);
-    const long long t = pix / g.W;
-    const int h = static_cast<int>(t % g.H);
-    const long long n = t / g.H;
-    float sc[8], sh[8], xv[8], gr[8], o[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      sc[j] = s_scale[cg * 8 + j];
-      sh[j] = s_shift[cg * 8 + j];
-    }
-    load8(x + pix * g.C + cg * 8, xv);
-    routed_grad(x, dy, g, n, h, w, cg, sc, sh, xv, gr);
+      for (int q = 0; q < 4; ++q) {
+        float o[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = cg * 8 + j;
-      const float xhat = (xv[j] - s_mean[c]) * s_rstd[c];
-      o[j] = sc[j] * (gr[j] - s_mg[c] - xhat * s_mgx[c]);
-      ab[j] += o[j];
+        for (int j = 0; j < 8; ++j) {
+          const float gr = (arg[j] == q) ? bf16_at(d, j) : 0.f;
+          o[j] = fmaf(sc[j], gr, fmaf(cA[j], bf16_at(v[q], j), cB[j]));
+          ab[j] += o[j];
+        }
+        store8(dx + it.ipix[q] * g.C + cg * 8, o);
+      }
     }
-    store8(dx + pix * g.C + cg * 8, o);
   }
   if (dbias != nullptr) {
-    if (my_group >= 0) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) atomicAdd(&s_acc[my_group * 8 + j], ab[j]);
-    }
+    for (int j = 0; j < 8; ++j) group_accumulate(s_acc, ab[j], groups, cg, j);
     __syncthreads();
     for (int c = threadIdx.x; c < g.C; c += blockDim.x) atomicAdd(&dbias[c], s_acc[c]);
   }
@@ -424,15 +443,26 @@ extern "C" int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float*
                                      cudaStream_t stream) {
   DDPB_BN_CHECK_GEOM("bn_relu_pool_bwd");
   BnGeom g{N, H, W, C, pool, eps};
-  const long long items = static_cast<long long>(N) * H * W * (C / 8);
+  DDPB_REQUIRE((C / 8) <= kBnThreads && kBnThreads % (C / 8) == 0,
+               "bn_relu_pool_bwd: C/8 must divide %d (got C=%d)", kBnThreads, C);
+  const long long items = static_cast<long long>(N) * (pool ? H / 2 : H) * (pool ? W / 2 : W) * (C / 8);
   const int grid = bn_grid(items);
-  bn_bwd_reduce_kernel<<<grid, kBnThreads, 6 * C * sizeof(float), stream>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), saved, gamma, beta, sums,
-      dbias, g);
-  DDPB_CHECK_CUDA(cudaGetLastError());
-  bn_bwd_apply_kernel<<<grid, kBnThreads, 7 * C * sizeof(float), stream>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), saved, gamma, beta, sums,
-      static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, dbias, g);
+  const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
+  const __nv_bfloat16* dyb = static_cast<const __nv_bfloat16*>(dy);
+  __nv_bfloat16* dxb = static_cast<__nv_bfloat16*>(dx);
+  if (pool) {
+    bn_bwd_reduce_kernel<true><<<grid, kBnThreads, 4 * C * sizeof(float), stream>>>(xb, dyb, saved, gamma, beta,
+                                                                                    sums, dbias, g);
+    DDPB_CHECK_CUDA(cudaGetLastError());
+    bn_bwd_apply_kernel<true><<<grid, kBnThreads, 5 * C * sizeof(float), stream>>>(
+        xb, dyb, saved, gamma, beta, sums, dxb, dgamma, dbeta, dbias, g);
+  } else {
+    bn_bwd_reduce_kernel<false><<<grid, kBnThreads, 4 * C * sizeof(float), stream>>>(xb, dyb, saved, gamma, beta,
+                                                                                     sums, dbias, g);
+    DDPB_CHECK_CUDA(cudaGetLastError());
+    bn_bwd_apply_kernel<false><<<grid, kBnThreads, 5 * C * sizeof(float), stream>>>(
+        xb, dyb, saved, gamma, beta, sums, dxb, dgamma, dbeta, dbias, g);
+  }
   DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -41,6 +41,7 @@ struct CommCtx {
 struct SgdArgs {
   float* p;   // parameter arena (local), null = no fused update
   float* m;   // momentum arena (local)
+  __nv_bfloat16* shadow;  // bf16 copy of the parameters (conv operand), may be null
   float lr, mu, wd;
 };
 
@@ -138,6 +139,8 @@ __device__ __forceinline__ void sgd_range(const CommCtx& c, const SgdArgs& s, lo
     pv.w = fmaf(-s.lr, mv.w, pv.w);
     reinterpret_cast<float4*>(p)[i] = pv;
     reinterpret_cast<float4*>(m)[i] = mv;
+    if (s.shadow != nullptr)
+      reinterpret_cast<uint2*>(s.shadow + off)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
   }
 }
 
@@ -280,13 +283,13 @@ extern "C" int ddpb_comm_max_ranks() { return kMaxRanks; }
 // off/n: range inside the gradient arena in floats.  p/m: local parameter and momentum
 // arenas for the fused SGD step (null = only synchronise).  use_mc selects NVLS.
 extern "C" int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int rank, int world, long long off,
-                                  long long n, int blocks, int slot_base, int use_mc, float* p, float* m, float lr,
-                                  float momentum, float weight_decay, cudaStream_t stream) {
+                                  long long n, int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow,
+                                  float lr, float momentum, float weight_decay, cudaStream_t stream) {
   CommCtx c;
   if (int rc = fill_ctx(&c, bufs, mc, rank, world)) return rc;
   if (int rc = check_range(off, n, blocks, slot_base)) return rc;
   DDPB_REQUIRE(!use_mc || c.mc != nullptr, "comm: multicast requested but no multicast mapping");
-  SgdArgs s{p, m, lr, momentum, weight_decay};
+  SgdArgs s{p, m, static_cast<__nv_bfloat16*>(shadow), lr, momentum, weight_decay};
   if (use_mc)
     allreduce_avg_kernel<true><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, s);
   else
@@ -297,13 +300,14 @@ extern "C" int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int r
 
 extern "C" int ddpb_reduce_root_bcast(const void* const* bufs, const void* mc, int rank, int world, int root,
                                       long long off, long long n, int blocks, int slot_base, int use_mc, float* p,
-                                      float* m, float lr, float momentum, float weight_decay, cudaStream_t stream) {
+                                      float* m, void* shadow, float lr, float momentum, float weight_decay,
+                                      cudaStream_t stream) {
   CommCtx c;
   if (int rc = fill_ctx(&c, bufs, mc, rank, world)) return rc;
   if (int rc = check_range(off, n, blocks, slot_base)) return rc;
   DDPB_REQUIRE(root >= 0 && root < world, "comm: bad root %d", root);
   DDPB_REQUIRE(!use_mc || c.mc != nullptr, "comm: multicast requested but no multicast mapping");
-  SgdArgs s{p, m, lr, momentum, weight_decay};
+  SgdArgs s{p, m, static_cast<__nv_bfloat16*>(shadow), lr, momentum, weight_decay};
   if (use_mc)
     reduce_root_bcast_kernel<true><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, root, s);
   else

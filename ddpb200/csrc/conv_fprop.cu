@@ -46,106 +46,14 @@ struct FpropParams {
   int C_in, C_out;
   int taps;              // 9 (3x3) or 1 (pre-gathered input)
   int bh, bn, hblocks;   // TMA box geometry: box = (64, W, bh, bn); hblocks = H / bh
+  float* partial;        // split-K: fp32 [gridDim.z][P][C_out] partial sums (null when gridDim.z == 1)
 };
 
+// Epilogue shared by the 1-CTA and CTA-pair kernels: this warp's 32 accumulator rows ->
+// (+bias, bf16, per-channel statistics) -> global, or raw fp32 partials under split-K.
 template <int BLOCK_N>
-__global__ void __launch_bounds__(kConvThreads)
-conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
-                  const FpropParams p) {
-  using Cfg = FpropCfg<BLOCK_N>;
-  extern __shared__ uint8_t smem_raw[];
-  // SWIZZLE_128B operand tiles need 1024-byte alignment.
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* tiles = smem;
-  float* s_stats = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes);
-  uint64_t* full_bar = bars;                       // [kStages]
-  uint64_t* empty_bar = bars + Cfg::kStages;       // [kStages]
-  uint64_t* tmem_full_bar = bars + 2 * Cfg::kStages;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * Cfg::kStages + 1);
-
-  const int warp = threadIdx.x >> 5;
-  const int m_tile = blockIdx.x;
-  const int n_tile = blockIdx.y;
-  const int cchunks = p.C_in / kBlockK;
-  const int num_k = p.taps * cchunks;
-
-  if (warp == 0 && elect_one()) {
-    tma_prefetch_desc(&tmap_x);
-    tma_prefetch_desc(&tmap_w);
-  }
-  if (warp == 1) {
-    if (elect_one()) {
-      for (int i = 0; i < Cfg::kStages; ++i) {
-        mbar_init(&full_bar[i], 1);
-        mbar_init(&empty_bar[i], 1);
-      }
-      mbar_init(tmem_full_bar, 1);
-      fence_mbar_init();
-    }
-    __syncwarp();
-    tmem_alloc(tmem_ptr_smem, BLOCK_N);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr_smem;
-
-  if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (elect_one()) {
-      const int n_img = (m_tile / p.hblocks) * p.bn;
-      const int h0 = (m_tile % p.hblocks) * p.bh;
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int k = 0; k < num_k; ++k) {
-        const int tap = k / cchunks;
-        const int cc = k - tap * cchunks;
-        int dr = 0, ds = 0;
-        if (p.taps == 9) {
-          dr = tap / 3 - 1;
-          ds = tap % 3 - 1;
-        }
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* a_dst = tiles + stage * Cfg::kStageBytes;
-        uint8_t* b_dst = a_dst + Cfg::kABytes;
-        mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-        tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
-        tma_load_2d(b_dst, &tmap_w, &full_bar[stage], tap * p.C_in + cc * kBlockK, n_tile * BLOCK_N);
-        if (++stage == Cfg::kStages) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int k = 0; k < num_k; ++k) {
-        mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        const uint32_t a_addr = smem_u32(tiles + stage * Cfg::kStageBytes);
-        const uint32_t b_addr = a_addr + Cfg::kABytes;
-#pragma unroll
-        for (int kk = 0; kk < kBlockK / kUmmaK; ++kk) {
-          const uint64_t adesc = make_smem_desc_sw128(a_addr + kk * kUmmaK * 2, 16, 1024);
-          const uint64_t bdesc = make_smem_desc_sw128(b_addr + kk * kUmmaK * 2, 16, 1024);
-          umma_f16(tmem_base, adesc, bdesc, idesc, (k | kk) != 0);
-        }
-        umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
-        if (++stage == Cfg::kStages) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-      umma_commit(tmem_full_bar);  // accumulator complete
-    }
-  } else {
-    // ===================== epilogue (warps 2..5) =====================
+__device__ __forceinline__ void conv_epilogue(const FpropParams& p, uint32_t tmem_base, uint64_t* tmem_full_bar,
+                                              float* s_stats, int warp, int m_tile, int n_tile) {
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     const int row = q * 32 + lane_id();
     const long long pix = static_cast<long long>(m_tile) * kBlockM + row;
@@ -153,6 +61,21 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     __nv_bfloat16* out_row = p.out + pix * p.C_out + n_tile * BLOCK_N;
+    if (p.partial != nullptr) {
+      // split-K: hand the raw fp32 tile to the finalize kernel (bias, rounding, statistics there)
+      float* prow = p.partial + (static_cast<long long>(blockIdx.z) * p.P + pix) * p.C_out + n_tile * BLOCK_N;
+#pragma unroll 1
+      for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
+        uint32_t raw[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + chunk * 32, raw);
+        tmem_ld_wait();
+        if (valid) {
+          uint4* dst = reinterpret_cast<uint4*>(prow + chunk * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dst[j] = make_uint4(raw[4 * j], raw[4 * j + 1], raw[4 * j + 2], raw[4 * j + 3]);
+        }
+      }
+    } else {
 #pragma unroll 1
     for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
       uint32_t raw[32];
@@ -199,6 +122,127 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
         atomicAdd(p.stats + which * p.C_out + n_tile * BLOCK_N + col, acc);
       }
     }
+    }  // direct (non split-K) epilogue
+  }
+
+// kDgrad: the B operand is read straight from the FPROP filter pack [C_out][taps][C_in]
+// as an MN-major tile (rows = reduction channel k, 64 output channels c contiguous), with the
+// taps visited in reverse -- dgrad needs no transposed / rotated copy of the filters.
+// In that mode p.C_in is the reduction width (the layer's C_out) and p.C_out the produced
+// width (the layer's C_in).
+template <int BLOCK_N, bool kDgrad>
+__global__ void __launch_bounds__(kConvThreads)
+conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                  const FpropParams p) {
+  using Cfg = FpropCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B operand tiles need 1024-byte alignment.
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tiles = smem;
+  float* s_stats = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes);
+  uint64_t* full_bar = bars;                       // [kStages]
+  uint64_t* empty_bar = bars + Cfg::kStages;       // [kStages]
+  uint64_t* tmem_full_bar = bars + 2 * Cfg::kStages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * Cfg::kStages + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int m_tile = blockIdx.x;
+  const int n_tile = blockIdx.y;
+  const int cchunks = p.C_in / kBlockK;
+  // split-K: blockIdx.z owns k-steps [k_begin, k_end) of the taps*C_in/64 reduction steps
+  const int total_k = p.taps * cchunks;
+  const int k_begin = static_cast<int>(static_cast<long long>(total_k) * blockIdx.z / gridDim.z);
+  const int k_end = static_cast<int>(static_cast<long long>(total_k) * (blockIdx.z + 1) / gridDim.z);
+  const int num_k = k_end - k_begin;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_w);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      for (int i = 0; i < Cfg::kStages; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], 1);
+      }
+      mbar_init(tmem_full_bar, 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_ptr_smem, BLOCK_N);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      const int n_img = (m_tile / p.hblocks) * p.bn;
+      const int h0 = (m_tile % p.hblocks) * p.bh;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int k = k_begin; k < k_end; ++k) {
+        const int tap = k / cchunks;
+        const int cc = k - tap * cchunks;
+        int dr = 0, ds = 0;
+        if (p.taps == 9) {
+          dr = tap / 3 - 1;
+          ds = tap % 3 - 1;
+        }
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* a_dst = tiles + stage * Cfg::kStageBytes;
+        uint8_t* b_dst = a_dst + Cfg::kABytes;
+        mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+        tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
+        if (!kDgrad) {
+          tma_load_2d(b_dst, &tmap_w, &full_bar[stage], tap * p.C_in + cc * kBlockK, n_tile * BLOCK_N);
+        } else {
+#pragma unroll
+          for (int j = 0; j < BLOCK_N / 64; ++j)
+            tma_load_2d(b_dst + j * 8192, &tmap_w, &full_bar[stage],
+                        (p.taps - 1 - tap) * p.C_out + n_tile * BLOCK_N + j * 64, cc * kBlockK);
+        }
+        if (++stage == Cfg::kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, 0, kDgrad ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int k = 0; k < num_k; ++k) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(tiles + stage * Cfg::kStageBytes);
+        const uint32_t b_addr = a_addr + Cfg::kABytes;
+#pragma unroll
+        for (int kk = 0; kk < kBlockK / kUmmaK; ++kk) {
+          const uint64_t adesc = make_smem_desc_sw128(a_addr + kk * kUmmaK * 2, 16, 1024);
+          // K-major B: 32 bytes further along the 128-byte row; MN-major B (dgrad): 16 rows down,
+          // 64-channel column blocks 8 KB apart
+          const uint64_t bdesc = kDgrad ? make_smem_desc_sw128(b_addr + kk * kUmmaK * 128, 8192, 1024)
+                                        : make_smem_desc_sw128(b_addr + kk * kUmmaK * 2, 16, 1024);
+          umma_f16(tmem_base, adesc, bdesc, idesc, (k | kk) != 0);
+        }
+        umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+        if (++stage == Cfg::kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tmem_full_bar);  // accumulator complete
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    conv_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, s_stats, warp, m_tile, n_tile);
   }
 
   tc_fence_before();
@@ -209,19 +253,307 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// CTA-pair variant (tcgen05 cta_group::2).  The kernels above are bound by how fast one SM
+// can pull operand tiles out of L2 (ncu: ~45 B/clk/SM, tensor pipe 38% busy at 128x128
+// tiles).  Here two CTAs of a (2,1,1) cluster share one M = 256 MMA: each loads its own 128
+// pixel rows of A but only HALF of the filter tile B, so the bytes per flop an SM must ingest
+// drop by up to 2x (BLOCK_N = 256: 32 KB per 128x256x64 instead of 32 KB per 128x128x64).
+//   * both CTAs: TMA producer (own A tile + own half of B) signalling the LEADER's full barrier
+//   * leader only: MMA issue; tcgen05.commit multicasts "slot free" / "accumulator ready" to
+//     the barriers of both CTAs
+//   * both CTAs: epilogue over their own 128 TMEM lanes
+// ------------------------------------------------------------------------------------------
 template <int BLOCK_N>
+struct PairCfg {
+  static constexpr int kStages = (BLOCK_N >= 256) ? 5 : 6;
+  static constexpr int kABytes = kBlockM * kBlockK * 2;            // 16 KB: this CTA's pixels
+  static constexpr int kBBytes = (BLOCK_N / 2) * kBlockK * 2;      // this CTA's half of the filters
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStatsBytes = 4 * 2 * BLOCK_N * 4;
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kStatsBytes + 256;
+};
+
+template <int BLOCK_N, bool kDgrad>
+__global__ void __launch_bounds__(kConvThreads)
+conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                 const FpropParams p) {
+  using Cfg = PairCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tiles = smem;
+  float* s_stats = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + Cfg::kStages;
+  uint64_t* tmem_full_bar = bars + 2 * Cfg::kStages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * Cfg::kStages + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const uint32_t rank = cluster_ctarank();     // 0 = leader
+  const int m_tile = blockIdx.x;               // the pair covers m-tiles (2i, 2i+1)
+  const int n_tile = blockIdx.y;
+  const int cchunks = p.C_in / kBlockK;
+  const int total_k = p.taps * cchunks;
+  const int k_begin = static_cast<int>(static_cast<long long>(total_k) * blockIdx.z / gridDim.z);
+  const int k_end = static_cast<int>(static_cast<long long>(total_k) * (blockIdx.z + 1) / gridDim.z);
+  const int num_k = k_end - k_begin;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_w);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      for (int i = 0; i < Cfg::kStages; ++i) {
+        mbar_init(&full_bar[i], 1);    // the leader's producer arrives (with the byte count of BOTH CTAs)
+        mbar_init(&empty_bar[i], 1);   // one multicast commit from the leader's MMA thread
+      }
+      mbar_init(tmem_full_bar, 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc_pair(tmem_ptr_smem, BLOCK_N);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();   // both CTAs' barriers exist before anything is signalled across the pair
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (elect_one()) {
+      const int n_img = (m_tile / p.hblocks) * p.bn;
+      const int h0 = (m_tile % p.hblocks) * p.bh;
+      const int b_row0 = n_tile * BLOCK_N + static_cast<int>(rank) * (BLOCK_N / 2);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int k = k_begin; k < k_end; ++k) {
+        const int tap = k / cchunks;
+        const int cc = k - tap * cchunks;
+        int dr = 0, ds = 0;
+        if (p.taps == 9) {
+          dr = tap / 3 - 1;
+          ds = tap % 3 - 1;
+        }
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* a_dst = tiles + stage * Cfg::kStageBytes;
+        uint8_t* b_dst = a_dst + Cfg::kABytes;
+        if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+        tma_load_4d_pair(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
+        if (!kDgrad) {
+          tma_load_2d_pair(b_dst, &tmap_w, &full_bar[stage], tap * p.C_in + cc * kBlockK, b_row0);
+        } else {
+#pragma unroll
+          for (int j = 0; j < BLOCK_N / 128; ++j)
+            tma_load_2d_pair(b_dst + j * 8192, &tmap_w, &full_bar[stage],
+                             (p.taps - 1 - tap) * p.C_out + b_row0 + j * 64, cc * kBlockK);
+        }
+        if (++stage == Cfg::kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * kBlockM, BLOCK_N, 0, kDgrad ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int k = 0; k < num_k; ++k) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(tiles + stage * Cfg::kStageBytes);
+        const uint32_t b_addr = a_addr + Cfg::kABytes;
+#pragma unroll
+        for (int kk = 0; kk < kBlockK / kUmmaK; ++kk) {
+          const uint64_t adesc = make_smem_desc_sw128(a_addr + kk * kUmmaK * 2, 16, 1024);
+          const uint64_t bdesc = kDgrad ? make_smem_desc_sw128(b_addr + kk * kUmmaK * 128, 8192, 1024)
+                                        : make_smem_desc_sw128(b_addr + kk * kUmmaK * 2, 16, 1024);
+          umma_f16_pair(tmem_base, adesc, bdesc, idesc, (k | kk) != 0);
+        }
+        umma_commit_pair(&empty_bar[stage], 0x3);   // slot free in BOTH CTAs
+        if (++stage == Cfg::kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit_pair(tmem_full_bar, 0x3);         // accumulators ready in BOTH CTAs
+    }
+  } else {
+    conv_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, s_stats, warp, m_tile, n_tile);
+  }
+
+  tc_fence_before();
+  cluster_sync_all();   // nobody frees TMEM or exits while the peer may still signal / read
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, BLOCK_N);
+  }
+}
+
+// Split-K finalize: y = bf16(sum_s partial[s] + bias); stats += (sum y, sum y^2) per channel.
+// One thread = one pixel x 8 channels; 256 % (C_out/8) == 0 keeps a thread on its channels.
+__global__ void __launch_bounds__(256)
+splitk_finalize_kernel(const float* __restrict__ partial, const float* __restrict__ bias,
+                       __nv_bfloat16* __restrict__ out, float* __restrict__ stats, int splits, long long P,
+                       int C_out) {
+  extern __shared__ float s_acc[];  // [2][C_out]
+  for (int c = threadIdx.x; c < 2 * C_out; c += blockDim.x) s_acc[c] = 0.f;
+  __syncthreads();
+  const int groups = C_out / 8;
+  const long long items = P * groups;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int cg = static_cast<int>((blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) % groups);
+  float b[8], a1[8], a2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    b[j] = bias != nullptr ? bias[cg * 8 + j] : 0.f;
+    a1[j] = a2[j] = 0.f;
+  }
+  const long long split_stride = P * C_out;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < items; i += stride) {
+    const float* src = partial + i * 8;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = b[j];
+    for (int sp = 0; sp < splits; ++sp) {
+      const float4 lo = *reinterpret_cast<const float4*>(src + sp * split_stride);
+      const float4 hi = *reinterpret_cast<const float4*>(src + sp * split_stride + 4);
+      v[0] += lo.x; v[1] += lo.y; v[2] += lo.z; v[3] += lo.w;
+      v[4] += hi.x; v[5] += hi.y; v[6] += hi.z; v[7] += hi.w;
+    }
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]);
+    o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]);
+    o.w = pack_bf16x2(v[6], v[7]);
+    reinterpret_cast<uint4*>(out)[i] = o;
+    if (stats != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float r = bf16_round(v[j]);
+        a1[j] += r;
+        a2[j] += r * r;
+      }
+    }
+  }
+  if (stats != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float x1 = a1[j], x2 = a2[j];
+      for (int off = 16; off >= groups; off >>= 1) {
+        x1 += __shfl_xor_sync(0xffffffffu, x1, off);
+        x2 += __shfl_xor_sync(0xffffffffu, x2, off);
+      }
+      if (groups >= 32 || static_cast<int>(lane_id()) < groups) {
+        atomicAdd(&s_acc[cg * 8 + j], x1);
+        atomicAdd(&s_acc[C_out + cg * 8 + j], x2);
+      }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < 2 * C_out; c += blockDim.x) atomicAdd(&stats[c], s_acc[c]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Launch planning.  Measured on B200 (profiles/): these kernels are bound by operand ingest
+// per SM (~45 B/clk) unless the tile is large, and by fixed per-CTA cost when the reduction is
+// short.  The planner estimates every legal (CTA pair?, BLOCK_N, split-K) choice with that
+// model and takes the cheapest.
+// ------------------------------------------------------------------------------------------
+struct ConvPlan {
+  int pair;      // 1: cta_group::2 kernel
+  int block_n;
+  int splits;
+};
+
+static int g_force_pair = -1, g_force_block_n = -1, g_force_splits = -1;
+
+static double plan_cost(int pair, int bn, int splits, long long P, int C_out, int total_k) {
+  const double kIngest = 45.0;        // bytes / clk / SM
+  const double kFixed = 3500.0;       // prologue + epilogue + launch ramp per CTA, cycles
+  int m_tiles = static_cast<int>((P + kBlockM - 1) / kBlockM);
+  if (pair) m_tiles = (m_tiles + 1) / 2 * 2;
+  const int ctas = m_tiles * (C_out / bn) * splits;
+  const int sms = sm_count();
+  const int per_sm = (ctas + sms - 1) / sms;
+  const double stage_bytes = 16384.0 + (pair ? bn / 2 : bn) * 128.0;
+  const double mma = 2.0 * bn;        // cycles per 64-deep k-step at full tensor rate
+  const double k_iters = static_cast<double>(total_k) / splits;
+  double t = per_sm * (k_iters * (stage_bytes / kIngest > mma ? stage_bytes / kIngest : mma) + kFixed);
+  if (splits > 1) t += 4000.0 + 2.0 * splits * static_cast<double>(P) * C_out * 4.0 / 5000.0;
+  return t;
+}
+
+static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint, bool allow_split) {
+  ConvPlan best{0, (C_out % 128 == 0) ? 128 : 64, 1};
+  double best_t = 1e30;
+  const int bns[3] = {64, 128, 256};
+  for (int pair = 0; pair <= 1; ++pair) {
+    if (g_force_pair >= 0 && pair != g_force_pair) continue;
+    for (int bi = 0; bi < 3; ++bi) {
+      const int bn = bns[bi];
+      if (C_out % bn != 0) continue;
+      if (pair && bn < 128) continue;
+      if (block_n_hint != 0 && bn != block_n_hint) continue;
+      if (g_force_block_n >= 0 && bn != g_force_block_n) continue;
+      if (block_n_hint == 0 && g_force_block_n < 0 && bn == 64 && C_out % 128 == 0) continue;
+      for (int splits = 1; splits <= 8; ++splits) {
+        if (g_force_splits >= 0 && splits != g_force_splits) continue;
+        if (splits > 1 && (!allow_split || total_k / splits < 4 || C_out / 8 > 256 || 256 % (C_out / 8) != 0)) continue;
+        const double t = plan_cost(pair, bn, splits, P, C_out, total_k);
+        if (t < best_t) {
+          best_t = t;
+          best = ConvPlan{pair, bn, splits};
+        }
+      }
+    }
+  }
+  return best;
+}
+
+template <int BLOCK_N, bool kDgrad>
 static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const FpropParams& p, int m_tiles,
-                        cudaStream_t stream) {
+                        int splits, cudaStream_t stream) {
   using Cfg = FpropCfg<BLOCK_N>;
   static bool configured = false;
   if (!configured) {
-    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N>,
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N, kDgrad>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured = true;
   }
-  dim3 grid(m_tiles, p.C_out / BLOCK_N);
-  conv_fprop_kernel<BLOCK_N><<<grid, kConvThreads, Cfg::kSmemBytes, stream>>>(tx, tw, p);
+  dim3 grid(m_tiles, p.C_out / BLOCK_N, splits);
+  conv_fprop_kernel<BLOCK_N, kDgrad><<<grid, kConvThreads, Cfg::kSmemBytes, stream>>>(tx, tw, p);
   DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int BLOCK_N, bool kDgrad>
+static int launch_pair(const CUtensorMap& tx, const CUtensorMap& tw, const FpropParams& p, int m_tiles,
+                       int splits, cudaStream_t stream) {
+  using Cfg = PairCfg<BLOCK_N>;
+  static bool configured = false;
+  if (!configured) {
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_pair_kernel<BLOCK_N, kDgrad>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((m_tiles + 1) / 2 * 2, p.C_out / BLOCK_N, splits);   // even: CTA pairs along M
+  cfg.blockDim = dim3(kConvThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  DDPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_pair_kernel<BLOCK_N, kDgrad>, tx, tw, p));
   return 0;
 }
 
@@ -229,21 +561,49 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const Fpro
 
 using namespace ddpb;
 
-// x: [N][H][W][C_in] bf16; w: [C_out][taps*C_in] bf16; y: [N*H*W][C_out] bf16.
-// bias (fp32, may be null) is added before rounding; stats (fp32 [2][C_out], may be
-// null) is ACCUMULATED into (caller zeroes it).  block_n: 0 = choose automatically.
-extern "C" int ddpb_conv_fprop(const void* x, const void* w, const float* bias, void* y, float* stats,
-                               int N, int H, int W, int C_in, int C_out, int taps, int block_n,
-                               cudaStream_t stream) {
-  DDPB_REQUIRE(taps == 1 || taps == 9, "conv_fprop: taps must be 1 or 9 (got %d)", taps);
-  DDPB_REQUIRE(C_in % 64 == 0 && C_in > 0, "conv_fprop: C_in must be a multiple of 64 (got %d)", C_in);
-  DDPB_REQUIRE(C_out % 64 == 0 && C_out > 0, "conv_fprop: C_out must be a multiple of 64 (got %d)", C_out);
+// Testing / tuning hook: force the planner's choice (-1 = automatic) for all later launches.
+extern "C" void ddpb_conv_force(int pair, int block_n, int splits) {
+  g_force_pair = pair;
+  g_force_block_n = block_n;
+  g_force_splits = splits;
+}
+
+// What the planner picks for this shape: out3 = {pair, block_n, splits}.
+extern "C" void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3) {
+  const ConvPlan pl = plan_conv(static_cast<long long>(N) * H * W, C_out, taps * (C_in / 64), block_n, true);
+  out3[0] = pl.pair;
+  out3[1] = pl.block_n;
+  out3[2] = pl.splits;
+}
+
+// Floats of scratch ddpb_conv_fprop wants for this shape (0: it will not split K).
+extern "C" long long ddpb_conv_fprop_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps,
+                                                   int block_n) {
+  const long long P = static_cast<long long>(N) * H * W;
+  if (C_out % 64 != 0 || C_in % 64 != 0) return 0;
+  const ConvPlan pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, true);
+  return pl.splits > 1 ? pl.splits * P * C_out : 0;
+}
+
+// Shared host path.  dgrad == 0: y[P][C_out] = conv(x[..C_in], w[C_out][taps*C_in]).
+// dgrad == 1: x is dY [..C_in := layer C_out], w is the layer's FPROP pack
+// [layer C_out][taps][layer C_in], y = dX [P][C_out := layer C_in].
+static int conv_impl(int dgrad, const void* x, const void* w, const float* bias, void* y, float* stats, int N, int H,
+                     int W, int C_in, int C_out, int taps, int block_n, float* scratch, cudaStream_t stream) {
+  const char* name = dgrad ? "conv_dgrad" : "conv_fprop";
+  DDPB_REQUIRE(taps == 1 || taps == 9, "%s: taps must be 1 or 9 (got %d)", name, taps);
+  DDPB_REQUIRE(C_in % 64 == 0 && C_in > 0, "%s: reduction channels must be a multiple of 64 (got %d)", name, C_in);
+  DDPB_REQUIRE(C_out % 64 == 0 && C_out > 0, "%s: output channels must be a multiple of 64 (got %d)", name, C_out);
   int bh, bn, hblocks;
-  DDPB_REQUIRE(pixel_box(H, W, kBlockM, &bh, &bn, &hblocks),
-               "conv_fprop: unsupported spatial size %dx%d for 128-pixel tiles", H, W);
-  if (block_n == 0) block_n = (C_out % 128 == 0) ? 128 : 64;
-  DDPB_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "conv_fprop: bad block_n %d", block_n);
-  DDPB_REQUIRE(C_out % block_n == 0, "conv_fprop: C_out %d not divisible by block_n %d", C_out, block_n);
+  DDPB_REQUIRE(pixel_box(H, W, kBlockM, &bh, &bn, &hblocks), "%s: unsupported spatial size %dx%d for 128-pixel tiles",
+               name, H, W);
+  DDPB_REQUIRE(block_n == 0 || block_n == 64 || block_n == 128 || block_n == 256, "%s: bad block_n %d", name, block_n);
+  DDPB_REQUIRE(block_n == 0 || C_out % block_n == 0, "%s: output channels %d not divisible by block_n %d", name,
+               C_out, block_n);
+  const long long P = static_cast<long long>(N) * H * W;
+  const ConvPlan pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, scratch != nullptr);
+  block_n = pl.block_n;
+  const int b_rows = pl.pair ? block_n / 2 : block_n;   // filter rows one CTA loads per k-step
 
   CUtensorMap tx, tw;
   {
@@ -254,10 +614,18 @@ extern "C" int ddpb_conv_fprop(const void* x, const void* w, const float* bias, 
                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B))
       return 3;
   }
-  {
+  if (!dgrad) {
     uint64_t dims[2] = {(uint64_t)taps * C_in, (uint64_t)C_out};
     uint64_t strides[1] = {(uint64_t)taps * C_in * 2};
-    uint32_t box[2] = {64, (uint32_t)block_n};
+    uint32_t box[2] = {64, (uint32_t)b_rows};
+    if (encode_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, w, dims, strides, box,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B))
+      return 3;
+  } else {
+    // fprop pack seen as rows = layer C_out (our reduction), columns = taps * layer C_in
+    uint64_t dims[2] = {(uint64_t)taps * C_out, (uint64_t)C_in};
+    uint64_t strides[1] = {(uint64_t)taps * C_out * 2};
+    uint32_t box[2] = {64, 64};
     if (encode_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, w, dims, strides, box,
                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B))
       return 3;
@@ -266,7 +634,7 @@ extern "C" int ddpb_conv_fprop(const void* x, const void* w, const float* bias, 
   p.out = static_cast<__nv_bfloat16*>(y);
   p.bias = bias;
   p.stats = stats;
-  p.P = N * H * W;
+  p.P = static_cast<int>(P);
   p.C_in = C_in;
   p.C_out = C_out;
   p.taps = taps;
@@ -274,9 +642,54 @@ extern "C" int ddpb_conv_fprop(const void* x, const void* w, const float* bias, 
   p.bn = bn;
   p.hblocks = hblocks;
   const int m_tiles = (p.P + kBlockM - 1) / kBlockM;
-  switch (block_n) {
-    case 64: return launch_fprop<64>(tx, tw, p, m_tiles, stream);
-    case 128: return launch_fprop<128>(tx, tw, p, m_tiles, stream);
-    default: return launch_fprop<256>(tx, tw, p, m_tiles, stream);
+  const int splits = pl.splits;
+  p.partial = splits > 1 ? scratch : nullptr;
+  int rc = 0;
+#define DDPB_CONV_DISPATCH(FN)                                                     \
+  if (!dgrad) {                                                                    \
+    switch (block_n) {                                                             \
+      case 64: rc = launch_fprop<64, false>(tx, tw, p, m_tiles, splits, stream); break;  \
+      case 128: rc = FN<128, false>(tx, tw, p, m_tiles, splits, stream); break;    \
+      default: rc = FN<256, false>(tx, tw, p, m_tiles, splits, stream); break;     \
+    }                                                                              \
+  } else {                                                                         \
+    switch (block_n) {                                                             \
+      case 64: rc = launch_fprop<64, true>(tx, tw, p, m_tiles, splits, stream); break;   \
+      case 128: rc = FN<128, true>(tx, tw, p, m_tiles, splits, stream); break;     \
+      default: rc = FN<256, true>(tx, tw, p, m_tiles, splits, stream); break;      \
+    }                                                                              \
   }
+  if (pl.pair) {
+    DDPB_CONV_DISPATCH(launch_pair)
+  } else {
+    DDPB_CONV_DISPATCH(launch_fprop)
+  }
+#undef DDPB_CONV_DISPATCH
+  if (rc != 0 || splits == 1) return rc;
+  const long long items = static_cast<long long>(p.P) * (C_out / 8);
+  long long blocks = (items + 255) / 256;
+  if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
+  splitk_finalize_kernel<<<static_cast<int>(blocks), 256, 2 * C_out * sizeof(float), stream>>>(
+      scratch, bias, p.out, stats, splits, p.P, C_out);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// x: [N][H][W][C_in] bf16; w: [C_out][taps*C_in] bf16; y: [N*H*W][C_out] bf16.
+// bias (fp32, may be null) is added before rounding; stats (fp32 [2][C_out], may be
+// null) is ACCUMULATED into (caller zeroes it).  block_n: 0 = choose automatically.
+// scratch: device buffer of ddpb_conv_fprop_scratch_elems() floats, or null to forbid
+// split-K (small problems then run on few SMs).
+extern "C" int ddpb_conv_fprop(const void* x, const void* w, const float* bias, void* y, float* stats,
+                               int N, int H, int W, int C_in, int C_out, int taps, int block_n,
+                               float* scratch, cudaStream_t stream) {
+  return conv_impl(0, x, w, bias, y, stats, N, H, W, C_in, C_out, taps, block_n, scratch, stream);
+}
+
+// Data gradient of the 3x3 convolution (O2).  dy: [N][H][W][C_out] bf16; w: the SAME bf16 pack
+// fprop uses, [C_out][9][C_in]; dx: [N*H*W][C_in] bf16.  scratch: as for fprop, sized with
+// ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n).
+extern "C" int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out,
+                               int block_n, float* scratch, cudaStream_t stream) {
+  return conv_impl(1, dy, w, nullptr, dx, nullptr, N, H, W, C_out, C_in, 9, block_n, scratch, stream);
 }

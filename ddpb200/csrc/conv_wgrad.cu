@@ -26,7 +26,7 @@ constexpr int kWgBoxBytes = kWgPix * 128;     // one (64 ch x 64 px) box = 8 KB
 
 template <int BLOCK_N>
 struct WgradCfg {
-  static constexpr int kStages = 4;
+  static constexpr int kStages = (BLOCK_N >= 128) ? 3 : 4;   // <= 97 KB: two CTAs per SM
   static constexpr int kABytes = 2 * kWgBoxBytes;                 // M = 128 channels of dY
   static constexpr int kBBytes = (BLOCK_N / 64) * kWgBoxBytes;    // N channels of X
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -186,17 +186,55 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
   }
 }
 
-// out[r][c] = sum_s ws[s][r][c] for c < cols_valid; fixed summation order.
-__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out, int splits,
-                                    long long split_stride, int rows, int cols_valid, int ws_ld, int out_ld) {
-  const long long total = static_cast<long long>(rows) * cols_valid;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int r = static_cast<int>(i / cols_valid), c = static_cast<int>(i - static_cast<long long>(r) * cols_valid);
-    const float* src = ws + static_cast<long long>(r) * ws_ld + c;
+// Second stage of the split reduction, fixed summation order (deterministic).
+// Dense form: the partial tiles have exactly the output's shape -> flat float4 streaming sum.
+__global__ void __launch_bounds__(256)
+wgrad_reduce_dense_kernel(const float4* __restrict__ ws, float4* __restrict__ out, int splits, long long stride4,
+                          long long n4) {
+  const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += step) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    int sp = 0;
+    for (; sp + 4 <= splits; sp += 4) {   // four independent loads in flight
+      const float4 a = ws[i + (sp + 0) * stride4], b = ws[i + (sp + 1) * stride4];
+      const float4 c = ws[i + (sp + 2) * stride4], d = ws[i + (sp + 3) * stride4];
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+      acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
+      acc.x += c.x; acc.y += c.y; acc.z += c.z; acc.w += c.w;
+      acc.x += d.x; acc.y += d.y; acc.z += d.z; acc.w += d.w;
+    }
+    for (; sp < splits; ++sp) {
+      const float4 a = ws[i + sp * stride4];
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+    }
+    out[i] = acc;
+  }
+}
+
+// Compact form (first layer: 27 of 64 columns, hundreds of splits): one block per output row,
+// 32 columns x 8 split lanes, then a fixed-order combine of the 8 lanes.
+__global__ void __launch_bounds__(256)
+wgrad_reduce_rows_kernel(const float* __restrict__ ws, float* __restrict__ out, int splits, long long split_stride,
+                         int cols_valid, int ws_ld, int out_ld) {
+  __shared__ float s_part[8][33];
+  const int r = blockIdx.x;
+  const int lane_s = threadIdx.x >> 5;
+  for (int c0 = 0; c0 < cols_valid; c0 += 32) {
+    const int c = c0 + (threadIdx.x & 31);
     float acc = 0.f;
-    for (int s = 0; s < splits; ++s) acc += src[s * split_stride];
-    out[static_cast<long long>(r) * out_ld + c] = acc;
+    if (c < cols_valid) {
+      const float* src = ws + static_cast<long long>(r) * ws_ld + c;
+      for (int sp = lane_s; sp < splits; sp += 8) acc += src[sp * split_stride];
+    }
+    s_part[lane_s][threadIdx.x & 31] = acc;
+    __syncthreads();
+    if (lane_s == 0 && c < cols_valid) {
+      float t = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t += s_part[j][threadIdx.x & 31];
+      out[static_cast<long long>(r) * out_ld + c] = t;
+    }
+    __syncthreads();
   }
 }
 
@@ -227,9 +265,10 @@ extern "C" int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, 
   const int m_tiles = (C_out + 127) / 128;
   const int tiles = taps * m_tiles * (C_in / block_n);
   const int pix_blocks = (P + kWgPix - 1) / kWgPix;
+  // two CTAs fit per SM: aim for ONE full wave (rounding down avoids a nearly empty second wave)
   int target = 2 * sm_count();
   if (target <= 0) target = 296;
-  int splits = (target + tiles - 1) / tiles;
+  int splits = target / tiles;
   // keep at least 8 pipeline steps (512 pixels) per CTA so the prologue amortises
   int max_splits = pix_blocks / 8;
   if (max_splits < 1) max_splits = 1;
@@ -303,11 +342,18 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
                             : launch_wgrad<64>(tdy, tx, p, splits, stream);
   if (rc) return rc;
   if (!direct) {
-    const long long total = static_cast<long long>(C_out) * dw_cols_valid;
-    int blocks = static_cast<int>((total + 255) / 256);
-    if (blocks > 4 * 148) blocks = 4 * 148;
-    wgrad_reduce_kernel<<<blocks, 256, 0, stream>>>(scratch, dw, splits, p.out_split_stride, C_out,
-                                                    dw_cols_valid, taps * C_in, dw_ld);
+    const bool dense = (dw_cols_valid == taps * C_in && dw_ld == taps * C_in && C_out >= 128);
+    if (dense) {
+      const long long n4 = static_cast<long long>(C_out) * taps * C_in / 4;
+      long long blocks = (n4 + 255) / 256;
+      if (blocks > 8LL * sm_count()) blocks = 8LL * sm_count();
+      wgrad_reduce_dense_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
+          reinterpret_cast<const float4*>(scratch), reinterpret_cast<float4*>(dw), splits, p.out_split_stride / 4,
+          n4);
+    } else {
+      wgrad_reduce_rows_kernel<<<C_out, 256, 0, stream>>>(scratch, dw, splits, p.out_split_stride, dw_cols_valid,
+                                                         taps * C_in, dw_ld);
+    }
     DDPB_CHECK_CUDA(cudaGetLastError());
   }
   return 0;

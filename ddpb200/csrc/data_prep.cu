@@ -37,47 +37,47 @@ __device__ __forceinline__ float src_value(const void* __restrict__ src, const P
   }
 }
 
+// One thread gathers the 27 neighbourhood values of one pixel (taps unrolled at compile
+// time), the block then writes its 256 rows of 128 bytes fully coalesced from shared memory.
 template <bool kUint8>
 __global__ void __launch_bounds__(256)
 first_layer_operand_kernel(const void* __restrict__ src, const signed char* __restrict__ aug,
                            __nv_bfloat16* __restrict__ out, PrepParams p) {
+  __shared__ uint32_t s_rows[256][17];   // 32 bf16 columns per pixel (+1 word of padding)
   const long long P = static_cast<long long>(p.N) * p.H * p.W;
-  // 8 threads per pixel, each writes one 16-byte chunk (8 columns) of the 128-byte row
-  const long long items = P * 8;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < items; i += stride) {
-    const int chunk = static_cast<int>(i & 7);
-    const long long pix = i >> 3;
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);
-    if (chunk < 4) {
-      const int w = static_cast<int>(pix % p.W);
-      const long long t = pix / p.W;
-      const int h = static_cast<int>(t % p.H);
-      const int n = static_cast<int>(t / p.H);
-      float v[8];
+  const long long pix = blockIdx.x * 256LL + threadIdx.x;
+  if (pix < P) {
+    const int w = static_cast<int>(pix % p.W);
+    const long long t = pix / p.W;
+    const int h = static_cast<int>(t % p.H);
+    const int n = static_cast<int>(t / p.H);
+    float v[32];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int col = chunk * 8 + j;
-        float x = 0.f;
-        if (col < 27) {
-          const int tap = col / 3, c = col - tap * 3;
-          x = src_value<kUint8>(src, p, aug, n, h + tap / 3 - 1, w + tap % 3 - 1, c);
-        }
-        v[j] = x;
+    for (int col = 0; col < 32; ++col) {
+      if (col < 27) {
+        const int tap = col / 3, c = col % 3;
+        v[col] = src_value<kUint8>(src, p, aug, n, h + tap / 3 - 1, w + tap % 3 - 1, c);
+      } else {
+        v[col] = 0.f;
       }
-      o.x = pack_bf16x2(v[0], v[1]);
-      o.y = pack_bf16x2(v[2], v[3]);
-      o.z = pack_bf16x2(v[4], v[5]);
-      o.w = pack_bf16x2(v[6], v[7]);
     }
-    reinterpret_cast<uint4*>(out)[i] = o;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s_rows[threadIdx.x][j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+  }
+  __syncthreads();
+  uint4* dst = reinterpret_cast<uint4*>(out) + blockIdx.x * 256LL * 8;
+  const long long rows_here = (P - blockIdx.x * 256LL) < 256 ? (P - blockIdx.x * 256LL) : 256;
+  for (int i = threadIdx.x; i < rows_here * 8; i += 256) {
+    const int r = i >> 3, chunk = i & 7;
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (chunk < 4) o = make_uint4(s_rows[r][chunk * 4], s_rows[r][chunk * 4 + 1], s_rows[r][chunk * 4 + 2],
+                                  s_rows[r][chunk * 4 + 3]);
+    dst[i] = o;
   }
 }
 
-static int prep_grid(long long items) {
-  long long blocks = (items + 255) / 256;
-  const long long cap = 8LL * sm_count();
-  if (blocks > cap) blocks = cap;
+static int prep_grid(long long pixels) {
+  long long blocks = (pixels + 255) / 256;   // one block per 256 pixels (not grid-stride)
   if (blocks < 1) blocks = 1;
   return static_cast<int>(blocks);
 }
@@ -93,7 +93,7 @@ extern "C" int ddpb_first_layer_operand_f32(const float* src, void* out, int N, 
   p.N = N;
   p.H = H;
   p.W = W;
-  first_layer_operand_kernel<false><<<prep_grid(static_cast<long long>(N) * H * W * 8), 256, 0, stream>>>(
+  first_layer_operand_kernel<false><<<prep_grid(static_cast<long long>(N) * H * W), 256, 0, stream>>>(
       src, nullptr, static_cast<__nv_bfloat16*>(out), p);
   DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -114,7 +114,7 @@ extern "C" int ddpb_first_layer_operand_u8(const unsigned char* src, const signe
     p.mean[c] = mean3[c];
     p.inv_std[c] = 1.f / std3[c];
   }
-  first_layer_operand_kernel<true><<<prep_grid(static_cast<long long>(N) * H * W * 8), 256, 0, stream>>>(
+  first_layer_operand_kernel<true><<<prep_grid(static_cast<long long>(N) * H * W), 256, 0, stream>>>(
       src, aug, static_cast<__nv_bfloat16*>(out), p);
   DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;

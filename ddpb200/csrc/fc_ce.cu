@@ -10,12 +10,15 @@ namespace ddpb {
 
 constexpr int kMaxClasses = 16;
 
-// One warp per row.  Writes logits, per-row loss, dlogits = (softmax - onehot)/B and a
-// per-row "prediction correct" flag.
+// One warp per row; the K x F weight matrix is staged in shared memory once per CTA.
+// Writes logits, per-row loss, dlogits = (softmax - onehot)/B and a per-row "correct" flag.
 __global__ void __launch_bounds__(256)
 fc_ce_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                  const long long* __restrict__ labels, float* __restrict__ logits, float* __restrict__ row_loss,
                  float* __restrict__ dlogits, int* __restrict__ row_correct, int B, int F, int K) {
+  extern __shared__ float s_w[];  // [K][F]
+  for (int i = threadIdx.x; i < K * F; i += blockDim.x) s_w[i] = w[i];
+  __syncthreads();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= B) return;
@@ -23,11 +26,12 @@ fc_ce_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ 
 #pragma unroll
   for (int j = 0; j < kMaxClasses; ++j) acc[j] = 0.f;
   const __nv_bfloat16* xr = x + static_cast<long long>(warp) * F;
+#pragma unroll 4
   for (int i = lane; i < F; i += 32) {
     const float xv = __bfloat162float(xr[i]);
 #pragma unroll
     for (int j = 0; j < kMaxClasses; ++j)
-      if (j < K) acc[j] = fmaf(xv, __ldg(w + j * F + i), acc[j]);
+      if (j < K) acc[j] = fmaf(xv, s_w[j * F + i], acc[j]);   // lanes hit consecutive banks
   }
 #pragma unroll
   for (int j = 0; j < kMaxClasses; ++j) {
@@ -99,53 +103,62 @@ loss_reduce_kernel(const float* __restrict__ row_loss, const int* __restrict__ r
 }
 
 // Backward.  CTA c owns features [c*32, c*32+32): dW[:, own], dx[:, own]; CTA 0 also db.
-// 256 threads = 32 features x 8 row slices.
+// 256 threads = 32 features x 8 row slices; dlogits are staged through shared memory in
+// chunks of kFcRows rows so the inner loop only issues the (independent) loads of x.
+constexpr int kFcRows = 512;
+
 __global__ void __launch_bounds__(256)
 fc_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ dlogits,
               float* __restrict__ dw, float* __restrict__ db, __nv_bfloat16* __restrict__ dx, int B, int F, int K) {
   __shared__ float s_part[8][kMaxClasses][33];
+  extern __shared__ float s_dl[];  // [kFcRows][K]
   const int f_local = threadIdx.x & 31;
   const int slice = threadIdx.x >> 5;
   const int f = blockIdx.x * 32 + f_local;
-  float wcol[kMaxClasses], acc[kMaxClasses];
+  const bool fok = f < F;
+  float wcol[kMaxClasses], acc[kMaxClasses], dbv = 0.f;
 #pragma unroll
   for (int j = 0; j < kMaxClasses; ++j) {
-    wcol[j] = (j < K && f < F) ? w[j * F + f] : 0.f;
+    wcol[j] = (j < K && fok) ? w[j * F + f] : 0.f;
     acc[j] = 0.f;
   }
-  for (int r = slice; r < B; r += 8) {
-    const float* dl = dlogits + r * K;
-    float xv = (f < F) ? __bfloat162float(x[static_cast<long long>(r) * F + f]) : 0.f;
-    float dxv = 0.f;
+  for (int r0 = 0; r0 < B; r0 += kFcRows) {
+    const int rows = (B - r0) < kFcRows ? (B - r0) : kFcRows;
+    for (int i = threadIdx.x; i < rows * K; i += blockDim.x) s_dl[i] = dlogits[static_cast<long long>(r0) * K + i];
+    __syncthreads();
+#pragma unroll 4
+    for (int r = slice; r < rows; r += 8) {
+      const float xv = fok ? __bfloat162float(x[static_cast<long long>(r0 + r) * F + f]) : 0.f;
+      float dxv = 0.f;
 #pragma unroll
-    for (int j = 0; j < kMaxClasses; ++j) {
-      if (j < K) {
-        const float d = __ldg(dl + j);
-        acc[j] = fmaf(d, xv, acc[j]);
-        dxv = fmaf(d, wcol[j], dxv);
+      for (int j = 0; j < kMaxClasses; ++j) {
+        if (j < K) {
+          const float d = s_dl[r * K + j];   // same address across the warp: broadcast
+          acc[j] = fmaf(d, xv, acc[j]);
+          dxv = fmaf(d, wcol[j], dxv);
+        }
       }
+      if (dx != nullptr && fok) dx[static_cast<long long>(r0 + r) * F + f] = __float2bfloat16_rn(dxv);
     }
-    if (dx != nullptr && f < F) dx[static_cast<long long>(r) * F + f] = __float2bfloat16_rn(dxv);
+    if (blockIdx.x == 0 && threadIdx.x < K)
+      for (int r = 0; r < rows; ++r) dbv += s_dl[r * K + threadIdx.x];
+    __syncthreads();
   }
 #pragma unroll
   for (int j = 0; j < kMaxClasses; ++j) s_part[slice][j][f_local] = acc[j];
   __syncthreads();
-  if (slice == 0 && f < F) {
+  if (slice == 0 && fok) {
 #pragma unroll
     for (int j = 0; j < kMaxClasses; ++j) {
       if (j < K) {
         float t = 0.f;
 #pragma unroll
-        for (int s = 0; s < 8; ++s) t += s_part[s][j][f_local];
+        for (int sl = 0; sl < 8; ++sl) t += s_part[sl][j][f_local];
         dw[j * F + f] = t;
       }
     }
   }
-  if (blockIdx.x == 0 && threadIdx.x < K) {
-    float t = 0.f;
-    for (int r = 0; r < B; ++r) t += dlogits[r * K + threadIdx.x];
-    db[threadIdx.x] = t;
-  }
+  if (blockIdx.x == 0 && threadIdx.x < K) db[threadIdx.x] = dbv;
 }
 
 }  // namespace ddpb
@@ -163,8 +176,10 @@ extern "C" int ddpb_fc_ce_fwd(const void* x, const float* w, const float* b, con
   DDPB_REQUIRE(row_loss != nullptr, "fc_ce_fwd: row_loss buffer is required");
   const int warps_per_block = 8;
   const int blocks = (B + warps_per_block - 1) / warps_per_block;
-  fc_ce_fwd_kernel<<<blocks, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), w, b, labels, logits,
-                                                row_loss, dlogits, row_correct, B, F, K);
+  const size_t smem = static_cast<size_t>(K) * F * sizeof(float);
+  DDPB_REQUIRE(smem <= 48 * 1024, "fc_ce_fwd: K*F = %d exceeds the 48 KB weight stage", K * F);
+  fc_ce_fwd_kernel<<<blocks, 256, smem, stream>>>(static_cast<const __nv_bfloat16*>(x), w, b, labels, logits,
+                                                   row_loss, dlogits, row_correct, B, F, K);
   DDPB_CHECK_CUDA(cudaGetLastError());
   if (loss != nullptr || correct != nullptr) {
     loss_reduce_kernel<<<1, 256, 0, stream>>>(row_loss, row_correct, loss, correct, B);
@@ -178,8 +193,8 @@ extern "C" int ddpb_fc_bwd(const void* x, const float* w, const float* dlogits, 
                            int B, int F, int K, cudaStream_t stream) {
   DDPB_REQUIRE(K >= 1 && K <= kMaxClasses, "fc_bwd: at most %d classes (got %d)", kMaxClasses, K);
   const int blocks = (F + 31) / 32;
-  fc_bwd_kernel<<<blocks, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db,
-                                            static_cast<__nv_bfloat16*>(dx), B, F, K);
+  fc_bwd_kernel<<<blocks, 256, static_cast<size_t>(kFcRows) * K * sizeof(float), stream>>>(
+      static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db, static_cast<__nv_bfloat16*>(dx), B, F, K);
   DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

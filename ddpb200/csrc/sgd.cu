@@ -29,8 +29,8 @@ __device__ __forceinline__ float4 sgd_update4(float4 p, float4 g, float4& m, flo
 }
 
 __global__ void __launch_bounds__(256)
-sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, long long n, float lr,
-           float mu, float wd, float gs) {
+sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+           __nv_bfloat16* __restrict__ shadow, long long n, float lr, float mu, float wd, float gs) {
   const long long n4 = n >> 2;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
@@ -40,6 +40,8 @@ sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict
     pv = sgd_update4(pv, gv, mv, lr, mu, wd, gs);
     reinterpret_cast<float4*>(p)[i] = pv;
     reinterpret_cast<float4*>(m)[i] = mv;
+    if (shadow != nullptr)   // bf16 copy in the same flat order = the conv kernels' filter operand
+      reinterpret_cast<uint2*>(shadow)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
   }
   // tail (arena sizes are padded to 4, but stay correct if they are not)
   for (long long i = (n4 << 2) + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
@@ -47,7 +49,9 @@ sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict
     const float gg = fmaf(gs, g[i], wd * p[i]);
     const float mm = fmaf(mu, m[i], gg);
     m[i] = mm;
-    p[i] = fmaf(-lr, mm, p[i]);
+    const float pn = fmaf(-lr, mm, p[i]);
+    p[i] = pn;
+    if (shadow != nullptr) shadow[i] = __float2bfloat16_rn(pn);
   }
 }
 
@@ -122,16 +126,20 @@ pack_weights_kernel(const __grid_constant__ PackTable tab) {
 using namespace ddpb;
 
 // In-place SGD step over n contiguous fp32 elements.  grad_scale multiplies the gradient
-// first (1/world_size when the caller holds a SUM of per-rank gradients).
-extern "C" int ddpb_sgd_step(float* p, const float* g, float* m, long long n, float lr, float momentum,
-                             float weight_decay, float grad_scale, cudaStream_t stream) {
+// first (1/world_size when the caller holds a SUM of per-rank gradients).  shadow (bf16, n
+// elements, may be null) receives the rounded new parameters: because conv filters are
+// stored [C_out][3][3][C_in] in the arena, that copy IS the tensor-core operand of fprop
+// and dgrad, so no separate repack pass is needed.
+extern "C" int ddpb_sgd_step(float* p, const float* g, float* m, void* shadow, long long n, float lr,
+                             float momentum, float weight_decay, float grad_scale, cudaStream_t stream) {
   DDPB_REQUIRE((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m)) % 16 == 0,
                "sgd_step: arenas must be 16-byte aligned");
   long long blocks = ((n >> 2) + 255) / 256;
   const long long cap = 8LL * sm_count();
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  sgd_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(p, g, m, n, lr, momentum, weight_decay, grad_scale);
+  sgd_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(p, g, m, static_cast<__nv_bfloat16*>(shadow), n, lr,
+                                                           momentum, weight_decay, grad_scale);
   DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

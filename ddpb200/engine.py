@@ -147,18 +147,21 @@ class VGGEngine:
             self.bsums.append(self.stat_arena[o:o + 2 * L.c_out])
             o += 2 * L.c_out
             self.saved.append(torch.empty(2 * L.c_out, **f32))
-        # --- packed bf16 filters
-        self.w_f, self.w_d = [], []
-        pack = []
+        # --- bf16 filter operands.  The arena keeps filters as [C_out][3][3][C_in], which is the
+        # K-major GEMM operand of fprop AND (read MN-major, taps reversed) of dgrad, so one bf16
+        # "shadow" of the whole arena -- refreshed by the SGD kernels -- serves both.  Only the
+        # first layer needs a real repack (27 values per filter, zero padded to a 64-wide row).
+        self.shadow = torch.zeros(self.arena.numel, **bf)
+        self.w_f = []
         for li, L in enumerate(self.layers):
-            ld = 64 if li == 0 else 9 * L.c_in
-            wf = torch.zeros(L.c_out, ld, **bf)
-            wd = None if li == 0 else torch.empty(L.c_in, 9 * L.c_out, **bf)
-            self.w_f.append(wf)
-            self.w_d.append(wd)
-            pack.append(dict(master=self.arena.flat_master(L.p_w), fprop=wf, dgrad=wd, K=L.c_out, C=L.c_in, taps=9,
-                             fprop_ld=ld, flat=li == 0))
-        self.pack_plan = K.PackPlan(pack)
+            if li == 0:
+                self.w_f.append(torch.zeros(L.c_out, 64, **bf))
+            else:
+                o = self.arena.offsets[L.p_w]
+                self.w_f.append(self.shadow[o:o + L.c_out * 9 * L.c_in].view(L.c_out, 9 * L.c_in))
+        L0 = self.layers[0]
+        self.pack_plan = K.PackPlan([dict(master=self.arena.flat_master(L0.p_w), fprop=self.w_f[0], dgrad=None,
+                                          K=L0.c_out, C=L0.c_in, taps=9, fprop_ld=64, flat=True)])
         # --- classifier / loss
         self.labels = torch.zeros(B, dtype=torch.int64, device=dev)
         self.logits = torch.empty(B, self.classes, **f32)
@@ -172,13 +175,25 @@ class VGGEngine:
         for li, L in enumerate(self.layers):
             need = max(need, K.conv_wgrad_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps))
         self.wgrad_scratch = torch.empty(need, **f32)
+        # --- fprop / dgrad split-K scratch (only the small late layers ask for it)
+        need = 1
+        for li, L in enumerate(self.layers):
+            need = max(need, K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps))
+            if li > 0:
+                need = max(need, K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_out, L.c_in, 9))
+        self.fprop_scratch = torch.empty(need, **f32)
         self.image_hw = image_hw
-        self.repack()
+        self.repack(full=True)
         _register_engine(self)
 
     # -- pieces ---------------------------------------------------------------------------------
-    def repack(self, stream=None):
-        """fp32 master filters -> bf16 fprop / dgrad operand layouts (after every update)."""
+    def repack(self, stream=None, full: bool = False):
+        """Refreshes the bf16 filter operands from the fp32 master arena.  The training step only
+        needs the first layer's padded pack (the SGD kernels keep the shadow current); ``full``
+        also recasts the whole shadow -- used after parameters were changed from outside
+        (initialisation, load_state_dict, a foreign optimizer)."""
+        if full:
+            self.shadow.copy_(self.arena.master)
         self.pack_plan.run(stream)
 
     def load_input_f32(self, x_nchw: torch.Tensor):
@@ -194,7 +209,7 @@ class VGGEngine:
         x = self.operand0
         for li, L in enumerate(self.layers):
             K.conv_fprop(x, self.w_f[li], a.flat_master(L.p_b), N, L.H, L.W, L.c_in_eff, L.c_out, L.taps,
-                         out=self.conv_out[li], stats=self.stats[li])
+                         out=self.conv_out[li], stats=self.stats[li], scratch=self.fprop_scratch)
             K.bn_relu_pool_fwd(self.conv_out[li], self.stats[li], a.flat_master(L.p_g), a.flat_master(L.p_beta), N,
                                L.H, L.W, L.c_out, L.pool, out=self.act[li], saved=self.saved[li])
             x = self.act[li]
@@ -229,14 +244,14 @@ class VGGEngine:
             K.conv_wgrad(self.dconv[li], x_in, N, L.H, L.W, L.c_in_eff, L.c_out, L.taps, out=a.flat_grad(L.p_w),
                          cols_valid=cols, out_ld=cols, scratch=self.wgrad_scratch)
             if li > 0:
-                K.conv_fprop(self.dconv[li], self.w_d[li], None, N, L.H, L.W, L.c_out, L.c_in, 9,
-                             out=self.dact[li - 1])
+                K.conv_dgrad(self.dconv[li], self.w_f[li], N, L.H, L.W, L.c_in, L.c_out, out=self.dact[li - 1],
+                             scratch=self.fprop_scratch)
             if after_layer is not None:
                 after_layer(li)
 
     def sgd(self, lr: float, momentum: float, weight_decay: float, grad_scale: float = 1.0):
         a = self.arena
-        K.sgd_step(a.master, a.grad, a.momentum, lr, momentum, weight_decay, grad_scale)
+        K.sgd_step(a.master, a.grad, a.momentum, lr, momentum, weight_decay, grad_scale, shadow=self.shadow)
 
     def launches_per_train_step(self, splits_reduce: bool = True) -> int:
         """How many of OUR kernels one fwd+bwd enqueues (excluding sync/SGD/repack/input prep)."""
@@ -244,6 +259,10 @@ class VGGEngine:
         B = self.max_batch
         for li, L in enumerate(self.layers):
             n += 2                  # fprop, bn fwd
+            if K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps):
+                n += 1              # split-K finalize
+            if li > 0 and K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_out, L.c_in, 9):
+                n += 1
             n += 2                  # bn bwd (two passes)
             n += 1                  # wgrad
             if K.conv_wgrad_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps):
@@ -316,9 +335,9 @@ def engine_forward(model, x: torch.Tensor) -> torch.Tensor:
         if p.grad is None:  # a stock optimizer's zero_grad(set_to_none=True) detached it
             p.grad = ParamArena._view(eng.arena.grad, p, o)
     if torch.is_grad_enabled() and any(p.requires_grad for p in eng.arena.params):
-        eng.repack()  # parameters may have been updated by any optimizer since the last call
+        eng.repack(full=True)  # parameters may have been updated by any optimizer since the last call
         return _EngineFn.apply(x, model, *eng.arena.params)
-    eng.repack()
+    eng.repack(full=True)
     eng.load_input_f32(x.float())
     eng.forward(x.shape[0], with_loss=False)
     return eng.logits[:x.shape[0]].clone()

@@ -28,7 +28,10 @@ _SIGNATURES = {
     "ddpb_abi_version": [],
     "ddpb_sm_count": [],
     "ddpb_conv_fprop": [c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
-                        c_void],
+                        c_void, c_void],
+    "ddpb_conv_fprop_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int, c_int],
+    "ddpb_conv_force": [c_int, c_int, c_int],
+    "ddpb_conv_plan": [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void],
     "ddpb_conv_wgrad_splits": [c_int, c_int, c_int, c_int, c_int, c_int],
     "ddpb_conv_wgrad_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int],
     "ddpb_conv_wgrad": [c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
@@ -41,7 +44,8 @@ _SIGNATURES = {
     "ddpb_fc_ce_fwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_int,
                        c_int, c_int, c_void],
     "ddpb_fc_bwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_void],
-    "ddpb_sgd_step": [c_void, c_void, c_void, c_ll, c_float, c_float, c_float, c_float, c_void],
+    "ddpb_sgd_step": [c_void, c_void, c_void, c_void, c_ll, c_float, c_float, c_float, c_float, c_void],
+    "ddpb_conv_dgrad": [c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_void, c_void],
     "ddpb_pack_weights": [c_int, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void],
     "ddpb_first_layer_operand_f32": [c_void, c_void, c_int, c_int, c_int, c_void],
     "ddpb_first_layer_operand_u8": [c_void, c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_int, c_void],
@@ -49,6 +53,7 @@ _SIGNATURES = {
 _RESTYPES = {
     "ddpb_last_error": C.c_char_p,
     "ddpb_conv_wgrad_scratch_elems": c_ll,
+    "ddpb_conv_fprop_scratch_elems": c_ll,
 }
 # entry points added by later translation units; bound if present
 _OPTIONAL: dict[str, list] = {}

@@ -19,21 +19,68 @@ def _s(stream):
     return nat.stream_ptr(stream)
 
 
+def conv_force(pair: int = -1, block_n: int = -1, splits: int = -1) -> None:
+    """Tuning/testing hook: pin the conv launch planner's choice (-1 = automatic)."""
+    nat.load().ddpb_conv_force(pair, block_n, splits)
+
+
+def conv_plan(N, H, W, C_in, C_out, taps=9, block_n=0) -> tuple[int, int, int]:
+    """(cta_pair, block_n, splits) the planner picks for this fprop-shaped problem."""
+    out = (C.c_int * 3)()
+    nat.load().ddpb_conv_plan(N, H, W, C_in, C_out, taps, block_n, out)
+    return tuple(out)
+
+
+def conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps=9, block_n=0) -> int:
+    """fp32 elements of split-K scratch conv_fprop wants for this shape (0 = no split)."""
+    return int(nat.load().ddpb_conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps, block_n))
+
+
 def conv_fprop(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, N: int, H: int, W: int, C_in: int,
                C_out: int, taps: int = 9, *, out: torch.Tensor | None = None, stats: torch.Tensor | None = None,
-               block_n: int = 0, stream=None) -> torch.Tensor:
+               block_n: int = 0, scratch: torch.Tensor | None | bool = True, stream=None) -> torch.Tensor:
     """O1 (and O2 when fed dY and the rotated filters): y[P,C_out] = conv3x3(x) (+bias).
 
     ``stats`` (fp32 [2, C_out]) is accumulated with per-channel sum / sum of squares of y.
+    ``scratch``: fp32 buffer for split-K on small problems; True = allocate if the launcher
+    wants one, False/None = never split.
     """
     nat.require_cuda(x, w)
     assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
     assert x.numel() == N * H * W * C_in and w.numel() == C_out * taps * C_in
     if out is None:
         out = torch.empty(N * H * W, C_out, dtype=torch.bfloat16, device=x.device)
+    if scratch is True:
+        need = conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps, block_n)
+        scratch = torch.empty(need, dtype=torch.float32, device=x.device) if need else None
+    elif scratch is False:
+        scratch = None
+    elif scratch is not None:
+        need = conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps, block_n)
+        assert scratch.numel() >= need, "split-K scratch too small"
     rc = nat.load().ddpb_conv_fprop(nat.ptr(x), nat.ptr(w), nat.ptr(bias), nat.ptr(out), nat.ptr(stats), N, H, W,
-                                    C_in, C_out, taps, block_n, _s(stream))
+                                    C_in, C_out, taps, block_n, nat.ptr(scratch), _s(stream))
     nat.check(rc, "ddpb_conv_fprop")
+    return out
+
+
+def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, C_in: int, C_out: int, *,
+               out: torch.Tensor | None = None, block_n: int = 0, scratch: torch.Tensor | None | bool = True,
+               stream=None) -> torch.Tensor:
+    """O2: dx[P, C_in] from dy[P, C_out] and the SAME bf16 filter pack fprop uses ([C_out, 9*C_in])."""
+    nat.require_cuda(dy, w_fprop)
+    assert dy.dtype == torch.bfloat16 and w_fprop.dtype == torch.bfloat16
+    assert dy.numel() == N * H * W * C_out and w_fprop.numel() == C_out * 9 * C_in
+    if out is None:
+        out = torch.empty(N * H * W, C_in, dtype=torch.bfloat16, device=dy.device)
+    if scratch is True:
+        need = conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n)
+        scratch = torch.empty(need, dtype=torch.float32, device=dy.device) if need else None
+    elif scratch is False:
+        scratch = None
+    rc = nat.load().ddpb_conv_dgrad(nat.ptr(dy), nat.ptr(w_fprop), nat.ptr(out), N, H, W, C_in, C_out, block_n,
+                                    nat.ptr(scratch), _s(stream))
+    nat.check(rc, "ddpb_conv_dgrad")
     return out
 
 
@@ -142,12 +189,13 @@ def fc_bwd(x, w, dlogits, *, dw=None, db=None, dx=None, want_dx=True, stream=Non
     return dw, db, dx
 
 
-def sgd_step(p, g, m, lr, momentum, weight_decay, grad_scale=1.0, *, stream=None):
-    """O11+O12 over flat fp32 arenas, in place."""
+def sgd_step(p, g, m, lr, momentum, weight_decay, grad_scale=1.0, *, shadow=None, stream=None):
+    """O11+O12 over flat fp32 arenas, in place; ``shadow`` (bf16) receives the rounded parameters."""
     nat.require_cuda(p, g, m)
     assert p.dtype == g.dtype == m.dtype == torch.float32 and p.numel() == g.numel() == m.numel()
-    rc = nat.load().ddpb_sgd_step(nat.ptr(p), nat.ptr(g), nat.ptr(m), p.numel(), lr, momentum, weight_decay,
-                                  grad_scale, _s(stream))
+    assert shadow is None or (shadow.dtype == torch.bfloat16 and shadow.numel() == p.numel())
+    rc = nat.load().ddpb_sgd_step(nat.ptr(p), nat.ptr(g), nat.ptr(m), nat.ptr(shadow), p.numel(), lr, momentum,
+                                  weight_decay, grad_scale, _s(stream))
     nat.check(rc, "ddpb_sgd_step")
 
 

@@ -47,8 +47,7 @@ class SGD(torch.optim.Optimizer):
                 self._engine = eng
         if self._engine is not None:
             lr, mu, wd = self.hyper
-            self._engine.sgd(lr, mu, wd)
-            self._engine.repack()
+            self._engine.sgd(lr, mu, wd)   # also refreshes the bf16 shadow the conv kernels read
             return None
         if self._fallback is None:
             lr, mu, wd = self.hyper

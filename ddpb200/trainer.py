@@ -96,12 +96,12 @@ class Trainer:
         torch.cuda.synchronize(self.device)
         a.master.copy_(a.grad)
         a.grad.zero_()
-        self.engine.repack()
+        self.engine.repack(full=True)
         torch.cuda.synchronize(self.device)
 
     def _sgd_args(self):
         a = self.engine.arena
-        return (a.master, a.momentum, self.lr, self.momentum, self.weight_decay)
+        return (a.master, a.momentum, self.engine.shadow, self.lr, self.momentum, self.weight_decay)
 
     def _sync_range(self, off, n, slot_base, stream=None):
         sgd = self._sgd_args() if self.fuse_sgd else None
@@ -116,6 +116,7 @@ class Trainer:
         """Everything between 'inputs are on the device' and 'parameters are updated'."""
         eng, a = self.engine, self.engine.arena
         B = self.batch_size if B is None else B
+        eng.repack()   # first layer's padded filter pack; every other operand is the SGD-maintained shadow
         if kind == "u8":
             eng.load_input_u8(self.in_u8[:B], self.in_aug[:B] if with_aug else None)
         else:
@@ -157,7 +158,6 @@ class Trainer:
                 self._sync_range(0, a.numel, slot_base=0)
             if not self.fuse_sgd:
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
-        eng.repack()
 
     def _stage_inputs(self, data: torch.Tensor, target: torch.Tensor, aug):
         eng = self.engine

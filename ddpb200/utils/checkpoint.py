@@ -46,7 +46,7 @@ def load_checkpoint(path, module: torch.nn.Module, optimizer=None) -> dict:
             dst.copy_(sd[k])        # in place: keeps arena views intact
     eng = getattr(getattr(module, "module", module), "_engine", None)
     if eng is not None:
-        eng.repack()
+        eng.repack(full=True)
     if optimizer is not None and "optimizer" in blob:
         optimizer.load_state_dict(blob["optimizer"])
     return blob

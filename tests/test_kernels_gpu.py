@@ -89,6 +89,43 @@ def test_conv_dgrad_via_rotated_filters(shape):
     assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
 
 
+# CTA-pair (cta_group::2) kernel, every legal tile / split combination, fprop and dgrad
+PAIR_CASES = [((8, 8, 8, 128, 256), 128, 1), ((8, 8, 8, 128, 256), 256, 1), ((8, 8, 8, 256, 256), 256, 2),
+              ((3, 8, 8, 128, 128), 128, 1), ((4, 16, 16, 64, 128), 128, 1), ((32, 4, 4, 256, 512), 256, 3),
+              ((37, 2, 2, 512, 512), 128, 4), ((2, 32, 32, 64, 128), 128, 1)]
+
+
+@pytest.mark.parametrize("case", PAIR_CASES)
+def test_conv_cta_pair_fprop_and_dgrad(case):
+    (N, H, W, Ci, Co), bn, splits = case
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
+    b = torch.randn(Co, device=DEV)
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    try:
+        K.conv_force(1, bn, splits)
+        stats = torch.zeros(2, Co, device=DEV)
+        y = K.conv_fprop(x, w, b, N, H, W, Ci, Co, stats=stats)
+        dx = K.conv_dgrad(dy, w, N, H, W, Ci, Co) if Ci % bn == 0 else None
+        torch.cuda.synchronize()
+    finally:
+        K.conv_force(-1, -1, -1)
+    assert _rel_err(y, R.conv_fprop(x, w, b, N, H, W, Ci, Co)) < 1e-2
+    assert torch.allclose(stats, R.channel_stats(y), rtol=2e-3, atol=1e-2 * (N * H * W) ** 0.5)
+    if dx is not None:
+        assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES[1:])
+def test_conv_dgrad_from_fprop_pack(shape):
+    """dgrad reads the very same [C_out][9*C_in] pack as fprop (MN-major B operand, taps reversed)."""
+    N, H, W, Ci, Co = shape
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Co) ** 0.5).bfloat16()
+    dx = K.conv_dgrad(dy, w, N, H, W, Ci, Co)
+    assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
+
+
 @pytest.mark.parametrize("shape", CONV_SHAPES + [(64, 32, 32, 64, 128)])
 def test_conv_wgrad(shape):
     N, H, W, Ci, Co = shape
@@ -167,12 +204,14 @@ def test_sgd_matches_torch_optim():
     ref_p = torch.nn.Parameter(p0.clone())
     opt = torch.optim.SGD([ref_p], lr=0.1, momentum=0.9, weight_decay=1e-4)
     m = torch.zeros_like(p)
+    shadow = torch.empty(n, dtype=torch.bfloat16, device=DEV)
     for _ in range(3):
         g = torch.randn(n, device=DEV)
         ref_p.grad = g.clone()
         opt.step()
-        K.sgd_step(p, g, m, 0.1, 0.9, 1e-4)
+        K.sgd_step(p, g, m, 0.1, 0.9, 1e-4, shadow=shadow)
     assert torch.allclose(p, ref_p.data, rtol=1e-5, atol=1e-6)
+    assert torch.equal(shadow, p.bfloat16())
 
 
 def test_pack_weights_layouts():
