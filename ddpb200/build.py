@@ -53,11 +53,19 @@ def _compile_one(nvcc: str, src: Path, obj: Path, extra: list[str]) -> str:
     return res.stderr
 
 
-def build(force: bool = False, verbose: bool = False, ptxas_v: bool = False) -> Path:
+def build(force: bool = False, verbose: bool = False, ptxas_v: bool = False, defines: list[str] | None = None,
+          out: Path | None = None) -> Path:
+    """``defines``/``out`` build an experiment variant (e.g. a different pipeline depth) into its
+    own .so; point DDPB_LIB at it to use it."""
+    global OBJ_DIR, LIB_PATH
     nvcc = find_nvcc()
+    if out is not None:
+        LIB_PATH = Path(out).resolve()
+        OBJ_DIR = LIB_PATH.parent / ("obj_" + LIB_PATH.stem)
+        force = True
     OBJ_DIR.mkdir(parents=True, exist_ok=True)
     hdr_m = _headers_mtime()
-    extra = ["-Xptxas", "-v"] if ptxas_v else []
+    extra = (["-Xptxas", "-v"] if ptxas_v else []) + [f"-D{d}" for d in (defines or [])]
     todo, objs = [], []
     for src in sources():
         obj = OBJ_DIR / (src.stem + ".o")
@@ -92,8 +100,10 @@ def main() -> None:
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--ptxas-v", action="store_true")
+    ap.add_argument("-D", dest="defines", action="append", default=[], help="extra preprocessor define")
+    ap.add_argument("--out", default=None, help="write the library here instead of the default path")
     a = ap.parse_args()
-    print(build(force=a.force, verbose=a.verbose, ptxas_v=a.ptxas_v))
+    print(build(force=a.force, verbose=a.verbose, ptxas_v=a.ptxas_v, defines=a.defines, out=a.out))
 
 
 if __name__ == "__main__":

@@ -29,7 +29,11 @@ constexpr int kConvThreads = 192;
 
 template <int BLOCK_N>
 struct FpropCfg {
+#ifdef DDPB_FPROP_STAGES
+  static constexpr int kStages = DDPB_FPROP_STAGES;
+#else
   static constexpr int kStages = (BLOCK_N >= 256) ? 4 : 3;
+#endif
   static constexpr int kABytes = kBlockM * kBlockK * 2;   // 16 KB
   static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -47,7 +51,15 @@ struct FpropParams {
   int taps;              // 9 (3x3) or 1 (pre-gathered input)
   int bh, bn, hblocks;   // TMA box geometry: box = (64, W, bh, bn); hblocks = H / bh
   float* partial;        // split-K: fp32 [gridDim.z][P][C_out] partial sums (null when gridDim.z == 1)
+  unsigned long long* dbg;  // optional per-CTA timestamps {start, after set-up, mainloop done, epilogue done}
 };
+
+__device__ __forceinline__ void dbg_stamp(const FpropParams& p, int slot) {
+  if (p.dbg != nullptr) {
+    const long long cta = blockIdx.x + gridDim.x * (blockIdx.y + static_cast<long long>(gridDim.y) * blockIdx.z);
+    p.dbg[cta * 4 + slot] = global_timer_ns();
+  }
+}
 
 // Epilogue shared by the 1-CTA and CTA-pair kernels: this warp's 32 accumulator rows ->
 // (+bias, bf16, per-channel statistics) -> global, or raw fp32 partials under split-K.
@@ -173,10 +185,12 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     tmem_alloc(tmem_ptr_smem, BLOCK_N);
     tmem_relinquish();
   }
+  if (threadIdx.x == 0) dbg_stamp(p, 0);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) dbg_stamp(p, 1);
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -196,8 +210,22 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* a_dst = tiles + stage * Cfg::kStageBytes;
         uint8_t* b_dst = a_dst + Cfg::kABytes;
+#if defined(DDPB_DBG_SKIP_A) || defined(DDPB_DBG_SKIP_B)
+        // timing experiments only (results are wrong): after the ring is primed, skip one operand
+        const bool primed = (k - k_begin) >= Cfg::kStages;
+#ifdef DDPB_DBG_SKIP_A
+        const bool do_a = !primed, do_b = true;
+#else
+        const bool do_a = true, do_b = !primed;
+#endif
+        mbar_expect_tx(&full_bar[stage], (do_a ? Cfg::kABytes : 0) + (do_b ? Cfg::kBBytes : 0));
+        if (do_a) tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
+        if (!do_b) {
+        } else
+#else
         mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
         tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
+#endif
         if (!kDgrad) {
           tma_load_2d(b_dst, &tmap_w, &full_bar[stage], tap * p.C_in + cc * kBlockK, n_tile * BLOCK_N);
         } else {
@@ -239,6 +267,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
         }
       }
       umma_commit(tmem_full_bar);  // accumulator complete
+      if (p.dbg != nullptr) {
+        mbar_wait(tmem_full_bar, 0);
+        dbg_stamp(p, 2);
+      }
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
@@ -247,6 +279,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) dbg_stamp(p, 3);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, BLOCK_N);
@@ -316,10 +349,12 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
     tmem_alloc_pair(tmem_ptr_smem, BLOCK_N);
     tmem_relinquish_pair();
   }
+  if (threadIdx.x == 0) dbg_stamp(p, 0);
   tc_fence_before();
   cluster_sync_all();   // both CTAs' barriers exist before anything is signalled across the pair
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) dbg_stamp(p, 1);
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
@@ -381,6 +416,10 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
         }
       }
       umma_commit_pair(tmem_full_bar, 0x3);         // accumulators ready in BOTH CTAs
+      if (p.dbg != nullptr) {
+        mbar_wait(tmem_full_bar, 0);
+        dbg_stamp(p, 2);
+      }
     }
   } else {
     conv_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, s_stats, warp, m_tile, n_tile);
@@ -388,6 +427,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
 
   tc_fence_before();
   cluster_sync_all();   // nobody frees TMEM or exits while the peer may still signal / read
+  if (threadIdx.x == 0) dbg_stamp(p, 3);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc_pair(tmem_base, BLOCK_N);
@@ -458,6 +498,8 @@ splitk_finalize_kernel(const float* __restrict__ partial, const float* __restric
   }
 }
 
+#include "conv_persist.inl"
+
 // ------------------------------------------------------------------------------------------
 // Launch planning.  Measured on B200 (profiles/): these kernels are bound by operand ingest
 // per SM (~45 B/clk) unless the tile is large, and by fixed per-CTA cost when the reduction is
@@ -465,26 +507,43 @@ splitk_finalize_kernel(const float* __restrict__ partial, const float* __restric
 // model and takes the cheapest.
 // ------------------------------------------------------------------------------------------
 struct ConvPlan {
-  int pair;      // 1: cta_group::2 kernel
+  int pair;      // kernel: 0 = one tile per CTA, 1 = CTA pair (cta_group::2), 2 = persistent
   int block_n;
   int splits;
 };
 
 static int g_force_pair = -1, g_force_block_n = -1, g_force_splits = -1;
+static unsigned long long* g_dbg = nullptr;
 
-static double plan_cost(int pair, int bn, int splits, long long P, int C_out, int total_k) {
-  const double kIngest = 45.0;        // bytes / clk / SM
-  const double kFixed = 3500.0;       // prologue + epilogue + launch ramp per CTA, cycles
+// Cycle estimates calibrated on B200 (profiles/): a TMA->MMA ring round trip of ~2200 cycles,
+// 2*BLOCK_N tensor cycles per 64-deep k-step, ~700 cycles of epilogue per 32 columns per warp.
+static double plan_cost(int mode, int bn, int splits, long long P, int C_out, int total_k) {
+  const double kRtt = 2200.0;
   int m_tiles = static_cast<int>((P + kBlockM - 1) / kBlockM);
-  if (pair) m_tiles = (m_tiles + 1) / 2 * 2;
-  const int ctas = m_tiles * (C_out / bn) * splits;
+  if (mode == 1) m_tiles = (m_tiles + 1) / 2 * 2;
+  const int items = m_tiles * (C_out / bn) * splits;
   const int sms = sm_count();
-  const int per_sm = (ctas + sms - 1) / sms;
-  const double stage_bytes = 16384.0 + (pair ? bn / 2 : bn) * 128.0;
-  const double mma = 2.0 * bn;        // cycles per 64-deep k-step at full tensor rate
   const double k_iters = static_cast<double>(total_k) / splits;
-  double t = per_sm * (k_iters * (stage_bytes / kIngest > mma ? stage_bytes / kIngest : mma) + kFixed);
-  if (splits > 1) t += 4000.0 + 2.0 * splits * static_cast<double>(P) * C_out * 4.0 / 5000.0;
+  const double mma = 2.0 * bn;
+  double t;
+  if (mode == 2) {
+    const int stages = (192 * 1024) / (16384 + bn * 128);
+    const double iter = mma > kRtt / stages ? mma : kRtt / stages;
+    const double mainloop = k_iters * iter;
+    const double epi = (bn / 64.0) * 1400.0 * (splits > 1 ? 0.5 : 1.0);
+    const int per_sm = (items + sms - 1) / sms;
+    t = per_sm * (mainloop > epi ? mainloop : epi) + (mainloop > epi ? epi : mainloop) + 3000.0;
+  } else {
+    const int stage_bytes = 16384 + (mode == 1 ? bn / 2 : bn) * 128;
+    const int stages = mode == 1 ? (bn >= 256 ? 5 : 6) : (bn >= 256 ? 4 : 3);
+    const int resident = (mode == 0 && stages * stage_bytes <= 100 * 1024) ? 2 : 1;
+    const double iter_one = mma > kRtt / stages ? mma : kRtt / stages;
+    const double epi = (bn / 32.0) * 1400.0;
+    const double per_cta = k_iters * iter_one + epi + 1500.0;
+    const int rounds = (items + sms * resident - 1) / (sms * resident);
+    t = rounds * per_cta * (resident == 2 ? 1.15 : 1.0);
+  }
+  if (splits > 1) t += 5000.0 + 2.0 * splits * static_cast<double>(P) * C_out * 4.0 / 4000.0;
   return t;
 }
 
@@ -492,22 +551,21 @@ static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint,
   ConvPlan best{0, (C_out % 128 == 0) ? 128 : 64, 1};
   double best_t = 1e30;
   const int bns[3] = {64, 128, 256};
-  for (int pair = 0; pair <= 1; ++pair) {
-    if (g_force_pair >= 0 && pair != g_force_pair) continue;
+  for (int mode = 0; mode <= 2; ++mode) {
+    if (g_force_pair >= 0 && mode != g_force_pair) continue;
     for (int bi = 0; bi < 3; ++bi) {
       const int bn = bns[bi];
       if (C_out % bn != 0) continue;
-      if (pair && bn < 128) continue;
+      if (mode == 1 && bn < 128) continue;
       if (block_n_hint != 0 && bn != block_n_hint) continue;
       if (g_force_block_n >= 0 && bn != g_force_block_n) continue;
-      if (block_n_hint == 0 && g_force_block_n < 0 && bn == 64 && C_out % 128 == 0) continue;
       for (int splits = 1; splits <= 8; ++splits) {
         if (g_force_splits >= 0 && splits != g_force_splits) continue;
         if (splits > 1 && (!allow_split || total_k / splits < 4 || C_out / 8 > 256 || 256 % (C_out / 8) != 0)) continue;
-        const double t = plan_cost(pair, bn, splits, P, C_out, total_k);
+        const double t = plan_cost(mode, bn, splits, P, C_out, total_k);
         if (t < best_t) {
           best_t = t;
-          best = ConvPlan{pair, bn, splits};
+          best = ConvPlan{mode, bn, splits};
         }
       }
     }
@@ -568,6 +626,10 @@ extern "C" void ddpb_conv_force(int pair, int block_n, int splits) {
   g_force_splits = splits;
 }
 
+// Profiling hook: device buffer of 4 x (number of CTAs) uint64 that every conv CTA stamps with
+// %globaltimer at start / after set-up / when its accumulator is complete / at exit (null = off).
+extern "C" void ddpb_conv_debug_timing(unsigned long long* buf) { g_dbg = buf; }
+
 // What the planner picks for this shape: out3 = {pair, block_n, splits}.
 extern "C" void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3) {
   const ConvPlan pl = plan_conv(static_cast<long long>(N) * H * W, C_out, taps * (C_in / 64), block_n, true);
@@ -603,7 +665,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   const long long P = static_cast<long long>(N) * H * W;
   const ConvPlan pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, scratch != nullptr);
   block_n = pl.block_n;
-  const int b_rows = pl.pair ? block_n / 2 : block_n;   // filter rows one CTA loads per k-step
+  const int b_rows = pl.pair == 1 ? block_n / 2 : block_n;   // filter rows one CTA loads per k-step
 
   CUtensorMap tx, tw;
   {
@@ -641,6 +703,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   p.bh = bh;
   p.bn = bn;
   p.hblocks = hblocks;
+  p.dbg = g_dbg;
   const int m_tiles = (p.P + kBlockM - 1) / kBlockM;
   const int splits = pl.splits;
   p.partial = splits > 1 ? scratch : nullptr;
@@ -648,19 +711,23 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
 #define DDPB_CONV_DISPATCH(FN)                                                     \
   if (!dgrad) {                                                                    \
     switch (block_n) {                                                             \
-      case 64: rc = launch_fprop<64, false>(tx, tw, p, m_tiles, splits, stream); break;  \
+      case 64: rc = (pl.pair == 2 ? launch_persist<64, false>(tx, tw, p, m_tiles, splits, stream)          \
+                                    : launch_fprop<64, false>(tx, tw, p, m_tiles, splits, stream)); break; \
       case 128: rc = FN<128, false>(tx, tw, p, m_tiles, splits, stream); break;    \
       default: rc = FN<256, false>(tx, tw, p, m_tiles, splits, stream); break;     \
     }                                                                              \
   } else {                                                                         \
     switch (block_n) {                                                             \
-      case 64: rc = launch_fprop<64, true>(tx, tw, p, m_tiles, splits, stream); break;   \
+      case 64: rc = (pl.pair == 2 ? launch_persist<64, true>(tx, tw, p, m_tiles, splits, stream)           \
+                                    : launch_fprop<64, true>(tx, tw, p, m_tiles, splits, stream)); break;  \
       case 128: rc = FN<128, true>(tx, tw, p, m_tiles, splits, stream); break;     \
       default: rc = FN<256, true>(tx, tw, p, m_tiles, splits, stream); break;      \
     }                                                                              \
   }
-  if (pl.pair) {
+  if (pl.pair == 1) {
     DDPB_CONV_DISPATCH(launch_pair)
+  } else if (pl.pair == 2) {
+    DDPB_CONV_DISPATCH(launch_persist)
   } else {
     DDPB_CONV_DISPATCH(launch_fprop)
   }

@@ -1,0 +1,297 @@
+// Persistent convolution kernel (included by conv_fprop.cu).
+//
+// Measured on B200 (profiles/r1_call10_conv_timeline.txt): in the one-tile-per-CTA kernel a
+// 128x128 tile spends 13.7 us in its main loop and 7.2 us in its epilogue, and a single CTA's
+// TMA -> MMA ring is latency bound (~1.1 us round trip, 3 stages).  This kernel fixes both:
+//   * one CTA per SM loops over tiles, so barrier / TMEM set-up happens once;
+//   * the whole shared memory is one deep operand ring (~192 KB in flight per SM);
+//   * two TMEM accumulators: while the eight epilogue warps drain tile i, the producer and
+//     the MMA warp already run tile i+1;
+//   * the epilogue reads the bias from shared memory, not from global.
+// Warp roles (320 threads): 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..9 = epilogue;
+// warps w and w+4 share a TMEM lane quarter and split the tile's columns between them.
+
+constexpr int kPersistThreads = 320;
+constexpr int kRingBytes = 192 * 1024;
+
+template <int BLOCK_N>
+struct PersistCfg {
+  static constexpr int kABytes = kBlockM * kBlockK * 2;
+  static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+#ifdef DDPB_PERSIST_STAGES
+  static constexpr int kStages = DDPB_PERSIST_STAGES;
+#else
+  static constexpr int kStages = kRingBytes / kStageBytes;     // 8 / 6 / 4 for BLOCK_N = 64 / 128 / 256
+#endif
+  static constexpr int kStatsBytes = 4 * 2 * BLOCK_N * 4;      // [quarter][sum, sumsq][column]
+  static constexpr int kBiasBytes = 8 * (BLOCK_N / 2) * 4;     // warp-private copies of the bias slice
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kStatsBytes + kBiasBytes + 512;
+  static constexpr int kTmemCols = 2 * BLOCK_N;                // two accumulators
+};
+
+struct PersistItem {
+  int m_tile, n_tile, split;
+};
+
+__device__ __forceinline__ PersistItem persist_item(int item, int m_tiles, int n_tiles) {
+  PersistItem it;
+  it.m_tile = item % m_tiles;
+  const int r = item / m_tiles;
+  it.n_tile = r % n_tiles;
+  it.split = r / n_tiles;
+  return it;
+}
+
+template <int BLOCK_N, bool kDgrad>
+__global__ void __launch_bounds__(kPersistThreads, 1)
+conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                    const FpropParams p, int m_tiles, int n_tiles, int splits) {
+  using Cfg = PersistCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tiles = smem;
+  float* s_stats = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  float* s_bias = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes);
+  uint64_t* bars =
+      reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes + Cfg::kBiasBytes);
+  uint64_t* full_bar = bars;                         // [kStages]
+  uint64_t* empty_bar = bars + Cfg::kStages;         // [kStages]
+  uint64_t* tmem_full = bars + 2 * Cfg::kStages;     // [2]
+  uint64_t* tmem_empty = tmem_full + 2;              // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int n_items = m_tiles * n_tiles * splits;
+  const int cchunks = p.C_in / kBlockK;
+  const int total_k = p.taps * cchunks;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_w);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      for (int i = 0; i < Cfg::kStages; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&tmem_full[i], 1);
+        mbar_init(&tmem_empty[i], 8);   // one arrival per epilogue warp
+      }
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_ptr_smem, Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  if (threadIdx.x == 0) dbg_stamp(p, 0);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) dbg_stamp(p, 1);
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const PersistItem it = persist_item(item, m_tiles, n_tiles);
+        const int n_img = (it.m_tile / p.hblocks) * p.bn;
+        const int h0 = (it.m_tile % p.hblocks) * p.bh;
+        const int k_begin = static_cast<int>(static_cast<long long>(total_k) * it.split / splits);
+        const int k_end = static_cast<int>(static_cast<long long>(total_k) * (it.split + 1) / splits);
+        for (int k = k_begin; k < k_end; ++k) {
+          const int tap = k / cchunks;
+          const int cc = k - tap * cchunks;
+          int dr = 0, ds = 0;
+          if (p.taps == 9) {
+            dr = tap / 3 - 1;
+            ds = tap % 3 - 1;
+          }
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = tiles + stage * Cfg::kStageBytes;
+          uint8_t* b_dst = a_dst + Cfg::kABytes;
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
+          if (!kDgrad) {
+            tma_load_2d(b_dst, &tmap_w, &full_bar[stage], tap * p.C_in + cc * kBlockK, it.n_tile * BLOCK_N);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BLOCK_N / 64; ++j)
+              tma_load_2d(b_dst + j * 8192, &tmap_w, &full_bar[stage],
+                          (p.taps - 1 - tap) * p.C_out + it.n_tile * BLOCK_N + j * 64, cc * kBlockK);
+          }
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, 0, kDgrad ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int local = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++local) {
+        const PersistItem it = persist_item(item, m_tiles, n_tiles);
+        const int k_begin = static_cast<int>(static_cast<long long>(total_k) * it.split / splits);
+        const int k_end = static_cast<int>(static_cast<long long>(total_k) * (it.split + 1) / splits);
+        const int buf = local & 1;
+        const uint32_t use = static_cast<uint32_t>(local >> 1);
+        mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);   // epilogue drained this accumulator (free at first use)
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * BLOCK_N;
+        for (int k = k_begin; k < k_end; ++k) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(tiles + stage * Cfg::kStageBytes);
+          const uint32_t b_addr = a_addr + Cfg::kABytes;
+#pragma unroll
+          for (int kk = 0; kk < kBlockK / kUmmaK; ++kk) {
+            const uint64_t adesc = make_smem_desc_sw128(a_addr + kk * kUmmaK * 2, 16, 1024);
+            const uint64_t bdesc = kDgrad ? make_smem_desc_sw128(b_addr + kk * kUmmaK * 128, 8192, 1024)
+                                          : make_smem_desc_sw128(b_addr + kk * kUmmaK * 2, 16, 1024);
+            umma_f16(d_tmem, adesc, bdesc, idesc, (k > k_begin) || (kk > 0));
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full[buf]);
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..9) =====================
+    const int ew = warp - 2;                 // 0..7
+    const int q = warp & 3;                  // TMEM lane quarter
+    const int half = ew >> 2;                // which half of the tile's columns
+    constexpr int kChunks = BLOCK_N / 32;
+    constexpr int kMyChunks = kChunks / 2;   // >= 1 (BLOCK_N >= 64)
+    const int chunk0 = half * kMyChunks;
+    float* my_bias = s_bias + ew * (BLOCK_N / 2);
+    const int row = q * 32 + lane_id();
+    int local = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++local) {
+      const PersistItem it = persist_item(item, m_tiles, n_tiles);
+      const int buf = local & 1;
+      const uint32_t use = static_cast<uint32_t>(local >> 1);
+      const long long pix = static_cast<long long>(it.m_tile) * kBlockM + row;
+      const bool valid = pix < p.P;
+      const bool direct = (p.partial == nullptr);
+      // stage this warp's slice of the bias while the accumulator is still being produced
+      if (direct && p.bias != nullptr) {
+#pragma unroll
+        for (int c = 0; c < kMyChunks; ++c)
+          my_bias[c * 32 + lane_id()] = __ldg(p.bias + it.n_tile * BLOCK_N + (chunk0 + c) * 32 + lane_id());
+        __syncwarp();
+      }
+      mbar_wait(&tmem_full[buf], use & 1);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + buf * BLOCK_N + (static_cast<uint32_t>(q * 32) << 16);
+      if (!direct) {
+        float* prow = p.partial + (static_cast<long long>(it.split) * p.P + pix) * p.C_out + it.n_tile * BLOCK_N;
+#pragma unroll 1
+        for (int c = 0; c < kMyChunks; ++c) {
+          uint32_t raw[32];
+          tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
+          tmem_ld_wait();
+          if (valid) {
+            uint4* dst = reinterpret_cast<uint4*>(prow + (chunk0 + c) * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              dst[j] = make_uint4(raw[4 * j], raw[4 * j + 1], raw[4 * j + 2], raw[4 * j + 3]);
+          }
+        }
+      } else {
+        __nv_bfloat16* out_row = p.out + pix * p.C_out + it.n_tile * BLOCK_N;
+#pragma unroll 1
+        for (int c = 0; c < kMyChunks; ++c) {
+          uint32_t raw[32];
+          tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
+          tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float x = __uint_as_float(raw[j]);
+            if (p.bias != nullptr) x += my_bias[c * 32 + j];   // same address in every lane: broadcast
+            v[j] = valid ? bf16_round(x) : 0.f;
+          }
+          if (valid) {
+            uint4* dst = reinterpret_cast<uint4*>(out_row + (chunk0 + c) * 32);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 o;
+              o.x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
+              o.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+              o.z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]);
+              o.w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+              dst[j] = o;
+            }
+          }
+          if (p.stats != nullptr) {
+            float sq[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) sq[j] = v[j] * v[j];
+            const float s1 = warp_transpose_reduce(v);
+            const float s2 = warp_transpose_reduce(sq);
+            s_stats[(q * 2 + 0) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] = s1;
+            s_stats[(q * 2 + 1) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] = s2;
+          }
+        }
+      }
+      // accumulator fully read: hand it back to the MMA warp before the (slower) statistics flush
+      tc_fence_before();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(&tmem_empty[buf]);
+      if (direct && p.stats != nullptr) {
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps
+        const int t = threadIdx.x - 64;
+        for (int c = t; c < 2 * BLOCK_N; c += 256) {
+          const int which = c / BLOCK_N, col = c - which * BLOCK_N;
+          float acc = 0.f;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) acc += s_stats[(w * 2 + which) * BLOCK_N + col];
+          atomicAdd(p.stats + which * p.C_out + it.n_tile * BLOCK_N + col, acc);
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // s_stats may be overwritten by the next tile
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x == 0) dbg_stamp(p, 3);
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+template <int BLOCK_N, bool kDgrad>
+static int launch_persist(const CUtensorMap& tx, const CUtensorMap& tw, const FpropParams& p, int m_tiles,
+                          int splits, cudaStream_t stream) {
+  using Cfg = PersistCfg<BLOCK_N>;
+  static bool configured = false;
+  if (!configured) {
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_persist_kernel<BLOCK_N, kDgrad>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  const int n_tiles = p.C_out / BLOCK_N;
+  const int items = m_tiles * n_tiles * splits;
+  int grid = sm_count();
+  if (grid > items) grid = items;
+  conv_persist_kernel<BLOCK_N, kDgrad><<<grid, kPersistThreads, Cfg::kSmemBytes, stream>>>(tx, tw, p, m_tiles,
+                                                                                           n_tiles, splits);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -16,7 +16,7 @@ from pathlib import Path
 import torch
 
 _LIB = None
-_LIB_PATH = Path(__file__).resolve().parent.parent / "_lib" / "libddpb200.so"
+_LIB_PATH = Path(os.environ.get("DDPB_LIB") or (Path(__file__).resolve().parent.parent / "_lib" / "libddpb200.so"))
 
 c_void = C.c_void_p
 c_int = C.c_int
@@ -31,6 +31,7 @@ _SIGNATURES = {
                         c_void, c_void],
     "ddpb_conv_fprop_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int, c_int],
     "ddpb_conv_force": [c_int, c_int, c_int],
+    "ddpb_conv_debug_timing": [c_void],
     "ddpb_conv_plan": [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void],
     "ddpb_conv_wgrad_splits": [c_int, c_int, c_int, c_int, c_int, c_int],
     "ddpb_conv_wgrad_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int],

@@ -95,15 +95,20 @@ PAIR_CASES = [((8, 8, 8, 128, 256), 128, 1), ((8, 8, 8, 128, 256), 256, 1), ((8,
               ((37, 2, 2, 512, 512), 128, 4), ((2, 32, 32, 64, 128), 128, 1)]
 
 
-@pytest.mark.parametrize("case", PAIR_CASES)
-def test_conv_cta_pair_fprop_and_dgrad(case):
-    (N, H, W, Ci, Co), bn, splits = case
+PERSIST_CASES = PAIR_CASES + [((4, 32, 32, 64, 64), 64, 1), ((64, 8, 8, 128, 128), 128, 1),
+                              ((300, 4, 4, 256, 256), 128, 2), ((8, 32, 32, 64, 128), 64, 1)]
+
+
+@pytest.mark.parametrize("case", [(1, c) for c in PAIR_CASES] + [(2, c) for c in PERSIST_CASES])
+def test_conv_kernel_variants_fprop_and_dgrad(case):
+    """mode 1 = CTA pair (cta_group::2), mode 2 = persistent kernel; both against the oracle."""
+    mode, ((N, H, W, Ci, Co), bn, splits) = case
     x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
     w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
     b = torch.randn(Co, device=DEV)
     dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
     try:
-        K.conv_force(1, bn, splits)
+        K.conv_force(mode, bn, splits)
         stats = torch.zeros(2, Co, device=DEV)
         y = K.conv_fprop(x, w, b, N, H, W, Ci, Co, stats=stats)
         dx = K.conv_dgrad(dy, w, N, H, W, Ci, Co) if Ci % bn == 0 else None
