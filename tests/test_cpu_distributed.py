@@ -1,0 +1,78 @@
+"""Multi-process CPU tests (gloo, 127.0.0.1): the three sync strategies against their
+definitions and against each other, plus replica consistency."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+WORKER = r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, os.environ["DDPB_ROOT"])
+import ddpb200
+mode = sys.argv[1]
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo")
+torch.set_num_threads(2)
+torch.manual_seed(89395)
+model = ddpb200.VGG11()
+tr = ddpb200.Trainer(model, mode=mode, batch_size=4, rank=rank, world_size=world, lr=0.05)
+g = torch.Generator().manual_seed(10 + rank)
+img = torch.randint(0, 256, (4, 32, 32, 3), dtype=torch.uint8, generator=g)
+lab = torch.randint(0, 10, (4,), generator=g)
+# gradient after sync == mean over ranks of the local gradients
+from ddpb200.ops.reference import augment_normalize_u8
+ref = ddpb200.VGG11(); ref.load_state_dict(model.state_dict())
+loss = torch.nn.functional.cross_entropy(ref(augment_normalize_u8(img, None)), lab); loss.backward()
+local = torch.cat([p.grad.reshape(-1) for p in ref.parameters()])
+gathered = [torch.empty_like(local) for _ in range(world)]
+dist.all_gather(gathered, local)
+expect = torch.stack(gathered).mean(0)
+p_before = torch.cat([p.detach().reshape(-1).clone() for p in model.parameters()])
+tr.step(img, lab)
+got = torch.cat([p.grad.reshape(-1) for p in model.parameters()])
+assert torch.allclose(got, expect, atol=1e-6), (mode, (got - expect).abs().max())
+# SGD first step: p1 = p0 - lr * (g + wd * p0)
+p_after = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+assert torch.allclose(p_after, p_before - 0.05 * (expect + 1e-4 * p_before), atol=1e-6)
+for _ in range(2):
+    tr.step(img, lab)
+flat = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+allp = [torch.empty_like(flat) for _ in range(world)]
+dist.all_gather(allp, flat)
+assert all(torch.equal(allp[0], q) for q in allp), "replicas diverged"
+if rank == 0:
+    torch.save(flat, os.environ["DDPB_OUT"] + f"/{mode}.pt")
+    print("OK", mode)
+dist.destroy_process_group()
+'''
+
+
+def _run(mode, world, tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    env = dict(os.environ, DDPB_ROOT=str(ROOT), DDPB_OUT=str(tmp_path), OMP_NUM_THREADS="2")
+    port = 29800 + (os.getpid() + hash(mode)) % 150
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), mode]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-3000:]
+    assert "OK " + mode in res.stdout
+
+
+@pytest.mark.parametrize("mode", ["gather_scatter", "allreduce", "ddp"])
+def test_sync_mode_matches_mean_of_local_gradients(mode, tmp_path):
+    _run(mode, 2, tmp_path)
+
+
+def test_three_modes_agree_with_each_other(tmp_path):
+    import torch
+
+    for mode in ("gather_scatter", "allreduce", "ddp"):
+        _run(mode, 2, tmp_path)
+    a, b, c = (torch.load(tmp_path / f"{m}.pt") for m in ("gather_scatter", "allreduce", "ddp"))
+    # different summation orders: equal to rounding, not bitwise
+    assert torch.allclose(a, b, atol=1e-5) and torch.allclose(b, c, atol=1e-5)

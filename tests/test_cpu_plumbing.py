@@ -1,0 +1,155 @@
+"""CPU-only tests of everything above the kernels: model / state_dict parity, CLI, data
+sharding, bucket planning, printed line formats (SURVEY.md §4 "Invariants" and "CLI")."""
+import io
+import math
+import re
+from contextlib import redirect_stdout
+
+import pytest
+import torch
+
+import ddpb200
+from ddpb200 import cli
+from ddpb200.data import BatchLoader, ShardSampler, create_data_loaders, synthetic_cifar10
+from ddpb200.parallel import sync as S
+
+# state_dict keys in model.parameters() order
+EXPECTED_KEYS = [f"layers.{i}.{n}" for i in (0, 1, 4, 5, 8, 9, 11, 12, 15, 16, 18, 19, 22, 23, 25, 26)
+                 for n in ("weight", "bias")] + ["fc1.weight", "fc1.bias"]
+
+
+def test_state_dict_layout_matches_reference():
+    m = ddpb200.VGG11()
+    sd = m.state_dict()
+    assert list(sd.keys()) == EXPECTED_KEYS
+    assert sum(v.numel() for v in sd.values()) == 9_231_114
+    assert sd["layers.0.weight"].shape == (64, 3, 3, 3) and sd["fc1.weight"].shape == (10, 512)
+    assert len(list(m.buffers())) == 0          # track_running_stats=False: no buffers
+    assert [b.pool for b in m.conv_blocks()] == [True, True, False, True, False, True, False, True]
+
+
+def test_same_seed_gives_reference_initialisation():
+    """Same construction order as model.py => same RNG consumption => same weights as a stock build."""
+    import torch.nn as nn
+
+    torch.manual_seed(89395)
+    mine = ddpb200.VGG11()
+    torch.manual_seed(89395)
+    layers, cin = [], 3
+    for c in [64, "M", 128, "M", 256, 256, "M", 512, 512, "M", 512, 512, "M"]:
+        if c == "M":
+            layers.append(nn.MaxPool2d(2, 2))
+        else:
+            layers += [nn.Conv2d(cin, c, 3, 1, 1, bias=True), nn.BatchNorm2d(c, track_running_stats=False),
+                       nn.ReLU(inplace=True)]
+            cin = c
+    stock_layers = nn.Sequential(*layers)
+    stock_fc = nn.Linear(512, 10)
+    for (k, v), w in zip(mine.state_dict().items(), list(stock_layers.state_dict().values()) + list(stock_fc.state_dict().values())):
+        assert torch.equal(v, w), k
+
+
+def test_other_vgg_depths_build():
+    for f, n in ((ddpb200.VGG13, 10), (ddpb200.VGG16, 13), (ddpb200.VGG19, 16)):
+        m = f()
+        assert len(m.conv_blocks()) == n
+        assert m(torch.randn(2, 3, 32, 32)).shape == (2, 10)
+
+
+def test_cli_flags_and_lazy_rank(monkeypatch):
+    assert cli.parse_arguments(["--num-nodes", "4", "--rank", "2"]) == ("10.10.1.1", "4000", 2, 4)
+    ip, port, rank, size = cli.parse_arguments(["--master-ip", "127.0.0.1", "--master-port", "29500", "--num-nodes",
+                                                "2", "--rank", "0"])
+    assert (ip, port, rank, size) == ("127.0.0.1", "29500", 0, 2) and isinstance(port, str)
+
+    class U:
+        nodename = "node3"
+
+    monkeypatch.setattr(cli.os, "uname", lambda: U)
+    assert cli.get_rank() == 3
+    assert cli.parse_arguments(["--num-nodes", "4"])[2] == 3
+    U.nodename = "vm"                                  # the reference dies here even with --rank (Q2)
+    assert cli.parse_arguments(["--num-nodes", "4", "--rank", "1"])[2] == 1
+    with pytest.raises(SystemExit):
+        cli.parse_arguments(["--num-nodes", "4"])
+
+
+def test_shard_sampler_matches_distributed_sampler():
+    from torch.utils.data.distributed import DistributedSampler
+
+    for n, w in ((50_000, 4), (50_000, 3), (1000, 8), (10, 4)):
+        for r in range(w):
+            ref = list(DistributedSampler(range(n), num_replicas=w, rank=r, shuffle=False, drop_last=False))
+            assert ShardSampler(n, w, r).indices().tolist() == ref
+
+
+def test_union_of_rank_batches_is_the_single_process_batch():
+    """with shuffle=False the ranks' i-th batches partition part1's i-th batch."""
+    w, n = 4, 2048
+    per = 256 // w
+    single = ShardSampler(n).indices()
+    shards = [ShardSampler(n, w, r).indices() for r in range(w)]
+    for i in range(n // 256):
+        union = torch.cat([s[i * per:(i + 1) * per] for s in shards]).sort().values
+        assert torch.equal(union, single[i * 256:(i + 1) * 256])
+
+
+def test_loaders_shapes_and_determinism():
+    tr, te = create_data_loaders(1, 4, 64, root=None, synthetic=True, train_size=1000, test_size=300)
+    assert len(tr) == math.ceil(250 / 64) and len(te) == math.ceil(300 / 64)
+    assert len(te.dataset) == 300                       # the test split is NOT sharded (Q10)
+    img, lab, aug = next(iter(tr))
+    assert img.dtype == torch.uint8 and img.shape == (64, 32, 32, 3) and lab.dtype == torch.int64
+    assert aug.shape == (64, 4) and int(aug[:, :2].max()) <= 8 and int(aug[:, 2].max()) <= 1
+    a = synthetic_cifar10(True, 128).images
+    b = synthetic_cifar10(True, 128).images
+    assert torch.equal(a, b)
+    tr.sampler.set_epoch(3)                             # API parity (Q13)
+    last = list(iter(BatchLoader(synthetic_cifar10(False, 100), 64)))[-1]
+    assert last[0].shape[0] == 36 and last[2] is None
+
+
+def test_bucket_plan_reproduces_ddp_layout():
+    """buckets of ~9.46 / 27.16 / 0.31 MB in gradient-ready order."""
+    m = ddpb200.VGG11()
+    groups = S.param_groups_of(m)
+    assert len(groups) == 9 and sum(g[2] for g in groups) == 9_231_114
+    b = S.plan_buckets(groups)
+    assert [x.numel for x in b] == [2_365_962, 6_789_120, 76_032]
+    assert [(x.first_param, x.last_param) for x in b] == [(28, 33), (8, 27), (0, 7)]
+    assert [x.ready_after_group for x in b] == [7, 2, 0]
+    fine = S.plan_buckets(groups, first_cap_bytes=0, cap_bytes=0)      # one bucket per layer group
+    assert len(fine) == 9
+
+
+def test_training_and_eval_print_formats():
+    from ddpb200.train import test_model, train_model
+
+    torch.manual_seed(0)
+    m = ddpb200.VGG11()
+    tr, te = create_data_loaders(0, 1, 8, root=None, synthetic=True, train_size=8 * 41, test_size=16)
+    opt = ddpb200.SGD(m.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
+    out = io.StringIO()
+    with redirect_stdout(out):
+        train_model(m, tr, opt, ddpb200.CrossEntropyLoss(), 0)
+        test_model(m, te, ddpb200.CrossEntropyLoss())
+    lines = out.getvalue().splitlines()
+    assert re.fullmatch(r"\[1,    20\] loss: \d+\.\d{3}", lines[0])
+    assert re.fullmatch(r"\[1,    40\] loss: \d+\.\d{3}", lines[1])
+    assert re.fullmatch(r"Total time for 1-39 iteration in ns: \d+", lines[2])
+    assert re.fullmatch(r"Average time for 1-39 iteration in ns: \d+\.\d+", lines[3])
+    assert re.fullmatch(r"Test set: Average loss: \d+\.\d{4}, Accuracy: \d+/16 \(\d+%\)", lines[-2])
+
+
+def test_checkpoint_roundtrip_cpu(tmp_path):
+    from ddpb200.train import DistributedDataParallel
+    from ddpb200.utils.checkpoint import load_checkpoint, save_checkpoint
+
+    torch.manual_seed(1)
+    m = ddpb200.VGG11()
+    save_checkpoint(tmp_path / "a.pt", m)
+    wrapped = DistributedDataParallel(ddpb200.VGG11())
+    assert list(wrapped.state_dict().keys()) == ["module." + k for k in EXPECTED_KEYS]
+    load_checkpoint(tmp_path / "a.pt", wrapped)          # prefix is added on load
+    for k, v in m.state_dict().items():
+        assert torch.equal(v, wrapped.state_dict()["module." + k])
