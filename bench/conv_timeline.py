@@ -23,6 +23,8 @@ for li, (S, Ci, Co, taps) in LAYERS.items():
     bias = torch.zeros(Co, device=dev)
     scratch = torch.empty(8 * P * Co, device=dev)
     for pair, bn, sp in cfgs:
+        if bn == 0:
+            bn = K.conv_plan(N, S, S, Ci, Co, taps)[1]
         if Co % bn:
             continue
         m_tiles = (P + 127) // 128
@@ -37,7 +39,8 @@ for li, (S, Ci, Co, taps) in LAYERS.items():
             for it in range(3):
                 flush.zero_() if "--cold" in sys.argv else None
                 lib.ddpb_conv_debug_timing(buf.data_ptr())
-                K.conv_fprop(x, w, bias, N, S, S, Ci, Co, taps, out=y, stats=stats, scratch=scratch)
+                K.conv_fprop(x, w, None if "--nobias" in sys.argv else bias, N, S, S, Ci, Co, taps, out=y,
+                             stats=None if "--nostats" in sys.argv else stats, scratch=scratch)
                 lib.ddpb_conv_debug_timing(None)
                 torch.cuda.synchronize()
         finally:

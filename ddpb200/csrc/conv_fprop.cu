@@ -515,58 +515,46 @@ struct ConvPlan {
 static int g_force_pair = -1, g_force_block_n = -1, g_force_splits = -1;
 static unsigned long long* g_dbg = nullptr;
 
-// Cycle estimates calibrated on B200 (profiles/): a TMA->MMA ring round trip of ~2200 cycles,
-// 2*BLOCK_N tensor cycles per 64-deep k-step, ~700 cycles of epilogue per 32 columns per warp.
-static double plan_cost(int mode, int bn, int splits, long long P, int C_out, int total_k) {
-  const double kRtt = 2200.0;
-  int m_tiles = static_cast<int>((P + kBlockM - 1) / kBlockM);
-  if (mode == 1) m_tiles = (m_tiles + 1) / 2 * 2;
+// Cycle estimates for the persistent kernel, calibrated on B200 with the in-kernel timeline
+// hook (profiles/r1_call11_conv_timeline.txt): a 64-deep k-step costs max(1.35 x tensor time,
+// stage bytes / 55 B per clk of operand ingest); draining a tile costs ~30 cycles per column
+// with eight epilogue warps and overlaps the next tile's main loop.
+static double plan_cost(int bn, int splits, long long P, int C_out, int total_k) {
+  const int m_tiles = static_cast<int>((P + kBlockM - 1) / kBlockM);
   const int items = m_tiles * (C_out / bn) * splits;
   const int sms = sm_count();
   const double k_iters = static_cast<double>(total_k) / splits;
-  const double mma = 2.0 * bn;
-  double t;
-  if (mode == 2) {
-    const int stages = (192 * 1024) / (16384 + bn * 128);
-    const double iter = mma > kRtt / stages ? mma : kRtt / stages;
-    const double mainloop = k_iters * iter;
-    const double epi = (bn / 64.0) * 1400.0 * (splits > 1 ? 0.5 : 1.0);
-    const int per_sm = (items + sms - 1) / sms;
-    t = per_sm * (mainloop > epi ? mainloop : epi) + (mainloop > epi ? epi : mainloop) + 3000.0;
-  } else {
-    const int stage_bytes = 16384 + (mode == 1 ? bn / 2 : bn) * 128;
-    const int stages = mode == 1 ? (bn >= 256 ? 5 : 6) : (bn >= 256 ? 4 : 3);
-    const int resident = (mode == 0 && stages * stage_bytes <= 100 * 1024) ? 2 : 1;
-    const double iter_one = mma > kRtt / stages ? mma : kRtt / stages;
-    const double epi = (bn / 32.0) * 1400.0;
-    const double per_cta = k_iters * iter_one + epi + 1500.0;
-    const int rounds = (items + sms * resident - 1) / (sms * resident);
-    t = rounds * per_cta * (resident == 2 ? 1.15 : 1.0);
-  }
-  if (splits > 1) t += 5000.0 + 2.0 * splits * static_cast<double>(P) * C_out * 4.0 / 4000.0;
+  const double stage_bytes = 16384.0 + bn * 128.0;
+  const double tensor = 2.0 * bn * 1.35, ingest = stage_bytes / 55.0;
+  const double mainloop = k_iters * (tensor > ingest ? tensor : ingest);
+  const double epi = 30.0 * bn * (splits > 1 ? 0.6 : 1.0);
+  const int per_sm = (items + sms - 1) / sms;
+  double t = per_sm * (mainloop > epi ? mainloop : epi) + (mainloop > epi ? epi : mainloop) + 2500.0;
+  // split-K finalize: re-reads splits x P x C_out floats (L2-resident at these sizes) + a launch
+  if (splits > 1) t += 6000.0 + splits * static_cast<double>(P) * C_out * 4.0 / 3000.0;
   return t;
 }
 
+// Automatic choice: the persistent kernel with the cheapest (BLOCK_N, split-K); the
+// one-tile-per-CTA and CTA-pair kernels stay available through ddpb_conv_force (mode 0 / 1).
 static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint, bool allow_split) {
-  ConvPlan best{0, (C_out % 128 == 0) ? 128 : 64, 1};
+  const int mode = g_force_pair >= 0 ? g_force_pair : 2;
+  ConvPlan best{mode, (C_out % 128 == 0) ? 128 : 64, 1};
   double best_t = 1e30;
   const int bns[3] = {64, 128, 256};
-  for (int mode = 0; mode <= 2; ++mode) {
-    if (g_force_pair >= 0 && mode != g_force_pair) continue;
-    for (int bi = 0; bi < 3; ++bi) {
-      const int bn = bns[bi];
-      if (C_out % bn != 0) continue;
-      if (mode == 1 && bn < 128) continue;
-      if (block_n_hint != 0 && bn != block_n_hint) continue;
-      if (g_force_block_n >= 0 && bn != g_force_block_n) continue;
-      for (int splits = 1; splits <= 8; ++splits) {
-        if (g_force_splits >= 0 && splits != g_force_splits) continue;
-        if (splits > 1 && (!allow_split || total_k / splits < 4 || C_out / 8 > 256 || 256 % (C_out / 8) != 0)) continue;
-        const double t = plan_cost(mode, bn, splits, P, C_out, total_k);
-        if (t < best_t) {
-          best_t = t;
-          best = ConvPlan{mode, bn, splits};
-        }
+  for (int bi = 0; bi < 3; ++bi) {
+    const int bn = bns[bi];
+    if (C_out % bn != 0) continue;
+    if (mode == 1 && bn < 128) continue;
+    if (block_n_hint != 0 && bn != block_n_hint) continue;
+    if (g_force_block_n >= 0 && bn != g_force_block_n) continue;
+    for (int splits = 1; splits <= 8; ++splits) {
+      if (g_force_splits >= 0 && splits != g_force_splits) continue;
+      if (splits > 1 && (!allow_split || total_k / splits < 4 || C_out / 8 > 256 || 256 % (C_out / 8) != 0)) continue;
+      const double t = plan_cost(bn, splits, P, C_out, total_k);
+      if (t < best_t) {
+        best_t = t;
+        best = ConvPlan{mode, bn, splits};
       }
     }
   }

@@ -179,9 +179,37 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     const int chunk0 = half * kMyChunks;
     float* my_bias = s_bias + ew * (BLOCK_N / 2);
     const int row = q * 32 + lane_id();
+    // Per-channel statistics are accumulated in shared memory across this CTA's tiles and
+    // flushed with atomics only when the column block changes (or at the end): with one flush
+    // per tile the 2*C_out atomic addresses were hit by every tile of the layer and serialised
+    // in L2 (first layer: 2048 tiles onto 128 addresses).
+    const bool do_stats = (p.partial == nullptr) && (p.stats != nullptr);
+    auto flush_stats = [&](int n_tile_done) {
+      asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps
+      for (int c = threadIdx.x - 64; c < 2 * BLOCK_N; c += 256) {
+        const int which = c / BLOCK_N, col = c - which * BLOCK_N;
+        float acc = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          acc += s_stats[(w * 2 + which) * BLOCK_N + col];
+          s_stats[(w * 2 + which) * BLOCK_N + col] = 0.f;
+        }
+        atomicAdd(p.stats + which * p.C_out + n_tile_done * BLOCK_N + col, acc);
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+    };
+    if (do_stats) {
+      for (int c = threadIdx.x - 64; c < 8 * BLOCK_N; c += 256) s_stats[c] = 0.f;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+    }
+    int cur_n = -1;
     int local = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++local) {
       const PersistItem it = persist_item(item, m_tiles, n_tiles);
+      if (do_stats && it.n_tile != cur_n) {
+        if (cur_n >= 0) flush_stats(cur_n);
+        cur_n = it.n_tile;
+      }
       const int buf = local & 1;
       const uint32_t use = static_cast<uint32_t>(local >> 1);
       const long long pix = static_cast<long long>(it.m_tile) * kBlockM + row;
@@ -243,8 +271,9 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             for (int j = 0; j < 32; ++j) sq[j] = v[j] * v[j];
             const float s1 = warp_transpose_reduce(v);
             const float s2 = warp_transpose_reduce(sq);
-            s_stats[(q * 2 + 0) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] = s1;
-            s_stats[(q * 2 + 1) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] = s2;
+            // entry (q, column) belongs to exactly this lane of this warp: plain accumulate
+            s_stats[(q * 2 + 0) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] += s1;
+            s_stats[(q * 2 + 1) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] += s2;
           }
         }
       }
@@ -252,19 +281,8 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       tc_fence_before();
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&tmem_empty[buf]);
-      if (direct && p.stats != nullptr) {
-        asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps
-        const int t = threadIdx.x - 64;
-        for (int c = t; c < 2 * BLOCK_N; c += 256) {
-          const int which = c / BLOCK_N, col = c - which * BLOCK_N;
-          float acc = 0.f;
-#pragma unroll
-          for (int w = 0; w < 4; ++w) acc += s_stats[(w * 2 + which) * BLOCK_N + col];
-          atomicAdd(p.stats + which * p.C_out + it.n_tile * BLOCK_N + col, acc);
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory");   // s_stats may be overwritten by the next tile
-      }
     }
+    if (do_stats && cur_n >= 0) flush_stats(cur_n);
   }
 
   tc_fence_before();

@@ -1,0 +1,119 @@
+/* ddpb200.h -- C ABI of libddpb200.so, the sm_100a kernel library of the ddpb200 framework.
+ *
+ * Every entry point returns 0 on success; on failure it returns non-zero and
+ * ddpb_last_error() describes the problem (thread local).  `stream` is a cudaStream_t passed
+ * as void*.  Activations are NHWC bf16 matrices [N*H*W][C]; 3x3 filters are bf16
+ * [C_out][9][C_in] (the fp32 masters have the same order); accumulation is fp32.
+ *
+ * Each comment names the operation of the reference it replaces (file:line under
+ * /root/reference, op numbers O1..O16 and kernel numbers K1..K16 from SURVEY.md).  The
+ * reference itself ships no native code (SURVEY.md par. 2.5): these are new implementations.
+ */
+#ifndef DDPB200_H_
+#define DDPB200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library ------------------------------------------------------------------------------ */
+const char* ddpb_last_error(void);
+int ddpb_abi_version(void);          /* bumped when a signature changes */
+int ddpb_sm_count(void);             /* SMs of the current device (148 without a device) */
+
+/* ---- convolution (K1, K2, K5, K6) ----------------------------------------------------------- */
+/* O1: nn.Conv2d(3x3, stride 1, pad 1, bias) forward, part1/model.py:18-23.
+ * y[N*H*W][C_out] = conv(x[N][H][W][C_in], w[C_out][taps*C_in]) (+bias), bf16 out.
+ * taps = 9, or 1 for the first layer's pre-gathered operand (see ddpb_first_layer_operand_*).
+ * stats (fp32 [2][C_out], may be null) is ACCUMULATED with per-channel sum / sum of squares of
+ * y (the BatchNorm statistics, O4).  block_n: 0 = automatic.  scratch: fp32 buffer of
+ * ddpb_conv_fprop_scratch_elems() floats for split-K, or null to forbid splitting. */
+int ddpb_conv_fprop(const void* x, const void* w, const float* bias, void* y, float* stats, int N, int H, int W,
+                    int C_in, int C_out, int taps, int block_n, float* scratch, void* stream);
+long long ddpb_conv_fprop_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps, int block_n);
+
+/* O2: data gradient of the same convolution (autograd of part1/model.py:18-23).
+ * dx[N*H*W][C_in] from dy[..][C_out] and the SAME filter pack fprop reads (no transposed copy).
+ * scratch sized with ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n). */
+int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out, int block_n,
+                    float* scratch, void* stream);
+
+/* O3: weight gradient.  dw (fp32 [C_out][dw_ld]) gets its first dw_cols_valid (<= taps*C_in)
+ * columns per row.  scratch: ddpb_conv_wgrad_scratch_elems() floats of device memory for the
+ * split reduction over pixels (may be null when that is 0). */
+int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* scratch, int N, int H, int W, int C_in,
+                    int C_out, int taps, int dw_cols_valid, int dw_ld, void* stream);
+long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps);
+int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps);
+
+/* Tuning / profiling hooks for the conv launch planner (kernel: 0 one tile per CTA, 1 CTA
+ * pair with cta_group::2, 2 persistent; -1 = automatic). */
+void ddpb_conv_force(int kernel, int block_n, int splits);
+void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3);
+void ddpb_conv_debug_timing(unsigned long long* per_cta_stamps);
+
+/* ---- BatchNorm + ReLU (+ MaxPool) (K3, K4) -------------------------------------------------- */
+/* O4+O6+O7: BatchNorm2d(track_running_stats=False) -> ReLU -> [MaxPool2d(2,2)],
+ * part1/model.py:15-16,24,25.  Batch statistics always (also in eval). */
+int ddpb_channel_stats(const void* x, float* stats, long long P, int C, void* stream);
+int ddpb_bn_relu_pool_fwd(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
+                          float* saved_mean_rstd, int N, int H, int W, int C, int pool, float eps, void* stream);
+/* O5+O6+O7 backward.  sums: fp32 [2][C] scratch that must be ZERO on entry. */
+int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float* saved_mean_rstd, const float* gamma,
+                          const float* beta, float* sums, void* dx, float* dgamma, float* dbeta, float* dbias, int N,
+                          int H, int W, int C, int pool, float eps, void* stream);
+
+/* ---- classifier + loss (K7, K8, K15) --------------------------------------------------------- */
+/* O9+O10+O15: Linear(512,10) + CrossEntropyLoss(mean) + top-1, part1/model.py:40,45,
+ * part1/main.py:75,105-106. */
+int ddpb_fc_ce_fwd(const void* x, const float* w, const float* b, const long long* labels, float* logits,
+                   float* row_loss, float* dlogits, int* row_correct, float* loss, int* correct, int B, int F, int K,
+                   void* stream);
+int ddpb_fc_bwd(const void* x, const float* w, const float* dlogits, float* dw, float* db, void* dx, int B, int F,
+                int K, void* stream);
+
+/* ---- optimizer (K9) -------------------------------------------------------------------------- */
+/* O11+O12: optim.SGD(lr, momentum, weight_decay).step() over the flat arena, part1/main.py:77,
+ * 124-125.  shadow (bf16, may be null) receives the rounded parameters = the conv operands. */
+int ddpb_sgd_step(float* p, const float* g, float* m, void* shadow, long long n, float lr, float momentum,
+                  float weight_decay, float grad_scale, void* stream);
+int ddpb_pack_weights(int count, const float* const* master, void* const* fprop, void* const* dgrad, const int* K,
+                      const int* C, const int* taps, const int* fprop_ld, const int* flat, void* stream);
+
+/* ---- input pipeline (K16) -------------------------------------------------------------------- */
+/* O16: RandomCrop(32,4) / RandomHorizontalFlip / ToTensor / Normalize, part1/main.py:20-28, fused
+ * with the gather that builds the first layer's [N*H*W][64] operand. */
+int ddpb_first_layer_operand_f32(const float* src_nchw, void* out, int N, int H, int W, void* stream);
+int ddpb_first_layer_operand_u8(const unsigned char* src_nhwc, const signed char* aug, void* out, int N, int H,
+                                int W, const float* mean3, const float* std3, int pad, void* stream);
+
+/* ---- gradient synchronisation over NVLink peer memory (K10-K14) ------------------------------ */
+/* bufs: `world` base pointers of the symmetric buffers ([64 KiB signal pad | fp32 payload]) as
+ * mapped in this process; mc: NVLS multicast mapping of the same buffer or null; off/n: payload
+ * range in floats (multiples of 4); blocks/slot_base: CTAs and their signal-pad slots;
+ * p/m/shadow: local parameter / momentum / bf16 arenas for the fused SGD step (p null = none). */
+int ddpb_comm_signal_pad_bytes(void);
+int ddpb_comm_max_ranks(void);
+/* part2b dist.all_reduce(SUM) + divide (part2/part2b/main.py:97-103) and part3's bucketed
+ * all-reduce (part3/main.py:174): in-place two-shot all-reduce, mean, optional SGD. */
+int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int rank, int world, long long off, long long n,
+                       int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow, float lr,
+                       float momentum, float weight_decay, void* stream);
+/* part2a gather -> mean on rank 0 -> scatter (part2/part2a/main.py:97-115). */
+int ddpb_reduce_root_bcast(const void* const* bufs, const void* mc, int rank, int world, int root, long long off,
+                           long long n, int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow,
+                           float lr, float momentum, float weight_decay, void* stream);
+/* DDP's constructor-time parameter broadcast. */
+int ddpb_broadcast(const void* const* bufs, const void* mc, int rank, int world, int root, long long off,
+                   long long n, int blocks, int slot_base, int use_mc, void* stream);
+int ddpb_peer_barrier(const void* const* bufs, int rank, int world, int blocks, int slot_base, void* stream);
+/* CUDA IPC bootstrap of the symmetric buffer (process-group rendezvous, part2b/main.py:52-58). */
+int ddpb_ipc_alloc(long long bytes, void** ptr, void* handle64);
+int ddpb_ipc_open(const void* handle64, void** ptr);
+int ddpb_ipc_close(void* ptr);
+int ddpb_ipc_free(void* ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDPB200_H_ */
