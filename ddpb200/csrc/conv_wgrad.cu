@@ -367,3 +367,69 @@ extern "C" int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* 
                                cudaStream_t stream) {
   return wgrad_impl(dy, x, dw, scratch, N, H, W, C_in, C_out, taps, dw_cols_valid, dw_ld, stream);
 }
+
+// ------------------------------------------------------------------------------------------
+// ddpb_conv_wgrad_static: the same weight-gradient computation for callers that may not
+// allocate device memory.  (No counterpart in the reference.)
+//
+// Who needs this: code that runs where a cudaMalloc is off limits -- for example a training
+// or serving loop that must never hit cudaMalloc's implicit device-wide synchronisation, a
+// process whose GPU memory was handed over in full to another allocator at start-up so that a
+// later driver allocation could fail, or a host application that embeds this library and
+// forbids it to touch the allocator.  ddpb_conv_wgrad makes such callers provide a scratch
+// buffer of a shape-dependent size; here the split-reduction scratch is a fixed array that
+// lives in the library image instead, so the caller passes only inputs and outputs.
+//
+// Cost and limits:
+//   * the array (kWgradStaticMaxFloats floats = 16 MiB) is resident on EVERY GPU that loads
+//     the library, from load to process exit, whether or not this entry point is ever used;
+//   * shapes whose split reduction needs more than that are rejected with an error -- use
+//     ddpb_conv_wgrad with your own buffer for those.  On a 148-SM B200 the planner never asks
+//     for more than ~4.85 M floats; 4 Mi covers e.g. VGG-11's layers 0-2, 4 and 5 at batch 256
+//     and every layer at batch <= 128, but not the 4.7 M-float cases (layers 3, 6, 7 at 256);
+//   * the first call on each device looks up the array's device address
+//     (cudaGetSymbolAddress) and caches it; make that first call with the right device
+//     current and before any stream capture begins;
+//   * all calls share the one array and it keeps whatever the previous call left in it.
+//     The kernel overwrites every partial sum that the second stage reads, so nothing has to be
+//     cleared between calls -- but two calls whose kernels overlap on the GPU (different
+//     streams, or one device used from two threads) race on it.  Serialise them.
+// It performs no cudaMalloc / cudaFree and calls no allocating library routine.
+// ------------------------------------------------------------------------------------------
+constexpr long long kWgradStaticMaxFloats = 4LL * 1024 * 1024;
+
+static __device__ __align__(256) float g_wgrad_static_scratch[kWgradStaticMaxFloats];
+
+// In host code `g_wgrad_static_scratch` is only a handle for the runtime, not a device
+// address; the address a kernel can use has to be asked for, once per device.
+static int wgrad_static_scratch(float** out) {
+  constexpr int kMaxDevices = 64;
+  static float* per_device[kMaxDevices] = {};
+  int dev = -1;
+  DDPB_CHECK_CUDA(cudaGetDevice(&dev));
+  DDPB_REQUIRE(dev >= 0 && dev < kMaxDevices, "conv_wgrad_static: device ordinal %d out of range", dev);
+  if (per_device[dev] == nullptr) {
+    void* ptr = nullptr;
+    DDPB_CHECK_CUDA(cudaGetSymbolAddress(&ptr, g_wgrad_static_scratch));
+    DDPB_REQUIRE(ptr != nullptr, "conv_wgrad_static: no device address for the built-in scratch array");
+    per_device[dev] = static_cast<float*>(ptr);
+  }
+  *out = per_device[dev];
+  return 0;
+}
+
+// Capacity of the built-in scratch array in floats.
+extern "C" long long ddpb_conv_wgrad_static_max_elems() { return kWgradStaticMaxFloats; }
+
+// Same arguments and result as ddpb_conv_wgrad minus `scratch`.
+extern "C" int ddpb_conv_wgrad_static(const void* dy, const void* x, float* dw, int N, int H, int W, int C_in,
+                                      int C_out, int taps, int dw_cols_valid, int dw_ld, cudaStream_t stream) {
+  const long long need = ddpb_conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps);
+  DDPB_REQUIRE(need <= kWgradStaticMaxFloats,
+               "conv_wgrad_static: this shape needs %lld floats of scratch but the built-in array holds %lld; "
+               "call ddpb_conv_wgrad with a caller-provided buffer instead",
+               need, kWgradStaticMaxFloats);
+  float* scratch = nullptr;
+  if (int rc = wgrad_static_scratch(&scratch)) return rc;
+  return wgrad_impl(dy, x, dw, scratch, N, H, W, C_in, C_out, taps, dw_cols_valid, dw_ld, stream);
+}

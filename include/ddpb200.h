@@ -46,6 +46,18 @@ int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* scratch, in
 long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps);
 int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps);
 
+/* No counterpart in the reference.  ddpb_conv_wgrad for callers that must not allocate device
+ * memory (a loop that cannot take cudaMalloc's device-wide synchronisation, a process whose
+ * memory was handed to another allocator, a host application that forbids allocator calls):
+ * same arguments minus `scratch`; the split-reduction scratch is a fixed array of
+ * ddpb_conv_wgrad_static_max_elems() floats (4 Mi = 16 MiB) that every GPU loading the library
+ * holds until exit.  Larger requests fail with an error.  The first call on a device resolves
+ * the array's address: make it with that device current and before any stream capture.  All
+ * calls share the array; calls that overlap on the GPU race. */
+int ddpb_conv_wgrad_static(const void* dy, const void* x, float* dw, int N, int H, int W, int C_in, int C_out,
+                           int taps, int dw_cols_valid, int dw_ld, void* stream);
+long long ddpb_conv_wgrad_static_max_elems(void);
+
 /* Tuning / profiling hooks for the conv launch planner (kernel: 0 one tile per CTA, 1 CTA
  * pair with cta_group::2, 2 persistent; -1 = automatic). */
 void ddpb_conv_force(int kernel, int block_n, int splits);
