@@ -99,7 +99,7 @@ def main():
         rows.append(dict(layer=li, op="bn_fwd", us=t, gbs=gb / (t * 1e-6)))
         tot["bn_fwd"] += t
         dact = torch.randn(Po, Co, device=dev).bfloat16()
-        sums = torch.zeros(2, Co, device=dev)
+        sums = torch.zeros(2 * Co + 32, device=dev)
         dxb = torch.empty(P, Co, dtype=torch.bfloat16, device=dev)
         dg, db_, dbias = torch.empty(Co, device=dev), torch.empty(Co, device=dev), torch.empty(Co, device=dev)
 

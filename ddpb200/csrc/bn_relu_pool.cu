@@ -393,6 +393,231 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   }
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Fused backward (one launch, one read of x and dy from memory).  Every layer but the first
+// is small enough that each of ~148 CTAs can keep ITS slice of (x, dy) in shared memory:
+// phase 1 streams the slice in, accumulates the per-channel sums and parks the data in smem;
+// a grid-wide barrier waits for the global sums; phase 2 produces dx from smem.  Launched
+// cooperatively (all CTAs co-resident); the barrier counter is one word the caller zeroes.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void grid_barrier_once(unsigned int* counter, unsigned int expected) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(counter, 1u);
+    const unsigned long long t0 = global_timer_ns();
+    unsigned int seen, spins = 0;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
+      if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_WAIT_TIMEOUT_NS) {
+        printf("ddpb200: bn_bwd_fused grid barrier timed out (block %d: %u of %u)\n", blockIdx.x, seen, expected);
+        __trap();
+      }
+    } while (seen < expected);
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+constexpr int kBnFusedThreads = 512;   // one CTA per SM: more threads = more loads in flight
+
+template <bool kPool>
+__global__ void __launch_bounds__(kBnFusedThreads, 1)
+bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                    const float* __restrict__ saved, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, float* __restrict__ sums /* [2][C] zero, then counter */,
+                    __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                    float* __restrict__ dbias, BnGeom g, int items_per_cta) {
+  constexpr int kSlot = kPool ? 5 : 2;          // uint4 words parked per item: window of x + dy
+  extern __shared__ uint4 s_raw[];
+  float* s_coef = reinterpret_cast<float*>(s_raw);          // scale, shift, A, Bc, acc[2]: 6*C floats
+  uint4* s_data = s_raw + (6 * g.C * 4 + 15) / 16;
+  float* s_scale = s_coef;
+  float* s_shift = s_coef + g.C;
+  float* s_A = s_coef + 2 * g.C;
+  float* s_B = s_coef + 3 * g.C;
+  float* s_acc = s_coef + 4 * g.C;
+  unsigned int* counter = reinterpret_cast<unsigned int*>(sums + 2 * g.C);
+  for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
+    const float mean = saved[c], rstd = saved[g.C + c];
+    const float sc = gamma[c] * rstd;
+    s_scale[c] = sc;
+    s_shift[c] = beta[c] - mean * sc;
+    s_acc[c] = 0.f;
+    s_acc[g.C + c] = 0.f;
+    if (blockIdx.x == 0 && dbias != nullptr) dbias[c] = 0.f;
+  }
+  __syncthreads();
+  const int groups = g.C / 8;
+  const long long out_pix = static_cast<long long>(g.N) * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
+  const long long items = out_pix * groups;
+  const long long begin = static_cast<long long>(blockIdx.x) * items_per_cta;   // multiple of 512, hence of groups
+  long long end = begin + items_per_cta;
+  if (end > items) end = items;
+  const int cg = static_cast<int>(threadIdx.x % groups);
+  float sc[8], sh[8], a1[8], a2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = s_scale[cg * 8 + j];
+    sh[j] = s_shift[cg * 8 + j];
+    a1[j] = a2[j] = 0.f;
+  }
+  // ---- phase 1: load, park, reduce
+  for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
+    const BwdItem it = bwd_item(g, i, groups);
+    uint4* slot = s_data + (i - begin) * kSlot;
+    const uint4 d = ldg16(dy + it.opix * g.C + cg * 8);
+    slot[kSlot - 1] = d;
+    if (!kPool) {
+      const uint4 v = ldg16(x + it.ipix[0] * g.C + cg * 8);
+      slot[0] = v;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xv = bf16_at(v, j);
+        const float gr = (fmaf(xv, sc[j], sh[j]) > 0.f) ? bf16_at(d, j) : 0.f;
+        a1[j] += gr;
+        a2[j] = fmaf(gr, xv, a2[j]);
+      }
+    } else {
+      uint4 v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        v[q] = ldg16(x + it.ipix[q] * g.C + cg * 8);
+        slot[q] = v[q];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float best = 0.f, xa = 0.f;
+        bool hit = false;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float xv = bf16_at(v[q], j);
+          const float z = fmaf(xv, sc[j], sh[j]);
+          if (z > best) {
+            best = z;
+            xa = xv;
+            hit = true;
+          }
+        }
+        const float gr = hit ? bf16_at(d, j) : 0.f;
+        a1[j] += gr;
+        a2[j] = fmaf(gr, xa, a2[j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    group_accumulate(s_acc, a1[j], groups, cg, j);
+    group_accumulate(s_acc + g.C, a2[j], groups, cg, j);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * g.C; c += blockDim.x) atomicAdd(&sums[c], s_acc[c]);
+  grid_barrier_once(counter, gridDim.x);
+  // ---- phase 2: coefficients from the global sums, dx from the parked slice
+  const float inv_count = 1.f / static_cast<float>(static_cast<long long>(g.N) * g.H * g.W);
+  for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
+    const float mean = saved[c], rstd = saved[g.C + c];
+    const float sum_g = __ldcg(sums + c);
+    const float sum_gxhat = rstd * (__ldcg(sums + g.C + c) - mean * sum_g);
+    const float A = -s_scale[c] * rstd * sum_gxhat * inv_count;
+    s_A[c] = A;
+    s_B[c] = -s_scale[c] * sum_g * inv_count - A * mean;
+    s_acc[c] = 0.f;
+    if (blockIdx.x == 0) {
+      if (dbeta) dbeta[c] = sum_g;
+      if (dgamma) dgamma[c] = sum_gxhat;
+    }
+  }
+  __syncthreads();
+  float cA[8], cB[8], ab[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    cA[j] = s_A[cg * 8 + j];
+    cB[j] = s_B[cg * 8 + j];
+    ab[j] = 0.f;
+  }
+  for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
+    const BwdItem it = bwd_item(g, i, groups);
+    const uint4* slot = s_data + (i - begin) * kSlot;
+    const uint4 d = slot[kSlot - 1];
+    if (!kPool) {
+      const uint4 v = slot[0];
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xv = bf16_at(v, j);
+        const float gr = (fmaf(xv, sc[j], sh[j]) > 0.f) ? bf16_at(d, j) : 0.f;
+        o[j] = fmaf(sc[j], gr, fmaf(cA[j], xv, cB[j]));
+        ab[j] += o[j];
+      }
+      store8(dx + it.ipix[0] * g.C + cg * 8, o);
+    } else {
+      uint4 v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) v[q] = slot[q];
+      int arg[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float best = 0.f;
+        arg[j] = -1;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float z = fmaf(bf16_at(v[q], j), sc[j], sh[j]);
+          if (z > best) {
+            best = z;
+            arg[j] = q;
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float gr = (arg[j] == q) ? bf16_at(d, j) : 0.f;
+          o[j] = fmaf(sc[j], gr, fmaf(cA[j], bf16_at(v[q], j), cB[j]));
+          ab[j] += o[j];
+        }
+        store8(dx + it.ipix[q] * g.C + cg * 8, o);
+      }
+    }
+  }
+  if (dbias != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) group_accumulate(s_acc, ab[j], groups, cg, j);
+    __syncthreads();
+    for (int c = threadIdx.x; c < g.C; c += blockDim.x) atomicAdd(&dbias[c], s_acc[c]);
+  }
+}
+
+// Tries the fused cooperative kernel; returns -1 if the shape does not fit in shared memory.
+template <bool kPool>
+static int launch_bn_bwd_fused(const __nv_bfloat16* x, const __nv_bfloat16* dy, const float* saved,
+                               const float* gamma, const float* beta, float* sums, __nv_bfloat16* dx,
+                               float* dgamma, float* dbeta, float* dbias, BnGeom g, long long items,
+                               cudaStream_t stream) {
+  const int sms = sm_count();
+  long long ipc = (items + sms - 1) / sms;
+  ipc = (ipc + kBnFusedThreads - 1) / kBnFusedThreads * kBnFusedThreads;
+  const int grid = static_cast<int>((items + ipc - 1) / ipc);
+  const size_t smem = ((6 * g.C * 4 + 15) / 16) * 16 + static_cast<size_t>(ipc) * (kPool ? 5 : 2) * 16;
+  if (smem > 200 * 1024) return -1;
+  static size_t configured = 0;
+  if (smem > configured) {
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_fused_kernel<kPool>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         200 * 1024));
+    configured = 200 * 1024;
+  }
+  int ipc_i = static_cast<int>(ipc);
+  void* args[] = {&x, &dy, &saved, &gamma, &beta, &sums, &dx, &dgamma, &dbeta, &dbias, &g, &ipc_i};
+  DDPB_CHECK_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bn_bwd_fused_kernel<kPool>), dim3(grid),
+                                              dim3(kBnFusedThreads), args, smem, stream));
+  return 0;
+}
+
+static int g_bn_fused = 1;   // 0: always use the two-kernel path
+
 static int bn_grid(long long items) {
   long long blocks = (items + kBnThreads - 1) / kBnThreads;
   const long long cap = 4LL * sm_count();
@@ -433,8 +658,11 @@ extern "C" int ddpb_bn_relu_pool_fwd(const void* x, const float* stats, const fl
   return 0;
 }
 
+extern "C" void ddpb_bn_bwd_set_fused(int enabled) { g_bn_fused = enabled; }
+
 // Backward of the fused block.  dy: gradient w.r.t. the (pooled) output, bf16.
-// sums: [2][C] fp32 scratch that MUST be zero on entry (pass 1 accumulates into it).
+// sums: fp32 scratch of 2*C + 32 floats that MUST be zero on entry (the per-channel sums are
+// accumulated into the first 2*C; the word after them is the fused kernel's grid barrier).
 // dx: [N*H*W][C] bf16 gradient w.r.t. the raw conv output.  dgamma/dbeta/dbias: fp32 [C]
 // (dbias may be null; it is cleared by pass 1 and accumulated by pass 2).
 extern "C" int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float* saved, const float* gamma,
@@ -450,6 +678,13 @@ extern "C" int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float*
   const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
   const __nv_bfloat16* dyb = static_cast<const __nv_bfloat16*>(dy);
   __nv_bfloat16* dxb = static_cast<__nv_bfloat16*>(dx);
+  if (g_bn_fused) {
+    const int rc = pool ? launch_bn_bwd_fused<true>(xb, dyb, saved, gamma, beta, sums, dxb, dgamma, dbeta, dbias, g,
+                                                    items, stream)
+                        : launch_bn_bwd_fused<false>(xb, dyb, saved, gamma, beta, sums, dxb, dgamma, dbeta, dbias, g,
+                                                     items, stream);
+    if (rc >= 0) return rc;   // -1: slice too large for shared memory, use the two-pass kernels
+  }
   if (pool) {
     bn_bwd_reduce_kernel<true><<<grid, kBnThreads, 4 * C * sizeof(float), stream>>>(xb, dyb, saved, gamma, beta,
                                                                                     sums, dbias, g);

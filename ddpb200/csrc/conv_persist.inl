@@ -27,7 +27,11 @@ struct PersistCfg {
   static constexpr int kStatsBytes = 4 * 2 * BLOCK_N * 4;      // [quarter][sum, sumsq][column]
   static constexpr int kBiasBytes = 8 * (BLOCK_N / 2) * 4;     // warp-private copies of the bias slice
   static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kStatsBytes + kBiasBytes + 512;
-  static constexpr int kTmemCols = 2 * BLOCK_N;                // two accumulators
+  // accumulators in TMEM: as many as fit in 512 columns, at most 4.  With short reductions
+  // (first layers: 1 or 9 k-steps per tile) the MMA -> epilogue -> MMA hand-off latency, not the
+  // work, bounds a 2-deep ring; 4 buffers let the MMA warp run three tiles ahead.
+  static constexpr int kAccBufs = (512 / BLOCK_N) < 4 ? (512 / BLOCK_N) : 4;
+  static constexpr int kTmemCols = kAccBufs * BLOCK_N;         // 256 / 512 / 512 columns
 };
 
 struct PersistItem {
@@ -57,9 +61,9 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes + Cfg::kBiasBytes);
   uint64_t* full_bar = bars;                         // [kStages]
   uint64_t* empty_bar = bars + Cfg::kStages;         // [kStages]
-  uint64_t* tmem_full = bars + 2 * Cfg::kStages;     // [2]
-  uint64_t* tmem_empty = tmem_full + 2;              // [2]
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* tmem_full = bars + 2 * Cfg::kStages;     // [kAccBufs]
+  uint64_t* tmem_empty = tmem_full + Cfg::kAccBufs;  // [kAccBufs]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + Cfg::kAccBufs);
 
   const int warp = threadIdx.x >> 5;
   const int n_items = m_tiles * n_tiles * splits;
@@ -76,7 +80,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         mbar_init(&full_bar[i], 1);
         mbar_init(&empty_bar[i], 1);
       }
-      for (int i = 0; i < 2; ++i) {
+      for (int i = 0; i < Cfg::kAccBufs; ++i) {
         mbar_init(&tmem_full[i], 1);
         mbar_init(&tmem_empty[i], 8);   // one arrival per epilogue warp
       }
@@ -143,8 +147,8 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         const PersistItem it = persist_item(item, m_tiles, n_tiles);
         const int k_begin = static_cast<int>(static_cast<long long>(total_k) * it.split / splits);
         const int k_end = static_cast<int>(static_cast<long long>(total_k) * (it.split + 1) / splits);
-        const int buf = local & 1;
-        const uint32_t use = static_cast<uint32_t>(local >> 1);
+        const int buf = local % Cfg::kAccBufs;
+        const uint32_t use = static_cast<uint32_t>(local / Cfg::kAccBufs);
         mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);   // epilogue drained this accumulator (free at first use)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * BLOCK_N;
@@ -210,8 +214,8 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         if (cur_n >= 0) flush_stats(cur_n);
         cur_n = it.n_tile;
       }
-      const int buf = local & 1;
-      const uint32_t use = static_cast<uint32_t>(local >> 1);
+      const int buf = local % Cfg::kAccBufs;
+      const uint32_t use = static_cast<uint32_t>(local / Cfg::kAccBufs);
       const long long pix = static_cast<long long>(it.m_tile) * kBlockM + row;
       const bool valid = pix < p.P;
       const bool direct = (p.partial == nullptr);

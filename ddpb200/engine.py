@@ -136,7 +136,7 @@ class VGGEngine:
             self.dconv.append(torch.empty(P, L.c_out, **bf))
             self.dact.append(torch.empty(Po, L.c_out, **bf))
         # --- per-channel statistics: one arena so a single memset clears all of it
-        csum = sum(2 * L.c_out for L in self.layers)
+        csum = sum(2 * L.c_out + 16 for L in self.layers)      # backward slots carry 32 extra words
         self.stat_arena = torch.zeros(2 * csum, **f32)
         self.stats, self.bsums, self.saved = [], [], []
         o = 0
@@ -144,8 +144,8 @@ class VGGEngine:
             self.stats.append(self.stat_arena[o:o + 2 * L.c_out])
             o += 2 * L.c_out
         for L in self.layers:
-            self.bsums.append(self.stat_arena[o:o + 2 * L.c_out])
-            o += 2 * L.c_out
+            self.bsums.append(self.stat_arena[o:o + 2 * L.c_out + 32])   # sums + grid-barrier word
+            o += 2 * L.c_out + 32
             self.saved.append(torch.empty(2 * L.c_out, **f32))
         # --- bf16 filter operands.  The arena keeps filters as [C_out][3][3][C_in], which is the
         # K-major GEMM operand of fprop AND (read MN-major, taps reversed) of dgrad, so one bf16
@@ -224,11 +224,21 @@ class VGGEngine:
             K.fc_ce_fwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), a.flat_master(self.p_fcb),
                         self.labels[:N], logits=self.logits, row_loss=self.row_loss)
 
-    def backward(self, N: int, after_layer=None):
-        """dlogits[:N] -> every gradient in the arena.  ``after_layer(li)`` is called once layer
-        li's gradients (and everything after it, classifier included) are enqueued -- the hook the
-        bucketed reducer uses to start a bucket while the rest of backward still runs."""
+    def backward(self, N: int, after_layer=None, side_stream=None):
+        """dlogits[:N] -> every gradient in the arena.
+
+        ``after_layer(li, events)`` is called once layer li's gradients (and everything after it,
+        classifier included) are enqueued -- the hook the bucketed reducer uses to start a bucket
+        while the rest of backward still runs; ``events`` must have completed before the bucket's
+        gradients are final.
+
+        ``side_stream``: wgrad(l) and dgrad(l) only share their input, so with a side stream the
+        weight gradient runs concurrently with the data gradient and the next BatchNorm backward
+        (two branches of the captured graph).  The late layers are latency bound, not throughput
+        bound, so the branches overlap almost perfectly."""
         a = self.arena
+        main = torch.cuda.current_stream()
+        side_events = []
         last = len(self.layers) - 1
         feat = self.act[last][:N]
         K.fc_bwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), self.dlogits[:N],
@@ -241,13 +251,26 @@ class VGGEngine:
                                dx=self.dconv[li], dgamma=a.flat_grad(L.p_g), dbeta=a.flat_grad(L.p_beta),
                                dbias=a.flat_grad(L.p_b))
             cols = 9 * L.c_in
-            K.conv_wgrad(self.dconv[li], x_in, N, L.H, L.W, L.c_in_eff, L.c_out, L.taps, out=a.flat_grad(L.p_w),
-                         cols_valid=cols, out_ld=cols, scratch=self.wgrad_scratch)
+            if side_stream is not None:
+                fork = torch.cuda.Event()
+                fork.record(main)
+                side_stream.wait_event(fork)
+                with torch.cuda.stream(side_stream):
+                    K.conv_wgrad(self.dconv[li], x_in, N, L.H, L.W, L.c_in_eff, L.c_out, L.taps,
+                                 out=a.flat_grad(L.p_w), cols_valid=cols, out_ld=cols, scratch=self.wgrad_scratch)
+                    done = torch.cuda.Event()
+                    done.record(side_stream)
+                side_events.append(done)
+            else:
+                K.conv_wgrad(self.dconv[li], x_in, N, L.H, L.W, L.c_in_eff, L.c_out, L.taps, out=a.flat_grad(L.p_w),
+                             cols_valid=cols, out_ld=cols, scratch=self.wgrad_scratch)
             if li > 0:
                 K.conv_dgrad(self.dconv[li], self.w_f[li], N, L.H, L.W, L.c_in, L.c_out, out=self.dact[li - 1],
                              scratch=self.fprop_scratch)
             if after_layer is not None:
-                after_layer(li)
+                after_layer(li, side_events[-1:] if side_stream is not None else [])
+        if side_stream is not None and side_events:
+            main.wait_event(side_events[-1])   # the side stream is in order: the last event covers all
 
     def sgd(self, lr: float, momentum: float, weight_decay: float, grad_scale: float = 1.0):
         a = self.arena
@@ -289,7 +312,7 @@ class _EngineFn(torch.autograd.Function):
     def backward(ctx, dlogits):
         eng, N = ctx.eng, ctx.N
         eng.dlogits[:N].copy_(dlogits)
-        eng.backward(N)
+        eng.backward(N)   # (single stream on the eager autograd path)
         # gradients were written straight into param.grad (arena views); nothing to hand to autograd
         return (None, None) + (None,) * len(eng.arena.params)
 

@@ -42,6 +42,7 @@ _SIGNATURES = {
                               c_float, c_void],
     "ddpb_bn_relu_pool_bwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void,
                               c_int, c_int, c_int, c_int, c_int, c_float, c_void],
+    "ddpb_bn_bwd_set_fused": [c_int],
     "ddpb_fc_ce_fwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_int,
                        c_int, c_int, c_void],
     "ddpb_fc_bwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_void],

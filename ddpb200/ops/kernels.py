@@ -135,13 +135,20 @@ def bn_relu_pool_fwd(x, stats, gamma, beta, N, H, W, C_, pool: bool, *, out=None
     return out, saved
 
 
+def bn_bwd_set_fused(enabled: bool) -> None:
+    """Testing hook: False forces the two-kernel BatchNorm backward (default: fused cooperative kernel
+    whenever a CTA's slice fits in shared memory)."""
+    nat.load().ddpb_bn_bwd_set_fused(int(enabled))
+
+
 def bn_relu_pool_bwd(x, dy, saved, gamma, beta, N, H, W, C_, pool: bool, *, sums=None, dx=None, dgamma=None,
                      dbeta=None, dbias=None, eps=BN_EPS, stream=None):
-    """O5+O6+O7 backward.  ``sums`` (fp32 [2,C]) must be zero on entry."""
+    """O5+O6+O7 backward.  ``sums`` (fp32, 2*C + 32 elements) must be zero on entry."""
     nat.require_cuda(x, dy, saved, gamma, beta)
     dev = x.device
     if sums is None:
-        sums = torch.zeros(2, C_, dtype=torch.float32, device=dev)
+        sums = torch.zeros(2 * C_ + 32, dtype=torch.float32, device=dev)
+    assert sums.numel() >= 2 * C_ + 32, "bn backward scratch needs 2*C + 32 zeroed floats"
     if dx is None:
         dx = torch.empty(N * H * W, C_, dtype=torch.bfloat16, device=dev)
     if dgamma is None:

@@ -32,7 +32,7 @@ class Trainer:
                  weight_decay: float = 1e-4, rank: int = 0, world_size: int = 1, granularity: str = "fused",
                  use_multicast: bool | str = "auto", use_graph: bool = True, comm_blocks: int | None = None,
                  first_bucket_bytes: int = S.MIB, bucket_bytes: int = 25 * S.MIB, symm_backend: str | None = None,
-                 fuse_sgd: bool = True):
+                 fuse_sgd: bool = True, overlap_wgrad: bool = True):
         if mode not in MODES:
             raise ValueError(f"mode must be one of {MODES}")
         if granularity not in ("fused", "param"):
@@ -44,6 +44,7 @@ class Trainer:
         self.granularity = granularity
         self.use_graph = use_graph
         self.fuse_sgd = fuse_sgd
+        self.overlap_wgrad = overlap_wgrad
         self.device = next(model.parameters()).device
         self.distributed = world_size > 1 and mode != "single"
         self.iteration = 0
@@ -78,6 +79,8 @@ class Trainer:
         # part3 reductions share the GPU with backward: a slice of the SMs; 2a/2b own the GPU
         self.comm_blocks = comm_blocks if comm_blocks is not None else (32 if self.mode == "ddp" else min(sms, 128))
         self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1) if self.mode == "ddp" else None
+        # wgrad runs on its own branch, concurrently with dgrad / the next BatchNorm backward
+        self.wgrad_stream = torch.cuda.Stream(device=self.device) if self.overlap_wgrad else None
         B = self.batch_size
         hw = self.engine.image_hw
         self.in_u8 = torch.zeros(B, hw, hw, 3, dtype=torch.uint8, device=self.device)
@@ -123,13 +126,13 @@ class Trainer:
             eng.load_input_f32(self.in_f32[:B])
         eng.forward(B, with_loss=True)
         if not self.distributed:
-            eng.backward(B)
+            eng.backward(B, side_stream=self.wgrad_stream)
             eng.sgd(self.lr, self.momentum, self.weight_decay)
         elif self.mode == "ddp":
             main = torch.cuda.current_stream()
             ready = {b.ready_after_group: bi for bi, b in enumerate(self.buckets)}
 
-            def after_layer(li):
+            def after_layer(li, side_events):
                 bi = ready.get(li)
                 if bi is None:
                     return
@@ -138,17 +141,19 @@ class Trainer:
                 ev = torch.cuda.Event()
                 ev.record(main)
                 self.comm_stream.wait_event(ev)
+                for sev in side_events:           # the bucket's last weight gradient (side branch)
+                    self.comm_stream.wait_event(sev)
                 with torch.cuda.stream(self.comm_stream):
                     self._sync_range(off, n, slot_base=bi * self.comm_blocks)
 
-            eng.backward(B, after_layer=after_layer)
+            eng.backward(B, after_layer=after_layer, side_stream=self.wgrad_stream)
             done = torch.cuda.Event()
             done.record(self.comm_stream)
             main.wait_event(done)
             if not self.fuse_sgd:
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
         else:
-            eng.backward(B)
+            eng.backward(B, side_stream=self.wgrad_stream)
             if self.granularity == "param":
                 # one launch per parameter tensor, like the reference's python loop
                 for i in range(len(a.params)):

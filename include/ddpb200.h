@@ -70,7 +70,7 @@ void ddpb_conv_debug_timing(unsigned long long* per_cta_stamps);
 int ddpb_channel_stats(const void* x, float* stats, long long P, int C, void* stream);
 int ddpb_bn_relu_pool_fwd(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
                           float* saved_mean_rstd, int N, int H, int W, int C, int pool, float eps, void* stream);
-/* O5+O6+O7 backward.  sums: fp32 [2][C] scratch that must be ZERO on entry. */
+/* O5+O6+O7 backward.  sums: fp32 scratch of 2*C + 32 floats that must be ZERO on entry. */
 int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float* saved_mean_rstd, const float* gamma,
                           const float* beta, float* sums, void* dx, float* dgamma, float* dbeta, float* dbias, int N,
                           int H, int W, int C, int pool, float eps, void* stream);

@@ -151,10 +151,13 @@ def test_conv_wgrad_first_layer_compact():
     assert _rel_err(dw, ref) < 2e-3
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("pool", [False, True])
-@pytest.mark.parametrize("geom", [(8, 32, 32, 64), (8, 8, 8, 256), (16, 2, 2, 512)])
-def test_bn_relu_pool_fwd_bwd(geom, pool):
+@pytest.mark.parametrize("geom", [(8, 32, 32, 64), (8, 8, 8, 256), (16, 2, 2, 512), (64, 16, 16, 128)])
+def test_bn_relu_pool_fwd_bwd(geom, pool, fused):
+    """fused=True: single cooperative kernel (slice parked in shared memory); False: two passes."""
     N, H, W, C = geom
+    K.bn_bwd_set_fused(fused)
     x = (torch.randn(N * H * W, C, device=DEV) * 1.5 + 0.3).bfloat16()
     gamma = torch.rand(C, device=DEV) + 0.5
     beta = torch.randn(C, device=DEV) * 0.2
@@ -171,6 +174,7 @@ def test_bn_relu_pool_fwd_bwd(geom, pool):
     assert _rel_err(dx, rdx) < 2e-2
     assert _rel_err(dgamma, rdg) < 5e-3
     assert _rel_err(dbeta, rdb) < 5e-3
+    K.bn_bwd_set_fused(True)
     # conv-bias gradient = column sums of dx: mathematically zero (SURVEY.md §2.5 numerics note)
     assert dbias.abs().max().item() < 1e-2 * dy.float().abs().sum(0).max().item()
 
