@@ -50,6 +50,9 @@ def parse():
     ap.add_argument("--no-multicast", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--comm-blocks", type=int, default=None)
+    ap.add_argument("--bucket-layout", choices=["per_layer", "reference"], default="reference")
+    ap.add_argument("--bucket-mb", type=float, default=None, help="explicit bucket cap in MiB (first bucket: min(1, cap))")
+    ap.add_argument("--no-fuse-sgd", action="store_true", help="run SGD as its own full-width kernel after the sync")
     ap.add_argument("--symm-backend", default=None)
     return ap.parse_args()
 
@@ -130,7 +133,10 @@ def run_ours(a):
     trainer = ddpb200.Trainer(model, mode=mode, batch_size=per_gpu, lr=0.1, momentum=0.9, weight_decay=1e-4,
                               rank=rank, world_size=world, granularity=a.granularity,
                               use_multicast=False if a.no_multicast else "auto", use_graph=not a.no_graph,
-                              comm_blocks=a.comm_blocks, symm_backend=a.symm_backend)
+                              comm_blocks=a.comm_blocks, symm_backend=a.symm_backend, bucket_layout=a.bucket_layout,
+                              fuse_sgd=not a.no_fuse_sgd,
+                              first_bucket_bytes=None if a.bucket_mb is None else int(min(1.0, a.bucket_mb) * 2**20),
+                              bucket_bytes=None if a.bucket_mb is None else int(a.bucket_mb * 2**20))
     n_rot = 8
     host = synthetic_host_batches(n_rot, per_gpu, seed=1234 + rank)
     dev_batches = [(i.to(device), l.to(device), g.to(device)) for i, l, g in host]
@@ -188,7 +194,7 @@ def run_ours(a):
                        "per_gpu_batch": per_gpu, "seq_len": None, "parallelism": f"{par}{world}", "mode": mode,
                        "optimizer": "SGD lr=0.1 momentum=0.9 wd=1e-4 (inside the timed step)",
                        "sync": None if world == 1 else {"backend": trainer.symm.backend, "multicast": trainer.use_mc,
-                                                       "granularity": a.granularity, "buckets_floats": [b.numel for b in trainer.buckets] if mode == "ddp" else None},
+                                                       "granularity": a.granularity, "bucket_layout": a.bucket_layout if mode == "ddp" else None, "comm_blocks": trainer.comm_blocks, "buckets_floats": [b.numel for b in trainer.buckets] if mode == "ddp" else None},
                        "cuda_graph": not a.no_graph,
                        "l2": f"no explicit flush: working set {ws_mb:.0f} MB/step > 126 MB L2; inputs rotate over {n_rot} device batches",
                        "baseline_ref": "BASELINE.md §1: published CPU/Gloo images/s for this worker count"},

@@ -420,10 +420,14 @@ __device__ __forceinline__ void grid_barrier_once(unsigned int* counter, unsigne
   __syncthreads();
 }
 
-constexpr int kBnFusedThreads = 512;   // one CTA per SM: more threads = more loads in flight
+// 256 threads x <=128 registers: small enough to share an SM with a gradient-sync CTA (512
+// threads, ~40 registers).  A cooperative launch needs ALL its CTAs resident at once, so a
+// fatter CTA would make every fused BatchNorm backward wait for the overlapped reductions of
+// mode 'ddp' to drain (measured: per-layer buckets got slower, profiles/r1_call18_*).
+constexpr int kBnFusedThreads = 256;
 
 template <bool kPool>
-__global__ void __launch_bounds__(kBnFusedThreads, 1)
+__global__ void __launch_bounds__(kBnFusedThreads, 2)
 bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                     const float* __restrict__ saved, const float* __restrict__ gamma,
                     const float* __restrict__ beta, float* __restrict__ sums /* [2][C] zero, then counter */,

@@ -43,6 +43,7 @@ struct SgdArgs {
   float* m;   // momentum arena (local)
   __nv_bfloat16* shadow;  // bf16 copy of the parameters (conv operand), may be null
   float lr, mu, wd;
+  long long off, n4;      // range the update covers (may be wider than the synchronised range)
 };
 
 #ifndef DDPB_COMM_TIMEOUT_NS
@@ -84,6 +85,40 @@ __device__ __forceinline__ void peer_barrier(const CommCtx& c, int slot) {
       }
     }
     __threadfence_system();
+  }
+  __syncthreads();
+}
+
+// All CTAs of THIS kernel on THIS GPU meet (sense-reversing, self-resetting: safe across
+// launches and graph replays).  peer_barrier only pairs CTA b with CTA b of the peers, so
+// "my peers' CTA b finished" says nothing about their CTA b'; the fused SGD reads the whole
+// range and therefore must wait until every local CTA has passed its peer barrier.  The two
+// words live at the end of the local signal pad.  Requires all CTAs co-resident (grid <= SMs;
+// used only by launches that own the GPU: the last reduction of an iteration).
+__device__ __forceinline__ void local_grid_barrier(const CommCtx& c) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* count = c.sig[c.rank] + (kSignalPadBytes / 4 - 2);
+    uint32_t* gen = count + 1;
+    uint32_t g;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(gen) : "memory");
+    __threadfence();
+    if (atomicAdd(count, 1u) == gridDim.x - 1) {
+      *count = 0;
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(gen), "r"(g + 1) : "memory");
+    } else {
+      const unsigned long long t0 = global_timer_ns();
+      uint32_t now, spins = 0;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(now) : "l"(gen) : "memory");
+        if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_COMM_TIMEOUT_NS) {
+          printf("ddpb200: rank %d local grid barrier timed out (block %d)\n", c.rank, blockIdx.x);
+          __trap();
+        }
+      } while (now == g);
+    }
+    __threadfence();
   }
   __syncthreads();
 }
@@ -179,7 +214,10 @@ allreduce_avg_kernel(const CommCtx c, long long off, long long n4, int slot_base
     }
   }
   peer_barrier(c, slot);  // every slice has landed everywhere
-  if (sgd.p != nullptr) sgd_range(c, sgd, off, n4);
+  if (sgd.p != nullptr) {
+    local_grid_barrier(c);   // ... as seen by ALL of this GPU's CTAs, not just this one
+    sgd_range(c, sgd, sgd.off, sgd.n4);
+  }
 }
 
 // part2a: the root pulls every rank's gradients, averages, pushes the mean to everyone.
@@ -213,7 +251,10 @@ reduce_root_bcast_kernel(const CommCtx c, long long off, long long n4, int slot_
     }
   }
   peer_barrier(c, slot);
-  if (sgd.p != nullptr) sgd_range(c, sgd, off, n4);
+  if (sgd.p != nullptr) {
+    local_grid_barrier(c);
+    sgd_range(c, sgd, sgd.off, sgd.n4);
+  }
 }
 
 // Root's range is copied into every peer's buffer.
@@ -266,7 +307,7 @@ static int fill_ctx(CommCtx* c, const void* const* bufs, const void* mc, int ran
 static int check_range(long long off, long long n, int blocks, int slot_base) {
   DDPB_REQUIRE(off >= 0 && off % 4 == 0 && n >= 0 && n % 4 == 0,
                "comm: offset/count must be multiples of 4 floats (got %lld/%lld)", off, n);
-  DDPB_REQUIRE(blocks >= 1 && slot_base >= 0 && (slot_base + blocks) * kMaxRanks * 4 <= kSignalPadBytes,
+  DDPB_REQUIRE(blocks >= 1 && slot_base >= 0 && (slot_base + blocks) * kMaxRanks * 4 <= kSignalPadBytes - 64,
                "comm: %d blocks from slot %d do not fit the signal pad", blocks, slot_base);
   return 0;
 }
@@ -282,14 +323,23 @@ extern "C" int ddpb_comm_max_ranks() { return kMaxRanks; }
 // (bufs[rank] is the local one); mc: multicast mapping of the same buffer or null.
 // off/n: range inside the gradient arena in floats.  p/m: local parameter and momentum
 // arenas for the fused SGD step (null = only synchronise).  use_mc selects NVLS.
+// sgd_off/sgd_n: range the fused update covers; sgd_n < 0 means "the synchronised range".  A
+// wider range lets the LAST reduction of an iteration also apply the update for gradients
+// that earlier (overlapped, SGD-free) reductions already averaged.
 extern "C" int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int rank, int world, long long off,
                                   long long n, int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow,
-                                  float lr, float momentum, float weight_decay, cudaStream_t stream) {
+                                  float lr, float momentum, float weight_decay, long long sgd_off, long long sgd_n,
+                                  cudaStream_t stream) {
   CommCtx c;
   if (int rc = fill_ctx(&c, bufs, mc, rank, world)) return rc;
   if (int rc = check_range(off, n, blocks, slot_base)) return rc;
   DDPB_REQUIRE(!use_mc || c.mc != nullptr, "comm: multicast requested but no multicast mapping");
-  SgdArgs s{p, m, static_cast<__nv_bfloat16*>(shadow), lr, momentum, weight_decay};
+  if (sgd_n < 0) {   // default: update exactly the synchronised range
+    sgd_off = off;
+    sgd_n = n;
+  }
+  DDPB_REQUIRE(sgd_off >= 0 && sgd_off % 4 == 0 && sgd_n % 4 == 0, "comm: SGD range must be multiples of 4 floats");
+  SgdArgs s{p, m, static_cast<__nv_bfloat16*>(shadow), lr, momentum, weight_decay, sgd_off, sgd_n / 4};
   if (use_mc)
     allreduce_avg_kernel<true><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, s);
   else
@@ -301,13 +351,18 @@ extern "C" int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int r
 extern "C" int ddpb_reduce_root_bcast(const void* const* bufs, const void* mc, int rank, int world, int root,
                                       long long off, long long n, int blocks, int slot_base, int use_mc, float* p,
                                       float* m, void* shadow, float lr, float momentum, float weight_decay,
-                                      cudaStream_t stream) {
+                                      long long sgd_off, long long sgd_n, cudaStream_t stream) {
   CommCtx c;
   if (int rc = fill_ctx(&c, bufs, mc, rank, world)) return rc;
   if (int rc = check_range(off, n, blocks, slot_base)) return rc;
   DDPB_REQUIRE(root >= 0 && root < world, "comm: bad root %d", root);
   DDPB_REQUIRE(!use_mc || c.mc != nullptr, "comm: multicast requested but no multicast mapping");
-  SgdArgs s{p, m, static_cast<__nv_bfloat16*>(shadow), lr, momentum, weight_decay};
+  if (sgd_n < 0) {   // default: update exactly the synchronised range
+    sgd_off = off;
+    sgd_n = n;
+  }
+  DDPB_REQUIRE(sgd_off >= 0 && sgd_off % 4 == 0 && sgd_n % 4 == 0, "comm: SGD range must be multiples of 4 floats");
+  SgdArgs s{p, m, static_cast<__nv_bfloat16*>(shadow), lr, momentum, weight_decay, sgd_off, sgd_n / 4};
   if (use_mc)
     reduce_root_bcast_kernel<true><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, root, s);
   else

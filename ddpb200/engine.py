@@ -243,6 +243,8 @@ class VGGEngine:
         feat = self.act[last][:N]
         K.fc_bwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), self.dlogits[:N],
                  dw=a.flat_grad(self.p_fcw), db=a.flat_grad(self.p_fcb), dx=self.dact[last])
+        if after_layer is not None:
+            after_layer(last + 1, [])   # the classifier is parameter group len(layers)
         for li in range(last, -1, -1):
             L = self.layers[li]
             x_in = self.operand0 if li == 0 else self.act[li - 1]

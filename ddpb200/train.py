@@ -43,7 +43,9 @@ class DistributedDataParallel(nn.Module):
     overlapped gradient averaging.  The reducer itself lives in Trainer (mode 'ddp'): buckets
     are slices of the flat gradient arena, reduced by a peer-memory kernel on a side stream."""
 
-    def __init__(self, module: nn.Module, bucket_cap_mb: float = 25.0):
+    def __init__(self, module: nn.Module, bucket_cap_mb: float | None = None):
+        """bucket_cap_mb=None: torch DDP's default layout (1 MiB first bucket, 25 MiB cap), as in the
+        reference; a number selects that cap instead."""
         super().__init__()
         self.module = module
         self.bucket_cap_mb = bucket_cap_mb
@@ -65,7 +67,8 @@ def _trainer_for(model, optimizer, mode, rank, world_size, batch_size, **kw) -> 
         return tr
     g = optimizer.param_groups[0] if optimizer is not None else dict(lr=0.1, momentum=0.9, weight_decay=1e-4)
     inner = model.module if isinstance(model, DistributedDataParallel) else model
-    if isinstance(model, DistributedDataParallel):
+    if isinstance(model, DistributedDataParallel) and model.bucket_cap_mb is not None:
+        kw.setdefault("bucket_layout", "reference")
         kw.setdefault("bucket_bytes", int(model.bucket_cap_mb * 1024 * 1024))
     tr = Trainer(inner, mode=mode, batch_size=batch_size, lr=g["lr"], momentum=g["momentum"],
                  weight_decay=g["weight_decay"], rank=rank, world_size=world_size, **kw)

@@ -103,18 +103,20 @@ int ddpb_first_layer_operand_u8(const unsigned char* src_nhwc, const signed char
 /* bufs: `world` base pointers of the symmetric buffers ([64 KiB signal pad | fp32 payload]) as
  * mapped in this process; mc: NVLS multicast mapping of the same buffer or null; off/n: payload
  * range in floats (multiples of 4); blocks/slot_base: CTAs and their signal-pad slots;
- * p/m/shadow: local parameter / momentum / bf16 arenas for the fused SGD step (p null = none). */
+ * p/m/shadow: local parameter / momentum / bf16 arenas for the fused SGD step (p null = none);
+ * sgd_off/sgd_n: range that update covers (sgd_n < 0: the synchronised range). */
 int ddpb_comm_signal_pad_bytes(void);
 int ddpb_comm_max_ranks(void);
 /* part2b dist.all_reduce(SUM) + divide (part2/part2b/main.py:97-103) and part3's bucketed
  * all-reduce (part3/main.py:174): in-place two-shot all-reduce, mean, optional SGD. */
 int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int rank, int world, long long off, long long n,
                        int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow, float lr,
-                       float momentum, float weight_decay, void* stream);
+                       float momentum, float weight_decay, long long sgd_off, long long sgd_n, void* stream);
 /* part2a gather -> mean on rank 0 -> scatter (part2/part2a/main.py:97-115). */
 int ddpb_reduce_root_bcast(const void* const* bufs, const void* mc, int rank, int world, int root, long long off,
                            long long n, int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow,
-                           float lr, float momentum, float weight_decay, void* stream);
+                           float lr, float momentum, float weight_decay, long long sgd_off, long long sgd_n,
+                           void* stream);
 /* DDP's constructor-time parameter broadcast. */
 int ddpb_broadcast(const void* const* bufs, const void* mc, int rank, int world, int root, long long off,
                    long long n, int blocks, int slot_base, int use_mc, void* stream);

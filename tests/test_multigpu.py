@@ -74,7 +74,8 @@ dist.destroy_process_group()
 '''
 
 
-def _run(mode, gran="fused", mc=False, world=2):
+def _run(mode, gran="fused", mc=False, world=None):
+    world = world or int(os.environ.get("DDPB_TEST_WORLD", "2"))
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     script = Path(os.environ.get("TMPDIR", "/tmp")) / "ddpb_mgpu_worker.py"
