@@ -20,20 +20,6 @@ struct BnGeom {
   float eps;
 };
 
-__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
-  const uint4 u = *reinterpret_cast<const uint4*>(p);
-  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
-}
-__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
-  uint4 u;
-  u.x = pack_bf16x2(v[0], v[1]);
-  u.y = pack_bf16x2(v[2], v[3]);
-  u.z = pack_bf16x2(v[4], v[5]);
-  u.w = pack_bf16x2(v[6], v[7]);
-  *reinterpret_cast<uint4*>(p) = u;
-}
-
 // scale/shift per channel in shared memory: y = x*scale + shift.
 __device__ __forceinline__ void bn_coeffs_to_smem(const float* __restrict__ stats, const float* __restrict__ gamma,
                                                   const float* __restrict__ beta, int C, float count, float eps,
@@ -650,9 +636,17 @@ extern "C" int ddpb_channel_stats(const void* x, float* stats, long long P, int 
 
 // y = maxpool2x2?(relu(batchnorm(x)));  x: [N*H*W][C] bf16 raw conv output, stats: [2][C]
 // sums over those rows, saved: [2][C] receives (mean, rstd) for the backward pass.
+int bn_relu_pool_fwd_launch(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
+                            float* saved, int N, int H, int W, int C, int pool, float eps, cudaStream_t stream);
+
 extern "C" int ddpb_bn_relu_pool_fwd(const void* x, const float* stats, const float* gamma, const float* beta,
                                      void* y, float* saved, int N, int H, int W, int C, int pool, float eps,
                                      cudaStream_t stream) {
+  return bn_relu_pool_fwd_launch(x, stats, gamma, beta, y, saved, N, H, W, C, pool, eps, stream);
+}
+
+int bn_relu_pool_fwd_launch(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
+                            float* saved, int N, int H, int W, int C, int pool, float eps, cudaStream_t stream) {
   DDPB_BN_CHECK_GEOM("bn_relu_pool_fwd");
   BnGeom g{N, H, W, C, pool, eps};
   const long long items = static_cast<long long>(N) * (pool ? H / 2 : H) * (pool ? W / 2 : W) * (C / 8);

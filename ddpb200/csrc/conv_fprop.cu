@@ -52,6 +52,14 @@ struct FpropParams {
   int bh, bn, hblocks;   // TMA box geometry: box = (64, W, bh, bn); hblocks = H / bh
   float* partial;        // split-K: fp32 [gridDim.z][P][C_out] partial sums (null when gridDim.z == 1)
   unsigned long long* dbg;  // optional per-CTA timestamps {start, after set-up, mainloop done, epilogue done}
+  // fused BatchNorm + ReLU (+2x2 max-pool) tail of the persistent kernel (act == null: off)
+  const float* gamma;
+  const float* beta;
+  __nv_bfloat16* act;    // [P or P/4][C_out]
+  float* saved;          // [2][C_out] mean, rstd for the backward pass
+  unsigned int* grid_sync;  // one zeroed word: all CTAs meet here once the statistics are complete
+  int H, W, pool;
+  float eps;
 };
 
 __device__ __forceinline__ void dbg_stamp(const FpropParams& p, int slot) {
@@ -638,8 +646,19 @@ extern "C" long long ddpb_conv_fprop_scratch_elems(int N, int H, int W, int C_in
 // Shared host path.  dgrad == 0: y[P][C_out] = conv(x[..C_in], w[C_out][taps*C_in]).
 // dgrad == 1: x is dY [..C_in := layer C_out], w is the layer's FPROP pack
 // [layer C_out][taps][layer C_in], y = dX [P][C_out := layer C_in].
+struct BnTail {
+  const float* gamma;
+  const float* beta;
+  void* act;
+  float* saved;
+  int pool;
+  float eps;
+};
+
+// Returns 0 on success; *fused_bn (if given) tells whether the BatchNorm tail ran inside the conv kernel.
 static int conv_impl(int dgrad, const void* x, const void* w, const float* bias, void* y, float* stats, int N, int H,
-                     int W, int C_in, int C_out, int taps, int block_n, float* scratch, cudaStream_t stream) {
+                     int W, int C_in, int C_out, int taps, int block_n, float* scratch, cudaStream_t stream,
+                     const BnTail* bn_tail = nullptr, int* fused_bn = nullptr) {
   const char* name = dgrad ? "conv_dgrad" : "conv_fprop";
   DDPB_REQUIRE(taps == 1 || taps == 9, "%s: taps must be 1 or 9 (got %d)", name, taps);
   DDPB_REQUIRE(C_in % 64 == 0 && C_in > 0, "%s: reduction channels must be a multiple of 64 (got %d)", name, C_in);
@@ -692,6 +711,26 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   p.bn = bn;
   p.hblocks = hblocks;
   p.dbg = g_dbg;
+  p.gamma = p.beta = nullptr;
+  p.act = nullptr;
+  p.saved = nullptr;
+  p.grid_sync = nullptr;
+  p.H = H;
+  p.W = W;
+  p.pool = 0;
+  p.eps = 0.f;
+  if (fused_bn != nullptr) *fused_bn = 0;
+  // BatchNorm tail inside the kernel: persistent kernel, no split-K, whole 2x2 windows per tile
+  if (bn_tail != nullptr && stats != nullptr && pl.pair == 2 && pl.splits == 1 && (!bn_tail->pool || bh % 2 == 0)) {
+    p.gamma = bn_tail->gamma;
+    p.beta = bn_tail->beta;
+    p.act = static_cast<__nv_bfloat16*>(bn_tail->act);
+    p.saved = bn_tail->saved;
+    p.grid_sync = reinterpret_cast<unsigned int*>(stats + 2 * C_out);
+    p.pool = bn_tail->pool;
+    p.eps = bn_tail->eps;
+    if (fused_bn != nullptr) *fused_bn = 1;
+  }
   const int m_tiles = (p.P + kBlockM - 1) / kBlockM;
   const int splits = pl.splits;
   p.partial = splits > 1 ? scratch : nullptr;
@@ -739,6 +778,26 @@ extern "C" int ddpb_conv_fprop(const void* x, const void* w, const float* bias, 
                                int N, int H, int W, int C_in, int C_out, int taps, int block_n,
                                float* scratch, cudaStream_t stream) {
   return conv_impl(0, x, w, bias, y, stats, N, H, W, C_in, C_out, taps, block_n, scratch, stream);
+}
+
+int bn_relu_pool_fwd_launch(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
+                            float* saved, int N, int H, int W, int C, int pool, float eps, cudaStream_t stream);
+
+// Convolution + BatchNorm(batch statistics) + ReLU (+ 2x2 max-pool) forward: O1+O4+O6+O7.
+// conv_out ([N*H*W][C_out] bf16) is still written (the backward pass needs it); act is the
+// block's output.  stats: fp32 scratch of 2*C_out + 32 floats, ZERO on entry.  When the
+// persistent kernel runs without split-K the normalisation happens inside it after a
+// grid-wide barrier; otherwise the separate BatchNorm kernel is launched.
+extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const float* bias, void* conv_out,
+                                          float* stats, const float* gamma, const float* beta, void* act,
+                                          float* saved, int N, int H, int W, int C_in, int C_out, int taps,
+                                          int pool, float eps, float* scratch, cudaStream_t stream) {
+  BnTail bn{gamma, beta, act, saved, pool, eps};
+  int fused = 0;
+  if (int rc = conv_impl(0, x, w, bias, conv_out, stats, N, H, W, C_in, C_out, taps, 0, scratch, stream, &bn, &fused))
+    return rc;
+  if (fused) return 0;
+  return bn_relu_pool_fwd_launch(conv_out, stats, gamma, beta, act, saved, N, H, W, C_out, pool, eps, stream);
 }
 
 // Data gradient of the 3x3 convolution (O2).  dy: [N][H][W][C_out] bf16; w: the SAME bf16 pack

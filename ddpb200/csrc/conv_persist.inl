@@ -291,11 +291,103 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
 
   tc_fence_before();
   __syncthreads();
-  if (threadIdx.x == 0) dbg_stamp(p, 3);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
+
+  // ===================== fused BatchNorm + ReLU (+ pool) =====================
+  // The conv output of this layer is only ever consumed by its BatchNorm, whose statistics
+  // were accumulated by the epilogues above.  Instead of a second kernel, all CTAs meet at a
+  // grid-wide barrier (they are co-resident: one per SM), turn the global sums into
+  // scale/shift and then normalise the tiles THEY just wrote (still in L2).  Every 128-pixel
+  // tile holds whole 2x2 pooling windows, so no CTA needs another CTA's pixels.
+  if (p.act != nullptr) {
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      atomicAdd(p.grid_sync, 1u);
+      const unsigned long long t0 = global_timer_ns();
+      unsigned int seen, spins = 0;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.grid_sync) : "memory");
+        if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_WAIT_TIMEOUT_NS) {
+          printf("ddpb200: conv+bn grid barrier timed out (block %d: %u of %u)\n", blockIdx.x, seen, gridDim.x);
+          __trap();
+        }
+      } while (seen < gridDim.x);
+      __threadfence();
+    }
+    __syncthreads();
+    // the operand ring is idle now: reuse it for the per-channel coefficients
+    float* s_scale = reinterpret_cast<float*>(tiles);
+    float* s_shift = s_scale + p.C_out;
+    const float inv_count = 1.f / static_cast<float>(p.P);
+    for (int c = threadIdx.x; c < p.C_out; c += blockDim.x) {
+      const float mean = __ldcg(p.stats + c) * inv_count;
+      float var = __ldcg(p.stats + p.C_out + c) * inv_count - mean * mean;
+      var = fmaxf(var, 0.f);
+      const float rstd = rsqrtf(var + p.eps);
+      const float sc = p.gamma[c] * rstd;
+      s_scale[c] = sc;
+      s_shift[c] = p.beta[c] - mean * sc;
+      if (blockIdx.x == 0 && p.saved != nullptr) {
+        p.saved[c] = mean;
+        p.saved[p.C_out + c] = rstd;
+      }
+    }
+    __syncthreads();
+    constexpr int kGroups = BLOCK_N / 8;                 // 16-byte channel groups per tile row
+    const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
+    const int out_rows = p.pool ? kBlockM / 4 : kBlockM; // output pixels per tile
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+      const PersistItem it = persist_item(item, m_tiles, n_tiles);
+      const int n_img0 = (it.m_tile / p.hblocks) * p.bn;
+      const int h0 = (it.m_tile % p.hblocks) * p.bh;
+      for (int w_item = threadIdx.x; w_item < out_rows * kGroups; w_item += blockDim.x) {
+        const int cgp = w_item % kGroups;
+        const int orow = w_item / kGroups;
+        const int ch = it.n_tile * BLOCK_N + cgp * 8;
+        float sc[8], sh[8], o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          sc[j] = s_scale[ch + j];
+          sh[j] = s_shift[ch + j];
+        }
+        long long opix;
+        if (!p.pool) {
+          const long long pix = static_cast<long long>(it.m_tile) * kBlockM + orow;
+          if (pix >= p.P) continue;
+          opix = pix;
+          float v[8];
+          load8(p.out + pix * p.C_out + ch, v);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = fmaxf(fmaf(v[j], sc[j], sh[j]), 0.f);
+        } else {
+          // output pixel (n_local, ho, wo) of this tile's (bn, bh/2, W/2) block
+          const int wo = orow % Wo;
+          const int t2 = orow / Wo;
+          const int ho = t2 % (p.bh / 2);
+          const int n_local = t2 / (p.bh / 2);
+          const int n_img = n_img0 + n_local;
+          const long long in00 = (static_cast<long long>(n_img) * p.H + h0 + 2 * ho) * p.W + 2 * wo;
+          if (in00 >= p.P) continue;
+          opix = (static_cast<long long>(n_img) * Ho + (h0 / 2 + ho)) * Wo + wo;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = 0.f;
+#pragma unroll
+          for (int d = 0; d < 4; ++d) {
+            float v[8];
+            load8(p.out + (in00 + (d >> 1) * p.W + (d & 1)) * p.C_out + ch, v);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], fmaf(v[j], sc[j], sh[j]));
+          }
+        }
+        store8(p.act + opix * p.C_out + ch, o);
+      }
+    }
+  }
+  if (threadIdx.x == 0) dbg_stamp(p, 3);
 }
 
 template <int BLOCK_N, bool kDgrad>

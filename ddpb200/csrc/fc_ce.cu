@@ -17,7 +17,15 @@ fc_ce_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ 
                  const long long* __restrict__ labels, float* __restrict__ logits, float* __restrict__ row_loss,
                  float* __restrict__ dlogits, int* __restrict__ row_correct, int B, int F, int K) {
   extern __shared__ float s_w[];  // [K][F]
-  for (int i = threadIdx.x; i < K * F; i += blockDim.x) s_w[i] = w[i];
+  {
+    // 16-byte loads, several in flight per thread: the staging is pure latency otherwise
+    const int n4 = (K * F) >> 2;
+    const float4* w4 = reinterpret_cast<const float4*>(w);
+    float4* s4 = reinterpret_cast<float4*>(s_w);
+#pragma unroll 8
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) s4[i] = __ldg(w4 + i);
+    for (int i = (n4 << 2) + threadIdx.x; i < K * F; i += blockDim.x) s_w[i] = w[i];
+  }
   __syncthreads();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -26,7 +34,7 @@ fc_ce_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ 
 #pragma unroll
   for (int j = 0; j < kMaxClasses; ++j) acc[j] = 0.f;
   const __nv_bfloat16* xr = x + static_cast<long long>(warp) * F;
-#pragma unroll 4
+#pragma unroll 16
   for (int i = lane; i < F; i += 32) {
     const float xv = __bfloat162float(xr[i]);
 #pragma unroll
@@ -124,9 +132,10 @@ fc_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, 
   }
   for (int r0 = 0; r0 < B; r0 += kFcRows) {
     const int rows = (B - r0) < kFcRows ? (B - r0) : kFcRows;
-    for (int i = threadIdx.x; i < rows * K; i += blockDim.x) s_dl[i] = dlogits[static_cast<long long>(r0) * K + i];
+#pragma unroll 8
+    for (int i = threadIdx.x; i < rows * K; i += blockDim.x) s_dl[i] = __ldg(dlogits + static_cast<long long>(r0) * K + i);
     __syncthreads();
-#pragma unroll 4
+#pragma unroll 16
     for (int r = slice; r < rows; r += 8) {
       const float xv = fok ? __bfloat162float(x[static_cast<long long>(r0 + r) * F + f]) : 0.f;
       float dxv = 0.f;
@@ -140,8 +149,13 @@ fc_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, 
       }
       if (dx != nullptr && fok) dx[static_cast<long long>(r0 + r) * F + f] = __float2bfloat16_rn(dxv);
     }
-    if (blockIdx.x == 0 && threadIdx.x < K)
-      for (int r = 0; r < rows; ++r) dbv += s_dl[r * K + threadIdx.x];
+    if (blockIdx.x == 0) {
+      // db: every thread sums a strided share of the rows for class (tid % 16), then the 16
+      // threads that share a class are combined below
+      const int j = threadIdx.x & 15;
+      if (j < K)
+        for (int r = threadIdx.x >> 4; r < rows; r += 16) dbv += s_dl[r * K + j];
+    }
     __syncthreads();
   }
 #pragma unroll
@@ -158,7 +172,18 @@ fc_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, 
       }
     }
   }
-  if (blockIdx.x == 0 && threadIdx.x < K) db[threadIdx.x] = dbv;
+  if (blockIdx.x == 0) {
+    __syncthreads();                      // s_part is free again
+    float* s_db = &s_part[0][0][0];       // [16 row groups][16 classes]
+    s_db[(threadIdx.x >> 4) * 16 + (threadIdx.x & 15)] = dbv;
+    __syncthreads();
+    if (threadIdx.x < K) {
+      float t = 0.f;
+#pragma unroll
+      for (int g = 0; g < 16; ++g) t += s_db[g * 16 + threadIdx.x];
+      db[threadIdx.x] = t;
+    }
+  }
 }
 
 }  // namespace ddpb

@@ -136,13 +136,13 @@ class VGGEngine:
             self.dconv.append(torch.empty(P, L.c_out, **bf))
             self.dact.append(torch.empty(Po, L.c_out, **bf))
         # --- per-channel statistics: one arena so a single memset clears all of it
-        csum = sum(2 * L.c_out + 16 for L in self.layers)      # backward slots carry 32 extra words
+        csum = sum(2 * L.c_out + 32 for L in self.layers)      # every slot carries 32 extra words
         self.stat_arena = torch.zeros(2 * csum, **f32)
         self.stats, self.bsums, self.saved = [], [], []
         o = 0
         for L in self.layers:
-            self.stats.append(self.stat_arena[o:o + 2 * L.c_out])
-            o += 2 * L.c_out
+            self.stats.append(self.stat_arena[o:o + 2 * L.c_out + 32])   # sums + grid-barrier word
+            o += 2 * L.c_out + 32
         for L in self.layers:
             self.bsums.append(self.stat_arena[o:o + 2 * L.c_out + 32])   # sums + grid-barrier word
             o += 2 * L.c_out + 32
@@ -208,10 +208,12 @@ class VGGEngine:
         self.stat_arena.zero_()
         x = self.operand0
         for li, L in enumerate(self.layers):
-            K.conv_fprop(x, self.w_f[li], a.flat_master(L.p_b), N, L.H, L.W, L.c_in_eff, L.c_out, L.taps,
-                         out=self.conv_out[li], stats=self.stats[li], scratch=self.fprop_scratch)
-            K.bn_relu_pool_fwd(self.conv_out[li], self.stats[li], a.flat_master(L.p_g), a.flat_master(L.p_beta), N,
-                               L.H, L.W, L.c_out, L.pool, out=self.act[li], saved=self.saved[li])
+            # conv (+bias, +statistics) and, inside the same persistent kernel after a grid-wide
+            # barrier, BatchNorm + ReLU (+pool); split-K layers fall back to the separate kernel
+            K.conv_bn_relu_pool_fwd(x, self.w_f[li], a.flat_master(L.p_b), a.flat_master(L.p_g),
+                                    a.flat_master(L.p_beta), N, L.H, L.W, L.c_in_eff, L.c_out, L.taps, L.pool,
+                                    conv_out=self.conv_out[li], act=self.act[li], stats=self.stats[li],
+                                    saved=self.saved[li], scratch=self.fprop_scratch)
             x = self.act[li]
         feat = x[:N]
         if with_loss:
@@ -283,9 +285,9 @@ class VGGEngine:
         n = 0
         B = self.max_batch
         for li, L in enumerate(self.layers):
-            n += 2                  # fprop, bn fwd
+            n += 1                  # fprop (BatchNorm forward fused in)
             if K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps):
-                n += 1              # split-K finalize
+                n += 2              # split-K finalize + separate BatchNorm forward
             if li > 0 and K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_out, L.c_in, 9):
                 n += 1
             n += 2                  # bn bwd (two passes)

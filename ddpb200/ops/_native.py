@@ -30,6 +30,7 @@ _SIGNATURES = {
     "ddpb_conv_fprop": [c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                         c_void, c_void],
     "ddpb_conv_fprop_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int, c_int],
+    "ddpb_conv_bn_relu_pool_fwd": [c_void] * 9 + [c_int] * 7 + [c_float, c_void, c_void],
     "ddpb_conv_force": [c_int, c_int, c_int],
     "ddpb_conv_debug_timing": [c_void],
     "ddpb_conv_plan": [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void],

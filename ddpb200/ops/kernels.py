@@ -64,6 +64,36 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, N: i
     return out
 
 
+def conv_bn_relu_pool_fwd(x, w, bias, gamma, beta, N, H, W, C_in, C_out, taps, pool: bool, *, conv_out=None, act=None,
+                          stats=None, saved=None, scratch: torch.Tensor | None | bool = True, eps=BN_EPS,
+                          stream=None):
+    """O1+O4+O6+O7: conv -> BatchNorm(batch stats) -> ReLU (-> 2x2 max-pool) in one call.  Returns
+    (conv_out, act, saved).  ``stats``: zeroed fp32 scratch of 2*C_out + 32 elements."""
+    nat.require_cuda(x, w, gamma, beta)
+    dev = x.device
+    P = N * H * W
+    Po = P // 4 if pool else P
+    if conv_out is None:
+        conv_out = torch.empty(P, C_out, dtype=torch.bfloat16, device=dev)
+    if act is None:
+        act = torch.empty(Po, C_out, dtype=torch.bfloat16, device=dev)
+    if stats is None:
+        stats = torch.zeros(2 * C_out + 32, dtype=torch.float32, device=dev)
+    assert stats.numel() >= 2 * C_out + 32
+    if saved is None:
+        saved = torch.empty(2, C_out, dtype=torch.float32, device=dev)
+    if scratch is True:
+        need = conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps, 0)
+        scratch = torch.empty(need, dtype=torch.float32, device=dev) if need else None
+    elif scratch is False:
+        scratch = None
+    rc = nat.load().ddpb_conv_bn_relu_pool_fwd(nat.ptr(x), nat.ptr(w), nat.ptr(bias), nat.ptr(conv_out), nat.ptr(stats),
+                                               nat.ptr(gamma), nat.ptr(beta), nat.ptr(act), nat.ptr(saved), N, H, W,
+                                               C_in, C_out, taps, int(pool), eps, nat.ptr(scratch), _s(stream))
+    nat.check(rc, "ddpb_conv_bn_relu_pool_fwd")
+    return conv_out, act, saved
+
+
 def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, C_in: int, C_out: int, *,
                out: torch.Tensor | None = None, block_n: int = 0, scratch: torch.Tensor | None | bool = True,
                stream=None) -> torch.Tensor:

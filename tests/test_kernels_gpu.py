@@ -179,6 +179,29 @@ def test_bn_relu_pool_fwd_bwd(geom, pool, fused):
     assert dbias.abs().max().item() < 1e-2 * dy.float().abs().sum(0).max().item()
 
 
+@pytest.mark.parametrize("pool", [False, True])
+@pytest.mark.parametrize("shape", [(8, 32, 32, 64, 64), (16, 16, 16, 64, 128), (37, 8, 8, 128, 256), (64, 4, 4, 256, 512),
+                                   (96, 2, 2, 512, 512)])
+def test_conv_bn_relu_pool_fused_forward(shape, pool):
+    """conv + BatchNorm + ReLU (+pool) in one call (BatchNorm tail inside the persistent kernel
+    after a grid barrier, or the split-K fallback) against the ATen composition."""
+    N, H, W, Ci, Co = shape
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
+    b = torch.randn(Co, device=DEV) * 0.1
+    gamma = torch.rand(Co, device=DEV) + 0.5
+    beta = torch.randn(Co, device=DEV) * 0.2
+    conv_out, act, saved = K.conv_bn_relu_pool_fwd(x, w, b, gamma, beta, N, H, W, Ci, Co, 9, pool)
+    torch.cuda.synchronize()
+    ref_conv = R.conv_fprop(x, w, b, N, H, W, Ci, Co)
+    assert _rel_err(conv_out, ref_conv) < 1e-2
+    ref_act = R.bn_relu_pool_fwd(conv_out, gamma, beta, N, H, W, pool)   # BatchNorm of the stored conv output
+    assert _rel_err(act, ref_act) < 1e-2
+    cf = conv_out.float()
+    assert torch.allclose(saved[0], cf.mean(0), rtol=1e-3, atol=1e-3)
+    assert torch.allclose(saved[1], (cf.var(0, unbiased=False) + 1e-5).rsqrt(), rtol=2e-3)
+
+
 @pytest.mark.parametrize("B", [32, 256, 85])
 def test_fc_cross_entropy_fwd_bwd(B):
     F_, Kc = 512, 10
