@@ -412,51 +412,55 @@ __device__ __forceinline__ void grid_barrier_once(unsigned int* counter, unsigne
 // mode 'ddp' to drain (measured: per-layer buckets got slower, profiles/r1_call18_*).
 constexpr int kBnFusedThreads = 256;
 
+constexpr int kSliceGroups = 8;   // a CTA owns 8 channel groups = 64 channels ...
+
+// ... and a range of output pixels.  Slicing the channels keeps the per-CTA fixed work
+// (coefficients, atomics: 2 x 64 instead of 2 x C) proportional to what the CTA processes;
+// with whole-C CTAs the 512-channel layers spent most of their time in that overhead.
 template <bool kPool>
 __global__ void __launch_bounds__(kBnFusedThreads, 2)
 bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                     const float* __restrict__ saved, const float* __restrict__ gamma,
                     const float* __restrict__ beta, float* __restrict__ sums /* [2][C] zero, then counter */,
                     __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                    float* __restrict__ dbias, BnGeom g, int items_per_cta) {
+                    float* __restrict__ dbias, BnGeom g, int pix_per_cta, int n_ranges) {
   constexpr int kSlot = kPool ? 5 : 2;          // uint4 words parked per item: window of x + dy
-  extern __shared__ uint4 s_raw[];
-  float* s_coef = reinterpret_cast<float*>(s_raw);          // scale, shift, A, Bc, acc[2]: 6*C floats
-  uint4* s_data = s_raw + (6 * g.C * 4 + 15) / 16;
-  float* s_scale = s_coef;
-  float* s_shift = s_coef + g.C;
-  float* s_A = s_coef + 2 * g.C;
-  float* s_B = s_coef + 3 * g.C;
-  float* s_acc = s_coef + 4 * g.C;
+  constexpr int SC = kSliceGroups * 8;          // channels per CTA
+  __shared__ float s_scale[SC], s_shift[SC], s_A[SC], s_B[SC], s_acc[2 * SC];
+  extern __shared__ uint4 s_data[];
   unsigned int* counter = reinterpret_cast<unsigned int*>(sums + 2 * g.C);
-  for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
-    const float mean = saved[c], rstd = saved[g.C + c];
-    const float sc = gamma[c] * rstd;
+  const int groups = g.C / 8;
+  const int slice = blockIdx.x / n_ranges, range = blockIdx.x % n_ranges;
+  const int c0 = slice * SC;
+  for (int c = threadIdx.x; c < SC; c += blockDim.x) {
+    const float mean = saved[c0 + c], rstd = saved[g.C + c0 + c];
+    const float sc = gamma[c0 + c] * rstd;
     s_scale[c] = sc;
-    s_shift[c] = beta[c] - mean * sc;
+    s_shift[c] = beta[c0 + c] - mean * sc;
     s_acc[c] = 0.f;
-    s_acc[g.C + c] = 0.f;
-    if (blockIdx.x == 0 && dbias != nullptr) dbias[c] = 0.f;
+    s_acc[SC + c] = 0.f;
+    if (range == 0 && dbias != nullptr) dbias[c0 + c] = 0.f;
   }
   __syncthreads();
-  const int groups = g.C / 8;
   const long long out_pix = static_cast<long long>(g.N) * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
-  const long long items = out_pix * groups;
-  const long long begin = static_cast<long long>(blockIdx.x) * items_per_cta;   // multiple of 512, hence of groups
-  long long end = begin + items_per_cta;
-  if (end > items) end = items;
-  const int cg = static_cast<int>(threadIdx.x % groups);
+  const long long p_begin = static_cast<long long>(range) * pix_per_cta;
+  long long p_end = p_begin + pix_per_cta;
+  if (p_end > out_pix) p_end = out_pix;
+  const int n_local = p_end > p_begin ? static_cast<int>(p_end - p_begin) * kSliceGroups : 0;
+  const int lg = threadIdx.x % kSliceGroups;            // my channel group inside the slice (fixed)
+  const int cg = slice * kSliceGroups + lg;             // ... and in the tensor
   float sc[8], sh[8], a1[8], a2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    sc[j] = s_scale[cg * 8 + j];
-    sh[j] = s_shift[cg * 8 + j];
+    sc[j] = s_scale[lg * 8 + j];
+    sh[j] = s_shift[lg * 8 + j];
     a1[j] = a2[j] = 0.f;
   }
   // ---- phase 1: load, park, reduce
-  for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
-    const BwdItem it = bwd_item(g, i, groups);
-    uint4* slot = s_data + (i - begin) * kSlot;
+  for (int i = threadIdx.x; i < n_local; i += blockDim.x) {
+    const long long opix = p_begin + i / kSliceGroups;
+    const BwdItem it = bwd_item(g, opix * groups + cg, groups);
+    uint4* slot = s_data + static_cast<long long>(i) * kSlot;
     const uint4 d = ldg16(dy + it.opix * g.C + cg * 8);
     slot[kSlot - 1] = d;
     if (!kPool) {
@@ -498,38 +502,40 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    group_accumulate(s_acc, a1[j], groups, cg, j);
-    group_accumulate(s_acc + g.C, a2[j], groups, cg, j);
+    group_accumulate(s_acc, a1[j], kSliceGroups, lg, j);
+    group_accumulate(s_acc + SC, a2[j], kSliceGroups, lg, j);
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < 2 * g.C; c += blockDim.x) atomicAdd(&sums[c], s_acc[c]);
+  for (int c = threadIdx.x; c < 2 * SC; c += blockDim.x)
+    atomicAdd(&sums[(c / SC) * g.C + c0 + (c % SC)], s_acc[c]);
   grid_barrier_once(counter, gridDim.x);
   // ---- phase 2: coefficients from the global sums, dx from the parked slice
   const float inv_count = 1.f / static_cast<float>(static_cast<long long>(g.N) * g.H * g.W);
-  for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
-    const float mean = saved[c], rstd = saved[g.C + c];
-    const float sum_g = __ldcg(sums + c);
-    const float sum_gxhat = rstd * (__ldcg(sums + g.C + c) - mean * sum_g);
+  for (int c = threadIdx.x; c < SC; c += blockDim.x) {
+    const float mean = saved[c0 + c], rstd = saved[g.C + c0 + c];
+    const float sum_g = __ldcg(sums + c0 + c);
+    const float sum_gxhat = rstd * (__ldcg(sums + g.C + c0 + c) - mean * sum_g);
     const float A = -s_scale[c] * rstd * sum_gxhat * inv_count;
     s_A[c] = A;
     s_B[c] = -s_scale[c] * sum_g * inv_count - A * mean;
     s_acc[c] = 0.f;
-    if (blockIdx.x == 0) {
-      if (dbeta) dbeta[c] = sum_g;
-      if (dgamma) dgamma[c] = sum_gxhat;
+    if (range == 0) {
+      if (dbeta) dbeta[c0 + c] = sum_g;
+      if (dgamma) dgamma[c0 + c] = sum_gxhat;
     }
   }
   __syncthreads();
   float cA[8], cB[8], ab[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    cA[j] = s_A[cg * 8 + j];
-    cB[j] = s_B[cg * 8 + j];
+    cA[j] = s_A[lg * 8 + j];
+    cB[j] = s_B[lg * 8 + j];
     ab[j] = 0.f;
   }
-  for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
-    const BwdItem it = bwd_item(g, i, groups);
-    const uint4* slot = s_data + (i - begin) * kSlot;
+  for (int i = threadIdx.x; i < n_local; i += blockDim.x) {
+    const long long opix = p_begin + i / kSliceGroups;
+    const BwdItem it = bwd_item(g, opix * groups + cg, groups);
+    const uint4* slot = s_data + static_cast<long long>(i) * kSlot;
     const uint4 d = slot[kSlot - 1];
     if (!kPool) {
       const uint4 v = slot[0];
@@ -575,9 +581,9 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   }
   if (dbias != nullptr) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) group_accumulate(s_acc, ab[j], groups, cg, j);
+    for (int j = 0; j < 8; ++j) group_accumulate(s_acc, ab[j], kSliceGroups, lg, j);
     __syncthreads();
-    for (int c = threadIdx.x; c < g.C; c += blockDim.x) atomicAdd(&dbias[c], s_acc[c]);
+    for (int c = threadIdx.x; c < SC; c += blockDim.x) atomicAdd(&dbias[c0 + c], s_acc[c]);
   }
 }
 
@@ -587,22 +593,36 @@ static int launch_bn_bwd_fused(const __nv_bfloat16* x, const __nv_bfloat16* dy, 
                                const float* gamma, const float* beta, float* sums, __nv_bfloat16* dx,
                                float* dgamma, float* dbeta, float* dbias, BnGeom g, long long items,
                                cudaStream_t stream) {
+  const int groups = g.C / 8;
+  if (groups % kSliceGroups != 0) return -1;
+  const int n_slices = groups / kSliceGroups;
   const int sms = sm_count();
-  long long ipc = (items + sms - 1) / sms;
-  ipc = (ipc + kBnFusedThreads - 1) / kBnFusedThreads * kBnFusedThreads;
-  const int grid = static_cast<int>((items + ipc - 1) / ipc);
-  const size_t smem = ((6 * g.C * 4 + 15) / 16) * 16 + static_cast<size_t>(ipc) * (kPool ? 5 : 2) * 16;
-  if (smem > 200 * 1024) return -1;
-  static size_t configured = 0;
-  if (smem > configured) {
+  const long long out_pix = items / groups;
+  // Two CTAs per SM when their slices fit (2 x <=100 KB): twice the loads in flight for a kernel
+  // that is bound by memory latency, not bandwidth.  Otherwise one CTA per SM with <=200 KB.
+  long long ppc = 0;
+  int n_ranges = 0;
+  size_t smem = 0;
+  for (int per_sm = 2; per_sm >= 1; --per_sm) {
+    n_ranges = (per_sm * sms) / n_slices;
+    if (n_ranges < 1) return -1;
+    if (n_ranges > out_pix) n_ranges = static_cast<int>(out_pix);
+    ppc = (out_pix + n_ranges - 1) / n_ranges;
+    n_ranges = static_cast<int>((out_pix + ppc - 1) / ppc);
+    smem = static_cast<size_t>(ppc) * kSliceGroups * (kPool ? 5 : 2) * 16;
+    if (smem <= static_cast<size_t>(per_sm == 2 ? 100 : 200) * 1024) break;
+    if (per_sm == 1) return -1;
+  }
+  static bool configured = false;
+  if (!configured) {
     DDPB_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_fused_kernel<kPool>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          200 * 1024));
-    configured = 200 * 1024;
+    configured = true;
   }
-  int ipc_i = static_cast<int>(ipc);
-  void* args[] = {&x, &dy, &saved, &gamma, &beta, &sums, &dx, &dgamma, &dbeta, &dbias, &g, &ipc_i};
-  DDPB_CHECK_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bn_bwd_fused_kernel<kPool>), dim3(grid),
-                                              dim3(kBnFusedThreads), args, smem, stream));
+  int ppc_i = static_cast<int>(ppc);
+  void* args[] = {&x, &dy, &saved, &gamma, &beta, &sums, &dx, &dgamma, &dbeta, &dbias, &g, &ppc_i, &n_ranges};
+  DDPB_CHECK_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bn_bwd_fused_kernel<kPool>),
+                                              dim3(n_slices * n_ranges), dim3(kBnFusedThreads), args, smem, stream));
   return 0;
 }
 

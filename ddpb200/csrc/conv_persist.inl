@@ -338,52 +338,68 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     }
     __syncthreads();
     constexpr int kGroups = BLOCK_N / 8;                 // 16-byte channel groups per tile row
+    constexpr int kUnroll = 4;                           // items per thread in flight (memory-level parallelism)
     const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
     const int out_rows = p.pool ? kBlockM / 4 : kBlockM; // output pixels per tile
+    const int per_tile = out_rows * kGroups;
+    const int nwin = p.pool ? 4 : 1;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
       const PersistItem it = persist_item(item, m_tiles, n_tiles);
       const int n_img0 = (it.m_tile / p.hblocks) * p.bn;
       const int h0 = (it.m_tile % p.hblocks) * p.bh;
-      for (int w_item = threadIdx.x; w_item < out_rows * kGroups; w_item += blockDim.x) {
-        const int cgp = w_item % kGroups;
-        const int orow = w_item / kGroups;
-        const int ch = it.n_tile * BLOCK_N + cgp * 8;
-        float sc[8], sh[8], o[8];
+      for (int base = threadIdx.x; base < per_tile; base += blockDim.x * kUnroll) {
+        uint4 raw[kUnroll][4];
+        long long opix[kUnroll];
+        int chv[kUnroll];
+        bool ok[kUnroll];
+        // 1) addresses + all loads of up to kUnroll items
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          sc[j] = s_scale[ch + j];
-          sh[j] = s_shift[ch + j];
-        }
-        long long opix;
-        if (!p.pool) {
-          const long long pix = static_cast<long long>(it.m_tile) * kBlockM + orow;
-          if (pix >= p.P) continue;
-          opix = pix;
-          float v[8];
-          load8(p.out + pix * p.C_out + ch, v);
+        for (int u = 0; u < kUnroll; ++u) {
+          const int w_item = base + u * blockDim.x;
+          ok[u] = w_item < per_tile;
+          const int cgp = w_item % kGroups;
+          const int orow = w_item / kGroups;
+          chv[u] = it.n_tile * BLOCK_N + cgp * 8;
+          long long in00;
+          if (!p.pool) {
+            in00 = static_cast<long long>(it.m_tile) * kBlockM + orow;
+            opix[u] = in00;
+          } else {
+            const int wo = orow % Wo;
+            const int t2 = orow / Wo;
+            const int ho = t2 % (p.bh / 2);
+            const int n_img = n_img0 + t2 / (p.bh / 2);
+            in00 = (static_cast<long long>(n_img) * p.H + h0 + 2 * ho) * p.W + 2 * wo;
+            opix[u] = (static_cast<long long>(n_img) * Ho + (h0 / 2 + ho)) * Wo + wo;
+          }
+          ok[u] = ok[u] && in00 < p.P;
+          if (ok[u]) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] = fmaxf(fmaf(v[j], sc[j], sh[j]), 0.f);
-        } else {
-          // output pixel (n_local, ho, wo) of this tile's (bn, bh/2, W/2) block
-          const int wo = orow % Wo;
-          const int t2 = orow / Wo;
-          const int ho = t2 % (p.bh / 2);
-          const int n_local = t2 / (p.bh / 2);
-          const int n_img = n_img0 + n_local;
-          const long long in00 = (static_cast<long long>(n_img) * p.H + h0 + 2 * ho) * p.W + 2 * wo;
-          if (in00 >= p.P) continue;
-          opix = (static_cast<long long>(n_img) * Ho + (h0 / 2 + ho)) * Wo + wo;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] = 0.f;
-#pragma unroll
-          for (int d = 0; d < 4; ++d) {
-            float v[8];
-            load8(p.out + (in00 + (d >> 1) * p.W + (d & 1)) * p.C_out + ch, v);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], fmaf(v[j], sc[j], sh[j]));
+            for (int d = 0; d < 4; ++d)
+              if (d < nwin)
+                raw[u][d] = *reinterpret_cast<const uint4*>(p.out + (in00 + (d >> 1) * p.W + (d & 1)) * p.C_out + chv[u]);
           }
         }
-        store8(p.act + opix * p.C_out + ch, o);
+        // 2) normalise, rectify, pool, store
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          if (!ok[u]) continue;
+          float o[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = 0.f;   // ReLU floor
+#pragma unroll
+          for (int d = 0; d < 4; ++d) {
+            if (d < nwin) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const uint32_t wv = (j < 2) ? raw[u][d].x : (j < 4) ? raw[u][d].y : (j < 6) ? raw[u][d].z : raw[u][d].w;
+                const float xv = __uint_as_float((j & 1) ? (wv & 0xffff0000u) : (wv << 16));
+                o[j] = fmaxf(o[j], fmaf(xv, s_scale[chv[u] + j], s_shift[chv[u] + j]));
+              }
+            }
+          }
+          store8(p.act + opix[u] * p.C_out + chv[u], o);
+        }
       }
     }
   }

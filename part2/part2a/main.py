@@ -1,13 +1,26 @@
-"""Entry point of part2a -- same command line as /root/reference/part2/part2a/main.py
-(README.md of the reference: `python main.py` for part1, `python main.py --num-nodes N
-[--master-ip IP --master-port P --rank R]` on every node for the others).
-All logic lives in ddpb200.train.run; this file only selects the mode."""
+"""Entry point of part2a -- same command line and the same module-level names as
+/root/reference/part2/part2a/main.py (README.md of the reference: `python main.py` for part1,
+`python main.py --num-nodes N [--master-ip IP --master-port P --rank R]` on every node for the
+others).  The logic lives in ddpb200; this file selects the mode and re-exports the
+reference's function names so code written against the reference scripts keeps working."""
 import os
 import sys
 
 sys.path.insert(0, os.path.abspath(os.path.join(os.path.dirname(__file__), "../..")))
 
-from ddpb200.train import run  # noqa: E402
+import model as mdl  # noqa: E402,F401  (local import, as in the reference)
+from ddpb200.cli import get_rank, parse_arguments  # noqa: E402,F401
+from ddpb200.data import create_data_loaders  # noqa: E402,F401
+from ddpb200.parallel import init_distributed_setup, test_distributed_setup  # noqa: E402,F401
+from ddpb200.parallel import sync_gradients_2a as sync_gradients  # noqa: E402,F401  (model, rank, world_size)
+from ddpb200.train import run, seed, test_model, train_model  # noqa: E402,F401
+
+device = "cuda"  # the reference hard-codes "cpu" (main.py:15); pass --device cpu for that
+
+
+def main():
+    run("part2a")
+
 
 if __name__ == "__main__":
-    run("part2a")
+    main()
