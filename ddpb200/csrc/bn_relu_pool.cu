@@ -432,6 +432,26 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   const int groups = g.C / 8;
   const int slice = blockIdx.x / n_ranges, range = blockIdx.x % n_ranges;
   const int c0 = slice * SC;
+  const long long out_pix = static_cast<long long>(g.N) * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
+  const long long p_begin = static_cast<long long>(range) * pix_per_cta;
+  long long p_end = p_begin + pix_per_cta;
+  if (p_end > out_pix) p_end = out_pix;
+  const int n_local = p_end > p_begin ? static_cast<int>(p_end - p_begin) * kSliceGroups : 0;
+  const int lg = threadIdx.x % kSliceGroups;            // my channel group inside the slice (fixed)
+  const int cg = slice * kSliceGroups + lg;             // ... and in the tensor
+  // ---- phase 1a: issue EVERY global load of this CTA's slice (x window + dy) and park the data
+  // in shared memory.  Nothing here depends on the coefficients, so these loads are in flight
+  // together with the coefficient loads below: the kernel is a chain of memory round trips
+  // (ncu: 8% of DRAM bandwidth, time in scoreboard waits), and this removes one of them while
+  // putting all of a thread's loads in flight at once.
+  for (int i = threadIdx.x; i < n_local; i += blockDim.x) {
+    const long long opix = p_begin + i / kSliceGroups;
+    const BwdItem it = bwd_item(g, opix * groups + cg, groups);
+    uint4* slot = s_data + static_cast<long long>(i) * kSlot;
+    slot[kSlot - 1] = ldg16(dy + it.opix * g.C + cg * 8);
+#pragma unroll
+    for (int q = 0; q < kSlot - 1; ++q) slot[q] = ldg16(x + it.ipix[q] * g.C + cg * 8);
+  }
   for (int c = threadIdx.x; c < SC; c += blockDim.x) {
     const float mean = saved[c0 + c], rstd = saved[g.C + c0 + c];
     const float sc = gamma[c0 + c] * rstd;
@@ -442,13 +462,6 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
     if (range == 0 && dbias != nullptr) dbias[c0 + c] = 0.f;
   }
   __syncthreads();
-  const long long out_pix = static_cast<long long>(g.N) * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
-  const long long p_begin = static_cast<long long>(range) * pix_per_cta;
-  long long p_end = p_begin + pix_per_cta;
-  if (p_end > out_pix) p_end = out_pix;
-  const int n_local = p_end > p_begin ? static_cast<int>(p_end - p_begin) * kSliceGroups : 0;
-  const int lg = threadIdx.x % kSliceGroups;            // my channel group inside the slice (fixed)
-  const int cg = slice * kSliceGroups + lg;             // ... and in the tensor
   float sc[8], sh[8], a1[8], a2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -456,16 +469,12 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
     sh[j] = s_shift[lg * 8 + j];
     a1[j] = a2[j] = 0.f;
   }
-  // ---- phase 1: load, park, reduce
+  // ---- phase 1b: per-channel sums from the parked data (each thread re-reads its own slots)
   for (int i = threadIdx.x; i < n_local; i += blockDim.x) {
-    const long long opix = p_begin + i / kSliceGroups;
-    const BwdItem it = bwd_item(g, opix * groups + cg, groups);
-    uint4* slot = s_data + static_cast<long long>(i) * kSlot;
-    const uint4 d = ldg16(dy + it.opix * g.C + cg * 8);
-    slot[kSlot - 1] = d;
+    const uint4* slot = s_data + static_cast<long long>(i) * kSlot;
+    const uint4 d = slot[kSlot - 1];
     if (!kPool) {
-      const uint4 v = ldg16(x + it.ipix[0] * g.C + cg * 8);
-      slot[0] = v;
+      const uint4 v = slot[0];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float xv = bf16_at(v, j);
@@ -476,10 +485,7 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
     } else {
       uint4 v[4];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        v[q] = ldg16(x + it.ipix[q] * g.C + cg * 8);
-        slot[q] = v[q];
-      }
+      for (int q = 0; q < 4; ++q) v[q] = slot[q];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float best = 0.f, xa = 0.f;

@@ -343,11 +343,12 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     const int out_rows = p.pool ? kBlockM / 4 : kBlockM; // output pixels per tile
     const int per_tile = out_rows * kGroups;
     const int nwin = p.pool ? 4 : 1;
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-      const PersistItem it = persist_item(item, m_tiles, n_tiles);
-      const int n_img0 = (it.m_tile / p.hblocks) * p.bn;
-      const int h0 = (it.m_tile % p.hblocks) * p.bh;
-      for (int base = threadIdx.x; base < per_tile; base += blockDim.x * kUnroll) {
+    // flat index over ALL of this CTA's tiles, so a thread always has kUnroll independent items
+    // in flight (a single tile is only 256..1024 items: fewer than the block has threads)
+    const int my_tiles = (n_items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const long long my_total = static_cast<long long>(my_tiles) * per_tile;
+    {
+      for (long long base = threadIdx.x; base < my_total; base += static_cast<long long>(blockDim.x) * kUnroll) {
         uint4 raw[kUnroll][4];
         long long opix[kUnroll];
         int chv[kUnroll];
@@ -355,8 +356,13 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         // 1) addresses + all loads of up to kUnroll items
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-          const int w_item = base + u * blockDim.x;
-          ok[u] = w_item < per_tile;
+          const long long flat = base + static_cast<long long>(u) * blockDim.x;
+          ok[u] = flat < my_total;
+          const int tile_local = static_cast<int>(flat / per_tile);
+          const int w_item = static_cast<int>(flat - static_cast<long long>(tile_local) * per_tile);
+          const PersistItem it = persist_item(blockIdx.x + tile_local * gridDim.x, m_tiles, n_tiles);
+          const int n_img0 = (it.m_tile / p.hblocks) * p.bn;
+          const int h0 = (it.m_tile % p.hblocks) * p.bh;
           const int cgp = w_item % kGroups;
           const int orow = w_item / kGroups;
           chv[u] = it.n_tile * BLOCK_N + cgp * 8;

@@ -47,7 +47,7 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, N: i
     """
     nat.require_cuda(x, w)
     assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
-    assert x.numel() == N * H * W * C_in and w.numel() == C_out * taps * C_in
+    assert x.numel() >= N * H * W * C_in and w.numel() == C_out * taps * C_in
     if out is None:
         out = torch.empty(N * H * W, C_out, dtype=torch.bfloat16, device=x.device)
     if scratch is True:
@@ -100,7 +100,7 @@ def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, 
     """O2: dx[P, C_in] from dy[P, C_out] and the SAME bf16 filter pack fprop uses ([C_out, 9*C_in])."""
     nat.require_cuda(dy, w_fprop)
     assert dy.dtype == torch.bfloat16 and w_fprop.dtype == torch.bfloat16
-    assert dy.numel() == N * H * W * C_out and w_fprop.numel() == C_out * 9 * C_in
+    assert dy.numel() >= N * H * W * C_out and w_fprop.numel() == C_out * 9 * C_in
     if out is None:
         out = torch.empty(N * H * W, C_in, dtype=torch.bfloat16, device=dy.device)
     if scratch is True:
