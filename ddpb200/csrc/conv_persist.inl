@@ -188,7 +188,23 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     // per tile the 2*C_out atomic addresses were hit by every tile of the layer and serialised
     // in L2 (first layer: 2048 tiles onto 128 addresses).
     const bool do_stats = (p.partial == nullptr) && (p.stats != nullptr);
+    // BLOCK_N = 64 (one 32-column chunk per warp; first layer: 2048 tiles of one k-step each, i.e.
+    // epilogue bound): keep the running sums per THREAD in registers and do the cross-lane
+    // reduction once per flush instead of once per tile (measured: statistics were 36% of that
+    // layer's kernel time, profiles/r1_call26_*).
+    constexpr bool kRegStats = (kMyChunks == 1);
+    float racc1[kRegStats ? 32 : 1], racc2[kRegStats ? 32 : 1];
+#pragma unroll
+    for (int j = 0; j < (kRegStats ? 32 : 1); ++j) racc1[j] = racc2[j] = 0.f;
     auto flush_stats = [&](int n_tile_done) {
+      if constexpr (kRegStats) {
+        const float s1 = warp_transpose_reduce(racc1);
+        const float s2 = warp_transpose_reduce(racc2);
+        s_stats[(q * 2 + 0) * BLOCK_N + chunk0 * 32 + lane_id()] += s1;
+        s_stats[(q * 2 + 1) * BLOCK_N + chunk0 * 32 + lane_id()] += s2;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) racc1[j] = racc2[j] = 0.f;
+      }
       asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps
       for (int c = threadIdx.x - 64; c < 2 * BLOCK_N; c += 256) {
         const int which = c / BLOCK_N, col = c - which * BLOCK_N;
@@ -270,14 +286,22 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             }
           }
           if (p.stats != nullptr) {
-            float sq[32];
+            if constexpr (kRegStats) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) sq[j] = v[j] * v[j];
-            const float s1 = warp_transpose_reduce(v);
-            const float s2 = warp_transpose_reduce(sq);
-            // entry (q, column) belongs to exactly this lane of this warp: plain accumulate
-            s_stats[(q * 2 + 0) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] += s1;
-            s_stats[(q * 2 + 1) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] += s2;
+              for (int j = 0; j < 32; ++j) {
+                racc1[j] += v[j];
+                racc2[j] = fmaf(v[j], v[j], racc2[j]);
+              }
+            } else {
+              float sq[32];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) sq[j] = v[j] * v[j];
+              const float s1 = warp_transpose_reduce(v);
+              const float s2 = warp_transpose_reduce(sq);
+              // entry (q, column) belongs to exactly this lane of this warp: plain accumulate
+              s_stats[(q * 2 + 0) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] += s1;
+              s_stats[(q * 2 + 1) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] += s2;
+            }
           }
         }
       }
