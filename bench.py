@@ -50,7 +50,8 @@ def parse():
     ap.add_argument("--no-multicast", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--comm-blocks", type=int, default=None)
-    ap.add_argument("--bucket-layout", choices=["per_layer", "reference"], default="reference")
+    ap.add_argument("--bucket-layout", choices=["per_layer", "reference", "balanced"], default="reference")
+    ap.add_argument("--comm-threads", type=int, default=512)
     ap.add_argument("--bucket-mb", type=float, default=None, help="explicit bucket cap in MiB (first bucket: min(1, cap))")
     ap.add_argument("--no-fuse-sgd", action="store_true", help="run SGD as its own full-width kernel after the sync")
     ap.add_argument("--symm-backend", default=None)
@@ -134,7 +135,7 @@ def run_ours(a):
                               rank=rank, world_size=world, granularity=a.granularity,
                               use_multicast=False if a.no_multicast else "auto", use_graph=not a.no_graph,
                               comm_blocks=a.comm_blocks, symm_backend=a.symm_backend, bucket_layout=a.bucket_layout,
-                              fuse_sgd=not a.no_fuse_sgd,
+                              fuse_sgd=not a.no_fuse_sgd, comm_threads=a.comm_threads,
                               first_bucket_bytes=None if a.bucket_mb is None else int(min(1.0, a.bucket_mb) * 2**20),
                               bucket_bytes=None if a.bucket_mb is None else int(a.bucket_mb * 2**20))
     n_rot = 8

@@ -593,6 +593,10 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   }
 }
 
+// 0: two-kernel path; 1: fused, one CTA per SM (leaves registers for a co-resident gradient-sync
+// CTA: a cooperative launch needs ALL its CTAs resident at once); 2: fused, up to two CTAs per SM
+static int g_bn_fused = 2;
+
 // Tries the fused cooperative kernel; returns -1 if the shape does not fit in shared memory.
 template <bool kPool>
 static int launch_bn_bwd_fused(const __nv_bfloat16* x, const __nv_bfloat16* dy, const float* saved,
@@ -609,7 +613,7 @@ static int launch_bn_bwd_fused(const __nv_bfloat16* x, const __nv_bfloat16* dy, 
   long long ppc = 0;
   int n_ranges = 0;
   size_t smem = 0;
-  for (int per_sm = 2; per_sm >= 1; --per_sm) {
+  for (int per_sm = (g_bn_fused >= 2 ? 2 : 1); per_sm >= 1; --per_sm) {
     n_ranges = (per_sm * sms) / n_slices;
     if (n_ranges < 1) return -1;
     if (n_ranges > out_pix) n_ranges = static_cast<int>(out_pix);
@@ -632,7 +636,7 @@ static int launch_bn_bwd_fused(const __nv_bfloat16* x, const __nv_bfloat16* dy, 
   return 0;
 }
 
-static int g_bn_fused = 1;   // 0: always use the two-kernel path
+
 
 static int bn_grid(long long items) {
   long long blocks = (items + kBnThreads - 1) / kBnThreads;

@@ -329,7 +329,12 @@ extern "C" int ddpb_comm_max_ranks() { return kMaxRanks; }
 extern "C" int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int rank, int world, long long off,
                                   long long n, int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow,
                                   float lr, float momentum, float weight_decay, long long sgd_off, long long sgd_n,
-                                  cudaStream_t stream) {
+                                  int threads, cudaStream_t stream) {
+  // threads per CTA: 512 (default, 0) when the launch owns the GPU; 256 for reductions that
+  // overlap backward, so that a CTA (256 x 40 registers) fits on an SM next to a persistent
+  // convolution CTA (320 x 152 registers) instead of displacing it.
+  if (threads <= 0) threads = kCommThreads;
+  DDPB_REQUIRE(threads % 32 == 0 && threads >= 64 && threads <= kCommThreads, "comm: bad CTA size %d", threads);
   CommCtx c;
   if (int rc = fill_ctx(&c, bufs, mc, rank, world)) return rc;
   if (int rc = check_range(off, n, blocks, slot_base)) return rc;
@@ -341,9 +346,9 @@ extern "C" int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int r
   DDPB_REQUIRE(sgd_off >= 0 && sgd_off % 4 == 0 && sgd_n % 4 == 0, "comm: SGD range must be multiples of 4 floats");
   SgdArgs s{p, m, static_cast<__nv_bfloat16*>(shadow), lr, momentum, weight_decay, sgd_off, sgd_n / 4};
   if (use_mc)
-    allreduce_avg_kernel<true><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, s);
+    allreduce_avg_kernel<true><<<blocks, threads, 0, stream>>>(c, off, n / 4, slot_base, s);
   else
-    allreduce_avg_kernel<false><<<blocks, kCommThreads, 0, stream>>>(c, off, n / 4, slot_base, s);
+    allreduce_avg_kernel<false><<<blocks, threads, 0, stream>>>(c, off, n / 4, slot_base, s);
   DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -165,10 +165,10 @@ def bn_relu_pool_fwd(x, stats, gamma, beta, N, H, W, C_, pool: bool, *, out=None
     return out, saved
 
 
-def bn_bwd_set_fused(enabled: bool) -> None:
-    """Testing hook: False forces the two-kernel BatchNorm backward (default: fused cooperative kernel
-    whenever a CTA's slice fits in shared memory)."""
-    nat.load().ddpb_bn_bwd_set_fused(int(enabled))
+def bn_bwd_set_fused(mode: bool | int) -> None:
+    """0/False: two-kernel BatchNorm backward; 1: fused cooperative kernel with one CTA per SM
+    (room for a co-resident gradient-sync CTA); 2/True... default is 2: up to two CTAs per SM."""
+    nat.load().ddpb_bn_bwd_set_fused(2 if mode is True else int(mode))
 
 
 def bn_relu_pool_bwd(x, dy, saved, gamma, beta, N, H, W, C_, pool: bool, *, sums=None, dx=None, dgamma=None,

@@ -29,7 +29,7 @@ c_void, c_int, c_ll, c_float = C.c_void_p, C.c_int, C.c_longlong, C.c_float
 nat.register_optional("ddpb_comm_signal_pad_bytes", [])
 nat.register_optional("ddpb_comm_max_ranks", [])
 nat.register_optional("ddpb_allreduce_avg", [c_void, c_void, c_int, c_int, c_ll, c_ll, c_int, c_int, c_int, c_void,
-                                             c_void, c_void, c_float, c_float, c_float, c_ll, c_ll, c_void])
+                                             c_void, c_void, c_float, c_float, c_float, c_ll, c_ll, c_int, c_void])
 nat.register_optional("ddpb_reduce_root_bcast", [c_void, c_void, c_int, c_int, c_int, c_ll, c_ll, c_int, c_int, c_int,
                                                  c_void, c_void, c_void, c_float, c_float, c_float, c_ll, c_ll, c_void])
 nat.register_optional("ddpb_broadcast", [c_void, c_void, c_int, c_int, c_int, c_ll, c_ll, c_int, c_int, c_int,
@@ -171,14 +171,15 @@ class SymmetricBuffer:
         return C.c_void_p(self.multicast_ptr) if (use_mc and self.multicast_ptr) else None
 
     def allreduce_avg(self, off: int, n: int, *, blocks: int, slot_base: int = 0, use_mc: bool = False, sgd=None,
-                      sgd_range: tuple[int, int] | None = None, stream=None) -> None:
+                      sgd_range: tuple[int, int] | None = None, threads: int = 0, stream=None) -> None:
         """grad[off:off+n] <- mean over ranks, in place on every rank; optional fused SGD.
+        ``threads``: CTA size (0 = 512; 256 lets a CTA share an SM with a persistent conv CTA).
         sgd = (param_arena, momentum_arena, bf16_shadow_or_None, lr, momentum, weight_decay) or None."""
         p, m, sh, lr, mu, wd = sgd if sgd is not None else (None, None, None, 0.0, 0.0, 0.0)
         so, sn = sgd_range if sgd_range is not None else (0, -1)
         rc = nat.load().ddpb_allreduce_avg(self._ptr_array, self._mc(use_mc), self.rank, self.world, off, n, blocks,
                                            slot_base, int(bool(use_mc and self.multicast_ptr)), nat.ptr(p), nat.ptr(m),
-                                           nat.ptr(sh), lr, mu, wd, so, sn, nat.stream_ptr(stream))
+                                           nat.ptr(sh), lr, mu, wd, so, sn, threads, nat.stream_ptr(stream))
         nat.check(rc, "ddpb_allreduce_avg")
 
     def reduce_root_bcast(self, off: int, n: int, *, root: int = 0, blocks: int, slot_base: int = 0,

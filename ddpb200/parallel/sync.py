@@ -69,7 +69,7 @@ class Bucket:
 
 
 def plan_buckets(group_sizes: list[tuple[int, int, int]], first_cap_bytes: int = MIB,
-                 cap_bytes: int = 25 * MIB) -> list[Bucket]:
+                 cap_bytes: int = 25 * MIB, tail_bytes: int = 0) -> list[Bucket]:
     """Assigns parameter groups to buckets the way torch's Reducer does after its first
     iteration: walk the groups in gradient-ready order (last layer first) and close a
     bucket when it EXCEEDS its cap -- 1 MiB for the first bucket, 25 MiB afterwards
@@ -81,7 +81,15 @@ def plan_buckets(group_sizes: list[tuple[int, int, int]], first_cap_bytes: int =
     cur: list[int] = []
     cur_bytes = 0
     cap = first_cap_bytes
-    for gi in range(len(group_sizes) - 1, -1, -1):
+    # tail_bytes > 0: the first (input-side) groups, up to that many bytes in total, are kept
+    # out of the walk and form the LAST bucket -- the one that is reduced at full width after
+    # backward -- so that it stays small whatever the cap of the other buckets is.
+    tail_end = 0
+    acc = 0
+    while tail_bytes > 0 and tail_end < len(group_sizes) - 1 and acc + group_sizes[tail_end][2] * 4 <= tail_bytes:
+        acc += group_sizes[tail_end][2] * 4
+        tail_end += 1
+    for gi in range(len(group_sizes) - 1, tail_end - 1, -1):
         cur.append(gi)
         cur_bytes += group_sizes[gi][2] * 4
         if cur_bytes > cap:
@@ -89,6 +97,8 @@ def plan_buckets(group_sizes: list[tuple[int, int, int]], first_cap_bytes: int =
             cur, cur_bytes, cap = [], 0, cap_bytes
     if cur:
         buckets.append(_close(group_sizes, cur))
+    if tail_end > 0:
+        buckets.append(_close(group_sizes, list(range(tail_end))))
     return buckets
 
 

@@ -33,7 +33,7 @@ class Trainer:
                  use_multicast: bool | str = "auto", use_graph: bool = True, comm_blocks: int | None = None,
                  bucket_layout: str = "reference", first_bucket_bytes: int | None = None,
                  bucket_bytes: int | None = None, symm_backend: str | None = None,
-                 fuse_sgd: bool = True, overlap_wgrad: bool = True):
+                 fuse_sgd: bool = True, overlap_wgrad: bool = True, comm_threads: int = 512):
         if mode not in MODES:
             raise ValueError(f"mode must be one of {MODES}")
         if granularity not in ("fused", "param"):
@@ -46,6 +46,10 @@ class Trainer:
         self.use_graph = use_graph
         self.fuse_sgd = fuse_sgd
         self.overlap_wgrad = overlap_wgrad
+        # CTA size of the reductions that overlap backward (mode 'ddp').  256-thread CTAs would fit on
+        # an SM next to a persistent conv CTA, but measured on 2 GPUs (profiles/r1_call30_*) the lost
+        # reduction throughput costs more than the co-residency gains: 512 x 32 CTAs stays default.
+        self.comm_threads = comm_threads
         self.device = next(model.parameters()).device
         self.distributed = world_size > 1 and mode != "single"
         self.iteration = 0
@@ -56,15 +60,21 @@ class Trainer:
         # three-bucket layout wins: NVLink moves all 36.9 MB in ~0.1 ms, so what matters is how
         # few reduction kernels (two cross-GPU barriers each, 32 CTAs taken from backward) run,
         # not how early they start.  Explicit byte caps override both.
-        if bucket_layout not in ("per_layer", "reference"):
-            raise ValueError("bucket_layout must be 'per_layer' or 'reference'")
+        if bucket_layout not in ("per_layer", "reference", "balanced"):
+            raise ValueError("bucket_layout must be 'per_layer', 'reference' or 'balanced'")
+        tail_bytes = 0
+        if bucket_layout == "balanced":
+            # small last bucket (first layers), ~20 MiB middle buckets: {fc,L7} {L6..L4} {L3,L2} {L1,L0}
+            first_bucket_bytes = S.MIB if first_bucket_bytes is None else first_bucket_bytes
+            bucket_bytes = 20 * S.MIB if bucket_bytes is None else bucket_bytes
+            tail_bytes = S.MIB
         if first_bucket_bytes is None:
             first_bucket_bytes = 0 if bucket_layout == "per_layer" else S.MIB
         if bucket_bytes is None:
             bucket_bytes = 0 if bucket_layout == "per_layer" else 25 * S.MIB
         self.bucket_layout = bucket_layout
         self.groups = S.param_groups_of(model)
-        self.buckets = S.plan_buckets(self.groups, first_bucket_bytes, bucket_bytes)
+        self.buckets = S.plan_buckets(self.groups, first_bucket_bytes, bucket_bytes, tail_bytes)
         if self.device.type == "cuda":
             self._init_cuda(use_multicast, comm_blocks, symm_backend)
         else:
@@ -102,6 +112,11 @@ class Trainer:
         self.in_f32 = torch.zeros(B, 3, hw, hw, dtype=torch.float32, device=self.device)
         self._capture_stream = torch.cuda.Stream(device=self.device)
         if self.distributed and self.mode == "ddp":
+            # fused BatchNorm backward is a cooperative launch: with two CTAs per SM it fills the
+            # register file and would have to wait for every overlapped reduction to finish
+            from .ops import kernels as K
+
+            K.bn_bwd_set_fused(1)
             self._broadcast_parameters()
 
     def _broadcast_parameters(self):
@@ -163,7 +178,7 @@ class Trainer:
                     self.comm_stream.wait_event(sev)
                 with torch.cuda.stream(self.comm_stream):
                     self.symm.allreduce_avg(off, n, blocks=self.comm_blocks, slot_base=bi * self.comm_blocks,
-                                            use_mc=self.use_mc, sgd=None)
+                                            use_mc=self.use_mc, sgd=None, threads=self.comm_threads)
 
             eng.backward(B, after_layer=after_layer, side_stream=self.wgrad_stream)
             done = torch.cuda.Event()

@@ -111,7 +111,8 @@ int ddpb_comm_max_ranks(void);
  * all-reduce (part3/main.py:174): in-place two-shot all-reduce, mean, optional SGD. */
 int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int rank, int world, long long off, long long n,
                        int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow, float lr,
-                       float momentum, float weight_decay, long long sgd_off, long long sgd_n, void* stream);
+                       float momentum, float weight_decay, long long sgd_off, long long sgd_n, int threads,
+                       void* stream);
 /* part2a gather -> mean on rank 0 -> scatter (part2/part2a/main.py:97-115). */
 int ddpb_reduce_root_bcast(const void* const* bufs, const void* mc, int rank, int world, int root, long long off,
                            long long n, int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow,
