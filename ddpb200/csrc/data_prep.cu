@@ -31,20 +31,55 @@ __device__ __forceinline__ float src_value(const void* __restrict__ src, const P
     float raw = 0.f;                                // torchvision pads the uint8 image with 0
     if (sh >= 0 && sh < p.H && sw >= 0 && sw < p.W)
       raw = static_cast<float>(static_cast<const unsigned char*>(src)[((static_cast<long long>(n) * p.H + sh) * p.W + sw) * 3 + c]);
-    return (raw * (1.f / 255.f) - p.mean[c]) * p.inv_std[c];
+    // selects, not p.mean[c]: a run-time index would move the parameter arrays to local memory
+    const float m = c == 0 ? p.mean[0] : (c == 1 ? p.mean[1] : p.mean[2]);
+    const float is = c == 0 ? p.inv_std[0] : (c == 1 ? p.inv_std[1] : p.inv_std[2]);
+    return (raw * (1.f / 255.f) - m) * is;
   } else {
     return static_cast<const float*>(src)[((static_cast<long long>(n) * 3 + c) * p.H + h) * p.W + w];
   }
 }
 
-// One thread gathers the 27 neighbourhood values of one pixel (taps unrolled at compile
-// time), the block then writes its 256 rows of 128 bytes fully coalesced from shared memory.
+// Zero-padded bf16 pack of the first layer's filters, [C_out][27] fp32 -> [C_out][64] bf16, done
+// by one extra CTA of the operand kernel (the filters change every step, the pack is 8 KB).
+struct PackArgs {
+  const float* master;      // null: no pack
+  __nv_bfloat16* packed;
+  int c_out;
+};
+
+__device__ __forceinline__ void pack_first_filters(const PackArgs& k) {
+  for (int i = threadIdx.x; i < k.c_out * 64; i += blockDim.x) {
+    const int row = i >> 6, col = i & 63;
+    k.packed[i] = __float2bfloat16_rn(col < 27 ? k.master[row * 27 + col] : 0.f);
+  }
+}
+
+__device__ __forceinline__ void write_rows(const uint32_t (*s_rows)[17], __nv_bfloat16* __restrict__ out,
+                                           long long P) {
+  uint4* dst = reinterpret_cast<uint4*>(out) + blockIdx.x * 256LL * 8;
+  const long long rows_here = (P - blockIdx.x * 256LL) < 256 ? (P - blockIdx.x * 256LL) : 256;
+  for (int i = threadIdx.x; i < rows_here * 8; i += 256) {
+    const int r = i >> 3, chunk = i & 7;
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (chunk < 4) o = make_uint4(s_rows[r][chunk * 4], s_rows[r][chunk * 4 + 1], s_rows[r][chunk * 4 + 2],
+                                  s_rows[r][chunk * 4 + 3]);
+    dst[i] = o;
+  }
+}
+
+// General shapes: one thread gathers the 27 neighbourhood values of one pixel from global
+// memory, the block then writes its 256 rows of 128 bytes coalesced from shared memory.
 template <bool kUint8>
 __global__ void __launch_bounds__(256)
 first_layer_operand_kernel(const void* __restrict__ src, const signed char* __restrict__ aug,
-                           __nv_bfloat16* __restrict__ out, PrepParams p) {
+                           __nv_bfloat16* __restrict__ out, PrepParams p, PackArgs k) {
   __shared__ uint32_t s_rows[256][17];   // 32 bf16 columns per pixel (+1 word of padding)
   const long long P = static_cast<long long>(p.N) * p.H * p.W;
+  if (blockIdx.x * 256LL >= P) {
+    pack_first_filters(k);
+    return;
+  }
   const long long pix = blockIdx.x * 256LL + threadIdx.x;
   if (pix < P) {
     const int w = static_cast<int>(pix % p.W);
@@ -65,21 +100,76 @@ first_layer_operand_kernel(const void* __restrict__ src, const signed char* __re
     for (int j = 0; j < 16; ++j) s_rows[threadIdx.x][j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
   }
   __syncthreads();
-  uint4* dst = reinterpret_cast<uint4*>(out) + blockIdx.x * 256LL * 8;
-  const long long rows_here = (P - blockIdx.x * 256LL) < 256 ? (P - blockIdx.x * 256LL) : 256;
-  for (int i = threadIdx.x; i < rows_here * 8; i += 256) {
-    const int r = i >> 3, chunk = i & 7;
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);
-    if (chunk < 4) o = make_uint4(s_rows[r][chunk * 4], s_rows[r][chunk * 4 + 1], s_rows[r][chunk * 4 + 2],
-                                  s_rows[r][chunk * 4 + 3]);
-    dst[i] = o;
-  }
+  write_rows(s_rows, out, P);
 }
 
-static int prep_grid(long long pixels) {
-  long long blocks = (pixels + 255) / 256;   // one block per 256 pixels (not grid-stride)
+// Tiled variant for images whose rows divide a CTA's 256 pixels (CIFAR: 8 rows of 32).  The CTA
+// first stages the (rows+2) x (W+2) x 3 source patch -- cropped, flipped, normalised, conv
+// padding included -- in shared memory with coalesced loads; a pixel's 27 values are then three
+// runs of 9 consecutive floats, read with compile-time offsets (lane stride 3 words: no bank
+// conflicts).  Every source byte is fetched once instead of nine times.
+constexpr int kPatchMax = 2400;   // (256/W + 2) * (W + 2) * 3 floats for any W dividing 256
+
+template <bool kUint8>
+__global__ void __launch_bounds__(256)
+first_layer_operand_tile_kernel(const void* __restrict__ src, const signed char* __restrict__ aug,
+                                __nv_bfloat16* __restrict__ out, PrepParams p, PackArgs k) {
+  __shared__ uint32_t s_rows[256][17];
+  __shared__ float s_patch[kPatchMax];
+  const long long P = static_cast<long long>(p.N) * p.H * p.W;
+  if (blockIdx.x * 256LL >= P) {
+    pack_first_filters(k);
+    return;
+  }
+  const int rows = 256 / p.W;                       // image rows of this CTA
+  const long long pix0 = blockIdx.x * 256LL;
+  const int n = static_cast<int>(pix0 / (p.H * p.W));
+  const int h0 = static_cast<int>((pix0 / p.W) % p.H);
+  const int pw = (p.W + 2) * 3;                     // patch row pitch in floats
+  const int total = (rows + 2) * pw;
+  for (int i = threadIdx.x; i < total; i += 256) {
+    const int pr = i / pw, rem = i - pr * pw;
+    const int pc = rem / 3, c = rem - pc * 3;
+    s_patch[i] = src_value<kUint8>(src, p, aug, n, h0 + pr - 1, pc - 1, c);
+  }
+  __syncthreads();
+  {
+    const int hl = threadIdx.x / p.W, w = threadIdx.x - hl * p.W;
+    const float* base = s_patch + hl * pw + w * 3;  // patch (hl, w) = source (h-1, w-1)
+    float v[28];
+#pragma unroll
+    for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+      for (int e = 0; e < 9; ++e) v[dy * 9 + e] = base[dy * pw + e];
+    v[27] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 14; ++j) s_rows[threadIdx.x][j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+    s_rows[threadIdx.x][14] = 0u;
+    s_rows[threadIdx.x][15] = 0u;
+  }
+  __syncthreads();
+  write_rows(s_rows, out, P);
+}
+
+static bool tile_shape(int H, int W) {
+  return W >= 1 && W <= 256 && 256 % W == 0 && (static_cast<long long>(H) * W) % 256 == 0;
+}
+
+// one block per 256 pixels (not grid-stride) plus one for the filter pack when asked
+static int prep_grid(long long pixels, const PackArgs& k) {
+  long long blocks = (pixels + 255) / 256;
   if (blocks < 1) blocks = 1;
-  return static_cast<int>(blocks);
+  return static_cast<int>(blocks) + (k.master != nullptr ? 1 : 0);
+}
+
+template <bool kUint8>
+static void launch_prep(const void* src, const signed char* aug, void* out, const PrepParams& p, const PackArgs& k,
+                        cudaStream_t stream) {
+  const int grid = prep_grid(static_cast<long long>(p.N) * p.H * p.W, k);
+  if (tile_shape(p.H, p.W))
+    first_layer_operand_tile_kernel<kUint8><<<grid, 256, 0, stream>>>(src, aug, static_cast<__nv_bfloat16*>(out), p, k);
+  else
+    first_layer_operand_kernel<kUint8><<<grid, 256, 0, stream>>>(src, aug, static_cast<__nv_bfloat16*>(out), p, k);
 }
 
 }  // namespace ddpb
@@ -87,14 +177,17 @@ static int prep_grid(long long pixels) {
 using namespace ddpb;
 
 // src: fp32 NCHW [N][3][H][W], already normalised.  out: bf16 [N*H*W][64].
-extern "C" int ddpb_first_layer_operand_f32(const float* src, void* out, int N, int H, int W,
-                                            cudaStream_t stream) {
+// w0_master / w0_packed (both or neither null): the first layer's fp32 filters [c_out0][27] and
+// their zero-padded bf16 GEMM operand [c_out0][64], refreshed by the same launch.
+extern "C" int ddpb_first_layer_operand_f32(const float* src, void* out, int N, int H, int W, const float* w0_master,
+                                            void* w0_packed, int c_out0, cudaStream_t stream) {
   PrepParams p{};
   p.N = N;
   p.H = H;
   p.W = W;
-  first_layer_operand_kernel<false><<<prep_grid(static_cast<long long>(N) * H * W), 256, 0, stream>>>(
-      src, nullptr, static_cast<__nv_bfloat16*>(out), p);
+  DDPB_REQUIRE((w0_master == nullptr) == (w0_packed == nullptr), "first_layer_operand: give both filter pointers or none");
+  PackArgs k{w0_master, static_cast<__nv_bfloat16*>(w0_packed), c_out0};
+  launch_prep<false>(src, nullptr, out, p, k, stream);
   DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -103,6 +196,7 @@ extern "C" int ddpb_first_layer_operand_f32(const float* src, void* out, int N, 
 // offsets in [0, 2*pad], or null for the evaluation transform (normalise only).
 extern "C" int ddpb_first_layer_operand_u8(const unsigned char* src, const signed char* aug, void* out, int N,
                                            int H, int W, const float* mean3, const float* std3, int pad,
+                                           const float* w0_master, void* w0_packed, int c_out0,
                                            cudaStream_t stream) {
   PrepParams p{};
   p.N = N;
@@ -114,8 +208,9 @@ extern "C" int ddpb_first_layer_operand_u8(const unsigned char* src, const signe
     p.mean[c] = mean3[c];
     p.inv_std[c] = 1.f / std3[c];
   }
-  first_layer_operand_kernel<true><<<prep_grid(static_cast<long long>(N) * H * W), 256, 0, stream>>>(
-      src, aug, static_cast<__nv_bfloat16*>(out), p);
+  DDPB_REQUIRE((w0_master == nullptr) == (w0_packed == nullptr), "first_layer_operand: give both filter pointers or none");
+  PackArgs k{w0_master, static_cast<__nv_bfloat16*>(w0_packed), c_out0};
+  launch_prep<true>(src, aug, out, p, k, stream);
   DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

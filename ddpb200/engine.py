@@ -196,14 +196,21 @@ class VGGEngine:
             self.shadow.copy_(self.arena.master)
         self.pack_plan.run(stream)
 
-    def load_input_f32(self, x_nchw: torch.Tensor):
-        K.first_layer_operand_f32(x_nchw.contiguous(), out=self.operand0)
+    def _pack_kw(self, pack: bool) -> dict:
+        if not pack:
+            return {}
+        return dict(w0_master=self.arena.flat_master(self.layers[0].p_w), w0_packed=self.w_f[0])
 
-    def load_input_u8(self, x_nhwc: torch.Tensor, aug: torch.Tensor | None):
-        K.first_layer_operand_u8(x_nhwc, aug, out=self.operand0)
+    def load_input_f32(self, x_nchw: torch.Tensor, pack: bool = False):
+        """``pack``: the same launch refreshes the first layer's padded filter pack (= repack())."""
+        K.first_layer_operand_f32(x_nchw.contiguous(), out=self.operand0, **self._pack_kw(pack))
 
-    def forward(self, N: int, with_loss: bool, want_dlogits: bool = True):
-        """operand0[:N*H*W] -> logits[:N] (and loss / dlogits / correct when with_loss)."""
+    def load_input_u8(self, x_nhwc: torch.Tensor, aug: torch.Tensor | None, pack: bool = False):
+        K.first_layer_operand_u8(x_nhwc, aug, out=self.operand0, **self._pack_kw(pack))
+
+    def forward(self, N: int, with_loss: bool, want_dlogits: bool = True, defer_loss: bool = False):
+        """operand0[:N*H*W] -> logits[:N] (and loss / dlogits / correct when with_loss).
+        ``defer_loss``: leave the reduction of the per-row losses to backward(reduce_loss=True)."""
         a = self.arena
         self.stat_arena.zero_()
         x = self.operand0
@@ -219,15 +226,18 @@ class VGGEngine:
         if with_loss:
             K.fc_ce_fwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), a.flat_master(self.p_fcb),
                         self.labels[:N], logits=self.logits, row_loss=self.row_loss,
-                        dlogits=self.dlogits if want_dlogits else None, row_correct=self.row_correct, loss=self.loss,
-                        correct=self.correct)
+                        dlogits=self.dlogits if want_dlogits else None, row_correct=self.row_correct,
+                        loss=None if defer_loss else self.loss, correct=None if defer_loss else self.correct)
         else:
             # logits only: labels are not read meaningfully, loss outputs are discarded
             K.fc_ce_fwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), a.flat_master(self.p_fcb),
                         self.labels[:N], logits=self.logits, row_loss=self.row_loss)
 
-    def backward(self, N: int, after_layer=None, side_stream=None):
+    def backward(self, N: int, after_layer=None, side_stream=None, reduce_loss: bool = False):
         """dlogits[:N] -> every gradient in the arena.
+
+        ``reduce_loss``: the classifier's backward kernel also writes ``loss`` / ``correct`` from
+        the per-row values forward(defer_loss=True) left behind.
 
         ``after_layer(li, events)`` is called once layer li's gradients (and everything after it,
         classifier included) are enqueued -- the hook the bucketed reducer uses to start a bucket
@@ -244,7 +254,9 @@ class VGGEngine:
         last = len(self.layers) - 1
         feat = self.act[last][:N]
         K.fc_bwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), self.dlogits[:N],
-                 dw=a.flat_grad(self.p_fcw), db=a.flat_grad(self.p_fcb), dx=self.dact[last])
+                 dw=a.flat_grad(self.p_fcw), db=a.flat_grad(self.p_fcb), dx=self.dact[last],
+                 **(dict(row_loss=self.row_loss[:N], row_correct=self.row_correct[:N], loss=self.loss,
+                         correct=self.correct) if reduce_loss else {}))
         if after_layer is not None:
             after_layer(last + 1, [])   # the classifier is parameter group len(layers)
         for li in range(last, -1, -1):
@@ -296,7 +308,7 @@ class VGGEngine:
                 n += 1              # split-K reduce
             if li > 0:
                 n += 1              # dgrad
-        return n + 2 + 1            # fc fwd + loss reduce, fc bwd
+        return n + 1 + 1            # fc fwd, fc bwd (+ loss reduction)
 
 
 # ---------------------------------------------------------------------------------------

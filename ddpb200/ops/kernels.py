@@ -209,7 +209,10 @@ def fc_ce_fwd(x, w, b, labels, *, logits=None, row_loss=None, dlogits=None, row_
     return row_loss
 
 
-def fc_bwd(x, w, dlogits, *, dw=None, db=None, dx=None, want_dx=True, stream=None):
+def fc_bwd(x, w, dlogits, *, dw=None, db=None, dx=None, want_dx=True, row_loss=None, row_correct=None, loss=None,
+           correct=None, stream=None):
+    """O9 backward.  With ``row_loss`` (+``row_correct``) and ``loss``/``correct`` the same launch also
+    reduces the forward's per-row losses to the mean loss / correct count."""
     nat.require_cuda(x, w, dlogits)
     B, F = x.shape
     K = w.shape[0]
@@ -221,7 +224,8 @@ def fc_bwd(x, w, dlogits, *, dw=None, db=None, dx=None, want_dx=True, stream=Non
     if dx is None and want_dx:
         dx = torch.empty(B, F, dtype=torch.bfloat16, device=dev)
     rc = nat.load().ddpb_fc_bwd(nat.ptr(x), nat.ptr(w), nat.ptr(dlogits), nat.ptr(dw), nat.ptr(db), nat.ptr(dx), B, F,
-                                K, _s(stream))
+                                K, nat.ptr(row_loss), nat.ptr(row_correct), nat.ptr(loss), nat.ptr(correct),
+                                _s(stream))
     nat.check(rc, "ddpb_fc_bwd")
     return dw, db, dx
 
@@ -261,14 +265,25 @@ class PackPlan:
         nat.check(rc, "ddpb_pack_weights")
 
 
-def first_layer_operand_f32(x_nchw: torch.Tensor, *, out=None, stream=None) -> torch.Tensor:
-    """O16 tail + im2col for layer 0 from a normalised fp32 NCHW batch."""
+def _pack_args(w0_master, w0_packed):
+    if w0_master is None:
+        return None, None, 0
+    assert w0_master.dtype == torch.float32 and w0_packed.dtype == torch.bfloat16 and w0_packed.shape[1] == 64
+    assert w0_master.numel() == w0_packed.shape[0] * 27
+    return nat.ptr(w0_master), nat.ptr(w0_packed), w0_packed.shape[0]
+
+
+def first_layer_operand_f32(x_nchw: torch.Tensor, *, out=None, w0_master=None, w0_packed=None,
+                            stream=None) -> torch.Tensor:
+    """O16 tail + im2col for layer 0 from a normalised fp32 NCHW batch.  ``w0_master`` (fp32
+    [C_out*27]) / ``w0_packed`` (bf16 [C_out][64]): also refresh the first layer's filter pack."""
     nat.require_cuda(x_nchw)
     assert x_nchw.dtype == torch.float32 and x_nchw.is_contiguous() and x_nchw.shape[1] == 3
     N, _, H, W = x_nchw.shape
     if out is None:
         out = torch.empty(N * H * W, 64, dtype=torch.bfloat16, device=x_nchw.device)
-    rc = nat.load().ddpb_first_layer_operand_f32(nat.ptr(x_nchw), nat.ptr(out), N, H, W, _s(stream))
+    rc = nat.load().ddpb_first_layer_operand_f32(nat.ptr(x_nchw), nat.ptr(out), N, H, W,
+                                                 *_pack_args(w0_master, w0_packed), _s(stream))
     nat.check(rc, "ddpb_first_layer_operand_f32")
     return out
 
@@ -278,7 +293,7 @@ _STD3 = (C.c_float * 3)(63.0 / 255.0, 62.1 / 255.0, 66.7 / 255.0)      # part1/m
 
 
 def first_layer_operand_u8(x_nhwc_u8: torch.Tensor, aug: torch.Tensor | None = None, *, out=None, pad: int = 4,
-                           stream=None) -> torch.Tensor:
+                           w0_master=None, w0_packed=None, stream=None) -> torch.Tensor:
     """O16: crop/flip/normalise raw uint8 NHWC pixels and emit the layer-0 GEMM operand."""
     nat.require_cuda(x_nhwc_u8)
     assert x_nhwc_u8.dtype == torch.uint8 and x_nhwc_u8.is_contiguous() and x_nhwc_u8.shape[-1] == 3
@@ -288,6 +303,6 @@ def first_layer_operand_u8(x_nhwc_u8: torch.Tensor, aug: torch.Tensor | None = N
     if out is None:
         out = torch.empty(N * H * W, 64, dtype=torch.bfloat16, device=x_nhwc_u8.device)
     rc = nat.load().ddpb_first_layer_operand_u8(nat.ptr(x_nhwc_u8), nat.ptr(aug), nat.ptr(out), N, H, W, _MEAN3,
-                                                _STD3, pad, _s(stream))
+                                                _STD3, pad, *_pack_args(w0_master, w0_packed), _s(stream))
     nat.check(rc, "ddpb_first_layer_operand_u8")
     return out

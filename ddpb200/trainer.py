@@ -148,14 +148,15 @@ class Trainer:
         """Everything between 'inputs are on the device' and 'parameters are updated'."""
         eng, a = self.engine, self.engine.arena
         B = self.batch_size if B is None else B
-        eng.repack()   # first layer's padded filter pack; every other operand is the SGD-maintained shadow
+        # the input kernel also refreshes the first layer's padded filter pack; every other conv
+        # operand is the SGD-maintained shadow
         if kind == "u8":
-            eng.load_input_u8(self.in_u8[:B], self.in_aug[:B] if with_aug else None)
+            eng.load_input_u8(self.in_u8[:B], self.in_aug[:B] if with_aug else None, pack=True)
         else:
-            eng.load_input_f32(self.in_f32[:B])
-        eng.forward(B, with_loss=True)
+            eng.load_input_f32(self.in_f32[:B], pack=True)
+        eng.forward(B, with_loss=True, defer_loss=True)
         if not self.distributed:
-            eng.backward(B, side_stream=self.wgrad_stream)
+            eng.backward(B, side_stream=self.wgrad_stream, reduce_loss=True)
             eng.sgd(self.lr, self.momentum, self.weight_decay)
         elif self.mode == "ddp":
             # Early buckets: reduction only, few CTAs, on the side stream while backward continues.
@@ -180,7 +181,7 @@ class Trainer:
                     self.symm.allreduce_avg(off, n, blocks=self.comm_blocks, slot_base=bi * self.comm_blocks,
                                             use_mc=self.use_mc, sgd=None, threads=self.comm_threads)
 
-            eng.backward(B, after_layer=after_layer, side_stream=self.wgrad_stream)
+            eng.backward(B, after_layer=after_layer, side_stream=self.wgrad_stream, reduce_loss=True)
             done = torch.cuda.Event()
             done.record(self.comm_stream)
             main.wait_event(done)
@@ -192,7 +193,7 @@ class Trainer:
             if not self.fuse_sgd:
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
         else:
-            eng.backward(B, side_stream=self.wgrad_stream)
+            eng.backward(B, side_stream=self.wgrad_stream, reduce_loss=True)
             if self.granularity == "param":
                 # one launch per parameter tensor, like the reference's python loop
                 for i in range(len(a.params)):
@@ -283,7 +284,7 @@ class Trainer:
         """Number of ddpb200 kernels one ``step`` enqueues (for bench.py's gpu_launches)."""
         if self.device.type != "cuda":
             return 0
-        n = 1 + self.engine.launches_per_train_step() + 1  # input prep ... repack
+        n = 1 + self.engine.launches_per_train_step()  # input prep (+ first-layer filter pack)
         if not self.distributed:
             n += 1
         elif self.mode == "ddp":

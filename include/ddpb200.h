@@ -81,8 +81,10 @@ int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float* saved_mean
 int ddpb_fc_ce_fwd(const void* x, const float* w, const float* b, const long long* labels, float* logits,
                    float* row_loss, float* dlogits, int* row_correct, float* loss, int* correct, int B, int F, int K,
                    void* stream);
+/* row_loss / row_correct / loss / correct (may all be null): also reduce the per-row losses of a
+ * preceding ddpb_fc_ce_fwd(loss = correct = null) to the mean loss / correct count. */
 int ddpb_fc_bwd(const void* x, const float* w, const float* dlogits, float* dw, float* db, void* dx, int B, int F,
-                int K, void* stream);
+                int K, const float* row_loss, const int* row_correct, float* loss, int* correct, void* stream);
 
 /* ---- optimizer (K9) -------------------------------------------------------------------------- */
 /* O11+O12: optim.SGD(lr, momentum, weight_decay).step() over the flat arena, part1/main.py:77,
@@ -94,10 +96,14 @@ int ddpb_pack_weights(int count, const float* const* master, void* const* fprop,
 
 /* ---- input pipeline (K16) -------------------------------------------------------------------- */
 /* O16: RandomCrop(32,4) / RandomHorizontalFlip / ToTensor / Normalize, part1/main.py:20-28, fused
- * with the gather that builds the first layer's [N*H*W][64] operand. */
-int ddpb_first_layer_operand_f32(const float* src_nchw, void* out, int N, int H, int W, void* stream);
+ * with the gather that builds the first layer's [N*H*W][64] operand.
+ * w0_master / w0_packed (both or neither null): fp32 filters [c_out0][27] of the first layer and
+ * their zero-padded bf16 operand [c_out0][64], refreshed by one extra CTA of the same launch. */
+int ddpb_first_layer_operand_f32(const float* src_nchw, void* out, int N, int H, int W, const float* w0_master,
+                                 void* w0_packed, int c_out0, void* stream);
 int ddpb_first_layer_operand_u8(const unsigned char* src_nhwc, const signed char* aug, void* out, int N, int H,
-                                int W, const float* mean3, const float* std3, int pad, void* stream);
+                                int W, const float* mean3, const float* std3, int pad, const float* w0_master,
+                                void* w0_packed, int c_out0, void* stream);
 
 /* ---- gradient synchronisation over NVLink peer memory (K10-K14) ------------------------------ */
 /* bufs: `world` base pointers of the symmetric buffers ([64 KiB signal pad | fp32 payload]) as

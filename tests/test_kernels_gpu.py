@@ -226,6 +226,33 @@ def test_fc_cross_entropy_fwd_bwd(B):
     assert torch.allclose(dw, rdw, rtol=1e-3, atol=1e-5)
     assert torch.allclose(db, rdb, rtol=1e-3, atol=1e-6)
     assert _rel_err(dx, rdx) < 1e-2
+    # the training step's arrangement: forward leaves the per-row losses, backward reduces them
+    row_loss = K.fc_ce_fwd(x, w, b, labels, dlogits=dlogits, row_correct=row_correct)
+    loss2 = torch.full((), -1.0, device=DEV)
+    correct2 = torch.full((), -1, dtype=torch.int32, device=DEV)
+    dw2, db2, _ = K.fc_bwd(x, w, dlogits, row_loss=row_loss, row_correct=row_correct, loss=loss2, correct=correct2)
+    assert torch.equal(loss2, loss) and torch.equal(correct2, correct)
+    assert torch.equal(dw2, dw) and torch.equal(db2, db)
+
+
+def test_fc_generic_class_count():
+    B, F_, Kc = 64, 256, 7
+    x = torch.randn(B, F_, device=DEV).bfloat16()
+    w = torch.randn(Kc, F_, device=DEV) / F_ ** 0.5
+    b = torch.randn(Kc, device=DEV) * 0.1
+    labels = torch.randint(0, Kc, (B,), device=DEV)
+    logits = torch.empty(B, Kc, device=DEV)
+    dlogits = torch.empty(B, Kc, device=DEV)
+    loss = torch.zeros((), device=DEV)
+    K.fc_ce_fwd(x, w, b, labels, logits=logits, dlogits=dlogits, loss=loss)
+    rl, rloss, rdl, _ = R.fc_ce(x, w, b, labels)
+    assert torch.allclose(logits, rl, rtol=1e-4, atol=1e-4)
+    assert abs(loss.item() - rloss.item()) < 1e-4
+    dw, db, dx = K.fc_bwd(x, w, dlogits)
+    rdw, rdb, rdx = R.fc_bwd(x, w, rdl)
+    assert torch.allclose(dw, rdw, rtol=1e-3, atol=1e-5)
+    assert torch.allclose(db, rdb, rtol=1e-3, atol=1e-6)
+    assert _rel_err(dx, rdx) < 1e-2
 
 
 def test_sgd_matches_torch_optim():
@@ -272,3 +299,24 @@ def test_first_layer_operand_u8_augmentation():
         op = K.first_layer_operand_u8(raw, a)
         ref = R.first_layer_operand(R.augment_normalize_u8(raw, a)).bfloat16()
         assert (op.float() - ref.float()).abs().max().item() < 2e-2
+
+
+@pytest.mark.parametrize("H,W", [(32, 32), (16, 16), (8, 64), (12, 20)])
+def test_first_layer_operand_shapes_and_filter_pack(H, W):
+    """Tiled kernel (rows divide 256 pixels) and the general one give the same operand; the extra
+    CTA writes the zero-padded first-layer filters."""
+    N = 5
+    img = torch.randn(N, 3, H, W, device=DEV)
+    m0 = torch.randn(64 * 27, device=DEV)
+    f0 = torch.full((64, 64), 5.0, dtype=torch.bfloat16, device=DEV)
+    op = K.first_layer_operand_f32(img, w0_master=m0, w0_packed=f0)
+    assert torch.equal(op, R.first_layer_operand(img).bfloat16())
+    assert torch.equal(f0[:, :27], m0.view(64, 27).bfloat16()) and f0[:, 27:].abs().max().item() == 0
+    raw = torch.randint(0, 256, (N, H, W, 3), dtype=torch.uint8, device=DEV)
+    aug = torch.stack([torch.randint(0, 9, (N,)), torch.randint(0, 9, (N,)), torch.randint(0, 2, (N,)),
+                       torch.zeros(N, dtype=torch.long)], 1).to(torch.int8).to(DEV)
+    f0.fill_(5.0)
+    op = K.first_layer_operand_u8(raw, aug, w0_master=m0, w0_packed=f0)
+    ref = R.first_layer_operand(R.augment_normalize_u8(raw, aug)).bfloat16()
+    assert (op.float() - ref.float()).abs().max().item() < 2e-2
+    assert torch.equal(f0[:, :27], m0.view(64, 27).bfloat16())
