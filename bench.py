@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--granularity", choices=["fused", "param"], default="fused")
     ap.add_argument("--no-multicast", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch")
+    ap.add_argument("--no-overlap-wgrad", action="store_true", help="weight gradients on the main stream")
     ap.add_argument("--comm-blocks", type=int, default=None)
     ap.add_argument("--bucket-layout", choices=["per_layer", "reference", "balanced"], default="reference")
     ap.add_argument("--comm-threads", type=int, default=512)
@@ -130,12 +132,16 @@ def run_ours(a):
     mode = a.mode if world > 1 else "single"
 
     torch.manual_seed(89395)
+    if a.no_pdl:
+        from ddpb200.ops import kernels as _K
+        _K.set_pdl(False)
     model = ddpb200.VGG11().to(device)
     trainer = ddpb200.Trainer(model, mode=mode, batch_size=per_gpu, lr=0.1, momentum=0.9, weight_decay=1e-4,
                               rank=rank, world_size=world, granularity=a.granularity,
                               use_multicast=False if a.no_multicast else "auto", use_graph=not a.no_graph,
                               comm_blocks=a.comm_blocks, symm_backend=a.symm_backend, bucket_layout=a.bucket_layout,
                               fuse_sgd=not a.no_fuse_sgd, comm_threads=a.comm_threads,
+                              overlap_wgrad=not a.no_overlap_wgrad,
                               first_bucket_bytes=None if a.bucket_mb is None else int(min(1.0, a.bucket_mb) * 2**20),
                               bucket_bytes=None if a.bucket_mb is None else int(a.bucket_mb * 2**20))
     n_rot = 8
@@ -196,7 +202,7 @@ def run_ours(a):
                        "optimizer": "SGD lr=0.1 momentum=0.9 wd=1e-4 (inside the timed step)",
                        "sync": None if world == 1 else {"backend": trainer.symm.backend, "multicast": trainer.use_mc,
                                                        "granularity": a.granularity, "bucket_layout": a.bucket_layout if mode == "ddp" else None, "comm_blocks": trainer.comm_blocks, "buckets_floats": [b.numel for b in trainer.buckets] if mode == "ddp" else None},
-                       "cuda_graph": not a.no_graph,
+                       "cuda_graph": not a.no_graph, "programmatic_dependent_launch": not a.no_pdl,
                        "l2": f"no explicit flush: working set {ws_mb:.0f} MB/step > 126 MB L2; inputs rotate over {n_rot} device batches",
                        "baseline_ref": "BASELINE.md §1: published CPU/Gloo images/s for this worker count"},
             "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "ms_per_step": round(e2e_ms / a.steps, 4),

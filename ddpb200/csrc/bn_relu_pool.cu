@@ -45,6 +45,8 @@ __device__ __forceinline__ void bn_coeffs_to_smem(const float* __restrict__ stat
 __global__ void __launch_bounds__(kBnThreads)
 channel_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ stats, long long P, int C) {
   extern __shared__ float s_acc[];  // [2][C]
+  pdl_launch_dependents();
+  pdl_wait();
   for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) s_acc[c] = 0.f;
   __syncthreads();
   const int groups = C / 8;
@@ -95,6 +97,8 @@ bn_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __rest
                         __nv_bfloat16* __restrict__ y, float* __restrict__ saved /* [2][C] mean, rstd */,
                         BnGeom g) {
   extern __shared__ float s_coef[];  // scale[C], shift[C], mean[C], rstd[C]
+  pdl_launch_dependents();
+  pdl_wait();
   float* s_scale = s_coef;
   float* s_shift = s_coef + g.C;
   float* s_mean = s_coef + 2 * g.C;
@@ -207,6 +211,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
                      const float* __restrict__ beta, float* __restrict__ sums /* [2][C] accumulated */,
                      float* __restrict__ dbias_clear /* [C] or null */, BnGeom g) {
   extern __shared__ float s_mem[];  // scale[C], shift[C], acc[2][C]
+  pdl_launch_dependents();
+  pdl_wait();
   float* s_scale = s_mem;
   float* s_shift = s_mem + g.C;
   float* s_acc = s_mem + 2 * g.C;
@@ -288,6 +294,8 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
                     __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
                     float* __restrict__ dbias, BnGeom g) {
   extern __shared__ float s_mem[];  // scale, shift, A, Bc, acc : 5*C
+  pdl_launch_dependents();
+  pdl_wait();
   float* s_scale = s_mem;
   float* s_shift = s_mem + g.C;
   float* s_A = s_mem + 2 * g.C;
@@ -428,6 +436,8 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   constexpr int SC = kSliceGroups * 8;          // channels per CTA
   __shared__ float s_scale[SC], s_shift[SC], s_A[SC], s_B[SC], s_acc[2 * SC];
   extern __shared__ uint4 s_data[];
+  pdl_launch_dependents();
+  pdl_wait();
   unsigned int* counter = reinterpret_cast<unsigned int*>(sums + 2 * g.C);
   const int groups = g.C / 8;
   const int slice = blockIdx.x / n_ranges, range = blockIdx.x % n_ranges;
@@ -658,9 +668,8 @@ using namespace ddpb;
 extern "C" int ddpb_channel_stats(const void* x, float* stats, long long P, int C, cudaStream_t stream) {
   DDPB_REQUIRE(C > 0 && C % 8 == 0 && C <= 2048, "channel_stats: bad C %d", C);
   const long long items = P * (C / 8);
-  channel_stats_kernel<<<bn_grid(items), kBnThreads, 2 * C * sizeof(float), stream>>>(
-      static_cast<const __nv_bfloat16*>(x), stats, P, C);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+  DDPB_CHECK_CUDA(launch_pdl(channel_stats_kernel, bn_grid(items), kBnThreads, 2 * C * sizeof(float), stream,
+                             static_cast<const __nv_bfloat16*>(x), stats, P, C));
   return 0;
 }
 
@@ -680,9 +689,9 @@ int bn_relu_pool_fwd_launch(const void* x, const float* stats, const float* gamm
   DDPB_BN_CHECK_GEOM("bn_relu_pool_fwd");
   BnGeom g{N, H, W, C, pool, eps};
   const long long items = static_cast<long long>(N) * (pool ? H / 2 : H) * (pool ? W / 2 : W) * (C / 8);
-  bn_relu_pool_fwd_kernel<<<bn_grid(items), kBnThreads, 4 * C * sizeof(float), stream>>>(
-      static_cast<const __nv_bfloat16*>(x), stats, gamma, beta, static_cast<__nv_bfloat16*>(y), saved, g);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+  DDPB_CHECK_CUDA(launch_pdl(bn_relu_pool_fwd_kernel, bn_grid(items), kBnThreads, 4 * C * sizeof(float), stream,
+                             static_cast<const __nv_bfloat16*>(x), stats, gamma, beta, static_cast<__nv_bfloat16*>(y),
+                             saved, g));
   return 0;
 }
 
@@ -713,19 +722,17 @@ extern "C" int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float*
                                                      items, stream);
     if (rc >= 0) return rc;   // -1: slice too large for shared memory, use the two-pass kernels
   }
+  const float* sums_c = sums;
   if (pool) {
-    bn_bwd_reduce_kernel<true><<<grid, kBnThreads, 4 * C * sizeof(float), stream>>>(xb, dyb, saved, gamma, beta,
-                                                                                    sums, dbias, g);
-    DDPB_CHECK_CUDA(cudaGetLastError());
-    bn_bwd_apply_kernel<true><<<grid, kBnThreads, 5 * C * sizeof(float), stream>>>(
-        xb, dyb, saved, gamma, beta, sums, dxb, dgamma, dbeta, dbias, g);
+    DDPB_CHECK_CUDA(launch_pdl(bn_bwd_reduce_kernel<true>, grid, kBnThreads, 4 * C * sizeof(float), stream, xb, dyb,
+                               saved, gamma, beta, sums, dbias, g));
+    DDPB_CHECK_CUDA(launch_pdl(bn_bwd_apply_kernel<true>, grid, kBnThreads, 5 * C * sizeof(float), stream, xb, dyb,
+                               saved, gamma, beta, sums_c, dxb, dgamma, dbeta, dbias, g));
   } else {
-    bn_bwd_reduce_kernel<false><<<grid, kBnThreads, 4 * C * sizeof(float), stream>>>(xb, dyb, saved, gamma, beta,
-                                                                                     sums, dbias, g);
-    DDPB_CHECK_CUDA(cudaGetLastError());
-    bn_bwd_apply_kernel<false><<<grid, kBnThreads, 5 * C * sizeof(float), stream>>>(
-        xb, dyb, saved, gamma, beta, sums, dxb, dgamma, dbeta, dbias, g);
+    DDPB_CHECK_CUDA(launch_pdl(bn_bwd_reduce_kernel<false>, grid, kBnThreads, 4 * C * sizeof(float), stream, xb, dyb,
+                               saved, gamma, beta, sums, dbias, g));
+    DDPB_CHECK_CUDA(launch_pdl(bn_bwd_apply_kernel<false>, grid, kBnThreads, 5 * C * sizeof(float), stream, xb, dyb,
+                               saved, gamma, beta, sums_c, dxb, dgamma, dbeta, dbias, g));
   }
-  DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -47,6 +47,30 @@ int encode_tmap(CUtensorMap* map, CUtensorMapDataType dtype, uint32_t rank, cons
 
 int sm_count();
 
+// Programmatic dependent launch (PDL).  Consecutive kernels of a step are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization: the next kernel's CTAs may become
+// resident -- and run their prologue: barrier init, TMEM allocation, descriptor prefetch --
+// while the previous kernel drains, and block in pdl_wait() until that kernel has completed
+// and its writes are visible.  EVERY kernel launched through launch_pdl() must execute
+// pdl_wait() before it touches global memory (the guarantee is transitive only then).
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // TMA box geometry shared by the conv kernels: `rows` consecutive NHWC pixels as a
 // (W, bh, bn) box; hblocks = boxes per image along H.
 inline bool pixel_box(int H, int W, int rows, int* bh, int* bn, int* hblocks) {
@@ -80,6 +104,10 @@ namespace ddpb {
 #ifndef DDPB_WAIT_TIMEOUT_NS
 #define DDPB_WAIT_TIMEOUT_NS 2000000000ull
 #endif
+
+// PDL, device side.  Both are no-ops in a kernel that was launched without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ unsigned long long global_timer_ns() {
   unsigned long long t;

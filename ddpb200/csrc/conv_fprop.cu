@@ -176,6 +176,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   const int k_end = static_cast<int>(static_cast<long long>(total_k) * (blockIdx.z + 1) / gridDim.z);
   const int num_k = k_end - k_begin;
 
+  pdl_launch_dependents();
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmap_x);
     tma_prefetch_desc(&tmap_w);
@@ -197,6 +198,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // everything above overlapped the previous kernel's tail; global memory from here on
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) dbg_stamp(p, 1);
 
@@ -340,6 +342,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   const int k_end = static_cast<int>(static_cast<long long>(total_k) * (blockIdx.z + 1) / gridDim.z);
   const int num_k = k_end - k_begin;
 
+  pdl_launch_dependents();
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmap_x);
     tma_prefetch_desc(&tmap_w);
@@ -361,6 +364,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   tc_fence_before();
   cluster_sync_all();   // both CTAs' barriers exist before anything is signalled across the pair
   tc_fence_after();
+  pdl_wait();
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) dbg_stamp(p, 1);
 
@@ -449,8 +453,10 @@ splitk_finalize_kernel(const float* __restrict__ partial, const float* __restric
                        __nv_bfloat16* __restrict__ out, float* __restrict__ stats, int splits, long long P,
                        int C_out) {
   extern __shared__ float s_acc[];  // [2][C_out]
+  pdl_launch_dependents();
   for (int c = threadIdx.x; c < 2 * C_out; c += blockDim.x) s_acc[c] = 0.f;
   __syncthreads();
+  pdl_wait();
   const int groups = C_out / 8;
   const long long items = P * groups;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -580,8 +586,7 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const Fpro
     configured = true;
   }
   dim3 grid(m_tiles, p.C_out / BLOCK_N, splits);
-  conv_fprop_kernel<BLOCK_N, kDgrad><<<grid, kConvThreads, Cfg::kSmemBytes, stream>>>(tx, tw, p);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+  DDPB_CHECK_CUDA(launch_pdl(conv_fprop_kernel<BLOCK_N, kDgrad>, grid, kConvThreads, Cfg::kSmemBytes, stream, tx, tw, p));
   return 0;
 }
 
@@ -600,13 +605,15 @@ static int launch_pair(const CUtensorMap& tx, const CUtensorMap& tw, const Fprop
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   DDPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_pair_kernel<BLOCK_N, kDgrad>, tx, tw, p));
   return 0;
 }
@@ -763,9 +770,9 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   const long long items = static_cast<long long>(p.P) * (C_out / 8);
   long long blocks = (items + 255) / 256;
   if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
-  splitk_finalize_kernel<<<static_cast<int>(blocks), 256, 2 * C_out * sizeof(float), stream>>>(
-      scratch, bias, p.out, stats, splits, p.P, C_out);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+  const float* partial = scratch;
+  DDPB_CHECK_CUDA(launch_pdl(splitk_finalize_kernel, static_cast<int>(blocks), 256, 2 * C_out * sizeof(float), stream,
+                             partial, bias, p.out, stats, splits, static_cast<long long>(p.P), C_out));
   return 0;
 }
 

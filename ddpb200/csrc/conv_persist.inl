@@ -70,6 +70,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   const int cchunks = p.C_in / kBlockK;
   const int total_k = p.taps * cchunks;
 
+  pdl_launch_dependents();
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmap_x);
     tma_prefetch_desc(&tmap_w);
@@ -94,6 +95,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // barrier init / TMEM allocation above overlapped the previous kernel's tail
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) dbg_stamp(p, 1);
 
@@ -450,8 +452,7 @@ static int launch_persist(const CUtensorMap& tx, const CUtensorMap& tw, const Fp
   const int items = m_tiles * n_tiles * splits;
   int grid = sm_count();
   if (grid > items) grid = items;
-  conv_persist_kernel<BLOCK_N, kDgrad><<<grid, kPersistThreads, Cfg::kSmemBytes, stream>>>(tx, tw, p, m_tiles,
-                                                                                           n_tiles, splits);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+  DDPB_CHECK_CUDA(launch_pdl(conv_persist_kernel<BLOCK_N, kDgrad>, grid, kPersistThreads, Cfg::kSmemBytes, stream, tx,
+                             tw, p, m_tiles, n_tiles, splits));
   return 0;
 }

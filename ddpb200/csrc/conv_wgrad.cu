@@ -17,6 +17,7 @@
 // (deterministic, unlike atomics).  With one split the tile is written straight to
 // its final place (for the training engine: the flat gradient arena).
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace ddpb {
 
@@ -24,9 +25,12 @@ constexpr int kWgThreads = 192;
 constexpr int kWgPix = 64;                    // pixels per pipeline stage
 constexpr int kWgBoxBytes = kWgPix * 128;     // one (64 ch x 64 px) box = 8 KB
 
-template <int BLOCK_N>
+// kDeep = false: <= 97 KB of shared memory, two CTAs per SM share the tensor pipe (the ring of one
+// CTA is latency bound: ~1.1 us TMA round trip over 3 stages).  kDeep = true: for grids of at
+// most one CTA per SM, the whole shared memory is one ring twice as deep.
+template <int BLOCK_N, bool kDeep = false>
 struct WgradCfg {
-  static constexpr int kStages = (BLOCK_N >= 128) ? 3 : 4;   // <= 97 KB: two CTAs per SM
+  static constexpr int kStages = ((BLOCK_N >= 128) ? 3 : 4) * (kDeep ? 2 : 1);
   static constexpr int kABytes = 2 * kWgBoxBytes;                 // M = 128 channels of dY
   static constexpr int kBBytes = (BLOCK_N / 64) * kWgBoxBytes;    // N channels of X
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -45,11 +49,11 @@ struct WgradParams {
   int dup_m;            // C_out == 64: both halves of M read the same 64 channels
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool kDeep>
 __global__ void __launch_bounds__(kWgThreads)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x,
                   const WgradParams p) {
-  using Cfg = WgradCfg<BLOCK_N>;
+  using Cfg = WgradCfg<BLOCK_N, kDeep>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
@@ -72,6 +76,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
   const int pb_end = static_cast<int>(static_cast<long long>(pix_blocks) * (split + 1) / splits);
   const int num_k = pb_end - pb_begin;
 
+  pdl_launch_dependents();
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmap_dy);
     tma_prefetch_desc(&tmap_x);
@@ -92,6 +97,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // the prologue above overlapped the previous kernel's tail
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   if (warp == 0) {
@@ -191,6 +197,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 __global__ void __launch_bounds__(256)
 wgrad_reduce_dense_kernel(const float4* __restrict__ ws, float4* __restrict__ out, int splits, long long stride4,
                           long long n4) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += step) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -217,6 +225,8 @@ __global__ void __launch_bounds__(256)
 wgrad_reduce_rows_kernel(const float* __restrict__ ws, float* __restrict__ out, int splits, long long split_stride,
                          int cols_valid, int ws_ld, int out_ld) {
   __shared__ float s_part[8][33];
+  pdl_launch_dependents();
+  pdl_wait();
   const int r = blockIdx.x;
   const int lane_s = threadIdx.x >> 5;
   for (int c0 = 0; c0 < cols_valid; c0 += 32) {
@@ -238,20 +248,31 @@ wgrad_reduce_rows_kernel(const float* __restrict__ ws, float* __restrict__ out, 
   }
 }
 
-template <int BLOCK_N>
-static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
-                        cudaStream_t stream) {
-  using Cfg = WgradCfg<BLOCK_N>;
+template <int BLOCK_N, bool kDeep>
+static int launch_wgrad_cfg(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
+                            cudaStream_t stream) {
+  using Cfg = WgradCfg<BLOCK_N, kDeep>;
   static bool configured = false;
   if (!configured) {
-    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BLOCK_N>,
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BLOCK_N, kDeep>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured = true;
   }
   dim3 grid(p.taps * p.m_tiles * p.n_tiles, splits);
-  conv_wgrad_kernel<BLOCK_N><<<grid, kWgThreads, Cfg::kSmemBytes, stream>>>(tdy, tx, p);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+  DDPB_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BLOCK_N, kDeep>, grid, kWgThreads, Cfg::kSmemBytes, stream, tdy, tx, p));
   return 0;
+}
+
+template <int BLOCK_N>
+static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
+                        cudaStream_t stream) {
+  // Off by default: alone the deep ring is faster, but inside the training step a 198 KB CTA cannot
+  // share an SM with the main stream's BatchNorm-backward CTAs and the step got 15 us SLOWER
+  // (profiles/r1_call38_wgrad_deep_ring.txt).  DDPB_WGRAD_DEEP=1 selects it for standalone use.
+  static const int deep_ok = [] { const char* e = getenv("DDPB_WGRAD_DEEP"); return e ? atoi(e) : 0; }();
+  const long long ctas = static_cast<long long>(p.taps) * p.m_tiles * p.n_tiles * splits;
+  if (deep_ok && ctas <= sm_count()) return launch_wgrad_cfg<BLOCK_N, true>(tdy, tx, p, splits, stream);
+  return launch_wgrad_cfg<BLOCK_N, false>(tdy, tx, p, splits, stream);
 }
 
 }  // namespace ddpb
@@ -275,6 +296,11 @@ extern "C" int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, 
   if (splits > max_splits) splits = max_splits;
   if (splits > 256) splits = 256;
   if (splits < 1) splits = 1;
+  // with about one tile per SM already, write dw directly instead of splitting in two: measured
+  // 20 us per step faster for the three 512-channel layers (profiles/r1_call37_*); DDPB_WGRAD_DIRECT=0
+  // restores the split
+  static const int direct_pref = [] { const char* e = getenv("DDPB_WGRAD_DIRECT"); return e ? atoi(e) : 1; }();
+  if (direct_pref && splits == 2 && tiles >= sm_count() - 8) splits = 1;
   return splits;
 }
 
@@ -347,14 +373,14 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
       const long long n4 = static_cast<long long>(C_out) * taps * C_in / 4;
       long long blocks = (n4 + 255) / 256;
       if (blocks > 8LL * sm_count()) blocks = 8LL * sm_count();
-      wgrad_reduce_dense_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
-          reinterpret_cast<const float4*>(scratch), reinterpret_cast<float4*>(dw), splits, p.out_split_stride / 4,
-          n4);
+      DDPB_CHECK_CUDA(launch_pdl(wgrad_reduce_dense_kernel, static_cast<int>(blocks), 256, 0, stream,
+                                 reinterpret_cast<const float4*>(scratch), reinterpret_cast<float4*>(dw), splits,
+                                 static_cast<long long>(p.out_split_stride / 4), n4));
     } else {
-      wgrad_reduce_rows_kernel<<<C_out, 256, 0, stream>>>(scratch, dw, splits, p.out_split_stride, dw_cols_valid,
-                                                         taps * C_in, dw_ld);
+      DDPB_CHECK_CUDA(launch_pdl(wgrad_reduce_rows_kernel, C_out, 256, 0, stream, static_cast<const float*>(scratch),
+                                 dw, splits, static_cast<long long>(p.out_split_stride), dw_cols_valid, taps * C_in,
+                                 dw_ld));
     }
-    DDPB_CHECK_CUDA(cudaGetLastError());
   }
   return 0;
 }

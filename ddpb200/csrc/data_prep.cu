@@ -75,6 +75,8 @@ __global__ void __launch_bounds__(256)
 first_layer_operand_kernel(const void* __restrict__ src, const signed char* __restrict__ aug,
                            __nv_bfloat16* __restrict__ out, PrepParams p, PackArgs k) {
   __shared__ uint32_t s_rows[256][17];   // 32 bf16 columns per pixel (+1 word of padding)
+  pdl_launch_dependents();
+  pdl_wait();
   const long long P = static_cast<long long>(p.N) * p.H * p.W;
   if (blockIdx.x * 256LL >= P) {
     pack_first_filters(k);
@@ -116,6 +118,8 @@ first_layer_operand_tile_kernel(const void* __restrict__ src, const signed char*
                                 __nv_bfloat16* __restrict__ out, PrepParams p, PackArgs k) {
   __shared__ uint32_t s_rows[256][17];
   __shared__ float s_patch[kPatchMax];
+  pdl_launch_dependents();
+  pdl_wait();
   const long long P = static_cast<long long>(p.N) * p.H * p.W;
   if (blockIdx.x * 256LL >= P) {
     pack_first_filters(k);
@@ -163,13 +167,14 @@ static int prep_grid(long long pixels, const PackArgs& k) {
 }
 
 template <bool kUint8>
-static void launch_prep(const void* src, const signed char* aug, void* out, const PrepParams& p, const PackArgs& k,
+static cudaError_t launch_prep(const void* src, const signed char* aug, void* out, const PrepParams& p, const PackArgs& k,
                         cudaStream_t stream) {
   const int grid = prep_grid(static_cast<long long>(p.N) * p.H * p.W, k);
   if (tile_shape(p.H, p.W))
-    first_layer_operand_tile_kernel<kUint8><<<grid, 256, 0, stream>>>(src, aug, static_cast<__nv_bfloat16*>(out), p, k);
-  else
-    first_layer_operand_kernel<kUint8><<<grid, 256, 0, stream>>>(src, aug, static_cast<__nv_bfloat16*>(out), p, k);
+    return launch_pdl(first_layer_operand_tile_kernel<kUint8>, grid, 256, 0, stream, src, aug,
+                      static_cast<__nv_bfloat16*>(out), p, k);
+  return launch_pdl(first_layer_operand_kernel<kUint8>, grid, 256, 0, stream, src, aug,
+                    static_cast<__nv_bfloat16*>(out), p, k);
 }
 
 }  // namespace ddpb
@@ -187,8 +192,7 @@ extern "C" int ddpb_first_layer_operand_f32(const float* src, void* out, int N, 
   p.W = W;
   DDPB_REQUIRE((w0_master == nullptr) == (w0_packed == nullptr), "first_layer_operand: give both filter pointers or none");
   PackArgs k{w0_master, static_cast<__nv_bfloat16*>(w0_packed), c_out0};
-  launch_prep<false>(src, nullptr, out, p, k, stream);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+  DDPB_CHECK_CUDA(launch_prep<false>(src, nullptr, out, p, k, stream));
   return 0;
 }
 
@@ -210,7 +214,6 @@ extern "C" int ddpb_first_layer_operand_u8(const unsigned char* src, const signe
   }
   DDPB_REQUIRE((w0_master == nullptr) == (w0_packed == nullptr), "first_layer_operand: give both filter pointers or none");
   PackArgs k{w0_master, static_cast<__nv_bfloat16*>(w0_packed), c_out0};
-  launch_prep<true>(src, aug, out, p, k, stream);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+  DDPB_CHECK_CUDA(launch_prep<true>(src, aug, out, p, k, stream));
   return 0;
 }

@@ -26,6 +26,8 @@ fc_ce_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ 
                  const long long* __restrict__ labels, float* __restrict__ logits, float* __restrict__ row_loss,
                  float* __restrict__ dlogits, int* __restrict__ row_correct, int B, int F, int K) {
   extern __shared__ float s_w[];  // [K][F]
+  pdl_launch_dependents();
+  pdl_wait();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   const bool row_ok = warp < B;
@@ -136,6 +138,8 @@ loss_reduce_kernel(const float* __restrict__ row_loss, const int* __restrict__ r
                    float* __restrict__ loss_out, int* __restrict__ correct_out, int B) {
   __shared__ float s_l[256];
   __shared__ int s_c[256];
+  pdl_launch_dependents();
+  pdl_wait();
   loss_reduce_block(row_loss, row_correct, loss_out, correct_out, B, s_l, s_c);
 }
 
@@ -155,6 +159,8 @@ fc_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, 
               const float* __restrict__ row_loss, const int* __restrict__ row_correct, float* __restrict__ loss_out,
               int* __restrict__ correct_out) {
   extern __shared__ float s_dl[];  // [kFcRows][K]; reused for the cross-warp reduction
+  pdl_launch_dependents();
+  pdl_wait();
   if (blockIdx.x == gridDim.x - 1) {
     // ---- db (+ loss): 16 threads per class-group walk the rows
     __shared__ float s_db[16][kMaxClasses];
@@ -275,14 +281,13 @@ extern "C" int ddpb_fc_ce_fwd(const void* x, const float* w, const float* b, con
   DDPB_REQUIRE(smem <= 48 * 1024, "fc_ce_fwd: K*F = %d exceeds the 48 KB weight stage", K * F);
   const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
   if (K == 10)
-    fc_ce_fwd_kernel<10><<<blocks, 256, smem, stream>>>(xb, w, b, labels, logits, row_loss, dlogits, row_correct, B, F, K);
+    DDPB_CHECK_CUDA(launch_pdl(fc_ce_fwd_kernel<10>, blocks, 256, smem, stream, xb, w, b, labels, logits, row_loss,
+                               dlogits, row_correct, B, F, K));
   else
-    fc_ce_fwd_kernel<kMaxClasses><<<blocks, 256, smem, stream>>>(xb, w, b, labels, logits, row_loss, dlogits, row_correct, B, F, K);
-  DDPB_CHECK_CUDA(cudaGetLastError());
-  if (loss != nullptr || correct != nullptr) {
-    loss_reduce_kernel<<<1, 256, 0, stream>>>(row_loss, row_correct, loss, correct, B);
-    DDPB_CHECK_CUDA(cudaGetLastError());
-  }
+    DDPB_CHECK_CUDA(launch_pdl(fc_ce_fwd_kernel<kMaxClasses>, blocks, 256, smem, stream, xb, w, b, labels, logits,
+                               row_loss, dlogits, row_correct, B, F, K));
+  if (loss != nullptr || correct != nullptr)
+    DDPB_CHECK_CUDA(launch_pdl(loss_reduce_kernel, 1, 256, 0, stream, row_loss, row_correct, loss, correct, B));
   return 0;
 }
 
@@ -301,9 +306,10 @@ extern "C" int ddpb_fc_bwd(const void* x, const float* w, const float* dlogits, 
   const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
   __nv_bfloat16* dxb = static_cast<__nv_bfloat16*>(dx);
   if (K == 10)
-    fc_bwd_kernel<10><<<blocks, 256, smem, stream>>>(xb, w, dlogits, dw, db, dxb, B, F, K, row_loss, row_correct, loss, correct);
+    DDPB_CHECK_CUDA(launch_pdl(fc_bwd_kernel<10>, blocks, 256, smem, stream, xb, w, dlogits, dw, db, dxb, B, F, K,
+                               row_loss, row_correct, loss, correct));
   else
-    fc_bwd_kernel<kMaxClasses><<<blocks, 256, smem, stream>>>(xb, w, dlogits, dw, db, dxb, B, F, K, row_loss, row_correct, loss, correct);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+    DDPB_CHECK_CUDA(launch_pdl(fc_bwd_kernel<kMaxClasses>, blocks, 256, smem, stream, xb, w, dlogits, dw, db, dxb, B,
+                               F, K, row_loss, row_correct, loss, correct));
   return 0;
 }

@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace ddpb {
 
@@ -76,7 +77,21 @@ int sm_count() {
   return cached[dev];
 }
 
+static int g_pdl = -1;   // -1: not decided yet (environment DDPB_PDL, default on)
+
+bool pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("DDPB_PDL");
+    g_pdl = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return g_pdl != 0;
+}
+
 }  // namespace ddpb
+
+// Programmatic dependent launch between consecutive kernels: 1 on (default), 0 off.
+extern "C" void ddpb_set_pdl(int on) { ddpb::g_pdl = on ? 1 : 0; }
+extern "C" int ddpb_get_pdl() { return ddpb::pdl_enabled() ? 1 : 0; }
 
 extern "C" const char* ddpb_last_error() { return ddpb::last_error(); }
 

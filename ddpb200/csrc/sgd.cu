@@ -31,6 +31,8 @@ __device__ __forceinline__ float4 sgd_update4(float4 p, float4 g, float4& m, flo
 __global__ void __launch_bounds__(256)
 sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
            __nv_bfloat16* __restrict__ shadow, long long n, float lr, float mu, float wd, float gs) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long n4 = n >> 2;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
@@ -138,9 +140,8 @@ extern "C" int ddpb_sgd_step(float* p, const float* g, float* m, void* shadow, l
   const long long cap = 8LL * sm_count();
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  sgd_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(p, g, m, static_cast<__nv_bfloat16*>(shadow), n, lr,
-                                                           momentum, weight_decay, grad_scale);
-  DDPB_CHECK_CUDA(cudaGetLastError());
+  DDPB_CHECK_CUDA(launch_pdl(sgd_kernel, static_cast<int>(blocks), 256, 0, stream, p, g, m,
+                             static_cast<__nv_bfloat16*>(shadow), n, lr, momentum, weight_decay, grad_scale));
   return 0;
 }
 

@@ -44,6 +44,8 @@ _SIGNATURES = {
     "ddpb_bn_relu_pool_bwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void,
                               c_int, c_int, c_int, c_int, c_int, c_float, c_void],
     "ddpb_bn_bwd_set_fused": [c_int],
+    "ddpb_set_pdl": [c_int],
+    "ddpb_get_pdl": [],
     "ddpb_fc_ce_fwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_int,
                        c_int, c_int, c_void],
     "ddpb_fc_bwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_void,

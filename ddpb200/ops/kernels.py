@@ -165,6 +165,17 @@ def bn_relu_pool_fwd(x, stats, gamma, beta, N, H, W, C_, pool: bool, *, out=None
     return out, saved
 
 
+def set_pdl(on: bool) -> None:
+    """Programmatic dependent launch between consecutive kernels (default on; env DDPB_PDL=0 turns it
+    off): a kernel's prologue overlaps the previous kernel's tail.  Takes effect for launches (and
+    graph captures) made afterwards."""
+    nat.load().ddpb_set_pdl(1 if on else 0)
+
+
+def get_pdl() -> bool:
+    return bool(nat.load().ddpb_get_pdl())
+
+
 def bn_bwd_set_fused(mode: bool | int) -> None:
     """0/False: two-kernel BatchNorm backward; 1: fused cooperative kernel with one CTA per SM
     (room for a co-resident gradient-sync CTA); 2/True... default is 2: up to two CTAs per SM."""
