@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch")
     ap.add_argument("--no-overlap-wgrad", action="store_true", help="weight gradients on the main stream")
+    ap.add_argument("--bn-fused", type=int, default=None, help="BatchNorm backward: 0 two kernels, 1/2 fused (CTAs per SM)")
     ap.add_argument("--comm-blocks", type=int, default=None)
     ap.add_argument("--bucket-layout", choices=["per_layer", "reference", "balanced"], default="reference")
     ap.add_argument("--comm-threads", type=int, default=512)
@@ -144,6 +145,9 @@ def run_ours(a):
                               overlap_wgrad=not a.no_overlap_wgrad,
                               first_bucket_bytes=None if a.bucket_mb is None else int(min(1.0, a.bucket_mb) * 2**20),
                               bucket_bytes=None if a.bucket_mb is None else int(a.bucket_mb * 2**20))
+    if a.bn_fused is not None:   # (after the Trainer, whose 'ddp' mode picks its own default)
+        from ddpb200.ops import kernels as _K2
+        _K2.bn_bwd_set_fused(a.bn_fused)
     n_rot = 8
     host = synthetic_host_batches(n_rot, per_gpu, seed=1234 + rank)
     dev_batches = [(i.to(device), l.to(device), g.to(device)) for i, l, g in host]

@@ -41,7 +41,8 @@ def sources() -> list[Path]:
 
 
 def _headers_mtime() -> float:
-    hs = list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h")) + list((ROOT.parent / "include").glob("*.h"))
+    hs = (list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.inl")) + list(CSRC.glob("*.h")) +
+          list((ROOT.parent / "include").glob("*.h")))
     return max((h.stat().st_mtime for h in hs), default=0.0)
 
 

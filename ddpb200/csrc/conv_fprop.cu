@@ -19,6 +19,7 @@
 // which also adds the bias and accumulates the per-channel sum / sum of squares
 // that BatchNorm needs (O4), so the conv output is not re-read for statistics.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace ddpb {
 
@@ -58,6 +59,7 @@ struct FpropParams {
   __nv_bfloat16* act;    // [P or P/4][C_out]
   float* saved;          // [2][C_out] mean, rstd for the backward pass
   unsigned int* grid_sync;  // one zeroed word: all CTAs meet here once the statistics are complete
+  unsigned int* fin_sync;   // persistent kernel, split-K: zeroed word -> partials are summed in-kernel (null: off)
   int H, W, pool;
   float eps;
 };
@@ -665,7 +667,7 @@ struct BnTail {
 // Returns 0 on success; *fused_bn (if given) tells whether the BatchNorm tail ran inside the conv kernel.
 static int conv_impl(int dgrad, const void* x, const void* w, const float* bias, void* y, float* stats, int N, int H,
                      int W, int C_in, int C_out, int taps, int block_n, float* scratch, cudaStream_t stream,
-                     const BnTail* bn_tail = nullptr, int* fused_bn = nullptr) {
+                     const BnTail* bn_tail = nullptr, int* fused_bn = nullptr, unsigned int* fin_sync = nullptr) {
   const char* name = dgrad ? "conv_dgrad" : "conv_fprop";
   DDPB_REQUIRE(taps == 1 || taps == 9, "%s: taps must be 1 or 9 (got %d)", name, taps);
   DDPB_REQUIRE(C_in % 64 == 0 && C_in > 0, "%s: reduction channels must be a multiple of 64 (got %d)", name, C_in);
@@ -722,13 +724,19 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   p.act = nullptr;
   p.saved = nullptr;
   p.grid_sync = nullptr;
+  p.fin_sync = nullptr;
   p.H = H;
   p.W = W;
   p.pool = 0;
   p.eps = 0.f;
   if (fused_bn != nullptr) *fused_bn = 0;
-  // BatchNorm tail inside the kernel: persistent kernel, no split-K, whole 2x2 windows per tile
-  if (bn_tail != nullptr && stats != nullptr && pl.pair == 2 && pl.splits == 1 && (!bn_tail->pool || bh % 2 == 0)) {
+  // split-K partials summed inside the persistent kernel (after a grid barrier) when the caller
+  // provides the barrier word and a thread can own one 8-channel group
+  const bool fin_in_kernel = pl.pair == 2 && pl.splits > 1 && fin_sync != nullptr && kPersistThreads % (C_out / 8) == 0;
+  if (fin_in_kernel) p.fin_sync = fin_sync;
+  // BatchNorm tail inside the kernel: persistent kernel, whole 2x2 windows per tile
+  if (bn_tail != nullptr && stats != nullptr && pl.pair == 2 && (pl.splits == 1 || fin_in_kernel) &&
+      (!bn_tail->pool || bh % 2 == 0)) {
     p.gamma = bn_tail->gamma;
     p.beta = bn_tail->beta;
     p.act = static_cast<__nv_bfloat16*>(bn_tail->act);
@@ -766,7 +774,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
     DDPB_CONV_DISPATCH(launch_fprop)
   }
 #undef DDPB_CONV_DISPATCH
-  if (rc != 0 || splits == 1) return rc;
+  if (rc != 0 || splits == 1 || fin_in_kernel) return rc;
   const long long items = static_cast<long long>(p.P) * (C_out / 8);
   long long blocks = (items + 255) / 256;
   if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
@@ -801,7 +809,13 @@ extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const fl
                                           int pool, float eps, float* scratch, cudaStream_t stream) {
   BnTail bn{gamma, beta, act, saved, pool, eps};
   int fused = 0;
-  if (int rc = conv_impl(0, x, w, bias, conv_out, stats, N, H, W, C_in, C_out, taps, 0, scratch, stream, &bn, &fused))
+  // words 2*C_out (BatchNorm barrier) and 2*C_out + 1 (split-K finalize barrier) of `stats`
+  // Off by default: summing the split-K partials inside the kernel (two grid barriers) measured
+  // 8 us per step SLOWER than the finalize + BatchNorm kernels with programmatic launch overlap
+  // (profiles/r1_call40_*); DDPB_FWD_FIN_IN_KERNEL=1 selects it.
+  static const int fin_in_kernel = [] { const char* e = getenv("DDPB_FWD_FIN_IN_KERNEL"); return e ? atoi(e) : 0; }();
+  if (int rc = conv_impl(0, x, w, bias, conv_out, stats, N, H, W, C_in, C_out, taps, 0, scratch, stream, &bn, &fused,
+                         fin_in_kernel ? reinterpret_cast<unsigned int*>(stats + 2 * C_out) + 1 : nullptr))
     return rc;
   if (fused) return 0;
   return bn_relu_pool_fwd_launch(conv_out, stats, gamma, beta, act, saved, N, H, W, C_out, pool, eps, stream);
@@ -809,8 +823,11 @@ extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const fl
 
 // Data gradient of the 3x3 convolution (O2).  dy: [N][H][W][C_out] bf16; w: the SAME bf16 pack
 // fprop uses, [C_out][9][C_in]; dx: [N*H*W][C_in] bf16.  scratch: as for fprop, sized with
-// ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n).
+// ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n).  sync: one 32-bit word of
+// device memory that is ZERO on entry (left non-zero), or null; with it a split-K launch sums its
+// partial tiles inside the same kernel instead of launching a finalize kernel.
 extern "C" int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out,
-                               int block_n, float* scratch, cudaStream_t stream) {
-  return conv_impl(1, dy, w, nullptr, dx, nullptr, N, H, W, C_out, C_in, 9, block_n, scratch, stream);
+                               int block_n, float* scratch, unsigned int* sync, cudaStream_t stream) {
+  return conv_impl(1, dy, w, nullptr, dx, nullptr, N, H, W, C_out, C_in, 9, block_n, scratch, stream, nullptr, nullptr,
+                   sync);
 }

@@ -47,6 +47,27 @@ __device__ __forceinline__ PersistItem persist_item(int item, int m_tiles, int n
   return it;
 }
 
+// Grid-wide barrier for the persistent kernel (all CTAs are co-resident: at most one per SM).
+// `word` must be zero when the kernel starts; each barrier of a launch needs its own word.
+__device__ __forceinline__ void persist_grid_barrier(unsigned int* word, const char* what) {
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    atomicAdd(word, 1u);
+    const unsigned long long t0 = global_timer_ns();
+    unsigned int seen, spins = 0;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(word) : "memory");
+      if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_WAIT_TIMEOUT_NS) {
+        printf("ddpb200: %s grid barrier timed out (block %d: %u of %u)\n", what, blockIdx.x, seen, gridDim.x);
+        __trap();
+      }
+    } while (seen < gridDim.x);
+    __threadfence();
+  }
+  __syncthreads();
+}
+
 template <int BLOCK_N, bool kDgrad>
 __global__ void __launch_bounds__(kPersistThreads, 1)
 conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
@@ -322,6 +343,57 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 
+  // ===================== in-kernel split-K finalize =====================
+  // With p.fin_sync the partial tiles in p.partial are summed here, after a grid-wide barrier,
+  // instead of by a second kernel: y = bf16(sum_s partial[s] + bias), statistics accumulated.
+  // One thread owns one 8-channel group (blockDim % (C_out/8) == 0, checked by the host) and
+  // walks pixels with a grid stride, so its running sums stay in registers.
+  if (p.fin_sync != nullptr) {
+    persist_grid_barrier(p.fin_sync, "split-K finalize");
+    const int groups = p.C_out / 8;
+    const int rows_per_pass = blockDim.x / groups;
+    const int g = threadIdx.x % groups, r = threadIdx.x / groups;
+    float bv[8], s1[8], s2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      bv[j] = p.bias != nullptr ? __ldg(p.bias + g * 8 + j) : 0.f;
+      s1[j] = s2[j] = 0.f;
+    }
+    for (long long pix = static_cast<long long>(blockIdx.x) * rows_per_pass + r; pix < p.P;
+         pix += static_cast<long long>(gridDim.x) * rows_per_pass) {
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = bv[j];   // same summation order as splitk_finalize_kernel
+#pragma unroll 4
+      for (int sp = 0; sp < splits; ++sp) {
+        const float4* src =
+            reinterpret_cast<const float4*>(p.partial + (static_cast<long long>(sp) * p.P + pix) * p.C_out + g * 8);
+        const float4 a = __ldcg(src), b = __ldcg(src + 1);   // written by other SMs: L2, not L1
+        v[0] += a.x; v[1] += a.y; v[2] += a.z; v[3] += a.w;
+        v[4] += b.x; v[5] += b.y; v[6] += b.z; v[7] += b.w;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[j] = bf16_round(v[j]);
+        s1[j] += v[j];
+        s2[j] = fmaf(v[j], v[j], s2[j]);
+      }
+      store8(p.out + pix * p.C_out + g * 8, v);
+    }
+    if (p.stats != nullptr) {
+      float* s_acc = reinterpret_cast<float*>(tiles);   // the operand ring is idle
+      for (int c = threadIdx.x; c < 2 * p.C_out; c += blockDim.x) s_acc[c] = 0.f;
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(&s_acc[g * 8 + j], s1[j]);
+        atomicAdd(&s_acc[p.C_out + g * 8 + j], s2[j]);
+      }
+      __syncthreads();
+      for (int c = threadIdx.x; c < 2 * p.C_out; c += blockDim.x) atomicAdd(p.stats + c, s_acc[c]);
+    }
+  }
+
   // ===================== fused BatchNorm + ReLU (+ pool) =====================
   // The conv output of this layer is only ever consumed by its BatchNorm, whose statistics
   // were accumulated by the epilogues above.  Instead of a second kernel, all CTAs meet at a
@@ -329,22 +401,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   // scale/shift and then normalise the tiles THEY just wrote (still in L2).  Every 128-pixel
   // tile holds whole 2x2 pooling windows, so no CTA needs another CTA's pixels.
   if (p.act != nullptr) {
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      atomicAdd(p.grid_sync, 1u);
-      const unsigned long long t0 = global_timer_ns();
-      unsigned int seen, spins = 0;
-      do {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.grid_sync) : "memory");
-        if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_WAIT_TIMEOUT_NS) {
-          printf("ddpb200: conv+bn grid barrier timed out (block %d: %u of %u)\n", blockIdx.x, seen, gridDim.x);
-          __trap();
-        }
-      } while (seen < gridDim.x);
-      __threadfence();
-    }
-    __syncthreads();
+    persist_grid_barrier(p.grid_sync, "conv+bn");
     // the operand ring is idle now: reuse it for the per-channel coefficients
     float* s_scale = reinterpret_cast<float*>(tiles);
     float* s_shift = s_scale + p.C_out;
@@ -371,7 +428,8 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     const int nwin = p.pool ? 4 : 1;
     // flat index over ALL of this CTA's tiles, so a thread always has kUnroll independent items
     // in flight (a single tile is only 256..1024 items: fewer than the block has threads)
-    const int my_tiles = (n_items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const int out_tiles = m_tiles * n_tiles;             // (with split-K, several items share a tile)
+    const int my_tiles = (out_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
     const long long my_total = static_cast<long long>(my_tiles) * per_tile;
     {
       for (long long base = threadIdx.x; base < my_total; base += static_cast<long long>(blockDim.x) * kUnroll) {
@@ -409,7 +467,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
 #pragma unroll
             for (int d = 0; d < 4; ++d)
               if (d < nwin)
-                raw[u][d] = *reinterpret_cast<const uint4*>(p.out + (in00 + (d >> 1) * p.W + (d & 1)) * p.C_out + chv[u]);
+                raw[u][d] = __ldcg(reinterpret_cast<const uint4*>(p.out + (in00 + (d >> 1) * p.W + (d & 1)) * p.C_out + chv[u]));
           }
         }
         // 2) normalise, rectify, pool, store

@@ -275,16 +275,19 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Wgr
   return launch_wgrad_cfg<BLOCK_N, false>(tdy, tx, p, splits, stream);
 }
 
-}  // namespace ddpb
+#include "conv_wgrad_taps.inl"
 
-using namespace ddpb;
+// Launch plan.  fused: the tap-fused cluster kernel (3x3 layers with C_out % 128 == 0) with
+// `cluster` CTAs per thread-block cluster and `groups` clusters per tile (global partial tiles
+// only when groups > 1); otherwise the one-tap kernel with `groups` pixel splits.
+struct WgPlan {
+  bool fused;
+  int block_n;
+  int cluster;
+  int groups;
+};
 
-// Number of pixel splits the launcher will use for this shape (so callers can size scratch).
-extern "C" int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps) {
-  const int P = N * H * W;
-  const int block_n = (C_in % 128 == 0) ? 128 : 64;
-  const int m_tiles = (C_out + 127) / 128;
-  const int tiles = taps * m_tiles * (C_in / block_n);
+static int legacy_splits(int P, int tiles) {
   const int pix_blocks = (P + kWgPix - 1) / kWgPix;
   // two CTAs fit per SM: aim for ONE full wave (rounding down avoids a nearly empty second wave)
   int target = 2 * sm_count();
@@ -297,18 +300,67 @@ extern "C" int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, 
   if (splits > 256) splits = 256;
   if (splits < 1) splits = 1;
   // with about one tile per SM already, write dw directly instead of splitting in two: measured
-  // 20 us per step faster for the three 512-channel layers (profiles/r1_call37_*); DDPB_WGRAD_DIRECT=0
-  // restores the split
-  static const int direct_pref = [] { const char* e = getenv("DDPB_WGRAD_DIRECT"); return e ? atoi(e) : 1; }();
-  if (direct_pref && splits == 2 && tiles >= sm_count() - 8) splits = 1;
+  // 20 us per step faster for the three 512-channel layers (profiles/r1_call37_*)
+  if (splits == 2 && tiles >= sm_count() - 8) splits = 1;
   return splits;
+}
+
+// 0 (default): one-tap kernel, global split reduction.  1: tap-fused cluster kernel.  Measured on
+// B200 at batch 256 (profiles/r1_call43_wgrad_tap_fused.txt): the fused kernel is correct and
+// deterministic but SLOWER -- 187 us (cluster 1) / 197 us (cluster 4) against 159 us for the eight
+// layers, 0.740 vs 0.697 ms per training step.  One 192 KB CTA per SM loses the overlap two
+// 97 KB CTAs give each other (prologue, epilogue, TMEM drain), and the MMA count is unchanged.
+static int g_wgrad_mode = -1;
+
+static WgPlan plan_wgrad(int N, int H, int W, int C_in, int C_out, int taps) {
+  if (g_wgrad_mode < 0) {
+    const char* e = getenv("DDPB_WGRAD_TAPS");
+    g_wgrad_mode = e ? atoi(e) : 0;
+  }
+  const int fused_ok = g_wgrad_mode;
+  WgPlan pl;
+  const int P = N * H * W;
+  pl.block_n = (C_in % 128 == 0) ? 128 : 64;
+  const int m_tiles = (C_out + 127) / 128;
+  const int n_tiles = C_in / pl.block_n;
+  pl.fused = fused_ok && taps == 9 && C_out % 128 == 0;
+  if (!pl.fused) {
+    pl.cluster = 1;
+    pl.groups = legacy_splits(P, taps * m_tiles * n_tiles);
+    return pl;
+  }
+  // one CTA per SM (its ring fills the shared memory): as many pixel splits as there are SMs per
+  // tile, at least 8 pipeline steps each; up to four of them share a cluster
+  const int tiles = kWg3Taps * m_tiles * n_tiles;
+  const int pix_blocks = (P + kWgPix - 1) / kWgPix;
+  int total = sm_count() / tiles;
+  if (total > pix_blocks / 8) total = pix_blocks / 8;
+  if (total < 1) total = 1;
+  static const int max_cluster = [] { const char* e = getenv("DDPB_WGRAD_CLUSTER"); return e ? atoi(e) : 4; }();
+  pl.cluster = (total >= 4 && max_cluster >= 4) ? 4 : ((total >= 2 && max_cluster >= 2) ? 2 : 1);
+  pl.groups = total / pl.cluster;
+  return pl;
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+// 0: one-tap kernel (default); 1: tap-fused kernel with the split reduction inside a cluster.
+// Changes ddpb_conv_wgrad_scratch_elems() for later calls.
+extern "C" void ddpb_conv_wgrad_set_mode(int mode) { ddpb::g_wgrad_mode = mode ? 1 : 0; }
+
+// Number of pixel splits the launcher will use for this shape (so callers can size scratch).
+extern "C" int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps) {
+  const WgPlan pl = plan_wgrad(N, H, W, C_in, C_out, taps);
+  return pl.cluster * pl.groups;
 }
 
 // Scratch floats needed by ddpb_conv_wgrad for this shape (0 if it writes dw directly).
 extern "C" long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps) {
-  const int splits = ddpb_conv_wgrad_splits(N, H, W, C_in, C_out, taps);
+  const WgPlan pl = plan_wgrad(N, H, W, C_in, C_out, taps);
   const long long rows = (C_out < 128) ? 128 : C_out;   // dup_m tiles still own 128 rows of scratch
-  return (splits > 1 || C_out < 128) ? static_cast<long long>(splits) * rows * taps * C_in : 0;
+  return (pl.groups > 1 || C_out < 128) ? static_cast<long long>(pl.groups) * rows * taps * C_in : 0;
 }
 
 // Shared implementation: `scratch` may be any device buffer of at least
@@ -322,9 +374,13 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
   int bh, bn, hblocks;
   DDPB_REQUIRE(pixel_box(H, W, kWgPix, &bh, &bn, &hblocks),
                "conv_wgrad: unsupported spatial size %dx%d for 64-pixel boxes", H, W);
-  const int block_n = (C_in % 128 == 0) ? 128 : 64;
-  const int splits = ddpb_conv_wgrad_splits(N, H, W, C_in, C_out, taps);
-  const bool direct = (splits == 1 && C_out >= 128 && dw_cols_valid == taps * C_in && dw_ld == taps * C_in);
+  const WgPlan pl = plan_wgrad(N, H, W, C_in, C_out, taps);
+  const int block_n = pl.block_n;
+  const int splits = pl.groups;   // partial tiles in global memory
+  DDPB_REQUIRE(!pl.fused || dw_cols_valid == taps * C_in, "conv_wgrad: a 3x3 layer's dw must take all %d columns",
+               taps * C_in);
+  const bool direct = (splits == 1 && C_out >= 128 && dw_cols_valid == taps * C_in &&
+                       (pl.fused || dw_ld == taps * C_in));
   DDPB_REQUIRE(direct || scratch != nullptr, "conv_wgrad: this shape needs scratch memory");
 
   CUtensorMap tdy, tx;
@@ -359,13 +415,19 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
   const long long rows = (C_out < 128) ? 128 : C_out;
   if (direct) {
     p.out = dw;
+    p.out_ld = dw_ld;
     p.out_split_stride = 0;
   } else {
     p.out = scratch;
     p.out_split_stride = rows * taps * C_in;
   }
-  int rc = (block_n == 128) ? launch_wgrad<128>(tdy, tx, p, splits, stream)
-                            : launch_wgrad<64>(tdy, tx, p, splits, stream);
+  int rc;
+  if (pl.fused)
+    rc = (block_n == 128) ? launch_wgrad3<128>(tdy, tx, p, pl.cluster, pl.groups, stream)
+                          : launch_wgrad3<64>(tdy, tx, p, pl.cluster, pl.groups, stream);
+  else
+    rc = (block_n == 128) ? launch_wgrad<128>(tdy, tx, p, splits, stream)
+                          : launch_wgrad<64>(tdy, tx, p, splits, stream);
   if (rc) return rc;
   if (!direct) {
     const bool dense = (dw_cols_valid == taps * C_in && dw_ld == taps * C_in && C_out >= 128);

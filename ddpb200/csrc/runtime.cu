@@ -89,6 +89,18 @@ bool pdl_enabled() {
 
 }  // namespace ddpb
 
+namespace ddpb {
+__global__ void stamp_kernel(unsigned long long* slot) { *slot = global_timer_ns(); }
+}  // namespace ddpb
+
+// Diagnostics: writes %globaltimer (ns) to *slot when the stream reaches this point -- a one-thread
+// kernel, launched without programmatic overlap so it runs after everything before it completed.
+extern "C" int ddpb_stamp(unsigned long long* slot, cudaStream_t stream) {
+  ddpb::stamp_kernel<<<1, 1, 0, stream>>>(slot);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // Programmatic dependent launch between consecutive kernels: 1 on (default), 0 off.
 extern "C" void ddpb_set_pdl(int on) { ddpb::g_pdl = on ? 1 : 0; }
 extern "C" int ddpb_get_pdl() { return ddpb::pdl_enabled() ? 1 : 0; }

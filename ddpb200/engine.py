@@ -21,6 +21,8 @@ from __future__ import annotations
 
 from dataclasses import dataclass
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -183,8 +185,33 @@ class VGGEngine:
                 need = max(need, K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_out, L.c_in, 9))
         self.fprop_scratch = torch.empty(need, **f32)
         self.image_hw = image_hw
+        self._tl = None
+        self._tl_labels = []
+        self.dgrad_sum_in_kernel = os.environ.get("DDPB_DGRAD_FIN_IN_KERNEL", "0") == "1"
         self.repack(full=True)
         _register_engine(self)
+
+    # -- diagnostics ----------------------------------------------------------------------------
+    def enable_timeline(self, slots: int = 256):
+        """Every mark() from now on stamps %globaltimer into a device buffer (bench/step_timeline.py).
+        Must be called before the step is captured in a graph."""
+        self._tl = torch.zeros(slots, dtype=torch.int64, device=self.device)
+        self._tl_labels = []
+
+    def mark(self, label: str, reset: bool = False):
+        if self._tl is None:
+            return
+        if reset:
+            self._tl_labels = []
+        i = len(self._tl_labels)
+        if i < self._tl.numel():
+            K.stamp(self._tl[i:i + 1])
+            self._tl_labels.append(label)
+
+    def timeline(self):
+        """[(label, microseconds since the first mark)] of the last executed step."""
+        t = self._tl[:len(self._tl_labels)].cpu().tolist()
+        return [(lab, (v - t[0]) / 1e3) for lab, v in zip(self._tl_labels, t)]
 
     # -- pieces ---------------------------------------------------------------------------------
     def repack(self, stream=None, full: bool = False):
@@ -213,6 +240,7 @@ class VGGEngine:
         ``defer_loss``: leave the reduction of the per-row losses to backward(reduce_loss=True)."""
         a = self.arena
         self.stat_arena.zero_()
+        self.mark("fwd begin")
         x = self.operand0
         for li, L in enumerate(self.layers):
             # conv (+bias, +statistics) and, inside the same persistent kernel after a grid-wide
@@ -221,6 +249,7 @@ class VGGEngine:
                                     a.flat_master(L.p_beta), N, L.H, L.W, L.c_in_eff, L.c_out, L.taps, L.pool,
                                     conv_out=self.conv_out[li], act=self.act[li], stats=self.stats[li],
                                     saved=self.saved[li], scratch=self.fprop_scratch)
+            self.mark(f"L{li} conv+bn fwd")
             x = self.act[li]
         feat = x[:N]
         if with_loss:
@@ -232,6 +261,7 @@ class VGGEngine:
             # logits only: labels are not read meaningfully, loss outputs are discarded
             K.fc_ce_fwd(feat, a.flat_master(self.p_fcw).view(self.classes, self.feat), a.flat_master(self.p_fcb),
                         self.labels[:N], logits=self.logits, row_loss=self.row_loss)
+        self.mark("fc fwd")
 
     def backward(self, N: int, after_layer=None, side_stream=None, reduce_loss: bool = False):
         """dlogits[:N] -> every gradient in the arena.
@@ -257,6 +287,7 @@ class VGGEngine:
                  dw=a.flat_grad(self.p_fcw), db=a.flat_grad(self.p_fcb), dx=self.dact[last],
                  **(dict(row_loss=self.row_loss[:N], row_correct=self.row_correct[:N], loss=self.loss,
                          correct=self.correct) if reduce_loss else {}))
+        self.mark("fc bwd")
         if after_layer is not None:
             after_layer(last + 1, [])   # the classifier is parameter group len(layers)
         for li in range(last, -1, -1):
@@ -266,6 +297,7 @@ class VGGEngine:
                                a.flat_master(L.p_beta), N, L.H, L.W, L.c_out, L.pool, sums=self.bsums[li],
                                dx=self.dconv[li], dgamma=a.flat_grad(L.p_g), dbeta=a.flat_grad(L.p_beta),
                                dbias=a.flat_grad(L.p_b))
+            self.mark(f"L{li} bn bwd")
             cols = 9 * L.c_in
             if side_stream is not None:
                 fork = torch.cuda.Event()
@@ -274,23 +306,33 @@ class VGGEngine:
                 with torch.cuda.stream(side_stream):
                     K.conv_wgrad(self.dconv[li], x_in, N, L.H, L.W, L.c_in_eff, L.c_out, L.taps,
                                  out=a.flat_grad(L.p_w), cols_valid=cols, out_ld=cols, scratch=self.wgrad_scratch)
+                    self.mark(f"L{li} wgrad (side)")
                     done = torch.cuda.Event()
                     done.record(side_stream)
                 side_events.append(done)
             else:
                 K.conv_wgrad(self.dconv[li], x_in, N, L.H, L.W, L.c_in_eff, L.c_out, L.taps, out=a.flat_grad(L.p_w),
                              cols_valid=cols, out_ld=cols, scratch=self.wgrad_scratch)
+                self.mark(f"L{li} wgrad")
             if li > 0:
+                # sync: a spare zeroed word of this layer's statistics slot lets a split-K dgrad sum its
+                # partial tiles in-kernel.  Off by default: a kernel with a grid barrier cannot start
+                # until every SM has room, and the weight-gradient CTAs of the side stream hold some
+                # (measured 0.691 -> 0.718 ms/step with it, profiles/r1_call39_*).
+                sync = self.bsums[li][2 * L.c_out + 16:2 * L.c_out + 17] if self.dgrad_sum_in_kernel else None
                 K.conv_dgrad(self.dconv[li], self.w_f[li], N, L.H, L.W, L.c_in, L.c_out, out=self.dact[li - 1],
-                             scratch=self.fprop_scratch)
+                             scratch=self.fprop_scratch, sync=sync)
+                self.mark(f"L{li} dgrad")
             if after_layer is not None:
                 after_layer(li, side_events[-1:] if side_stream is not None else [])
         if side_stream is not None and side_events:
             main.wait_event(side_events[-1])   # the side stream is in order: the last event covers all
+            self.mark("bwd joined")
 
     def sgd(self, lr: float, momentum: float, weight_decay: float, grad_scale: float = 1.0):
         a = self.arena
         K.sgd_step(a.master, a.grad, a.momentum, lr, momentum, weight_decay, grad_scale, shadow=self.shadow)
+        self.mark("sgd")
 
     def launches_per_train_step(self, splits_reduce: bool = True) -> int:
         """How many of OUR kernels one fwd+bwd enqueues (excluding sync/SGD/repack/input prep)."""
@@ -302,7 +344,10 @@ class VGGEngine:
                 n += 2              # split-K finalize + separate BatchNorm forward
             if li > 0 and K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_out, L.c_in, 9):
                 n += 1
-            n += 2                  # bn bwd (two passes)
+            # bn bwd: one cooperative kernel when the layer's data fits in shared memory, else two passes
+            slot = 5 if L.pool else 2
+            out_pix = B * L.H * L.W // (4 if L.pool else 1)
+            n += 1 if out_pix * (L.c_out // 8) * slot * 16 <= K.sm_count() * 200 * 1024 else 2
             n += 1                  # wgrad
             if K.conv_wgrad_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps):
                 n += 1              # split-K reduce

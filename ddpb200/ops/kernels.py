@@ -96,8 +96,10 @@ def conv_bn_relu_pool_fwd(x, w, bias, gamma, beta, N, H, W, C_in, C_out, taps, p
 
 def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, C_in: int, C_out: int, *,
                out: torch.Tensor | None = None, block_n: int = 0, scratch: torch.Tensor | None | bool = True,
-               stream=None) -> torch.Tensor:
-    """O2: dx[P, C_in] from dy[P, C_out] and the SAME bf16 filter pack fprop uses ([C_out, 9*C_in])."""
+               sync: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """O2: dx[P, C_in] from dy[P, C_out] and the SAME bf16 filter pack fprop uses ([C_out, 9*C_in]).
+    ``sync``: a ZEROED 4-byte tensor (left non-zero); with it a split-K launch sums its partial tiles
+    inside the conv kernel instead of launching a finalize kernel."""
     nat.require_cuda(dy, w_fprop)
     assert dy.dtype == torch.bfloat16 and w_fprop.dtype == torch.bfloat16
     assert dy.numel() >= N * H * W * C_out and w_fprop.numel() == C_out * 9 * C_in
@@ -108,14 +110,21 @@ def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, 
         scratch = torch.empty(need, dtype=torch.float32, device=dy.device) if need else None
     elif scratch is False:
         scratch = None
+    assert sync is None or (sync.is_cuda and sync.element_size() == 4 and sync.numel() >= 1)
     rc = nat.load().ddpb_conv_dgrad(nat.ptr(dy), nat.ptr(w_fprop), nat.ptr(out), N, H, W, C_in, C_out, block_n,
-                                    nat.ptr(scratch), _s(stream))
+                                    nat.ptr(scratch), nat.ptr(sync), _s(stream))
     nat.check(rc, "ddpb_conv_dgrad")
     return out
 
 
 def conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps=9) -> int:
     return int(nat.load().ddpb_conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps))
+
+
+def conv_wgrad_set_mode(mode: int) -> None:
+    """0: one-tap weight-gradient kernel with a global split reduction (default, measured faster);
+    1: three taps per CTA, pixel splits summed through distributed shared memory in a cluster."""
+    nat.load().ddpb_conv_wgrad_set_mode(int(mode))
 
 
 def conv_wgrad_splits(N, H, W, C_in, C_out, taps=9) -> int:
@@ -163,6 +172,16 @@ def bn_relu_pool_fwd(x, stats, gamma, beta, N, H, W, C_, pool: bool, *, out=None
                                           nat.ptr(saved), N, H, W, C_, int(pool), eps, _s(stream))
     nat.check(rc, "ddpb_bn_relu_pool_fwd")
     return out, saved
+
+
+def stamp(slot: torch.Tensor, stream=None) -> None:
+    """Diagnostics: a one-thread kernel writes %globaltimer (ns) into ``slot`` (int64[1])."""
+    assert slot.is_cuda and slot.dtype == torch.int64 and slot.numel() >= 1
+    nat.check(nat.load().ddpb_stamp(nat.ptr(slot), _s(stream)), "ddpb_stamp")
+
+
+def sm_count() -> int:
+    return int(nat.load().ddpb_sm_count())
 
 
 def set_pdl(on: bool) -> None:

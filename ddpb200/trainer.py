@@ -150,6 +150,7 @@ class Trainer:
         B = self.batch_size if B is None else B
         # the input kernel also refreshes the first layer's padded filter pack; every other conv
         # operand is the SGD-maintained shadow
+        eng.mark("step begin", reset=True)
         if kind == "u8":
             eng.load_input_u8(self.in_u8[:B], self.in_aug[:B] if with_aug else None, pack=True)
         else:

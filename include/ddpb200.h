@@ -20,6 +20,12 @@ extern "C" {
 const char* ddpb_last_error(void);
 int ddpb_abi_version(void);          /* bumped when a signature changes */
 int ddpb_sm_count(void);             /* SMs of the current device (148 without a device) */
+/* Programmatic dependent launch between the library's consecutive kernels (default on, env
+ * DDPB_PDL=0): each kernel's prologue overlaps the previous kernel's tail. */
+void ddpb_set_pdl(int on);
+int ddpb_get_pdl(void);
+/* Diagnostics: a one-thread kernel writes %globaltimer (ns) to *slot at this point of the stream. */
+int ddpb_stamp(unsigned long long* slot, void* stream);
 
 /* ---- convolution (K1, K2, K5, K6) ----------------------------------------------------------- */
 /* O1: nn.Conv2d(3x3, stride 1, pad 1, bias) forward, part1/model.py:18-23.
@@ -34,9 +40,11 @@ long long ddpb_conv_fprop_scratch_elems(int N, int H, int W, int C_in, int C_out
 
 /* O2: data gradient of the same convolution (autograd of part1/model.py:18-23).
  * dx[N*H*W][C_in] from dy[..][C_out] and the SAME filter pack fprop reads (no transposed copy).
- * scratch sized with ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n). */
+ * scratch sized with ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n).
+ * sync: one zeroed 32-bit device word (left non-zero) or null; with it a split-K launch sums its
+ * partial tiles inside the same kernel after a grid barrier instead of in a second kernel. */
 int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out, int block_n,
-                    float* scratch, void* stream);
+                    float* scratch, unsigned int* sync, void* stream);
 
 /* O3: weight gradient.  dw (fp32 [C_out][dw_ld]) gets its first dw_cols_valid (<= taps*C_in)
  * columns per row.  scratch: ddpb_conv_wgrad_scratch_elems() floats of device memory for the
@@ -45,6 +53,10 @@ int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* scratch, in
                     int C_out, int taps, int dw_cols_valid, int dw_ld, void* stream);
 long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps);
 int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps);
+/* 0 (default): one tap per CTA, split reduction through global memory.  1: three taps per CTA and
+ * the split reduction over distributed shared memory inside a thread-block cluster (measured
+ * slower on B200 at the training shapes; kept selectable).  Changes the scratch size. */
+void ddpb_conv_wgrad_set_mode(int mode);
 
 /* No counterpart in the reference.  ddpb_conv_wgrad for callers that must not allocate device
  * memory (a loop that cannot take cudaMalloc's device-wide synchronisation, a process whose

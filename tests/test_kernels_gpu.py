@@ -131,6 +131,23 @@ def test_conv_dgrad_from_fprop_pack(shape):
     assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
 
 
+@pytest.mark.parametrize("shape", [(256, 2, 2, 512, 512), (96, 2, 2, 512, 256), (64, 4, 4, 128, 512)])
+def test_conv_dgrad_split_k_summed_in_kernel(shape):
+    """With a zeroed sync word the split-K partial tiles are summed inside the persistent kernel
+    (grid barrier) -- same result as the separate finalize kernel, twice in a row."""
+    N, H, W, Ci, Co = shape
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Co) ** 0.5).bfloat16()
+    assert K.conv_fprop_scratch_elems(N, H, W, Co, Ci, 9) > 0, "shape is meant to split K"
+    ref = K.conv_dgrad(dy, w, N, H, W, Ci, Co)
+    for _ in range(2):
+        sync = torch.zeros(1, dtype=torch.int32, device=DEV)
+        dx = K.conv_dgrad(dy, w, N, H, W, Ci, Co, sync=sync)
+        assert sync.item() != 0, "the in-kernel finalize did not run"
+        assert torch.equal(dx, ref)
+    assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
+
+
 @pytest.mark.parametrize("shape", CONV_SHAPES + [(64, 32, 32, 64, 128)])
 def test_conv_wgrad(shape):
     N, H, W, Ci, Co = shape
@@ -139,6 +156,25 @@ def test_conv_wgrad(shape):
     dw = K.conv_wgrad(dy, x, N, H, W, Ci, Co)
     ref = R.conv_wgrad(dy, x, N, H, W, Ci, Co)
     assert _rel_err(dw, ref) < 2e-3   # fp32 output: only the summation order differs
+
+
+@pytest.mark.parametrize("shape", [(256, 8, 8, 128, 256), (256, 8, 8, 256, 256), (256, 4, 4, 256, 512),
+                                   (256, 4, 4, 512, 512), (256, 2, 2, 512, 512), (100, 16, 16, 64, 128)])
+def test_conv_wgrad_tap_fused_cluster_reduction(shape):
+    """The training shapes: three taps per CTA, pixel splits summed through distributed shared
+    memory inside a cluster (plus global groups for the long pixel ranges); deterministic."""
+    N, H, W, Ci, Co = shape
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    ref = R.conv_wgrad(dy, x, N, H, W, Ci, Co)
+    try:
+        K.conv_wgrad_set_mode(1)
+        dw = K.conv_wgrad(dy, x, N, H, W, Ci, Co)
+        assert _rel_err(dw, ref) < 2e-3
+        assert torch.equal(dw, K.conv_wgrad(dy, x, N, H, W, Ci, Co))
+    finally:
+        K.conv_wgrad_set_mode(0)
+    assert _rel_err(K.conv_wgrad(dy, x, N, H, W, Ci, Co), ref) < 2e-3   # default kernel, same shapes
 
 
 def test_conv_wgrad_first_layer_compact():
@@ -181,7 +217,7 @@ def test_bn_relu_pool_fwd_bwd(geom, pool, fused):
 
 @pytest.mark.parametrize("pool", [False, True])
 @pytest.mark.parametrize("shape", [(8, 32, 32, 64, 64), (16, 16, 16, 64, 128), (37, 8, 8, 128, 256), (64, 4, 4, 256, 512),
-                                   (96, 2, 2, 512, 512)])
+                                   (96, 2, 2, 512, 512), (256, 2, 2, 512, 512)])
 def test_conv_bn_relu_pool_fused_forward(shape, pool):
     """conv + BatchNorm + ReLU (+pool) in one call (BatchNorm tail inside the persistent kernel
     after a grid barrier, or the split-K fallback) against the ATen composition."""
