@@ -206,7 +206,7 @@ def run_ours(a):
                        "optimizer": "SGD lr=0.1 momentum=0.9 wd=1e-4 (inside the timed step)",
                        "sync": None if world == 1 else {"backend": trainer.symm.backend, "multicast": trainer.use_mc,
                                                        "granularity": a.granularity, "bucket_layout": a.bucket_layout if mode == "ddp" else None, "comm_blocks": trainer.comm_blocks, "buckets_floats": [b.numel for b in trainer.buckets] if mode == "ddp" else None},
-                       "cuda_graph": not a.no_graph, "programmatic_dependent_launch": not a.no_pdl,
+                       "cuda_graph": not a.no_graph, "programmatic_dependent_launch": bool(_pdl_state()),
                        "l2": f"no explicit flush: working set {ws_mb:.0f} MB/step > 126 MB L2; inputs rotate over {n_rot} device batches",
                        "baseline_ref": "BASELINE.md §1: published CPU/Gloo images/s for this worker count"},
             "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "ms_per_step": round(e2e_ms / a.steps, 4),
@@ -363,6 +363,11 @@ def run_reference(a):
         })
     if world > 1:
         dist.destroy_process_group()
+
+
+def _pdl_state():
+    from ddpb200.ops import kernels as _K
+    return _K.get_pdl()
 
 
 def main():

@@ -1,0 +1,17 @@
+#!/bin/bash
+mkdir -p gpurun_out
+run() { local name=$1; local n=$2; shift 2
+  timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29600 + RANDOM % 300)) bench.py --gpus $n --steps 200 --warmup 10 "$@" > gpurun_out/$name.json 2> gpurun_out/$name.err
+  python - "$name" <<'PY'
+import json,sys
+n=sys.argv[1]
+try:
+    d=json.loads([l for l in open(f"gpurun_out/{n}.json") if l.startswith("{")][0]); print(n, d["ms_per_step"], d["value"], "e2e", d["e2e"]["ms_per_step"], d["config"]["sync"]["comm_blocks"], d["clocks"]["reasons"])
+except Exception as e: print(n, "FAILED", e); print(open(f"gpurun_out/{n}.err").read()[-1500:])
+PY
+}
+run g8_ddp_8 8 --mode ddp
+run g8_ddp_8_cb32 8 --mode ddp --comm-blocks 32
+DDPB_TEST_WORLD=8 timeout 200 python -m pytest tests/test_multigpu.py -m gpu -q --timeout 150 -k "p2p and allreduce" > gpurun_out/tests49.log 2>&1
+tail -2 gpurun_out/tests49.log
+run g8_ddp_4 4 --mode ddp

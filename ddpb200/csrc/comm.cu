@@ -154,28 +154,42 @@ __device__ __forceinline__ void sgd_range(const CommCtx& c, const SgdArgs& s, lo
   const float* g = c.buf[c.rank] + off;
   float* p = s.p + off;
   float* m = s.m + off;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
-    const float4 gv = ld_sys(g + 4 * i);   // peers wrote this: do not trust L1
-    float4 pv = reinterpret_cast<float4*>(p)[i];
-    float4 mv = reinterpret_cast<float4*>(m)[i];
-    float4 gg;
-    gg.x = fmaf(s.wd, pv.x, gv.x);
-    gg.y = fmaf(s.wd, pv.y, gv.y);
-    gg.z = fmaf(s.wd, pv.z, gv.z);
-    gg.w = fmaf(s.wd, pv.w, gv.w);
-    mv.x = fmaf(s.mu, mv.x, gg.x);
-    mv.y = fmaf(s.mu, mv.y, gg.y);
-    mv.z = fmaf(s.mu, mv.z, gg.z);
-    mv.w = fmaf(s.mu, mv.w, gg.w);
-    pv.x = fmaf(-s.lr, mv.x, pv.x);
-    pv.y = fmaf(-s.lr, mv.y, pv.y);
-    pv.z = fmaf(-s.lr, mv.z, pv.z);
-    pv.w = fmaf(-s.lr, mv.w, pv.w);
-    reinterpret_cast<float4*>(p)[i] = pv;
-    reinterpret_cast<float4*>(m)[i] = mv;
-    if (s.shadow != nullptr)
-      reinterpret_cast<uint2*>(s.shadow + off)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+  constexpr int kU = 2;   // iterations in flight per thread (the stores of one would otherwise fence the next loads)
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * kU;
+  for (long long base = blockIdx.x * static_cast<long long>(blockDim.x) * kU + threadIdx.x; base < n4; base += stride) {
+    float4 gv[kU], pv[kU], mv[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = base + static_cast<long long>(u) * blockDim.x;
+      if (i < n4) {
+        gv[u] = ld_sys(g + 4 * i);   // peers wrote this: do not trust L1
+        pv[u] = reinterpret_cast<const float4*>(p)[i];
+        mv[u] = reinterpret_cast<const float4*>(m)[i];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = base + static_cast<long long>(u) * blockDim.x;
+      if (i >= n4) continue;
+      float4 gg;
+      gg.x = fmaf(s.wd, pv[u].x, gv[u].x);
+      gg.y = fmaf(s.wd, pv[u].y, gv[u].y);
+      gg.z = fmaf(s.wd, pv[u].z, gv[u].z);
+      gg.w = fmaf(s.wd, pv[u].w, gv[u].w);
+      mv[u].x = fmaf(s.mu, mv[u].x, gg.x);
+      mv[u].y = fmaf(s.mu, mv[u].y, gg.y);
+      mv[u].z = fmaf(s.mu, mv[u].z, gg.z);
+      mv[u].w = fmaf(s.mu, mv[u].w, gg.w);
+      pv[u].x = fmaf(-s.lr, mv[u].x, pv[u].x);
+      pv[u].y = fmaf(-s.lr, mv[u].y, pv[u].y);
+      pv[u].z = fmaf(-s.lr, mv[u].z, pv[u].z);
+      pv[u].w = fmaf(-s.lr, mv[u].w, pv[u].w);
+      reinterpret_cast<float4*>(p)[i] = pv[u];
+      reinterpret_cast<float4*>(m)[i] = mv[u];
+      if (s.shadow != nullptr)
+        reinterpret_cast<uint2*>(s.shadow + off)[i] =
+            make_uint2(pack_bf16x2(pv[u].x, pv[u].y), pack_bf16x2(pv[u].z, pv[u].w));
+    }
   }
 }
 
@@ -187,30 +201,62 @@ allreduce_avg_kernel(const CommCtx c, long long off, long long n4, int slot_base
   peer_barrier(c, slot);  // every rank's gradients for this range are complete
   const float inv_w = 1.f / static_cast<float>(c.world);
   const long long lo = n4 * c.rank / c.world, hi = n4 * (c.rank + 1) / c.world;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = lo + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
-    const long long e = off + 4 * i;
-    float4 acc;
+  // Every remote access is a round trip over NVLink (through the switch for multimem): a thread
+  // keeps kU independent 16-byte requests per peer in flight instead of one.  With one, the 32-CTA
+  // reductions that overlap backward moved 256 KB per round trip and took longer than the
+  // backward pass they were meant to hide behind.
+  // (P2P path: the loads from all `world` peers are already independent; kU = 1 keeps the CTA at
+  // half the register file so that it can share an SM)
+  constexpr int kU = kMc ? 4 : 1;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * kU;
+  for (long long base = lo + blockIdx.x * static_cast<long long>(blockDim.x) * kU + threadIdx.x; base < hi;
+       base += stride) {
+    float4 acc[kU];
     if (kMc) {
-      acc = mc_ld_reduce(c.mc + e);
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = base + static_cast<long long>(u) * blockDim.x;
+        if (i < hi) acc[u] = mc_ld_reduce(c.mc + off + 4 * i);
+      }
     } else {
-      acc = ld_sys(c.buf[0] + e);
-      for (int r = 1; r < c.world; ++r) {   // fixed order: identical rounding on every rank
-        const float4 v = ld_sys(c.buf[r] + e);
-        acc.x += v.x;
-        acc.y += v.y;
-        acc.z += v.z;
-        acc.w += v.w;
+      float4 v[kU][kMaxRanks];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = base + static_cast<long long>(u) * blockDim.x;
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (i < hi && r < c.world) v[u][r] = ld_sys(c.buf[r] + off + 4 * i);
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        acc[u] = v[u][0];
+#pragma unroll
+        for (int r = 1; r < kMaxRanks; ++r) {   // fixed order: identical rounding on every rank
+          if (r < c.world) {
+            acc[u].x += v[u][r].x;
+            acc[u].y += v[u][r].y;
+            acc[u].z += v[u][r].z;
+            acc[u].w += v[u][r].w;
+          }
+        }
       }
     }
-    acc.x *= inv_w;
-    acc.y *= inv_w;
-    acc.z *= inv_w;
-    acc.w *= inv_w;
-    if (kMc) {
-      mc_st(c.mc + e, acc);
-    } else {
-      for (int r = 0; r < c.world; ++r) st_sys(c.buf[r] + e, acc);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = base + static_cast<long long>(u) * blockDim.x;
+      if (i >= hi) continue;
+      const long long e = off + 4 * i;
+      acc[u].x *= inv_w;
+      acc[u].y *= inv_w;
+      acc[u].z *= inv_w;
+      acc[u].w *= inv_w;
+      if (kMc) {
+        mc_st(c.mc + e, acc[u]);
+      } else {
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < c.world) st_sys(c.buf[r] + e, acc[u]);
+      }
     }
   }
   peer_barrier(c, slot);  // every slice has landed everywhere
@@ -228,25 +274,44 @@ reduce_root_bcast_kernel(const CommCtx c, long long off, long long n4, int slot_
   peer_barrier(c, slot);
   if (c.rank == root) {
     const float inv_w = 1.f / static_cast<float>(c.world);
-    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
-      const long long e = off + 4 * i;
-      float4 acc = ld_sys(c.buf[0] + e);
-      for (int r = 1; r < c.world; ++r) {
-        const float4 v = ld_sys(c.buf[r] + e);
-        acc.x += v.x;
-        acc.y += v.y;
-        acc.z += v.z;
-        acc.w += v.w;
+    constexpr int kU = 1;   // the loads from all peers are issued together (see allreduce_avg_kernel)
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * kU;
+    for (long long base = blockIdx.x * static_cast<long long>(blockDim.x) * kU + threadIdx.x; base < n4;
+         base += stride) {
+      float4 v[kU][kMaxRanks];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = base + static_cast<long long>(u) * blockDim.x;
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (i < n4 && r < c.world) v[u][r] = ld_sys(c.buf[r] + off + 4 * i);
       }
-      acc.x *= inv_w;
-      acc.y *= inv_w;
-      acc.z *= inv_w;
-      acc.w *= inv_w;
-      if (kMc) {
-        mc_st(c.mc + e, acc);
-      } else {
-        for (int r = 0; r < c.world; ++r) st_sys(c.buf[r] + e, acc);
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = base + static_cast<long long>(u) * blockDim.x;
+        if (i >= n4) continue;
+        const long long e = off + 4 * i;
+        float4 acc = v[u][0];
+#pragma unroll
+        for (int r = 1; r < kMaxRanks; ++r) {
+          if (r < c.world) {
+            acc.x += v[u][r].x;
+            acc.y += v[u][r].y;
+            acc.z += v[u][r].z;
+            acc.w += v[u][r].w;
+          }
+        }
+        acc.x *= inv_w;
+        acc.y *= inv_w;
+        acc.z *= inv_w;
+        acc.w *= inv_w;
+        if (kMc) {
+          mc_st(c.mc + e, acc);
+        } else {
+#pragma unroll
+          for (int r = 0; r < kMaxRanks; ++r)
+            if (r < c.world) st_sys(c.buf[r] + e, acc);
+        }
       }
     }
   }

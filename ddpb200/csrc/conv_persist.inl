@@ -69,7 +69,7 @@ __device__ __forceinline__ void persist_grid_barrier(unsigned int* word, const c
 }
 
 template <int BLOCK_N, bool kDgrad>
-__global__ void __launch_bounds__(kPersistThreads, 1)
+__global__ void __launch_bounds__(512, 1)   // 512, not 320: caps the kernel at 128 registers per thread
 conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                     const FpropParams p, int m_tiles, int n_tiles, int splits) {
   using Cfg = PersistCfg<BLOCK_N>;

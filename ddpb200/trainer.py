@@ -18,6 +18,8 @@ runs the stock torch modules with the restatements in parallel/sync.py over Gloo
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
@@ -101,7 +103,10 @@ class Trainer:
         self.use_mc = bool(use_multicast and self.symm is not None and self.symm.has_multicast)
         sms = torch.cuda.get_device_properties(self.device).multi_processor_count
         # part3 reductions share the GPU with backward: a slice of the SMs; 2a/2b own the GPU
-        self.comm_blocks = comm_blocks if comm_blocks is not None else (32 if self.mode == "ddp" else min(sms, 128))
+        # 'ddp': CTAs of the reductions that overlap backward.  Each thread keeps four 16-byte
+        # requests in flight, so 16 CTAs already move a bucket in time and leave the SMs to backward
+        # (2 GPUs: 8 / 16 / 32 / 64 CTAs -> 0.797 / 0.787 / 0.802 / 0.826 ms per step, profiles/r1_call48_*)
+        self.comm_blocks = comm_blocks if comm_blocks is not None else (16 if self.mode == "ddp" else min(sms, 128))
         self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1) if self.mode == "ddp" else None
         # wgrad runs on its own branch, concurrently with dgrad / the next BatchNorm backward
         self.wgrad_stream = torch.cuda.Stream(device=self.device) if self.overlap_wgrad else None
@@ -111,11 +116,16 @@ class Trainer:
         self.in_aug = torch.zeros(B, 4, dtype=torch.int8, device=self.device)
         self.in_f32 = torch.zeros(B, 3, hw, hw, dtype=torch.float32, device=self.device)
         self._capture_stream = torch.cuda.Stream(device=self.device)
+        from .ops import kernels as K
+
+        if os.environ.get("DDPB_PDL") is None:
+            # programmatic dependent launch: +0.6% on one GPU, but in 'ddp' mode the early-resident
+            # CTAs of the next kernel keep the overlapped reductions off the SMs (2 GPUs: 0.874 ms
+            # per step with it, 0.831 without; profiles/r1_call45_*)
+            K.set_pdl(not (self.distributed and self.mode == "ddp"))
         if self.distributed and self.mode == "ddp":
             # fused BatchNorm backward is a cooperative launch: with two CTAs per SM it fills the
             # register file and would have to wait for every overlapped reduction to finish
-            from .ops import kernels as K
-
             K.bn_bwd_set_fused(1)
             self._broadcast_parameters()
 
