@@ -13,6 +13,7 @@ from ddpb200.data import create_data_loaders  # noqa: E402,F401
 from ddpb200.train import run, seed, test_model, train_model  # noqa: E402,F401
 
 device = "cuda"  # the reference hard-codes "cpu" (main.py:15); pass --device cpu for that
+batch_size = 256  # main.py:17
 
 
 def main():

@@ -153,3 +153,37 @@ def test_checkpoint_roundtrip_cpu(tmp_path):
     load_checkpoint(tmp_path / "a.pt", wrapped)          # prefix is added on load
     for k, v in m.state_dict().items():
         assert torch.equal(v, wrapped.state_dict()["module." + k])
+
+
+def test_entry_points_export_the_reference_names():
+    """Every module-level name of the reference's scripts exists under the same
+    path, so code written against them keeps importing."""
+    import importlib.util
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    common = ["seed", "device", "create_data_loaders", "train_model", "test_model", "main"]
+    dist_names = ["parse_arguments", "get_rank", "test_distributed_setup", "init_distributed_setup"]
+    want = {
+        "part1/main.py": common + ["batch_size"],
+        "part2/part2a/main.py": common + dist_names + ["sync_gradients"],
+        "part2/part2b/main.py": common + dist_names + ["sync_gradients"],
+        "part3/main.py": common + dist_names + ["DDP"],
+    }
+    for rel in ["part1/model.py", "part2/part2a/model.py", "part2/part2b/model.py", "part3/model.py"]:
+        want[rel] = ["_cfg", "_make_layers", "_VGG", "VGG11"]
+    for rel, names in want.items():
+        path = root / rel
+        sys.path.insert(0, str(path.parent))
+        try:
+            spec = importlib.util.spec_from_file_location("entry_" + rel.replace("/", "_")[:-3], path)
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+        finally:
+            sys.path.remove(str(path.parent))
+            sys.modules.pop("model", None)   # each part has its own model.py
+        missing = [n for n in names if not hasattr(mod, n)]
+        assert not missing, f"{rel} lacks {missing}"
+    assert mod.VGG11().fc1.out_features == 10
+
