@@ -57,6 +57,22 @@ def sync_gradients_allreduce(model: torch.nn.Module, world_size: int) -> None:
             g.copy_(buf)
 
 
+def verify_param_shapes_across_ranks(model: torch.nn.Module) -> None:
+    """What DistributedDataParallel's constructor checks before it broadcasts the parameters
+    (torch `_verify_param_shape_across_processes`): every rank must hold the same
+    list of parameter shapes.  Raises RuntimeError on every rank if one differs."""
+    import hashlib
+
+    desc = ";".join(f"{n}:{tuple(p.shape)}:{p.dtype}" for n, p in model.named_parameters())
+    digest = hashlib.sha1(desc.encode()).hexdigest()
+    seen = [None] * dist.get_world_size()
+    dist.all_gather_object(seen, digest)
+    if any(d != seen[0] for d in seen):
+        bad = [r for r, d in enumerate(seen) if d != seen[0]]
+        raise RuntimeError(f"parameter shapes differ across ranks (ranks {bad} disagree with rank 0); "
+                           "every rank must build the same model")
+
+
 # ---------------------------------------------------------------------------------------
 # bucket layout shared by the GPU reducer and the CPU restatement
 # ---------------------------------------------------------------------------------------

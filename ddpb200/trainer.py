@@ -75,6 +75,10 @@ class Trainer:
         if bucket_bytes is None:
             bucket_bytes = 0 if bucket_layout == "per_layer" else 25 * S.MIB
         self.bucket_layout = bucket_layout
+        if self.distributed and self.mode == "ddp":
+            if self.device.type == "cuda":
+                torch.cuda.set_device(self.device)      # object collectives of NCCL use the current device
+            S.verify_param_shapes_across_ranks(model)   # DDP constructor, SURVEY.md C7
         self.groups = S.param_groups_of(model)
         self.buckets = S.plan_buckets(self.groups, first_bucket_bytes, bucket_bytes, tail_bytes)
         if self.device.type == "cuda":

@@ -76,3 +76,36 @@ def test_three_modes_agree_with_each_other(tmp_path):
     a, b, c = (torch.load(tmp_path / f"{m}.pt") for m in ("gather_scatter", "allreduce", "ddp"))
     # different summation orders: equal to rounding, not bitwise
     assert torch.allclose(a, b, atol=1e-5) and torch.allclose(b, c, atol=1e-5)
+
+
+MISMATCH_WORKER = r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, os.environ["DDPB_ROOT"])
+import ddpb200
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo")
+torch.set_num_threads(2)
+model = ddpb200.VGG11()
+if rank == 1:   # a rank that built a different classifier
+    model.fc1 = torch.nn.Linear(512, 11)
+try:
+    ddpb200.Trainer(model, mode="ddp", batch_size=4, rank=rank, world_size=world)
+except RuntimeError as e:
+    assert "parameter shapes differ" in str(e), e
+    print("REFUSED", rank)
+dist.destroy_process_group()
+'''
+
+
+def test_ddp_refuses_ranks_with_different_models(tmp_path):
+    """DistributedDataParallel's constructor verifies the parameter shapes across ranks before its
+    broadcast (SURVEY.md C7); so does Trainer(mode='ddp')."""
+    script = tmp_path / "mismatch.py"
+    script.write_text(MISMATCH_WORKER)
+    env = dict(os.environ, DDPB_ROOT=str(ROOT), OMP_NUM_THREADS="2")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", str(29960 + os.getpid() % 30), str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-3000:]
+    assert "REFUSED 0" in res.stdout and "REFUSED 1" in res.stdout
+
