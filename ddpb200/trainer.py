@@ -50,7 +50,7 @@ class Trainer:
         self.overlap_wgrad = overlap_wgrad
         # CTA size of the reductions that overlap backward (mode 'ddp').  256-thread CTAs would fit on
         # an SM next to a persistent conv CTA, but measured on 2 GPUs (profiles/r1_call30_*) the lost
-        # reduction throughput costs more than the co-residency gains: 512 x 32 CTAs stays default.
+        # reduction throughput costs more than the co-residency gains: 512-thread CTAs stay default.
         self.comm_threads = comm_threads
         self.device = next(model.parameters()).device
         self.distributed = world_size > 1 and mode != "single"
@@ -60,8 +60,9 @@ class Trainer:
         # bucket, 25 MiB cap: 9.46 / 27.16 / 0.31 MB for VGG-11).  "per_layer" closes a bucket after
         # every parameter group.  Measured on 2 and 8 B200s (profiles/r1_call20*, r1_call21*) the
         # three-bucket layout wins: NVLink moves all 36.9 MB in ~0.1 ms, so what matters is how
-        # few reduction kernels (two cross-GPU barriers each, 32 CTAs taken from backward) run,
-        # not how early they start.  Explicit byte caps override both.
+        # few reduction kernels (two cross-GPU barriers each, CTAs taken from backward) run,
+        # not how early they start; re-measured with the final kernels in profiles/r1_call46_*.
+        # Explicit byte caps override both.
         if bucket_layout not in ("per_layer", "reference", "balanced"):
             raise ValueError("bucket_layout must be 'per_layer', 'reference' or 'balanced'")
         tail_bytes = 0
@@ -106,8 +107,7 @@ class Trainer:
             use_multicast = bool(self.symm is not None and self.symm.has_multicast)
         self.use_mc = bool(use_multicast and self.symm is not None and self.symm.has_multicast)
         sms = torch.cuda.get_device_properties(self.device).multi_processor_count
-        # part3 reductions share the GPU with backward: a slice of the SMs; 2a/2b own the GPU
-        # 'ddp': CTAs of the reductions that overlap backward.  Each thread keeps four 16-byte
+        # 2a / 2b reductions own the GPU (full width).  'ddp': CTAs of the reductions that overlap backward.  Each thread keeps four 16-byte
         # requests in flight, so 16 CTAs already move a bucket in time and leave the SMs to backward
         # (2 GPUs: 8 / 16 / 32 / 64 CTAs -> 0.797 / 0.787 / 0.802 / 0.826 ms per step, profiles/r1_call48_*)
         self.comm_blocks = comm_blocks if comm_blocks is not None else (16 if self.mode == "ddp" else min(sms, 128))
@@ -280,18 +280,15 @@ class Trainer:
         N = data.shape[0]
         if N > self.batch_size:
             raise ValueError("evaluation batch larger than the engine was sized for")
+        # pack=True: the first layer's padded filter pack is refreshed by the input kernel; after a
+        # training step it still holds the filters from BEFORE that step's update
+        eng.labels[:N].copy_(target, non_blocking=True)
         if data.dtype == torch.uint8:
             self.in_u8[:N].copy_(data, non_blocking=True)
-            eng.labels[:N].copy_(target, non_blocking=True)
-            from .ops import kernels as K
-
-            K.first_layer_operand_u8(self.in_u8[:N], None, out=eng.operand0)
+            eng.load_input_u8(self.in_u8[:N], None, pack=True)
         else:
             self.in_f32[:N].copy_(data, non_blocking=True)
-            eng.labels[:N].copy_(target, non_blocking=True)
-            from .ops import kernels as K
-
-            K.first_layer_operand_f32(self.in_f32[:N], out=eng.operand0)
+            eng.load_input_f32(self.in_f32[:N], pack=True)
         eng.forward(N, with_loss=True, want_dlogits=False)
         return eng.loss.clone(), eng.correct.clone()
 
