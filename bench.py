@@ -177,7 +177,7 @@ def run_ours(a):
         img, lab, aug = dev_batches[it % n_rot]
         trainer.step(img, lab, aug)
     first_loss = float(trainer.engine.loss.item())
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(local_rank, uuid=_gpu_uuid(local_rank)) as clocks:
         dev_ms, _, _ = timed(dev_batches, a.steps, readback=False)
     # end to end from pinned host memory (a few extra warm-up steps for the copy path)
     for it in range(3):
@@ -334,7 +334,7 @@ def run_reference(a):
     import io
 
     sink = io.StringIO()
-    with ClockSampler(local_rank) as clocks, contextlib.redirect_stdout(sink):
+    with ClockSampler(local_rank, uuid=_gpu_uuid(local_rank)) as clocks, contextlib.redirect_stdout(sink):
         if part == "part1" or part == "part3":
             ref.train_model(net, loader, optimizer, criterion, 0)
         else:
@@ -363,6 +363,16 @@ def run_reference(a):
         })
     if world > 1:
         dist.destroy_process_group()
+
+
+def _gpu_uuid(index):
+    """UUID of cuda:index (NVML indices ignore CUDA_VISIBLE_DEVICES; the UUID does not)."""
+    try:
+        import torch
+
+        return str(torch.cuda.get_device_properties(index).uuid)
+    except Exception:  # noqa: BLE001
+        return None
 
 
 def _pdl_state():

@@ -187,3 +187,30 @@ def test_entry_points_export_the_reference_names():
         assert not missing, f"{rel} lacks {missing}"
     assert mod.VGG11().fc1.out_features == 10
 
+
+
+def test_clock_sampler_nvml_path_and_summary(monkeypatch):
+    """The bench's clock sampler: NVML in-process when present (fake module here), throttle bits
+    decoded into the reason names bench.py reports."""
+    import sys
+    import time
+    import types
+
+    from ddpb200.utils.timing import ClockSampler
+
+    fake = types.ModuleType("pynvml")
+    fake.NVML_CLOCK_SM = 1
+    fake.nvmlInit = lambda: None
+    fake.nvmlDeviceGetHandleByIndex = lambda i: ("h", i)
+    fake.nvmlDeviceGetHandleByUUID = lambda u: ("h", u)
+    fake.nvmlDeviceGetClockInfo = lambda h, k: 1965
+    fake.nvmlDeviceGetMaxClockInfo = lambda h, k: 1965
+    fake.nvmlDeviceGetPowerUsage = lambda h: 512000
+    fake.nvmlDeviceGetCurrentClocksEventReasons = lambda h: 0x4   # software power cap
+    monkeypatch.setitem(sys.modules, "pynvml", fake)
+    with ClockSampler(0, period_s=0.002, uuid="abc") as c:
+        time.sleep(0.1)
+    out = c.summary()
+    assert out["source"] == "nvml" and out["samples"] >= 5
+    assert out["sm_mhz"] == 1965 and out["sm_max_mhz"] == 1965 and out["power_w_max"] == 512.0
+    assert out["reasons"] == ["sw_power_cap"]

@@ -261,6 +261,10 @@ def test_ragged_batches_and_evaluation():
         assert l == l, f"loss is NaN for a batch of {n}"
     img, lab = _batch(16, seed=1)          # the reference's last test batch has 16 images
     loss, correct = tr.evaluate(img, lab)
+    # evaluation sees the parameters AFTER the last update, first layer's padded filter pack included
+    eng = tr.engine
+    w0 = eng.arena.flat_master(eng.layers[0].p_w).view(64, 27)
+    assert torch.equal(eng.w_f[0][:, :27], w0.bfloat16()) and eng.w_f[0][:, 27:].abs().max().item() == 0
     x = augment_normalize_u8(img, None).to(DEV)
     with torch.no_grad():
         logits = model(x)
