@@ -515,6 +515,7 @@ splitk_finalize_kernel(const float* __restrict__ partial, const float* __restric
 }
 
 #include "conv_persist.inl"
+#include "conv_pair_persist.inl"
 
 // ------------------------------------------------------------------------------------------
 // Launch planning.  Measured on B200 (profiles/): these kernels are bound by operand ingest
@@ -553,19 +554,20 @@ static double plan_cost(int bn, int splits, long long P, int C_out, int total_k)
 
 // Automatic choice: the persistent kernel with the cheapest (BLOCK_N, split-K); the
 // one-tile-per-CTA and CTA-pair kernels stay available through ddpb_conv_force (mode 0 / 1).
-static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint, bool allow_split) {
-  const int mode = g_force_pair >= 0 ? g_force_pair : 2;
+static ConvPlan plan_conv_mode(int mode, long long P, int C_out, int total_k, int block_n_hint, bool allow_split,
+                               bool* found) {
   ConvPlan best{mode, (C_out % 128 == 0) ? 128 : 64, 1};
   double best_t = 1e30;
   const int bns[3] = {64, 128, 256};
   for (int bi = 0; bi < 3; ++bi) {
     const int bn = bns[bi];
     if (C_out % bn != 0) continue;
-    if (mode == 1 && bn < 128) continue;
+    if ((mode == 1 || mode == 3) && bn < 128) continue;   // a CTA pair splits B in halves of >= 64 rows
     if (block_n_hint != 0 && bn != block_n_hint) continue;
     if (g_force_block_n >= 0 && bn != g_force_block_n) continue;
     for (int splits = 1; splits <= 8; ++splits) {
       if (g_force_splits >= 0 && splits != g_force_splits) continue;
+      if (mode == 3 && splits > 1) continue;              // the persistent CTA-pair kernel does not split K
       if (splits > 1 && (!allow_split || total_k / splits < 4 || C_out / 8 > 256 || 256 % (C_out / 8) != 0)) continue;
       const double t = plan_cost(bn, splits, P, C_out, total_k);
       if (t < best_t) {
@@ -574,7 +576,17 @@ static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint,
       }
     }
   }
+  if (found != nullptr) *found = best_t < 1e30;
   return best;
+}
+
+static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint, bool allow_split) {
+  const int mode = g_force_pair >= 0 ? g_force_pair : 2;
+  bool found = false;
+  const ConvPlan pl = plan_conv_mode(mode, P, C_out, total_k, block_n_hint, allow_split, &found);
+  // mode 3 (persistent CTA pair) has no 64-wide tile and no split-K: such shapes use mode 2
+  if (mode == 3 && !found) return plan_conv_mode(2, P, C_out, total_k, block_n_hint, allow_split, nullptr);
+  return pl;
 }
 
 template <int BLOCK_N, bool kDgrad>
@@ -681,7 +693,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   const long long P = static_cast<long long>(N) * H * W;
   const ConvPlan pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, scratch != nullptr);
   block_n = pl.block_n;
-  const int b_rows = pl.pair == 1 ? block_n / 2 : block_n;   // filter rows one CTA loads per k-step
+  const int b_rows = (pl.pair == 1 || pl.pair == 3) ? block_n / 2 : block_n;   // filter rows one CTA loads per k-step
 
   CUtensorMap tx, tw;
   {
@@ -770,6 +782,8 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
     DDPB_CONV_DISPATCH(launch_pair)
   } else if (pl.pair == 2) {
     DDPB_CONV_DISPATCH(launch_persist)
+  } else if (pl.pair == 3) {
+    DDPB_CONV_DISPATCH(launch_pair_persist)
   } else {
     DDPB_CONV_DISPATCH(launch_fprop)
   }

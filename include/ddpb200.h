@@ -71,7 +71,8 @@ int ddpb_conv_wgrad_static(const void* dy, const void* x, float* dw, int N, int 
 long long ddpb_conv_wgrad_static_max_elems(void);
 
 /* Tuning / profiling hooks for the conv launch planner (kernel: 0 one tile per CTA, 1 CTA
- * pair with cta_group::2, 2 persistent; -1 = automatic). */
+ * pair with cta_group::2, 2 persistent, 3 persistent CTA pair -- no split-K, no 64-wide tile:
+ * such shapes fall back to 2; -1 = automatic = 2). */
 void ddpb_conv_force(int kernel, int block_n, int splits);
 void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3);
 void ddpb_conv_debug_timing(unsigned long long* per_cta_stamps);
