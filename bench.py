@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch")
     ap.add_argument("--no-overlap-wgrad", action="store_true", help="weight gradients on the main stream")
     ap.add_argument("--bn-fused", type=int, default=None, help="BatchNorm backward: 0 two kernels, 1/2 fused (CTAs per SM)")
+    ap.add_argument("--conv-mode", type=int, default=-1,
+                    help="conv kernel of fprop/dgrad: -1 automatic (persistent), 1 CTA pair, 3 persistent CTA pair")
     ap.add_argument("--comm-blocks", type=int, default=None)
     ap.add_argument("--bucket-layout", choices=["per_layer", "reference", "balanced"], default="reference")
     ap.add_argument("--comm-threads", type=int, default=512)
@@ -136,6 +138,9 @@ def run_ours(a):
     if a.no_pdl:
         from ddpb200.ops import kernels as _K
         _K.set_pdl(False)
+    if a.conv_mode >= 0:
+        from ddpb200.ops import kernels as _K3
+        _K3.conv_force(a.conv_mode, -1, -1)
     model = ddpb200.VGG11().to(device)
     trainer = ddpb200.Trainer(model, mode=mode, batch_size=per_gpu, lr=0.1, momentum=0.9, weight_decay=1e-4,
                               rank=rank, world_size=world, granularity=a.granularity,
@@ -207,6 +212,7 @@ def run_ours(a):
                        "sync": None if world == 1 else {"backend": trainer.symm.backend, "multicast": trainer.use_mc,
                                                        "granularity": a.granularity, "bucket_layout": a.bucket_layout if mode == "ddp" else None, "comm_blocks": trainer.comm_blocks, "buckets_floats": [b.numel for b in trainer.buckets] if mode == "ddp" else None},
                        "cuda_graph": not a.no_graph, "programmatic_dependent_launch": bool(_pdl_state()),
+                       "conv_mode": "automatic" if a.conv_mode < 0 else a.conv_mode,
                        "l2": f"no explicit flush: working set {ws_mb:.0f} MB/step > 126 MB L2; inputs rotate over {n_rot} device batches",
                        "baseline_ref": "BASELINE.md §1: published CPU/Gloo images/s for this worker count"},
             "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "ms_per_step": round(e2e_ms / a.steps, 4),

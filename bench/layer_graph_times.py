@@ -55,11 +55,16 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--bn-fused", type=int, default=2)
+    ap.add_argument("--conv-mode", type=int, default=-1,
+                    help="conv kernel: -1 automatic, 0 one tile per CTA, 1 CTA pair, 2 persistent, 3 persistent CTA pair")
+    ap.add_argument("--block-n", type=int, default=-1, help="force the tile width of fprop / dgrad")
     a = ap.parse_args()
+    K.conv_force(a.conv_mode, a.block_n, -1)
     N, reps = a.batch, a.reps
     K.bn_bwd_set_fused(a.bn_fused)
     tot = dict(fwd=0.0, bn_bwd=0.0, wgrad=0.0, dgrad=0.0)
-    print(f"batch {N}, pdl {K.get_pdl()}, bn fused mode {a.bn_fused}; microseconds per call in a graph")
+    print(f"batch {N}, pdl {K.get_pdl()}, bn fused mode {a.bn_fused}, conv mode {a.conv_mode}, block_n {a.block_n}; "
+          "microseconds per call in a graph")
     for li, (S, Ci, Co, pool) in enumerate(LAYERS):
         H = W = S
         P = N * H * W
