@@ -51,11 +51,20 @@ dist.destroy_process_group()
 '''
 
 
+def _free_port() -> int:
+    """A port nobody listens on right now (a fixed formula collided once in a while)."""
+    import socket
+
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as sk:
+        sk.bind(("127.0.0.1", 0))
+        return sk.getsockname()[1]
+
+
 def _run(mode, world, tmp_path):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
     env = dict(os.environ, DDPB_ROOT=str(ROOT), DDPB_OUT=str(tmp_path), OMP_NUM_THREADS="2")
-    port = 29800 + (os.getpid() + hash(mode)) % 150
+    port = _free_port()
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), mode]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
@@ -104,7 +113,7 @@ def test_ddp_refuses_ranks_with_different_models(tmp_path):
     script.write_text(MISMATCH_WORKER)
     env = dict(os.environ, DDPB_ROOT=str(ROOT), OMP_NUM_THREADS="2")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
-           "127.0.0.1", "--master-port", str(29960 + os.getpid() % 30), str(script)]
+           "127.0.0.1", "--master-port", str(_free_port()), str(script)]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-3000:]
     assert "REFUSED 0" in res.stdout and "REFUSED 1" in res.stdout

@@ -81,7 +81,11 @@ def _run(mode, gran="fused", mc=False, world=None):
     script = Path(os.environ.get("TMPDIR", "/tmp")) / "ddpb_mgpu_worker.py"
     script.write_text(WORKER)
     env = dict(os.environ, DDPB_ROOT=str(ROOT))
-    port = 29700 + (os.getpid() + hash((mode, gran, mc))) % 200
+    import socket
+
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as sk:   # a port that is free right now
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), mode, gran, "1" if mc else "0"]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
