@@ -101,7 +101,7 @@ try:
     ddpb200.Trainer(model, mode="ddp", batch_size=4, rank=rank, world_size=world)
 except RuntimeError as e:
     assert "parameter shapes differ" in str(e), e
-    print("REFUSED", rank)
+    os.write(1, f"REFUSED-{rank};".encode())   # one write: the two ranks' lines must not interleave
 dist.destroy_process_group()
 '''
 
@@ -116,5 +116,5 @@ def test_ddp_refuses_ranks_with_different_models(tmp_path):
            "127.0.0.1", "--master-port", str(_free_port()), str(script)]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-3000:]
-    assert "REFUSED 0" in res.stdout and "REFUSED 1" in res.stdout
+    assert "REFUSED-0;" in res.stdout and "REFUSED-1;" in res.stdout
 
