@@ -747,7 +747,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   const bool fin_in_kernel = pl.pair == 2 && pl.splits > 1 && fin_sync != nullptr && kPersistThreads % (C_out / 8) == 0;
   if (fin_in_kernel) p.fin_sync = fin_sync;
   // BatchNorm tail inside the kernel: persistent kernel, whole 2x2 windows per tile
-  if (bn_tail != nullptr && stats != nullptr && pl.pair == 2 && (pl.splits == 1 || fin_in_kernel) &&
+  if (bn_tail != nullptr && stats != nullptr && (pl.pair == 2 || pl.pair == 3) && (pl.splits == 1 || fin_in_kernel) &&
       (!bn_tail->pool || bh % 2 == 0)) {
     p.gamma = bn_tail->gamma;
     p.beta = bn_tail->beta;

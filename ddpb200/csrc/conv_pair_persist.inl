@@ -17,8 +17,8 @@
 //     multicast to both), TMA completions of BOTH CTAs count on the LEADER's full barrier, and
 //     "accumulator drained" is 16 arrivals (8 epilogue warps x 2 CTAs) on the LEADER's barrier,
 //     the peer's warps arriving remotely through the cluster address space.
-// Split-K and the fused BatchNorm tail are not implemented here (callers fall back to the separate
-// finalize / BatchNorm kernels).
+// Split-K is not implemented here (such shapes use the persistent one-CTA kernel).  The fused
+// BatchNorm tail at the end mirrors conv_persist.inl.
 
 template <int BLOCK_N>
 struct PairPersistCfg {
@@ -276,6 +276,99 @@ conv_pair_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+  }
+
+  // ===================== fused BatchNorm + ReLU (+ pool) =====================
+  // Same scheme as in conv_persist.inl: all CTAs meet at a grid-wide barrier once the statistics
+  // are complete (one CTA per SM, all co-resident), then every CTA normalises the 128-pixel tiles
+  // IT wrote (m-tile 2 mp + rank of each of its cluster's pair tiles), which hold whole 2x2
+  // pooling windows.  NOT YET RUN ON HARDWARE (the numerics tests of round 1 covered act == null).
+  if (p.act != nullptr) {
+    persist_grid_barrier(p.grid_sync, "pair conv+bn");
+    float* s_scale = reinterpret_cast<float*>(tiles);   // the operand ring is idle now
+    float* s_shift = s_scale + p.C_out;
+    const float inv_count = 1.f / static_cast<float>(p.P);
+    for (int c = threadIdx.x; c < p.C_out; c += blockDim.x) {
+      const float mean = __ldcg(p.stats + c) * inv_count;
+      float var = __ldcg(p.stats + p.C_out + c) * inv_count - mean * mean;
+      var = fmaxf(var, 0.f);
+      const float rstd = rsqrtf(var + p.eps);
+      const float sc = p.gamma[c] * rstd;
+      s_scale[c] = sc;
+      s_shift[c] = p.beta[c] - mean * sc;
+      if (blockIdx.x == 0 && p.saved != nullptr) {
+        p.saved[c] = mean;
+        p.saved[p.C_out + c] = rstd;
+      }
+    }
+    __syncthreads();
+    constexpr int kGroups = BLOCK_N / 8;                 // 16-byte channel groups per tile row
+    constexpr int kUnroll = 4;                           // items per thread in flight
+    const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
+    const int out_rows = p.pool ? kBlockM / 4 : kBlockM; // output pixels per tile
+    const int per_tile = out_rows * kGroups;
+    const int nwin = p.pool ? 4 : 1;
+    const int my_tiles = (n_items - pair_id + n_pairs - 1) / n_pairs;
+    const long long my_total = static_cast<long long>(my_tiles) * per_tile;
+    for (long long base = threadIdx.x; base < my_total; base += static_cast<long long>(blockDim.x) * kUnroll) {
+      uint4 raw[kUnroll][4];
+      long long opix[kUnroll];
+      int chv[kUnroll];
+      bool ok[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long flat = base + static_cast<long long>(u) * blockDim.x;
+        ok[u] = flat < my_total;
+        const int tile_local = static_cast<int>(flat / per_tile);
+        const int w_item = static_cast<int>(flat - static_cast<long long>(tile_local) * per_tile);
+        const int item = pair_id + tile_local * n_pairs;
+        const int mp = item % m_pairs, n_tile = item / m_pairs;
+        const int m_tile = 2 * mp + static_cast<int>(rank);
+        const int n_img0 = (m_tile / p.hblocks) * p.bn;
+        const int h0 = (m_tile % p.hblocks) * p.bh;
+        const int cgp = w_item % kGroups;
+        const int orow = w_item / kGroups;
+        chv[u] = n_tile * BLOCK_N + cgp * 8;
+        long long in00;
+        if (!p.pool) {
+          in00 = static_cast<long long>(m_tile) * kBlockM + orow;
+          opix[u] = in00;
+        } else {
+          const int wo = orow % Wo;
+          const int t2 = orow / Wo;
+          const int ho = t2 % (p.bh / 2);
+          const int n_img = n_img0 + t2 / (p.bh / 2);
+          in00 = (static_cast<long long>(n_img) * p.H + h0 + 2 * ho) * p.W + 2 * wo;
+          opix[u] = (static_cast<long long>(n_img) * Ho + (h0 / 2 + ho)) * Wo + wo;
+        }
+        ok[u] = ok[u] && in00 < p.P;
+        if (ok[u]) {
+#pragma unroll
+          for (int d = 0; d < 4; ++d)
+            if (d < nwin)
+              raw[u][d] = __ldcg(reinterpret_cast<const uint4*>(p.out + (in00 + (d >> 1) * p.W + (d & 1)) * p.C_out + chv[u]));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        if (!ok[u]) continue;
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = 0.f;   // ReLU floor
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+          if (d < nwin) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t wv = (j < 2) ? raw[u][d].x : (j < 4) ? raw[u][d].y : (j < 6) ? raw[u][d].z : raw[u][d].w;
+              const float xv = __uint_as_float((j & 1) ? (wv & 0xffff0000u) : (wv << 16));
+              o[j] = fmaxf(o[j], fmaf(xv, s_scale[chv[u] + j], s_shift[chv[u] + j]));
+            }
+          }
+        }
+        store8(p.act + opix[u] * p.C_out + chv[u], o);
+      }
+    }
   }
 }
 

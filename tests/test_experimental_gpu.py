@@ -50,3 +50,33 @@ def test_persistent_cta_pair_conv(case):
     assert torch.allclose(stats, R.channel_stats(y), rtol=2e-3, atol=1e-2 * (N * H * W) ** 0.5)
     if dx is not None:
         assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
+
+
+@pytest.mark.parametrize("pool", [False, True])
+@pytest.mark.parametrize("case", [((16, 16, 16, 64, 128), 128), ((37, 8, 8, 128, 256), 256), ((256, 8, 8, 256, 256), 256),
+                                  ((64, 4, 4, 256, 512), 128)])
+def test_persistent_cta_pair_conv_with_batchnorm_tail(case, pool):
+    """Mode 3 with the BatchNorm + ReLU (+pool) tail after the grid barrier (not yet run on hardware
+    at the end of round 1)."""
+    from ddpb200.ops import kernels as K
+    from ddpb200.ops import reference as R
+
+    (N, H, W, Ci, Co), bn = case
+    torch.manual_seed(1)
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
+    b = torch.randn(Co, device=DEV) * 0.1
+    gamma = torch.rand(Co, device=DEV) + 0.5
+    beta = torch.randn(Co, device=DEV) * 0.2
+    try:
+        K.conv_force(3, bn, 1)
+        conv_out, act, saved = K.conv_bn_relu_pool_fwd(x, w, b, gamma, beta, N, H, W, Ci, Co, 9, pool)
+        torch.cuda.synchronize()
+    finally:
+        K.conv_force(-1, -1, -1)
+    assert _rel_err(conv_out, R.conv_fprop(x, w, b, N, H, W, Ci, Co)) < 1e-2
+    assert _rel_err(act, R.bn_relu_pool_fwd(conv_out, gamma, beta, N, H, W, pool)) < 1e-2
+    cf = conv_out.float()
+    assert torch.allclose(saved[0], cf.mean(0), rtol=1e-3, atol=1e-3)
+    assert torch.allclose(saved[1], (cf.var(0, unbiased=False) + 1e-5).rsqrt(), rtol=2e-3)
+
