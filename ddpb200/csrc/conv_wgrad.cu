@@ -276,12 +276,14 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Wgr
 }
 
 #include "conv_wgrad_taps.inl"
+#include "conv_wgrad_pair.inl"
 
 // Launch plan.  fused: the tap-fused cluster kernel (3x3 layers with C_out % 128 == 0) with
 // `cluster` CTAs per thread-block cluster and `groups` clusters per tile (global partial tiles
 // only when groups > 1); otherwise the one-tap kernel with `groups` pixel splits.
 struct WgPlan {
   bool fused;
+  bool pair;      // CTA-pair kernel (mode 2): tiles of 256 output channels x block_n input channels
   int block_n;
   int cluster;
   int groups;
@@ -317,9 +319,25 @@ static WgPlan plan_wgrad(int N, int H, int W, int C_in, int C_out, int taps) {
     const char* e = getenv("DDPB_WGRAD_TAPS");
     g_wgrad_mode = e ? atoi(e) : 0;
   }
-  const int fused_ok = g_wgrad_mode;
+  const int fused_ok = g_wgrad_mode == 1;
   WgPlan pl;
+  pl.pair = false;
   const int P = N * H * W;
+  if (g_wgrad_mode == 2 && taps == 9 && C_out % 256 == 0 && C_in % 128 == 0) {
+    // CTA pairs: 2 x tiles x splits CTAs of <= 97 KB, two per SM -> about one wave
+    pl.pair = true;
+    pl.fused = false;
+    pl.block_n = (C_in % 256 == 0) ? 256 : 128;
+    pl.cluster = 1;
+    const int tiles = taps * (C_out / 256) * (C_in / pl.block_n);
+    const int pix_blocks = (P + kWgPix - 1) / kWgPix;
+    int splits = sm_count() / tiles;
+    if (splits > pix_blocks / 8) splits = pix_blocks / 8;
+    if (splits > 256) splits = 256;
+    if (splits < 1) splits = 1;
+    pl.groups = splits;
+    return pl;
+  }
   pl.block_n = (C_in % 128 == 0) ? 128 : 64;
   const int m_tiles = (C_out + 127) / 128;
   const int n_tiles = C_in / pl.block_n;
@@ -346,9 +364,10 @@ static WgPlan plan_wgrad(int N, int H, int W, int C_in, int C_out, int taps) {
 
 using namespace ddpb;
 
-// 0: one-tap kernel (default); 1: tap-fused kernel with the split reduction inside a cluster.
+// 0: one-tap kernel (default); 1: tap-fused kernel with the split reduction inside a cluster;
+// 2: CTA-pair (cta_group::2) kernel where the shape allows (C_out % 256 == 0, C_in % 128 == 0).
 // Changes ddpb_conv_wgrad_scratch_elems() for later calls.
-extern "C" void ddpb_conv_wgrad_set_mode(int mode) { ddpb::g_wgrad_mode = mode ? 1 : 0; }
+extern "C" void ddpb_conv_wgrad_set_mode(int mode) { ddpb::g_wgrad_mode = (mode >= 0 && mode <= 2) ? mode : 0; }
 
 // Number of pixel splits the launcher will use for this shape (so callers can size scratch).
 extern "C" int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps) {
@@ -405,7 +424,7 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
   p.C_in = C_in;
   p.C_out = C_out;
   p.taps = taps;
-  p.m_tiles = (C_out + 127) / 128;
+  p.m_tiles = pl.pair ? C_out / 256 : (C_out + 127) / 128;
   p.n_tiles = C_in / block_n;
   p.bh = bh;
   p.bn = bn;
@@ -422,7 +441,10 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
     p.out_split_stride = rows * taps * C_in;
   }
   int rc;
-  if (pl.fused)
+  if (pl.pair)
+    rc = (block_n == 256) ? launch_wgrad_pair<256>(tdy, tx, p, splits, stream)
+                          : launch_wgrad_pair<128>(tdy, tx, p, splits, stream);
+  else if (pl.fused)
     rc = (block_n == 128) ? launch_wgrad3<128>(tdy, tx, p, pl.cluster, pl.groups, stream)
                           : launch_wgrad3<64>(tdy, tx, p, pl.cluster, pl.groups, stream);
   else

@@ -123,7 +123,8 @@ def conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps=9) -> int:
 
 def conv_wgrad_set_mode(mode: int) -> None:
     """0: one-tap weight-gradient kernel with a global split reduction (default, measured faster);
-    1: three taps per CTA, pixel splits summed through distributed shared memory in a cluster."""
+    1: three taps per CTA, pixel splits summed through distributed shared memory in a cluster;
+    2: CTA-pair (cta_group::2) kernel for C_out % 256 == 0 and C_in % 128 == 0 (experimental)."""
     nat.load().ddpb_conv_wgrad_set_mode(int(mode))
 
 

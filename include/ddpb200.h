@@ -55,7 +55,9 @@ long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out
 int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps);
 /* 0 (default): one tap per CTA, split reduction through global memory.  1: three taps per CTA and
  * the split reduction over distributed shared memory inside a thread-block cluster (measured
- * slower on B200 at the training shapes; kept selectable).  Changes the scratch size. */
+ * slower on B200 at the training shapes; kept selectable).  2: CTA-pair kernel (cta_group::2,
+ * 256 output channels x 128/256 input channels per pair) where C_out % 256 == 0 and
+ * C_in % 128 == 0 -- experimental, see docs/NEXT.md.  Changes the scratch size. */
 void ddpb_conv_wgrad_set_mode(int mode);
 
 /* No counterpart in the reference.  ddpb_conv_wgrad for callers that must not allocate device

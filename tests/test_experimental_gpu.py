@@ -80,3 +80,27 @@ def test_persistent_cta_pair_conv_with_batchnorm_tail(case, pool):
     assert torch.allclose(saved[0], cf.mean(0), rtol=1e-3, atol=1e-3)
     assert torch.allclose(saved[1], (cf.var(0, unbiased=False) + 1e-5).rsqrt(), rtol=2e-3)
 
+
+@pytest.mark.parametrize("shape", [(256, 8, 8, 128, 256), (256, 8, 8, 256, 256), (256, 4, 4, 256, 512),
+                                   (256, 4, 4, 512, 512), (256, 2, 2, 512, 512), (3, 8, 8, 128, 256)])
+def test_cta_pair_wgrad(shape):
+    """ddpb_conv_wgrad_set_mode(2): weight gradient with cta_group::2 (not yet run on hardware at the
+    end of round 1); deterministic, same tolerance as the default kernel."""
+    from ddpb200.ops import kernels as K
+    from ddpb200.ops import reference as R
+
+    N, H, W, Ci, Co = shape
+    torch.manual_seed(2)
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    ref = R.conv_wgrad(dy, x, N, H, W, Ci, Co)
+    try:
+        K.conv_wgrad_set_mode(2)
+        dw = K.conv_wgrad(dy, x, N, H, W, Ci, Co)
+        again = K.conv_wgrad(dy, x, N, H, W, Ci, Co)
+        torch.cuda.synchronize()
+    finally:
+        K.conv_wgrad_set_mode(0)
+    assert _rel_err(dw, ref) < 2e-3
+    assert torch.equal(dw, again)
+
