@@ -52,7 +52,10 @@ struct FpropParams {
   int taps;              // 9 (3x3) or 1 (pre-gathered input)
   int bh, bn, hblocks;   // TMA box geometry: box = (64, W, bh, bn); hblocks = H / bh
   float* partial;        // split-K: fp32 [gridDim.z][P][C_out] partial sums (null when gridDim.z == 1)
-  unsigned long long* dbg;  // optional per-CTA timestamps {start, after set-up, mainloop done, epilogue done}
+  unsigned long long* dbg;  // optional per-CTA timestamps, 8 slots per CTA: {start, after set-up, main loop done,
+                            // epilogue done / exit, [persistent kernels: 4 = epilogues done, 5 = past the grid barrier]}
+  int dbg_mode;             // timing probes (results are WRONG): bit 0 = skip the B loads, bit 1 = skip the A loads
+                            // once the ring is primed
   // fused BatchNorm + ReLU (+2x2 max-pool) tail of the persistent kernel (act == null: off)
   const float* gamma;
   const float* beta;
@@ -67,7 +70,7 @@ struct FpropParams {
 __device__ __forceinline__ void dbg_stamp(const FpropParams& p, int slot) {
   if (p.dbg != nullptr) {
     const long long cta = blockIdx.x + gridDim.x * (blockIdx.y + static_cast<long long>(gridDim.y) * blockIdx.z);
-    p.dbg[cta * 4 + slot] = global_timer_ns();
+    p.dbg[cta * 8 + slot] = global_timer_ns();
   }
 }
 
@@ -531,6 +534,7 @@ struct ConvPlan {
 
 static int g_force_pair = -1, g_force_block_n = -1, g_force_splits = -1;
 static unsigned long long* g_dbg = nullptr;
+static int g_dbg_mode = 0;
 
 // Cycle estimates for the persistent kernel, calibrated on B200 with the in-kernel timeline
 // hook (profiles/r1_call11_conv_timeline.txt): a 64-deep k-step costs max(1.35 x tensor time,
@@ -643,9 +647,13 @@ extern "C" void ddpb_conv_force(int pair, int block_n, int splits) {
   g_force_splits = splits;
 }
 
-// Profiling hook: device buffer of 4 x (number of CTAs) uint64 that every conv CTA stamps with
+// Profiling hook: device buffer of 8 x (number of CTAs) uint64 that every conv CTA stamps with
 // %globaltimer at start / after set-up / when its accumulator is complete / at exit (null = off).
 extern "C" void ddpb_conv_debug_timing(unsigned long long* buf) { g_dbg = buf; }
+
+// Timing probes for the persistent kernels (the results are numerically wrong): bit 0 = the producer
+// stops loading B once the ring is primed, bit 1 = same for A.  0 = normal operation.
+extern "C" void ddpb_conv_debug_mode(int mode) { g_dbg_mode = mode; }
 
 // What the planner picks for this shape: out3 = {pair, block_n, splits}.
 extern "C" void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3) {
@@ -678,8 +686,9 @@ struct BnTail {
 
 // Returns 0 on success; *fused_bn (if given) tells whether the BatchNorm tail ran inside the conv kernel.
 static int conv_impl(int dgrad, const void* x, const void* w, const float* bias, void* y, float* stats, int N, int H,
-                     int W, int C_in, int C_out, int taps, int block_n, float* scratch, cudaStream_t stream,
-                     const BnTail* bn_tail = nullptr, int* fused_bn = nullptr, unsigned int* fin_sync = nullptr) {
+                     int W, int C_in, int C_out, int taps, int block_n, float* scratch, long long scratch_elems,
+                     cudaStream_t stream, const BnTail* bn_tail = nullptr, int* fused_bn = nullptr,
+                     unsigned int* fin_sync = nullptr) {
   const char* name = dgrad ? "conv_dgrad" : "conv_fprop";
   DDPB_REQUIRE(taps == 1 || taps == 9, "%s: taps must be 1 or 9 (got %d)", name, taps);
   DDPB_REQUIRE(C_in % 64 == 0 && C_in > 0, "%s: reduction channels must be a multiple of 64 (got %d)", name, C_in);
@@ -691,7 +700,15 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   DDPB_REQUIRE(block_n == 0 || C_out % block_n == 0, "%s: output channels %d not divisible by block_n %d", name,
                C_out, block_n);
   const long long P = static_cast<long long>(N) * H * W;
-  const ConvPlan pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, scratch != nullptr);
+  ConvPlan pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, scratch != nullptr);
+  // The split-K choice is cost based, so a smaller batch can want MORE scratch than a larger one.  A plan
+  // whose partial tiles do not fit in the caller's buffer is never launched: plan again without split-K.
+  if (pl.splits > 1 && static_cast<long long>(pl.splits) * P * C_out > scratch_elems) {
+    DDPB_REQUIRE(g_force_splits < 0,
+                 "%s: split-K x%d was forced but the scratch buffer holds %lld floats (needs %lld)", name, pl.splits,
+                 scratch_elems, static_cast<long long>(pl.splits) * P * C_out);
+    pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, false);
+  }
   block_n = pl.block_n;
   const int b_rows = (pl.pair == 1 || pl.pair == 3) ? block_n / 2 : block_n;   // filter rows one CTA loads per k-step
 
@@ -732,6 +749,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   p.bn = bn;
   p.hblocks = hblocks;
   p.dbg = g_dbg;
+  p.dbg_mode = g_dbg_mode;
   p.gamma = p.beta = nullptr;
   p.act = nullptr;
   p.saved = nullptr;
@@ -801,12 +819,14 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
 // x: [N][H][W][C_in] bf16; w: [C_out][taps*C_in] bf16; y: [N*H*W][C_out] bf16.
 // bias (fp32, may be null) is added before rounding; stats (fp32 [2][C_out], may be
 // null) is ACCUMULATED into (caller zeroes it).  block_n: 0 = choose automatically.
-// scratch: device buffer of ddpb_conv_fprop_scratch_elems() floats, or null to forbid
-// split-K (small problems then run on few SMs).
+// scratch: device buffer of scratch_elems floats (ddpb_conv_fprop_scratch_elems() says how many the
+// planner would like), or null to forbid split-K (small problems then run on few SMs).  A plan
+// that does not fit in scratch_elems is replaced by one without split-K, never launched.
 extern "C" int ddpb_conv_fprop(const void* x, const void* w, const float* bias, void* y, float* stats,
                                int N, int H, int W, int C_in, int C_out, int taps, int block_n,
-                               float* scratch, cudaStream_t stream) {
-  return conv_impl(0, x, w, bias, y, stats, N, H, W, C_in, C_out, taps, block_n, scratch, stream);
+                               float* scratch, long long scratch_elems, cudaStream_t stream) {
+  return conv_impl(0, x, w, bias, y, stats, N, H, W, C_in, C_out, taps, block_n, scratch,
+                   scratch != nullptr ? scratch_elems : 0, stream);
 }
 
 int bn_relu_pool_fwd_launch(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
@@ -820,7 +840,8 @@ int bn_relu_pool_fwd_launch(const void* x, const float* stats, const float* gamm
 extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const float* bias, void* conv_out,
                                           float* stats, const float* gamma, const float* beta, void* act,
                                           float* saved, int N, int H, int W, int C_in, int C_out, int taps,
-                                          int pool, float eps, float* scratch, cudaStream_t stream) {
+                                          int pool, float eps, float* scratch, long long scratch_elems,
+                                          cudaStream_t stream) {
   BnTail bn{gamma, beta, act, saved, pool, eps};
   int fused = 0;
   // words 2*C_out (BatchNorm barrier) and 2*C_out + 1 (split-K finalize barrier) of `stats`
@@ -828,7 +849,8 @@ extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const fl
   // 8 us per step SLOWER than the finalize + BatchNorm kernels with programmatic launch overlap
   // (profiles/r1_call40_*); DDPB_FWD_FIN_IN_KERNEL=1 selects it.
   static const int fin_in_kernel = [] { const char* e = getenv("DDPB_FWD_FIN_IN_KERNEL"); return e ? atoi(e) : 0; }();
-  if (int rc = conv_impl(0, x, w, bias, conv_out, stats, N, H, W, C_in, C_out, taps, 0, scratch, stream, &bn, &fused,
+  if (int rc = conv_impl(0, x, w, bias, conv_out, stats, N, H, W, C_in, C_out, taps, 0, scratch,
+                         scratch != nullptr ? scratch_elems : 0, stream, &bn, &fused,
                          fin_in_kernel ? reinterpret_cast<unsigned int*>(stats + 2 * C_out) + 1 : nullptr))
     return rc;
   if (fused) return 0;
@@ -841,7 +863,8 @@ extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const fl
 // device memory that is ZERO on entry (left non-zero), or null; with it a split-K launch sums its
 // partial tiles inside the same kernel instead of launching a finalize kernel.
 extern "C" int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out,
-                               int block_n, float* scratch, unsigned int* sync, cudaStream_t stream) {
-  return conv_impl(1, dy, w, nullptr, dx, nullptr, N, H, W, C_out, C_in, 9, block_n, scratch, stream, nullptr, nullptr,
-                   sync);
+                               int block_n, float* scratch, long long scratch_elems, unsigned int* sync,
+                               cudaStream_t stream) {
+  return conv_impl(1, dy, w, nullptr, dx, nullptr, N, H, W, C_out, C_in, 9, block_n, scratch,
+                   scratch != nullptr ? scratch_elems : 0, stream, nullptr, nullptr, sync);
 }

@@ -92,16 +92,18 @@ conv_pair_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
     tmem_alloc_pair(tmem_ptr_smem, Cfg::kTmemCols);
     tmem_relinquish_pair();
   }
+  if (threadIdx.x == 0) dbg_stamp(p, 0);
   tc_fence_before();
   cluster_sync_all();   // both CTAs' barriers exist before anything is signalled across the pair
   tc_fence_after();
   pdl_wait();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) dbg_stamp(p, 1);
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
     if (elect_one()) {
-      int stage = 0;
+      int stage = 0, issued = 0;
       uint32_t phase = 0;
       for (int item = pair_id; item < n_items; item += n_pairs) {
         const int mp = item % m_pairs, n_tile = item / m_pairs;
@@ -120,9 +122,13 @@ conv_pair_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = tiles + stage * Cfg::kStageBytes;
           uint8_t* b_dst = a_dst + Cfg::kABytes;
-          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
-          tma_load_4d_pair(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
-          if (!kDgrad) {
+          const bool primed = issued >= Cfg::kStages;
+          ++issued;
+          const bool do_a = !(primed && (p.dbg_mode & 2)), do_b = !(primed && (p.dbg_mode & 1));
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * ((do_a ? Cfg::kABytes : 0) + (do_b ? Cfg::kBBytes : 0)));
+          if (do_a) tma_load_4d_pair(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
+          if (!do_b) {
+          } else if (!kDgrad) {
             tma_load_2d_pair(b_dst, &tmap_w, &full_bar[stage], tap * p.C_in + cc * kBlockK, b_row0);
           } else {
 #pragma unroll
@@ -169,6 +175,10 @@ conv_pair_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
           }
         }
         umma_commit_pair(&tmem_full[buf], 0x3);       // accumulators ready in BOTH CTAs
+        if (p.dbg != nullptr && item + n_pairs >= n_items) {
+          mbar_wait(&tmem_full[buf], use & 1);
+          dbg_stamp(p, 2);
+        }
       }
     }
   } else {
@@ -269,6 +279,7 @@ conv_pair_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
       }
     }
     if (do_stats && cur_n >= 0) flush_stats(cur_n);
+    if (threadIdx.x == 64) dbg_stamp(p, 4);
   }
 
   tc_fence_before();
@@ -285,6 +296,7 @@ conv_pair_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
   // pooling windows.  NOT YET RUN ON HARDWARE (the numerics tests of round 1 covered act == null).
   if (p.act != nullptr) {
     persist_grid_barrier(p.grid_sync, "pair conv+bn");
+    if (threadIdx.x == 0) dbg_stamp(p, 5);
     float* s_scale = reinterpret_cast<float*>(tiles);   // the operand ring is idle now
     float* s_shift = s_scale + p.C_out;
     const float inv_count = 1.f / static_cast<float>(p.P);
@@ -370,6 +382,7 @@ conv_pair_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
       }
     }
   }
+  if (threadIdx.x == 0) dbg_stamp(p, 3);
 }
 
 template <int BLOCK_N, bool kDgrad>

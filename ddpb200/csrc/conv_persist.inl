@@ -123,7 +123,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
-      int stage = 0;
+      int stage = 0, issued = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const PersistItem it = persist_item(item, m_tiles, n_tiles);
@@ -142,9 +142,13 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = tiles + stage * Cfg::kStageBytes;
           uint8_t* b_dst = a_dst + Cfg::kABytes;
-          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
-          if (!kDgrad) {
+          const bool primed = issued >= Cfg::kStages;
+          ++issued;
+          const bool do_a = !(primed && (p.dbg_mode & 2)), do_b = !(primed && (p.dbg_mode & 1));
+          mbar_expect_tx(&full_bar[stage], (do_a ? Cfg::kABytes : 0) + (do_b ? Cfg::kBBytes : 0));
+          if (do_a) tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
+          if (!do_b) {
+          } else if (!kDgrad) {
             tma_load_2d(b_dst, &tmap_w, &full_bar[stage], tap * p.C_in + cc * kBlockK, it.n_tile * BLOCK_N);
           } else {
 #pragma unroll
@@ -194,6 +198,10 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           }
         }
         umma_commit(&tmem_full[buf]);
+        if (p.dbg != nullptr && item + static_cast<int>(gridDim.x) >= n_items) {
+          mbar_wait(&tmem_full[buf], use & 1);
+          dbg_stamp(p, 2);
+        }
       }
     }
   } else {
@@ -334,6 +342,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       if (lane_id() == 0) mbar_arrive(&tmem_empty[buf]);
     }
     if (do_stats && cur_n >= 0) flush_stats(cur_n);
+    if (threadIdx.x == 64) dbg_stamp(p, 4);
   }
 
   tc_fence_before();
@@ -402,6 +411,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   // tile holds whole 2x2 pooling windows, so no CTA needs another CTA's pixels.
   if (p.act != nullptr) {
     persist_grid_barrier(p.grid_sync, "conv+bn");
+    if (threadIdx.x == 0) dbg_stamp(p, 5);
     // the operand ring is idle now: reuse it for the per-channel coefficients
     float* s_scale = reinterpret_cast<float*>(tiles);
     float* s_shift = s_scale + p.C_out;

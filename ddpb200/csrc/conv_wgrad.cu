@@ -375,17 +375,31 @@ extern "C" int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, 
   return pl.cluster * pl.groups;
 }
 
-// Scratch floats needed by ddpb_conv_wgrad for this shape (0 if it writes dw directly).
-extern "C" long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps) {
-  const WgPlan pl = plan_wgrad(N, H, W, C_in, C_out, taps);
+// Floats of scratch a launch with this plan writes.  `dense`: dw takes every column with no row padding
+// (dw_cols_valid == dw_ld == taps * C_in); any other dw layout goes through scratch even with one split.
+static long long wgrad_scratch_need(const WgPlan& pl, int C_in, int C_out, int taps, bool dense) {
   const long long rows = (C_out < 128) ? 128 : C_out;   // dup_m tiles still own 128 rows of scratch
-  return (pl.groups > 1 || C_out < 128) ? static_cast<long long>(pl.groups) * rows * taps * C_in : 0;
+  const bool direct = pl.groups == 1 && C_out >= 128 && dense;
+  return direct ? 0 : static_cast<long long>(pl.groups) * rows * taps * C_in;
+}
+
+// Scratch floats needed by ddpb_conv_wgrad for this shape with a dense dw (0 if it writes dw directly).
+extern "C" long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps) {
+  return wgrad_scratch_need(plan_wgrad(N, H, W, C_in, C_out, taps), C_in, C_out, taps, true);
+}
+
+// Same for an arbitrary dw layout: a dw with padded rows (dw_ld > taps * C_in) or fewer valid columns
+// is always assembled from scratch, also when the reduction is not split.
+extern "C" long long ddpb_conv_wgrad_scratch_elems_ld(int N, int H, int W, int C_in, int C_out, int taps,
+                                                      int dw_cols_valid, int dw_ld) {
+  const bool dense = dw_cols_valid == taps * C_in && dw_ld == taps * C_in;
+  return wgrad_scratch_need(plan_wgrad(N, H, W, C_in, C_out, taps), C_in, C_out, taps, dense);
 }
 
 // Shared implementation: `scratch` may be any device buffer of at least
 // ddpb_conv_wgrad_scratch_elems floats.
-static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, int N, int H, int W, int C_in,
-                      int C_out, int taps, int dw_cols_valid, int dw_ld, cudaStream_t stream) {
+static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, long long scratch_elems, int N, int H,
+                      int W, int C_in, int C_out, int taps, int dw_cols_valid, int dw_ld, cudaStream_t stream) {
   DDPB_REQUIRE(taps == 1 || taps == 9, "conv_wgrad: taps must be 1 or 9 (got %d)", taps);
   DDPB_REQUIRE(C_in % 64 == 0 && C_in > 0, "conv_wgrad: C_in must be a multiple of 64 (got %d)", C_in);
   DDPB_REQUIRE(C_out == 64 || C_out % 128 == 0, "conv_wgrad: C_out must be 64 or a multiple of 128 (got %d)",
@@ -400,7 +414,17 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
                taps * C_in);
   const bool direct = (splits == 1 && C_out >= 128 && dw_cols_valid == taps * C_in &&
                        (pl.fused || dw_ld == taps * C_in));
-  DDPB_REQUIRE(direct || scratch != nullptr, "conv_wgrad: this shape needs scratch memory");
+  DDPB_REQUIRE(dw_cols_valid > 0 && dw_cols_valid <= taps * C_in && dw_ld >= dw_cols_valid,
+               "conv_wgrad: bad dw layout (cols_valid %d, ld %d, taps*C_in %d)", dw_cols_valid, dw_ld, taps * C_in);
+  {
+    // what this launch will really write: also one split goes through scratch when dw is not dense
+    const long long rows_need = (C_out < 128) ? 128 : C_out;
+    const long long need = direct ? 0 : static_cast<long long>(splits) * rows_need * taps * C_in;
+    DDPB_REQUIRE(direct || scratch != nullptr, "conv_wgrad: this shape needs %lld floats of scratch memory", need);
+    DDPB_REQUIRE(need <= scratch_elems || direct,
+                 "conv_wgrad: this shape and dw layout need %lld floats of scratch but the buffer holds %lld", need,
+                 scratch_elems);
+  }
 
   CUtensorMap tdy, tx;
   {
@@ -471,11 +495,14 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
 
 // dy: [N*H*W][C_out] bf16; x: [N][H][W][C_in] bf16; dw: fp32 [C_out][dw_ld], of which the
 // first dw_cols_valid (<= taps*C_in) columns of every row are written.  scratch: device
-// buffer of ddpb_conv_wgrad_scratch_elems() floats (may be null when that is 0).
-extern "C" int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* scratch, int N, int H, int W,
-                               int C_in, int C_out, int taps, int dw_cols_valid, int dw_ld,
+// buffer of scratch_elems floats; ddpb_conv_wgrad_scratch_elems_ld() says how many this shape
+// and dw layout need (null / 0 allowed when that is 0).  A buffer that is too small is an error,
+// never an out-of-bounds write.
+extern "C" int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* scratch, long long scratch_elems,
+                               int N, int H, int W, int C_in, int C_out, int taps, int dw_cols_valid, int dw_ld,
                                cudaStream_t stream) {
-  return wgrad_impl(dy, x, dw, scratch, N, H, W, C_in, C_out, taps, dw_cols_valid, dw_ld, stream);
+  return wgrad_impl(dy, x, dw, scratch, scratch != nullptr ? scratch_elems : 0, N, H, W, C_in, C_out, taps,
+                    dw_cols_valid, dw_ld, stream);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -499,7 +526,8 @@ extern "C" int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* 
 //     and every layer at batch <= 128, but not the 4.7 M-float cases (layers 3, 6, 7 at 256);
 //   * the first call on each device looks up the array's device address
 //     (cudaGetSymbolAddress) and caches it; make that first call with the right device
-//     current and before any stream capture begins;
+//     current, before any stream capture begins, and from ONE thread (the cache is written
+//     without a lock; later calls may come from any thread);
 //   * all calls share the one array and it keeps whatever the previous call left in it.
 //     The kernel overwrites every partial sum that the second stage reads, so nothing has to be
 //     cleared between calls -- but two calls whose kernels overlap on the GPU (different
@@ -534,12 +562,13 @@ extern "C" long long ddpb_conv_wgrad_static_max_elems() { return kWgradStaticMax
 // Same arguments and result as ddpb_conv_wgrad minus `scratch`.
 extern "C" int ddpb_conv_wgrad_static(const void* dy, const void* x, float* dw, int N, int H, int W, int C_in,
                                       int C_out, int taps, int dw_cols_valid, int dw_ld, cudaStream_t stream) {
-  const long long need = ddpb_conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps);
+  const long long need = ddpb_conv_wgrad_scratch_elems_ld(N, H, W, C_in, C_out, taps, dw_cols_valid, dw_ld);
   DDPB_REQUIRE(need <= kWgradStaticMaxFloats,
                "conv_wgrad_static: this shape needs %lld floats of scratch but the built-in array holds %lld; "
                "call ddpb_conv_wgrad with a caller-provided buffer instead",
                need, kWgradStaticMaxFloats);
   float* scratch = nullptr;
   if (int rc = wgrad_static_scratch(&scratch)) return rc;
-  return wgrad_impl(dy, x, dw, scratch, N, H, W, C_in, C_out, taps, dw_cols_valid, dw_ld, stream);
+  return wgrad_impl(dy, x, dw, scratch, kWgradStaticMaxFloats, N, H, W, C_in, C_out, taps, dw_cols_valid, dw_ld,
+                    stream);
 }

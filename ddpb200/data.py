@@ -135,11 +135,19 @@ class ShardSampler:
 
 
 class BatchLoader:
-    """Yields (uint8 NHWC batch, int64 labels, int8 aug-or-None) from pinned staging buffers.
+    """Iterating it gives what the reference's DataLoader gives: ``(data, target)`` pairs with
+    ``data`` a normalised (and, for the train split, randomly cropped / flipped) fp32
+    ``[N, 3, 32, 32]`` tensor and ``target`` int64 labels, on the host -- a loop written against
+    /root/reference/part1/main.py:65-75 consumes it unchanged.
+
+    ``raw()`` is the fast path ddpb200's own ``train_model`` / ``test_model`` use: it yields
+    ``(uint8 NHWC batch, int64 labels, int8 aug-or-None)`` from pinned staging buffers and leaves
+    crop / flip / normalise to the input kernel on the GPU (csrc/data_prep.cu).  Both views draw
+    the same crop offsets and flip bits for the same (seed, epoch, rank).
 
     Two staging slots alternate so the async H2D copy of batch i can overlap the host
-    gather of batch i+1.  ``len()`` and ``.dataset`` / ``.sampler`` mirror DataLoader, which
-    is what the reference's loops rely on (part1/main.py:65,108-111).
+    gather of batch i+1.  ``len()`` and ``.dataset`` / ``.sampler`` / ``.batch_size`` mirror
+    DataLoader, which is what the reference's loops rely on (part1/main.py:65,108-111).
     """
 
     def __init__(self, dataset: ImageDataset, batch_size: int, sampler: ShardSampler | None = None,
@@ -159,6 +167,12 @@ class BatchLoader:
         return n // self.batch_size if self.drop_last else math.ceil(n / self.batch_size)
 
     def __iter__(self):
+        from .ops.reference import augment_normalize_u8
+
+        for img, lab, aug in self.raw():
+            yield augment_normalize_u8(img, aug, self.pad), lab.clone()
+
+    def raw(self):
         idx = self.sampler.indices()
         g = torch.Generator().manual_seed(self.seed + 7919 * self.sampler.epoch + self.sampler.rank)
         slot = 0

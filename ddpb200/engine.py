@@ -98,13 +98,24 @@ class _Layer:
 class VGGEngine:
     """Owns buffers + launch sequences for one model instance on one device."""
 
-    def __init__(self, model, max_batch: int, grad_storage: torch.Tensor | None = None, image_hw: int = 32):
+    def __init__(self, model, max_batch: int, grad_storage: torch.Tensor | None = None, image_hw: int = 32,
+                 share_from: "VGGEngine | None" = None):
+        """``share_from``: an existing engine of the SAME model whose parameter / gradient / momentum
+        arenas, bf16 shadow and first-layer filter pack this engine adopts instead of re-homing the
+        parameters again.  Used when a larger batch than the first engine was sized for shows up
+        (get_engine): only activation and scratch buffers are new, so a Trainer, a bound optimizer
+        or captured CUDA graphs that still use the old engine keep seeing the same parameters and
+        momentum."""
         self.model = model
         params = list(model.parameters())
         self.device = params[0].device
         assert self.device.type == "cuda", "VGGEngine needs the model on a CUDA device"
         self.max_batch = max_batch
-        self.arena = ParamArena(params, self.device, grad_storage)
+        if share_from is not None:
+            assert share_from.model is model and grad_storage is None
+            self.arena = share_from.arena
+        else:
+            self.arena = ParamArena(params, self.device, grad_storage)
         index = {id(p): i for i, p in enumerate(params)}
         dev = self.device
 
@@ -153,17 +164,20 @@ class VGGEngine:
         # K-major GEMM operand of fprop AND (read MN-major, taps reversed) of dgrad, so one bf16
         # "shadow" of the whole arena -- refreshed by the SGD kernels -- serves both.  Only the
         # first layer needs a real repack (27 values per filter, zero padded to a 64-wide row).
-        self.shadow = torch.zeros(self.arena.numel, **bf)
-        self.w_f = []
-        for li, L in enumerate(self.layers):
-            if li == 0:
-                self.w_f.append(torch.zeros(L.c_out, 64, **bf))
-            else:
-                o = self.arena.offsets[L.p_w]
-                self.w_f.append(self.shadow[o:o + L.c_out * 9 * L.c_in].view(L.c_out, 9 * L.c_in))
-        L0 = self.layers[0]
-        self.pack_plan = K.PackPlan([dict(master=self.arena.flat_master(L0.p_w), fprop=self.w_f[0], dgrad=None,
-                                          K=L0.c_out, C=L0.c_in, taps=9, fprop_ld=64, flat=True)])
+        if share_from is not None:
+            self.shadow, self.w_f, self.pack_plan = share_from.shadow, share_from.w_f, share_from.pack_plan
+        else:
+            self.shadow = torch.zeros(self.arena.numel, **bf)
+            self.w_f = []
+            for li, L in enumerate(self.layers):
+                if li == 0:
+                    self.w_f.append(torch.zeros(L.c_out, 64, **bf))
+                else:
+                    o = self.arena.offsets[L.p_w]
+                    self.w_f.append(self.shadow[o:o + L.c_out * 9 * L.c_in].view(L.c_out, 9 * L.c_in))
+            L0 = self.layers[0]
+            self.pack_plan = K.PackPlan([dict(master=self.arena.flat_master(L0.p_w), fprop=self.w_f[0], dgrad=None,
+                                              K=L0.c_out, C=L0.c_in, taps=9, fprop_ld=64, flat=True)])
         # --- classifier / loss
         self.labels = torch.zeros(B, dtype=torch.int64, device=dev)
         self.logits = torch.empty(B, self.classes, **f32)
@@ -172,24 +186,27 @@ class VGGEngine:
         self.row_correct = torch.empty(B, dtype=torch.int32, device=dev)
         self.loss = torch.zeros((), **f32)
         self.correct = torch.zeros((), dtype=torch.int32, device=dev)
-        # --- wgrad split-K scratch, shared by all layers (launches are stream ordered)
-        need = 1
+        # --- split reduction scratch, shared by all layers (launches are stream ordered).  The
+        # planners are cost based, so a ragged last batch (any N <= max_batch) can want MORE
+        # scratch than the full batch: size for the maximum over every N.  (The native side also
+        # checks the capacity it is given and never writes past it.)
+        need_w = need_f = 1
         for li, L in enumerate(self.layers):
-            need = max(need, K.conv_wgrad_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps))
-        self.wgrad_scratch = torch.empty(need, **f32)
-        # --- fprop / dgrad split-K scratch (only the small late layers ask for it)
-        need = 1
-        for li, L in enumerate(self.layers):
-            need = max(need, K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps))
-            if li > 0:
-                need = max(need, K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_out, L.c_in, 9))
-        self.fprop_scratch = torch.empty(need, **f32)
+            cols = 27 if li == 0 else 9 * L.c_in
+            for n in range(1, B + 1):
+                need_w = max(need_w, K.conv_wgrad_scratch_elems(n, L.H, L.W, L.c_in_eff, L.c_out, L.taps, cols, cols))
+                need_f = max(need_f, K.conv_fprop_scratch_elems(n, L.H, L.W, L.c_in_eff, L.c_out, L.taps))
+                if li > 0:
+                    need_f = max(need_f, K.conv_fprop_scratch_elems(n, L.H, L.W, L.c_out, L.c_in, 9))
+        self.wgrad_scratch = torch.empty(need_w, **f32)
+        self.fprop_scratch = torch.empty(need_f, **f32)
         self.image_hw = image_hw
         self._tl = None
         self._tl_labels = []
         self.dgrad_sum_in_kernel = os.environ.get("DDPB_DGRAD_FIN_IN_KERNEL", "0") == "1"
-        self.repack(full=True)
-        _register_engine(self)
+        if share_from is None:
+            self.repack(full=True)
+            _register_engine(self)
 
     # -- diagnostics ----------------------------------------------------------------------------
     def enable_timeline(self, slots: int = 256):
@@ -275,9 +292,9 @@ class VGGEngine:
         gradients are final.
 
         ``side_stream``: wgrad(l) and dgrad(l) only share their input, so with a side stream the
-        weight gradient runs concurrently with the data gradient and the next BatchNorm backward
-        (two branches of the captured graph).  The late layers are latency bound, not throughput
-        bound, so the branches overlap almost perfectly."""
+        weight gradient is a second branch of the captured graph next to the data gradient and the
+        next BatchNorm backward.  How much the branches really overlap depends on the kernels leaving
+        each other room on the SMs (measured in DESIGN.md par. 7)."""
         a = self.arena
         main = torch.cuda.current_stream()
         side_events = []
@@ -402,11 +419,16 @@ def engine_of_parameter(p: torch.Tensor):
 
 
 def get_engine(model, batch: int, grad_storage: torch.Tensor | None = None) -> VGGEngine:
+    """The model's engine, sized for at least ``batch`` images.  A larger batch than the current
+    engine holds gets a new engine that SHARES the parameter / gradient / momentum arenas of the
+    old one (only activations are reallocated): a Trainer or optimizer bound to the old engine
+    keeps training the very tensors ``model.parameters()`` and ``state_dict()`` show."""
     eng = model._engine
-    if eng is None or eng.max_batch < batch:
-        if eng is not None and grad_storage is None:
-            grad_storage = None
+    if eng is None:
         eng = VGGEngine(model, batch, grad_storage)
+        model._engine = eng
+    elif eng.max_batch < batch:
+        eng = VGGEngine(model, batch, image_hw=eng.image_hw, share_from=eng)
         model._engine = eng
     return eng
 

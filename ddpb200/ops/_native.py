@@ -28,15 +28,17 @@ _SIGNATURES = {
     "ddpb_abi_version": [],
     "ddpb_sm_count": [],
     "ddpb_conv_fprop": [c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
-                        c_void, c_void],
+                        c_void, c_ll, c_void],
     "ddpb_conv_fprop_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int, c_int],
-    "ddpb_conv_bn_relu_pool_fwd": [c_void] * 9 + [c_int] * 7 + [c_float, c_void, c_void],
+    "ddpb_conv_bn_relu_pool_fwd": [c_void] * 9 + [c_int] * 7 + [c_float, c_void, c_ll, c_void],
     "ddpb_conv_force": [c_int, c_int, c_int],
     "ddpb_conv_debug_timing": [c_void],
+    "ddpb_conv_debug_mode": [c_int],
     "ddpb_conv_plan": [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void],
     "ddpb_conv_wgrad_splits": [c_int, c_int, c_int, c_int, c_int, c_int],
     "ddpb_conv_wgrad_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int],
-    "ddpb_conv_wgrad": [c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+    "ddpb_conv_wgrad_scratch_elems_ld": [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int],
+    "ddpb_conv_wgrad": [c_void, c_void, c_void, c_void, c_ll, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                         c_void],
     "ddpb_channel_stats": [c_void, c_void, c_ll, c_int, c_void],
     "ddpb_bn_relu_pool_fwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int,
@@ -53,7 +55,8 @@ _SIGNATURES = {
     "ddpb_fc_bwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_void,
                     c_void, c_void],
     "ddpb_sgd_step": [c_void, c_void, c_void, c_void, c_ll, c_float, c_float, c_float, c_float, c_void],
-    "ddpb_conv_dgrad": [c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_void, c_void, c_void],
+    "ddpb_conv_dgrad": [c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_void, c_ll, c_void,
+                        c_void],
     "ddpb_pack_weights": [c_int, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void],
     "ddpb_first_layer_operand_f32": [c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_int, c_void],
     "ddpb_first_layer_operand_u8": [c_void, c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_int, c_void,
@@ -62,6 +65,7 @@ _SIGNATURES = {
 _RESTYPES = {
     "ddpb_last_error": C.c_char_p,
     "ddpb_conv_wgrad_scratch_elems": c_ll,
+    "ddpb_conv_wgrad_scratch_elems_ld": c_ll,
     "ddpb_conv_fprop_scratch_elems": c_ll,
 }
 # entry points added by later translation units; bound if present

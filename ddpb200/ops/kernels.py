@@ -19,6 +19,14 @@ def _s(stream):
     return nat.stream_ptr(stream)
 
 
+def _numel(t) -> int:
+    """Capacity (in elements) the native side may use of an optional fp32 scratch tensor."""
+    if t is None:
+        return 0
+    assert t.dtype == torch.float32 and t.is_contiguous()
+    return t.numel()
+
+
 def conv_force(pair: int = -1, block_n: int = -1, splits: int = -1) -> None:
     """Tuning/testing hook: pin the conv launch planner's choice (-1 = automatic)."""
     nat.load().ddpb_conv_force(pair, block_n, splits)
@@ -55,11 +63,8 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, N: i
         scratch = torch.empty(need, dtype=torch.float32, device=x.device) if need else None
     elif scratch is False:
         scratch = None
-    elif scratch is not None:
-        need = conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps, block_n)
-        assert scratch.numel() >= need, "split-K scratch too small"
     rc = nat.load().ddpb_conv_fprop(nat.ptr(x), nat.ptr(w), nat.ptr(bias), nat.ptr(out), nat.ptr(stats), N, H, W,
-                                    C_in, C_out, taps, block_n, nat.ptr(scratch), _s(stream))
+                                    C_in, C_out, taps, block_n, nat.ptr(scratch), _numel(scratch), _s(stream))
     nat.check(rc, "ddpb_conv_fprop")
     return out
 
@@ -89,7 +94,8 @@ def conv_bn_relu_pool_fwd(x, w, bias, gamma, beta, N, H, W, C_in, C_out, taps, p
         scratch = None
     rc = nat.load().ddpb_conv_bn_relu_pool_fwd(nat.ptr(x), nat.ptr(w), nat.ptr(bias), nat.ptr(conv_out), nat.ptr(stats),
                                                nat.ptr(gamma), nat.ptr(beta), nat.ptr(act), nat.ptr(saved), N, H, W,
-                                               C_in, C_out, taps, int(pool), eps, nat.ptr(scratch), _s(stream))
+                                               C_in, C_out, taps, int(pool), eps, nat.ptr(scratch), _numel(scratch),
+                                               _s(stream))
     nat.check(rc, "ddpb_conv_bn_relu_pool_fwd")
     return conv_out, act, saved
 
@@ -112,13 +118,20 @@ def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, 
         scratch = None
     assert sync is None or (sync.is_cuda and sync.element_size() == 4 and sync.numel() >= 1)
     rc = nat.load().ddpb_conv_dgrad(nat.ptr(dy), nat.ptr(w_fprop), nat.ptr(out), N, H, W, C_in, C_out, block_n,
-                                    nat.ptr(scratch), nat.ptr(sync), _s(stream))
+                                    nat.ptr(scratch), _numel(scratch), nat.ptr(sync), _s(stream))
     nat.check(rc, "ddpb_conv_dgrad")
     return out
 
 
-def conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps=9) -> int:
-    return int(nat.load().ddpb_conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps))
+def conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps=9, cols_valid: int | None = None,
+                             out_ld: int | None = None) -> int:
+    """fp32 elements of scratch conv_wgrad needs; a dw with padded rows / fewer valid columns
+    (``cols_valid``, ``out_ld``) is assembled from scratch even when the reduction is not split."""
+    if cols_valid is None and out_ld is None:
+        return int(nat.load().ddpb_conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps))
+    cols_valid = taps * C_in if cols_valid is None else cols_valid
+    out_ld = cols_valid if out_ld is None else out_ld
+    return int(nat.load().ddpb_conv_wgrad_scratch_elems_ld(N, H, W, C_in, C_out, taps, cols_valid, out_ld))
 
 
 def conv_wgrad_set_mode(mode: int) -> None:
@@ -142,11 +155,11 @@ def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, N: int, H: int, W: int, C_in: 
     out_ld = cols_valid if out_ld is None else out_ld
     if out is None:
         out = torch.empty(C_out, out_ld, dtype=torch.float32, device=x.device)
-    need = conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps)
+    need = conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps, cols_valid, out_ld)
     if need and (scratch is None or scratch.numel() < need):
         scratch = torch.empty(need, dtype=torch.float32, device=x.device)
-    rc = nat.load().ddpb_conv_wgrad(nat.ptr(dy), nat.ptr(x), nat.ptr(out), nat.ptr(scratch), N, H, W, C_in, C_out,
-                                    taps, cols_valid, out_ld, _s(stream))
+    rc = nat.load().ddpb_conv_wgrad(nat.ptr(dy), nat.ptr(x), nat.ptr(out), nat.ptr(scratch), _numel(scratch), N, H, W,
+                                    C_in, C_out, taps, cols_valid, out_ld, _s(stream))
     nat.check(rc, "ddpb_conv_wgrad")
     return out
 

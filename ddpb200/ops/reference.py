@@ -131,13 +131,14 @@ def augment_normalize_u8(x_nhwc_u8: torch.Tensor, aug: torch.Tensor | None, pad:
     N, H, W, _ = x_nhwc_u8.shape
     x = x_nhwc_u8.permute(0, 3, 1, 2).float()
     if aug is not None:
+        # one gather for the whole batch: row / column index of every output pixel in the padded image
         xp = F.pad(x, (pad, pad, pad, pad))
-        out = torch.empty_like(x)
-        for n in range(N):
-            oy, ox, flip = int(aug[n, 0]), int(aug[n, 1]), int(aug[n, 2])
-            img = xp[n, :, oy:oy + H, ox:ox + W]
-            out[n] = img.flip(-1) if flip else img
-        x = out
+        a = aug.to(torch.int64)
+        rows = a[:, 0:1] + torch.arange(H, device=x.device)                      # [N, H]
+        cols = torch.arange(W, device=x.device).expand(N, W)
+        cols = torch.where(a[:, 2:3] != 0, W - 1 - cols, cols) + a[:, 1:2]       # flip, then shift
+        n_idx = torch.arange(N, device=x.device)[:, None, None]
+        x = xp.permute(0, 2, 3, 1)[n_idx, rows[:, :, None], cols[:, None, :]].permute(0, 3, 1, 2)
     mean = CIFAR_MEAN.to(x.device).view(1, 3, 1, 1)
     std = CIFAR_STD.to(x.device).view(1, 3, 1, 1)
     return (x / 255.0 - mean) / std

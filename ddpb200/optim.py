@@ -49,9 +49,11 @@ class SGD(torch.optim.Optimizer):
             lr, mu, wd = self.hyper
             self._engine.sgd(lr, mu, wd)   # also refreshes the bf16 shadow the conv kernels read
             return None
+        lr, mu, wd = self.hyper
         if self._fallback is None:
-            lr, mu, wd = self.hyper
             self._fallback = torch.optim.SGD(self.param_groups[0]["params"], lr=lr, momentum=mu, weight_decay=wd)
+        for g in self._fallback.param_groups:   # follow later changes of our own param group (LR schedules)
+            g["lr"], g["momentum"], g["weight_decay"] = lr, mu, wd
         return self._fallback.step(closure)
 
     def state_dict(self):

@@ -71,24 +71,53 @@ def _trainer_for(model, optimizer, mode, rank, world_size, batch_size, **kw) -> 
         kw.setdefault("bucket_layout", "reference")
         kw.setdefault("bucket_bytes", int(model.bucket_cap_mb * 1024 * 1024))
     tr = Trainer(inner, mode=mode, batch_size=batch_size, lr=g["lr"], momentum=g["momentum"],
-                 weight_decay=g["weight_decay"], rank=rank, world_size=world_size, **kw)
+                 weight_decay=g["weight_decay"], rank=rank, world_size=world_size, optimizer=optimizer, **kw)
     if isinstance(optimizer, SGD) and getattr(tr, "engine", None) is not None:
         optimizer.bind(tr.engine)
     object.__setattr__(model, "_ddpb_trainer", tr)
     return tr
 
 
-def train_model(model, train_loader, optimizer, criterion, epoch, rank: int = 0, world_size: int = 1,
-                mode: str | None = None, max_iters: int | None = None, **trainer_kw):
-    """One epoch.  ``mode`` defaults to 'ddp' for a DistributedDataParallel-wrapped model,
-    'single' for one rank, and 'allreduce' otherwise."""
+def _batches(loader):
+    """(data, target, aug) triples: our loaders' raw uint8 view when they have one, else whatever
+    (data, target) pairs the loader yields (e.g. a torch DataLoader)."""
+    if hasattr(loader, "raw"):
+        yield from loader.raw()
+    else:
+        for data, target in loader:
+            yield data, target, None
+
+
+def train_model(model, *args, rank: int | None = None, world_size: int | None = None, mode: str | None = None,
+                max_iters: int | None = None, **trainer_kw):
+    """One epoch.  Accepts both positional orders of the reference:
+
+        train_model(model, train_loader, optimizer, criterion, epoch)                      part1, part3
+        train_model(model, rank, world_size, train_loader, optimizer, criterion, epoch)    part2a, part2b
+
+    (/root/reference/part1/main.py:52, part3/main.py:98, part2/part2a/main.py:118-119,
+    part2/part2b/main.py:106-107).  Without explicit rank / world_size the initialised process
+    group is asked, as part3's DDP does.  ``mode`` defaults to 'ddp' for a
+    DistributedDataParallel-wrapped model, 'single' for one rank, and 'allreduce' otherwise."""
+    if len(args) == 6 and isinstance(args[0], int):
+        rank, world_size, train_loader, optimizer, criterion, epoch = args
+    elif len(args) == 4:
+        train_loader, optimizer, criterion, epoch = args
+    elif len(args) == 6:       # legacy ddpb200 order: (..., epoch, rank, world_size)
+        train_loader, optimizer, criterion, epoch, rank, world_size = args
+    else:
+        raise TypeError("train_model(model, [rank, world_size,] train_loader, optimizer, criterion, epoch)")
+    if world_size is None:
+        world_size = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+    if rank is None:
+        rank = dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
     if mode is None:
         mode = "ddp" if isinstance(model, DistributedDataParallel) else ("single" if world_size == 1 else "allreduce")
     trainer = _trainer_for(model, optimizer, mode, rank, world_size, train_loader.batch_size, **trainer_kw)
     device = trainer.device
     running_loss = 0.0
     total_time = 0
-    for batch_idx, (data, target, aug) in enumerate(train_loader):
+    for batch_idx, (data, target, aug) in enumerate(_batches(train_loader)):
         if max_iters is not None and batch_idx >= max_iters:
             break
         start_time = time.perf_counter_ns()
@@ -116,7 +145,7 @@ def test_model(model, test_loader, criterion, max_iters: int | None = None):
     test_loss = 0.0
     correct = 0
     batches = 0
-    for batch_idx, (data, target, _aug) in enumerate(test_loader):
+    for batch_idx, (data, target, _aug) in enumerate(_batches(test_loader)):
         if max_iters is not None and batch_idx >= max_iters:
             break
         loss, ok = trainer.evaluate(data, target)
@@ -172,16 +201,20 @@ def run(part: str, argv=None) -> None:
                                                     train_size=args.train_size, test_size=args.test_size)
     model = VGG11()
     model.to(device)
-    if args.resume:
-        load_checkpoint(args.resume, model)
+    blob = load_checkpoint(args.resume, model) if args.resume else None
     net = DistributedDataParallel(model) if part == "part3" else model
     optimizer = SGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0001)
     kw = dict(use_graph=not args.no_graph)
     if distributed:
         kw.update(granularity=args.sync_granularity, use_multicast=False if args.no_multicast else "auto")
+    if blob is not None and "optimizer" in blob:
+        # the momentum buffers live in the engine's arena: bind first, then restore them, so a
+        # resumed run continues exactly where the saved one stopped
+        _trainer_for(net, optimizer, mode, rank, world_size, train_loader.batch_size, **kw)
+        optimizer.load_state_dict(blob["optimizer"])
     for epoch in range(args.epochs):
         train_loader.sampler.set_epoch(epoch)
-        train_model(net, train_loader, optimizer, criterion, epoch, rank, world_size, mode=mode,
+        train_model(net, train_loader, optimizer, criterion, epoch, rank=rank, world_size=world_size, mode=mode,
                     max_iters=args.max_iters, **kw)
         test_model(net, test_loader, criterion, max_iters=args.max_iters)
     if args.save and rank == 0:

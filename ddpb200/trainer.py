@@ -35,7 +35,8 @@ class Trainer:
                  use_multicast: bool | str = "auto", use_graph: bool = True, comm_blocks: int | None = None,
                  bucket_layout: str = "reference", first_bucket_bytes: int | None = None,
                  bucket_bytes: int | None = None, symm_backend: str | None = None,
-                 fuse_sgd: bool = True, overlap_wgrad: bool = True, comm_threads: int = 512):
+                 fuse_sgd: bool = True, overlap_wgrad: bool = True, comm_threads: int = 512, optimizer=None,
+                 overlap_sgd: bool = True):
         if mode not in MODES:
             raise ValueError(f"mode must be one of {MODES}")
         if granularity not in ("fused", "param"):
@@ -48,6 +49,11 @@ class Trainer:
         self.use_graph = use_graph
         self.fuse_sgd = fuse_sgd
         self.overlap_wgrad = overlap_wgrad
+        # The SGD update of a layer only needs that layer's gradients and that nobody reads its
+        # weights any more in this step (its dgrad is enqueued).  With overlap_sgd the update of each
+        # parameter group ('single') / each reduced bucket ('ddp') runs on a side stream while the
+        # rest of backward continues, instead of as one 30 us pass over all 9.2 M parameters at the end.
+        self.overlap_sgd = overlap_sgd
         # CTA size of the reductions that overlap backward (mode 'ddp').  256-thread CTAs would fit on
         # an SM next to a persistent conv CTA, but measured on 2 GPUs (profiles/r1_call30_*) the lost
         # reduction throughput costs more than the co-residency gains: 512-thread CTAs stay default.
@@ -55,6 +61,10 @@ class Trainer:
         self.device = next(model.parameters()).device
         self.distributed = world_size > 1 and mode != "single"
         self.iteration = 0
+        # ``optimizer``: the user's optimizer object.  Its param_groups[0] stays the source of truth
+        # for lr / momentum / weight_decay (checked before every step, so an LR scheduler works);
+        # on CPU it is also the object that is stepped, so its state_dict carries the momentum.
+        self._hyper_source = optimizer
         self._graphs: dict[str, torch.cuda.CUDAGraph] = {}
         # Bucket layout of mode 'ddp'.  "reference" (default) = torch DDP's defaults (1 MiB first
         # bucket, 25 MiB cap: 9.46 / 27.16 / 0.31 MB for VGG-11).  "per_layer" closes a bucket after
@@ -114,6 +124,7 @@ class Trainer:
         self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1) if self.mode == "ddp" else None
         # wgrad runs on its own branch, concurrently with dgrad / the next BatchNorm backward
         self.wgrad_stream = torch.cuda.Stream(device=self.device) if self.overlap_wgrad else None
+        self.update_stream = torch.cuda.Stream(device=self.device) if self.overlap_sgd else None
         B = self.batch_size
         hw = self.engine.image_hw
         self.in_u8 = torch.zeros(B, hw, hw, 3, dtype=torch.uint8, device=self.device)
@@ -149,6 +160,14 @@ class Trainer:
         a = self.engine.arena
         return (a.master, a.momentum, self.engine.shadow, self.lr, self.momentum, self.weight_decay)
 
+    def _sgd_slice(self, off: int, n: int):
+        """Plain (local) SGD update of arena range [off, off + n) on the current stream."""
+        from .ops import kernels as K
+
+        a, eng = self.engine.arena, self.engine
+        K.sgd_step(a.master[off:off + n], a.grad[off:off + n], a.momentum[off:off + n], self.lr, self.momentum,
+                   self.weight_decay, 1.0, shadow=eng.shadow[off:off + n])
+
     def _sync_range(self, off, n, slot_base, stream=None):
         sgd = self._sgd_args() if self.fuse_sgd else None
         if self.mode == "gather_scatter":
@@ -171,8 +190,32 @@ class Trainer:
             eng.load_input_f32(self.in_f32[:B], pack=True)
         eng.forward(B, with_loss=True, defer_loss=True)
         if not self.distributed:
-            eng.backward(B, side_stream=self.wgrad_stream, reduce_loss=True)
-            eng.sgd(self.lr, self.momentum, self.weight_decay)
+            if self.overlap_sgd and self.update_stream is not None:
+                # per parameter group: update as soon as the group's gradients are final and its dgrad
+                # (the last reader of its weights in this step) is enqueued
+                main = torch.cuda.current_stream()
+                upd = self.update_stream
+
+                def after_layer(gi, side_events):
+                    first, last, _ = self.groups[gi]
+                    off, n = a.range_of(first, last)
+                    ev = torch.cuda.Event()
+                    ev.record(main)
+                    upd.wait_event(ev)
+                    for sev in side_events:           # the group's weight gradient (side branch)
+                        upd.wait_event(sev)
+                    with torch.cuda.stream(upd):
+                        self._sgd_slice(off, n)
+                        eng.mark(f"sgd group {gi} (side)")
+
+                eng.backward(B, after_layer=after_layer, side_stream=self.wgrad_stream, reduce_loss=True)
+                done = torch.cuda.Event()
+                done.record(upd)
+                main.wait_event(done)
+                eng.mark("sgd joined")
+            else:
+                eng.backward(B, side_stream=self.wgrad_stream, reduce_loss=True)
+                eng.sgd(self.lr, self.momentum, self.weight_decay)
         elif self.mode == "ddp":
             # Early buckets: reduction only, few CTAs, on the side stream while backward continues.
             # Last bucket (the first layers, ready when backward ends): one full-width kernel that
@@ -180,6 +223,7 @@ class Trainer:
             main = torch.cuda.current_stream()
             ready = {b.ready_after_group: bi for bi, b in enumerate(self.buckets)}
             last_bi = len(self.buckets) - 1
+            early_sgd = self.overlap_sgd and self.fuse_sgd
 
             def after_layer(li, side_events):
                 bi = ready.get(li)
@@ -195,6 +239,10 @@ class Trainer:
                 with torch.cuda.stream(self.comm_stream):
                     self.symm.allreduce_avg(off, n, blocks=self.comm_blocks, slot_base=bi * self.comm_blocks,
                                             use_mc=self.use_mc, sgd=None, threads=self.comm_threads)
+                    if early_sgd:
+                        # the bucket's mean is final on this rank once its reduction kernel has ended:
+                        # update it now (a local kernel, no peer waits), not in the tail after backward
+                        self._sgd_slice(off, n)
 
             eng.backward(B, after_layer=after_layer, side_stream=self.wgrad_stream, reduce_loss=True)
             done = torch.cuda.Event()
@@ -204,7 +252,8 @@ class Trainer:
             off, n = a.range_of(b.first_param, b.last_param)
             wide = min(torch.cuda.get_device_properties(self.device).multi_processor_count, 128)
             self.symm.allreduce_avg(off, n, blocks=wide, slot_base=1024, use_mc=self.use_mc,
-                                    sgd=self._sgd_args() if self.fuse_sgd else None, sgd_range=(0, a.numel))
+                                    sgd=self._sgd_args() if self.fuse_sgd else None,
+                                    sgd_range=(off, n) if early_sgd else (0, a.numel))
             if not self.fuse_sgd:
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
         else:
@@ -235,13 +284,36 @@ class Trainer:
         eng.labels[:N].copy_(target, non_blocking=True)
         return kind
 
+    def set_hyperparameters(self, lr: float | None = None, momentum: float | None = None,
+                            weight_decay: float | None = None) -> None:
+        """Changes the SGD hyper-parameters of the following steps.  On CUDA they are kernel
+        arguments baked into the captured step, so a change drops the captured graphs (the next
+        step runs eagerly and is captured again: about a millisecond, once per change -- fine for
+        an epoch-wise schedule; for a per-step schedule build the Trainer with use_graph=False)."""
+        new = (self.lr if lr is None else float(lr), self.momentum if momentum is None else float(momentum),
+               self.weight_decay if weight_decay is None else float(weight_decay))
+        if new != (self.lr, self.momentum, self.weight_decay):
+            self.lr, self.momentum, self.weight_decay = new
+            self._graphs.clear()
+            opt = getattr(self, "optimizer", None)
+            if self.device.type != "cuda" and opt is not None and opt is not self._hyper_source:
+                for g in opt.param_groups:
+                    g["lr"], g["momentum"], g["weight_decay"] = new
+
+    def _refresh_hyper(self) -> None:
+        src = self._hyper_source
+        if src is not None:
+            g = src.param_groups[0]
+            self.set_hyperparameters(g["lr"], g.get("momentum", 0.0), g.get("weight_decay", 0.0))
+
     def step(self, data: torch.Tensor, target: torch.Tensor, aug: torch.Tensor | None = None) -> torch.Tensor:
         """One training iteration.  ``data`` is either raw uint8 NHWC pixels (plus optional
         per-image crop/flip parameters ``aug``) or a normalised fp32 NCHW batch, on the host
         (ideally pinned) or on the device.  Returns the mean loss as a 0-d device tensor that is
         overwritten by the next call."""
+        self._refresh_hyper()
         if self.device.type != "cuda":
-            return self._step_cpu(data, target)
+            return self._step_cpu(data, target, aug)
         kind = self._stage_inputs(data, target, aug)
         with_aug = aug is not None
         key = f"{kind}:{int(with_aug)}"
@@ -298,9 +370,10 @@ class Trainer:
             return 0
         n = 1 + self.engine.launches_per_train_step()  # input prep (+ first-layer filter pack)
         if not self.distributed:
-            n += 1
+            n += len(self.groups) if (self.overlap_sgd and self.update_stream is not None) else 1
         elif self.mode == "ddp":
-            n += len(self.buckets) + (0 if self.fuse_sgd else 1)
+            early = self.overlap_sgd and self.fuse_sgd
+            n += len(self.buckets) + (len(self.buckets) - 1 if early else 0) + (0 if self.fuse_sgd else 1)
         else:
             n += (len(self.engine.arena.params) if self.granularity == "param" else 1) + (0 if self.fuse_sgd else 1)
         return n
@@ -315,8 +388,9 @@ class Trainer:
     # CPU path (stock modules + torch.distributed): plumbing tests and the oracle
     # =====================================================================================
     def _init_cpu(self):
-        self.optimizer = torch.optim.SGD(self.model.parameters(), lr=self.lr, momentum=self.momentum,
-                                         weight_decay=self.weight_decay)
+        # step the caller's optimizer when there is one (its state_dict then holds the momentum)
+        self.optimizer = self._hyper_source if self._hyper_source is not None else torch.optim.SGD(
+            self.model.parameters(), lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay)
         self.reducer = None
         if self.distributed and self.mode == "ddp":
             for p in self.model.parameters():  # constructor-time broadcast, as DDP does
@@ -325,15 +399,15 @@ class Trainer:
             self.buckets = self.reducer.buckets
 
     @staticmethod
-    def _to_float_batch(data: torch.Tensor) -> torch.Tensor:
+    def _to_float_batch(data: torch.Tensor, aug: torch.Tensor | None = None) -> torch.Tensor:
         if data.dtype == torch.uint8:
             from .ops.reference import augment_normalize_u8
 
-            return augment_normalize_u8(data, None)
+            return augment_normalize_u8(data, aug)   # crop / flip / normalise, as the device kernel does
         return data
 
-    def _step_cpu(self, data, target):
-        data = self._to_float_batch(data)
+    def _step_cpu(self, data, target, aug=None):
+        data = self._to_float_batch(data, aug)
         self.optimizer.zero_grad()
         loss = F.cross_entropy(self.model(data), target)
         loss.backward()

@@ -33,10 +33,24 @@ int ddpb_stamp(unsigned long long* slot, void* stream);
  * taps = 9, or 1 for the first layer's pre-gathered operand (see ddpb_first_layer_operand_*).
  * stats (fp32 [2][C_out], may be null) is ACCUMULATED with per-channel sum / sum of squares of
  * y (the BatchNorm statistics, O4).  block_n: 0 = automatic.  scratch: fp32 buffer of
- * ddpb_conv_fprop_scratch_elems() floats for split-K, or null to forbid splitting. */
+ * scratch_elems floats for split-K (ddpb_conv_fprop_scratch_elems() says how many the planner
+ * would like for this shape), or null to forbid splitting.  A split-K plan that does not fit in
+ * scratch_elems is replaced by one without split-K; nothing is ever written past the buffer. */
 int ddpb_conv_fprop(const void* x, const void* w, const float* bias, void* y, float* stats, int N, int H, int W,
-                    int C_in, int C_out, int taps, int block_n, float* scratch, void* stream);
+                    int C_in, int C_out, int taps, int block_n, float* scratch, long long scratch_elems,
+                    void* stream);
 long long ddpb_conv_fprop_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps, int block_n);
+
+/* O1+O4+O6+O7 in one call: convolution, then BatchNorm(batch statistics) + ReLU (+2x2 max-pool),
+ * part1/model.py:15-25.  conv_out ([N*H*W][C_out] bf16) is still written (the backward pass reads
+ * it); act is the block's output; saved_mean_rstd fp32 [2][C_out].  stats: fp32 scratch of
+ * 2*C_out + 32 floats, ZERO on entry.  The persistent kernel normalises its own tiles after a
+ * grid-wide barrier; split-K shapes run the separate finalize and BatchNorm kernels.
+ * scratch / scratch_elems as for ddpb_conv_fprop. */
+int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const float* bias, void* conv_out, float* stats,
+                               const float* gamma, const float* beta, void* act, float* saved_mean_rstd, int N, int H,
+                               int W, int C_in, int C_out, int taps, int pool, float eps, float* scratch,
+                               long long scratch_elems, void* stream);
 
 /* O2: data gradient of the same convolution (autograd of part1/model.py:18-23).
  * dx[N*H*W][C_in] from dy[..][C_out] and the SAME filter pack fprop reads (no transposed copy).
@@ -44,14 +58,19 @@ long long ddpb_conv_fprop_scratch_elems(int N, int H, int W, int C_in, int C_out
  * sync: one zeroed 32-bit device word (left non-zero) or null; with it a split-K launch sums its
  * partial tiles inside the same kernel after a grid barrier instead of in a second kernel. */
 int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out, int block_n,
-                    float* scratch, unsigned int* sync, void* stream);
+                    float* scratch, long long scratch_elems, unsigned int* sync, void* stream);
 
 /* O3: weight gradient.  dw (fp32 [C_out][dw_ld]) gets its first dw_cols_valid (<= taps*C_in)
- * columns per row.  scratch: ddpb_conv_wgrad_scratch_elems() floats of device memory for the
- * split reduction over pixels (may be null when that is 0). */
-int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* scratch, int N, int H, int W, int C_in,
-                    int C_out, int taps, int dw_cols_valid, int dw_ld, void* stream);
+ * columns per row.  scratch: scratch_elems floats of device memory for the split reduction over
+ * pixels; ddpb_conv_wgrad_scratch_elems_ld() gives the need for this shape AND dw layout (a dw
+ * with padded rows or fewer valid columns goes through scratch even without a split),
+ * ddpb_conv_wgrad_scratch_elems() the need for a dense dw (dw_cols_valid == dw_ld == taps*C_in).
+ * Null / 0 are allowed when the need is 0; a buffer that is too small is reported as an error. */
+int ddpb_conv_wgrad(const void* dy, const void* x, float* dw, float* scratch, long long scratch_elems, int N, int H,
+                    int W, int C_in, int C_out, int taps, int dw_cols_valid, int dw_ld, void* stream);
 long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps);
+long long ddpb_conv_wgrad_scratch_elems_ld(int N, int H, int W, int C_in, int C_out, int taps, int dw_cols_valid,
+                                           int dw_ld);
 int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps);
 /* 0 (default): one tap per CTA, split reduction through global memory.  1: three taps per CTA and
  * the split reduction over distributed shared memory inside a thread-block cluster (measured
@@ -65,9 +84,11 @@ void ddpb_conv_wgrad_set_mode(int mode);
  * memory was handed to another allocator, a host application that forbids allocator calls):
  * same arguments minus `scratch`; the split-reduction scratch is a fixed array of
  * ddpb_conv_wgrad_static_max_elems() floats (4 Mi = 16 MiB) that every GPU loading the library
- * holds until exit.  Larger requests fail with an error.  The first call on a device resolves
- * the array's address: make it with that device current and before any stream capture.  All
- * calls share the array; calls that overlap on the GPU race. */
+ * holds until exit.  Larger requests (ddpb_conv_wgrad_scratch_elems_ld() above that size) fail
+ * with an error.  The first call on a device resolves the array's address: make it with that
+ * device current, before any stream capture, and from one thread (the per-device cache is not
+ * locked; later calls may come from any thread).  All calls share the array; calls that overlap
+ * on the GPU race. */
 int ddpb_conv_wgrad_static(const void* dy, const void* x, float* dw, int N, int H, int W, int C_in, int C_out,
                            int taps, int dw_cols_valid, int dw_ld, void* stream);
 long long ddpb_conv_wgrad_static_max_elems(void);
@@ -77,7 +98,8 @@ long long ddpb_conv_wgrad_static_max_elems(void);
  * such shapes fall back to 2; -1 = automatic = 2). */
 void ddpb_conv_force(int kernel, int block_n, int splits);
 void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3);
-void ddpb_conv_debug_timing(unsigned long long* per_cta_stamps);
+void ddpb_conv_debug_timing(unsigned long long* per_cta_stamps);   /* 8 slots per CTA, see bench/conv_probe2.py */
+void ddpb_conv_debug_mode(int mode);   /* timing probes, wrong results: bit 0 skip B loads, bit 1 skip A loads */
 
 /* ---- BatchNorm + ReLU (+ MaxPool) (K3, K4) -------------------------------------------------- */
 /* O4+O6+O7: BatchNorm2d(track_running_stats=False) -> ReLU -> [MaxPool2d(2,2)],

@@ -98,14 +98,27 @@ def test_loaders_shapes_and_determinism():
     tr, te = create_data_loaders(1, 4, 64, root=None, synthetic=True, train_size=1000, test_size=300)
     assert len(tr) == math.ceil(250 / 64) and len(te) == math.ceil(300 / 64)
     assert len(te.dataset) == 300                       # the test split is NOT sharded (Q10)
-    img, lab, aug = next(iter(tr))
+    img, lab, aug = next(iter(tr.raw()))
     assert img.dtype == torch.uint8 and img.shape == (64, 32, 32, 3) and lab.dtype == torch.int64
     assert aug.shape == (64, 4) and int(aug[:, :2].max()) <= 8 and int(aug[:, 2].max()) <= 1
+    # plain iteration = what the reference's DataLoader yields (part1/main.py:65): normalised fp32 NCHW pairs,
+    # same crop / flip draws as the raw view
+    data, target = next(iter(tr))
+    assert data.dtype == torch.float32 and data.shape == (64, 3, 32, 32) and torch.equal(target, lab)
+    from ddpb200.ops.reference import augment_normalize_u8
+    assert torch.equal(data, augment_normalize_u8(img, aug))
+    n0 = 5
+    oy, ox, flip = (int(v) for v in aug[n0, :3])
+    padded = torch.nn.functional.pad(img[n0].permute(2, 0, 1).float(), (4, 4, 4, 4))[:, oy:oy + 32, ox:ox + 32]
+    want = (padded.flip(-1) if flip else padded) / 255.0
+    mean = torch.tensor([125.3, 123.0, 113.9]).view(3, 1, 1) / 255.0
+    std = torch.tensor([63.0, 62.1, 66.7]).view(3, 1, 1) / 255.0
+    assert torch.allclose(data[n0], (want - mean) / std, atol=1e-6)
     a = synthetic_cifar10(True, 128).images
     b = synthetic_cifar10(True, 128).images
     assert torch.equal(a, b)
     tr.sampler.set_epoch(3)                             # API parity (Q13)
-    last = list(iter(BatchLoader(synthetic_cifar10(False, 100), 64)))[-1]
+    last = list(BatchLoader(synthetic_cifar10(False, 100), 64).raw())[-1]
     assert last[0].shape[0] == 36 and last[2] is None
 
 
@@ -214,3 +227,70 @@ def test_clock_sampler_nvml_path_and_summary(monkeypatch):
     assert out["source"] == "nvml" and out["samples"] >= 5
     assert out["sm_mhz"] == 1965 and out["sm_max_mhz"] == 1965 and out["power_w_max"] == 512.0
     assert out["reasons"] == ["sw_power_cap"]
+
+
+def test_reference_style_loop_and_both_train_model_orders():
+    """A loop written against the reference's scripts (part1/main.py:65-80) runs unchanged on our loader,
+    model, criterion and optimizer; train_model takes part1/part3's AND part2a/part2b's argument order
+    (part2/part2b/main.py:106-107)."""
+    from ddpb200.train import train_model
+
+    torch.manual_seed(0)
+    device = "cpu"
+    model = ddpb200.VGG11()
+    train_loader, _ = create_data_loaders(0, 1, 8, root=None, synthetic=True, train_size=24, test_size=8)
+    optimizer = ddpb200.SGD(model.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
+    criterion = ddpb200.CrossEntropyLoss().to(device)
+    losses = []
+    for batch_idx, (data, target) in enumerate(train_loader):
+        data, target = data.to(device), target.to(device)
+        optimizer.zero_grad()
+        output = model(data)
+        loss = criterion(output, target)
+        loss.backward()
+        optimizer.step()
+        losses.append(loss.item())
+    assert len(losses) == 3 and all(l == l for l in losses)
+    out = io.StringIO()
+    with redirect_stdout(out):
+        train_model(model, train_loader, optimizer, criterion, 0)              # part1 / part3 order
+        train_model(model, 0, 1, train_loader, optimizer, criterion, 0)        # part2a / part2b order
+    with pytest.raises(TypeError):
+        train_model(model, train_loader, optimizer)
+
+
+def test_resume_restores_momentum_and_lr_changes_are_followed(tmp_path):
+    """--save / --resume keep the SGD momentum: two steps straight == one step, save,
+    load into a fresh model + optimizer, one more step.  And a changed param_groups[0]['lr'] is used
+    by the next Trainer.step."""
+    from ddpb200.utils.checkpoint import load_checkpoint, save_checkpoint
+
+    x = torch.randint(0, 256, (8, 32, 32, 3), dtype=torch.uint8)
+    y = torch.randint(0, 10, (8,))
+
+    def make():
+        torch.manual_seed(3)
+        m = ddpb200.VGG11()
+        o = ddpb200.SGD(m.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+        return m, o, ddpb200.Trainer(m, mode="single", batch_size=8, lr=0.05, optimizer=o)
+
+    m1, o1, t1 = make()
+    t1.step(x, y), t1.step(x, y)
+    m2, o2, t2 = make()
+    t2.step(x, y)
+    save_checkpoint(tmp_path / "c.pt", m2, o2)
+    m3, o3, t3 = make()
+    load_checkpoint(tmp_path / "c.pt", m3, o3)
+    t3.step(x, y)
+    for a, b in zip(m1.parameters(), m3.parameters()):
+        assert torch.allclose(a, b, atol=1e-6), "momentum was lost across save/resume"
+    # LR schedule: the trainer follows the optimizer's param group
+    before = [p.detach().clone() for p in m3.parameters()]
+    o3.param_groups[0]["lr"] = 0.0
+    o3.param_groups[0]["momentum"] = 0.0
+    o3.param_groups[0]["weight_decay"] = 0.0
+    t3.step(x, y)
+    assert t3.lr == 0.0
+    # lr = 0: parameters must not move (momentum buffers do not matter with lr 0)
+    for a, b in zip(before, m3.parameters()):
+        assert torch.equal(a, b)

@@ -271,3 +271,45 @@ def test_ragged_batches_and_evaluation():
     ref_loss = torch.nn.functional.cross_entropy(logits, lab.to(DEV))
     assert abs(loss.item() - ref_loss.item()) < 2e-2 * abs(ref_loss.item())   # u8 vs f32 input path: bf16 rounding
     assert abs(int(correct) - int((logits.argmax(1).cpu() == lab).sum())) <= 1
+
+
+def test_larger_eager_batch_keeps_the_trainers_parameters_and_momentum():
+    """model(x) with a batch larger than the Trainer's engine used to re-home the
+    parameters into a NEW arena, so the trainer kept training tensors nobody could see any more.  The
+    regrown engine now shares the arenas: only activations are reallocated."""
+    torch.manual_seed(6)
+    model = ddpb200.VGG11().to(DEV)
+    tr = ddpb200.Trainer(model, mode="single", batch_size=32, lr=0.05)
+    img, lab = _batch(32)
+    tr.step(img, lab)
+    master_ptr = tr.engine.arena.master.data_ptr()
+    mom = tr.engine.arena.momentum.clone()
+    assert float(mom.abs().sum()) > 0
+    with torch.no_grad():
+        big = model(torch.randn(64, 3, 32, 32, device=DEV))     # twice the trainer's batch
+    assert big.shape == (64, 10) and model._engine.max_batch >= 64
+    assert model._engine.arena is tr.engine.arena and model._engine.arena.master.data_ptr() == master_ptr
+    assert torch.equal(tr.engine.arena.momentum, mom)
+    before = model.fc1.weight.detach().clone()
+    tr.step(img, lab)                                           # still trains what model.parameters() shows
+    torch.cuda.synchronize()
+    assert not torch.equal(before, model.fc1.weight.detach())
+    assert model.fc1.weight.data_ptr() >= master_ptr
+
+
+def test_scratch_is_sized_for_every_batch_up_to_the_maximum():
+    """a 256-batch engine must hold the split-K scratch of every N <= 256."""
+    from ddpb200.ops import kernels as K
+
+    torch.manual_seed(7)
+    model = ddpb200.VGG11().to(DEV)
+    tr = ddpb200.Trainer(model, mode="single", batch_size=256, lr=0.01, use_graph=False)
+    eng = tr.engine
+    for n in (103, 136, 192, 232):
+        for li, L in enumerate(eng.layers):
+            assert K.conv_fprop_scratch_elems(n, L.H, L.W, L.c_in_eff, L.c_out, L.taps) <= eng.fprop_scratch.numel()
+            if li:
+                assert K.conv_fprop_scratch_elems(n, L.H, L.W, L.c_out, L.c_in, 9) <= eng.fprop_scratch.numel()
+    img, lab = _batch(232, seed=9)
+    l = tr.step(img, lab).item()        # 1000 % 256 = 232: one of the sizes that used to overrun
+    assert l == l

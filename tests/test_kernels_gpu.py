@@ -356,3 +356,56 @@ def test_first_layer_operand_shapes_and_filter_pack(H, W):
     ref = R.first_layer_operand(R.augment_normalize_u8(raw, aug)).bfloat16()
     assert (op.float() - ref.float()).abs().max().item() < 2e-2
     assert torch.equal(f0[:, :27], m0.view(64, 27).bfloat16())
+
+
+def test_conv_split_k_never_overruns_a_small_scratch():
+    """the split-K plan is cost based, so a caller's scratch can be smaller than what
+    the planner wants for another batch size.  The launcher must then fall back to a plan without
+    split-K (same result), and a FORCED split that does not fit must be an error, never a write past
+    the buffer (checked with a canary behind the capacity the call was given)."""
+    N, H, W, Ci, Co = 64, 2, 2, 512, 512
+    want = K.conv_fprop_scratch_elems(N, H, W, Ci, Co, 9)
+    assert want > 0, "shape is meant to split K"
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    ref = R.conv_fprop(x, w, None, N, H, W, Ci, Co)
+    backing = torch.full((want,), 12345.0, device=DEV)
+    small = backing[:want // 4]                       # capacity the call is told about
+    y = K.conv_fprop(x, w, None, N, H, W, Ci, Co, scratch=small)
+    dx = K.conv_dgrad(dy, w, N, H, W, Ci, Co, scratch=small)
+    gamma, beta = torch.ones(Co, device=DEV), torch.zeros(Co, device=DEV)
+    conv_out, act, _ = K.conv_bn_relu_pool_fwd(x, w, None, gamma, beta, N, H, W, Ci, Co, 9, True, scratch=small)
+    torch.cuda.synchronize()
+    assert _rel_err(y, ref) < 1e-2 and _rel_err(conv_out, ref) < 1e-2
+    assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
+    assert bool((backing[want // 4:] == 12345.0).all()), "wrote past the scratch capacity"
+    try:
+        K.conv_force(-1, -1, 4)
+        with pytest.raises(RuntimeError, match="scratch"):
+            K.conv_fprop(x, w, None, N, H, W, Ci, Co, scratch=small)
+    finally:
+        K.conv_force(-1, -1, -1)
+
+
+def test_conv_wgrad_padded_dw_goes_through_scratch_even_without_a_split():
+    """with one split and C_out >= 128 a DENSE dw is written directly and needs no
+    scratch, but a dw with padded rows is assembled from scratch: the size query must say so and a
+    too-small buffer must be refused."""
+    from ddpb200.ops import _native as nat
+
+    N, H, W, Ci, Co = 64, 2, 2, 512, 512
+    assert K.conv_wgrad_splits(N, H, W, Ci, Co) == 1 and K.conv_wgrad_scratch_elems(N, H, W, Ci, Co) == 0
+    ld = 9 * Ci + 64
+    need = K.conv_wgrad_scratch_elems(N, H, W, Ci, Co, 9, 9 * Ci, ld)
+    assert need == Co * 9 * Ci
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    out = torch.full((Co, ld), 7.0, device=DEV)
+    K.conv_wgrad(dy, x, N, H, W, Ci, Co, out=out, cols_valid=9 * Ci, out_ld=ld)
+    ref = R.conv_wgrad(dy, x, N, H, W, Ci, Co)
+    assert _rel_err(out[:, :9 * Ci], ref) < 2e-3 and bool((out[:, 9 * Ci:] == 7.0).all())
+    small = torch.empty(need // 2, device=DEV)
+    rc = nat.load().ddpb_conv_wgrad(nat.ptr(dy), nat.ptr(x), nat.ptr(out), nat.ptr(small), small.numel(), N, H, W, Ci,
+                                    Co, 9, 9 * Ci, ld, nat.stream_ptr(None))
+    assert rc != 0 and b"scratch" in nat.load().ddpb_last_error()
