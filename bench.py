@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch")
     ap.add_argument("--no-overlap-wgrad", action="store_true", help="weight gradients on the main stream")
-    ap.add_argument("--bn-fused", type=int, default=None, help="BatchNorm backward: 0 two kernels, 1/2 fused (CTAs per SM)")
+    ap.add_argument("--bn-fused", type=int, default=None, help="BatchNorm backward: 3 deterministic two-kernel (default), 1/2 cooperative fused, 0 two-pass atomics")
     ap.add_argument("--conv-mode", type=int, default=-1,
                     help="conv kernel of fprop/dgrad: -1 automatic (persistent), 1 CTA pair, 3 persistent CTA pair")
     ap.add_argument("--comm-blocks", type=int, default=None)
@@ -59,6 +59,8 @@ def parse():
     ap.add_argument("--comm-threads", type=int, default=512)
     ap.add_argument("--bucket-mb", type=float, default=None, help="explicit bucket cap in MiB (first bucket: min(1, cap))")
     ap.add_argument("--no-fuse-sgd", action="store_true", help="run SGD as its own full-width kernel after the sync")
+    ap.add_argument("--no-overlap-sgd", action="store_true",
+                    help="one SGD pass after backward instead of per-group / per-bucket updates on a side stream")
     ap.add_argument("--symm-backend", default=None)
     return ap.parse_args()
 
@@ -147,7 +149,7 @@ def run_ours(a):
                               use_multicast=False if a.no_multicast else "auto", use_graph=not a.no_graph,
                               comm_blocks=a.comm_blocks, symm_backend=a.symm_backend, bucket_layout=a.bucket_layout,
                               fuse_sgd=not a.no_fuse_sgd, comm_threads=a.comm_threads,
-                              overlap_wgrad=not a.no_overlap_wgrad,
+                              overlap_wgrad=not a.no_overlap_wgrad, overlap_sgd=not a.no_overlap_sgd,
                               first_bucket_bytes=None if a.bucket_mb is None else int(min(1.0, a.bucket_mb) * 2**20),
                               bucket_bytes=None if a.bucket_mb is None else int(a.bucket_mb * 2**20))
     if a.bn_fused is not None:   # (after the Trainer, whose 'ddp' mode picks its own default)

@@ -54,7 +54,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--reps", type=int, default=20)
-    ap.add_argument("--bn-fused", type=int, default=2)
+    ap.add_argument("--bn-fused", type=int, default=3)
     ap.add_argument("--conv-mode", type=int, default=-1,
                     help="conv kernel: -1 automatic, 0 one tile per CTA, 1 CTA pair, 2 persistent, 3 persistent CTA pair")
     ap.add_argument("--block-n", type=int, default=-1, help="force the tile width of fprop / dgrad")
@@ -86,8 +86,10 @@ def main():
         dact = torch.randn(Po, Co, device=dev).bfloat16()
         dconv = torch.empty(P, Co, dtype=torch.bfloat16, device=dev)
         dg, db_, dbias = torch.empty(Co, device=dev), torch.empty(Co, device=dev), torch.empty(Co, device=dev)
+        part = torch.empty(max(1, K.bn_bwd_partials_elems(N, H, W, Co, pool)), device=dev)
         t_b = timed(lambda i: K.bn_relu_pool_bwd(conv_out, dact, saved, gamma, beta, N, H, W, Co, pool, sums=stats[i],
-                                                 dx=dconv, dgamma=dg, dbeta=db_, dbias=dbias), reps, zero=stats)
+                                                 dx=dconv, dgamma=dg, dbeta=db_, dbias=dbias, partials=part), reps,
+                    zero=stats)
         cols = 27 if li == 0 else 9 * Ci
         dw = torch.empty(Co, cols, device=dev)
         ws = torch.empty(max(1, K.conv_wgrad_scratch_elems(N, H, W, Cin_eff, Co, taps)), device=dev)

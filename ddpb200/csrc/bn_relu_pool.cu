@@ -603,9 +603,309 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   }
 }
 
-// 0: two-kernel path; 1: fused, one CTA per SM (leaves registers for a co-resident gradient-sync
-// CTA: a cooperative launch needs ALL its CTAs resident at once); 2: fused, up to two CTAs per SM
-static int g_bn_fused = 2;
+// ------------------------------------------------------------------------------------------
+// Deterministic two-kernel backward (default, mode 3).  The cooperative kernel above needs every one
+// of its CTAs resident at once, so inside the training step it could not start while CTAs of the
+// weight-gradient branch (or of an overlapped gradient reduction / SGD update) still held SMs: the
+// branches of the backward graph serialised on it (profiles/r1_call40_*, r2_call04_*).  These two
+// kernels are ordinary launches with a small footprint (256 threads, 3 KB of shared memory) that
+// co-run with tensor-core CTAs, use no float atomics -- every sum is taken in a fixed order, so
+// dgamma / dbeta are bitwise reproducible -- and keep several 16-byte loads per thread in flight.
+//
+//   reduce: CTA (slice of 64 channels, pixel range) -> partial (sum g, sum g*x) per channel into
+//           partials[slice][range][2][64]; the LAST CTA of a slice to finish (ticket counter) adds the
+//           slice's partials in range order into sums[2][C] and resets the counter for the next launch.
+//   apply : coefficients from sums, dx = scale*g + A*x + Bc streamed out; CTA (slice, 0) publishes
+//           dgamma, dbeta and the conv-bias gradient.  The latter is sum(dx) = scale*sum(g) +
+//           A*sum(x) + Bc*P evaluated from the sums: analytically zero (BatchNorm removes the channel
+//           mean; SURVEY.md par. 2.5), numerically fp32 rounding noise like the reference's value.
+// ------------------------------------------------------------------------------------------
+constexpr int kBn2Threads = 256;
+constexpr int kBn2Rows = kBn2Threads / kSliceGroups;   // 32 output pixels per CTA pass
+
+struct Bn2Plan {
+  int n_slices, n_ranges, pix_per_cta;
+};
+
+static Bn2Plan bn2_plan(long long out_pix, int C) {
+  Bn2Plan pl;
+  pl.n_slices = C / (kSliceGroups * 8);
+  // one resident wave (two CTAs per SM over all slices), at least two 32-pixel passes per CTA
+  long long ranges = (2LL * sm_count()) / pl.n_slices;
+  const long long max_ranges = (out_pix + 2 * kBn2Rows - 1) / (2 * kBn2Rows);
+  if (ranges > max_ranges) ranges = max_ranges;
+  if (ranges < 1) ranges = 1;
+  long long ppc = (out_pix + ranges - 1) / ranges;
+  ppc = (ppc + kBn2Rows - 1) / kBn2Rows * kBn2Rows;
+  pl.pix_per_cta = static_cast<int>(ppc);
+  pl.n_ranges = static_cast<int>((out_pix + ppc - 1) / ppc);
+  return pl;
+}
+
+// Loads one work item: dy of output pixel `opix` and the matching x window (1 pixel, or the 2x2 pooling
+// window whose first pixel index is returned).  32-bit pixel arithmetic (the host checks N*H*W*C < 2^31):
+// the 64-bit divisions of the older kernels cost more instructions than the rest of the item.
+template <bool kPool>
+__device__ __forceinline__ int bn2_load(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                        const BnGeom& g, int opix, int cg, uint4 (&v)[kPool ? 4 : 1], uint4& d) {
+  int base = opix;
+  if (kPool) {
+    const int Ho = g.H >> 1, Wo = g.W >> 1;
+    const int wo = opix % Wo;
+    const int t = opix / Wo;
+    const int ho = t % Ho;
+    const int n = t / Ho;
+    base = (n * g.H + 2 * ho) * g.W + 2 * wo;
+  }
+  d = ldg16(dy + static_cast<size_t>(opix) * g.C + cg * 8);
+#pragma unroll
+  for (int q = 0; q < (kPool ? 4 : 1); ++q)
+    v[q] = ldg16(x + static_cast<size_t>(base + (q >> 1) * g.W + (q & 1)) * g.C + cg * 8);
+  return base;
+}
+
+template <bool kPool>
+__global__ void __launch_bounds__(kBn2Threads, 3)
+bn_bwd2_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                      const float* __restrict__ saved, const float* __restrict__ gamma,
+                      const float* __restrict__ beta, float* __restrict__ sums, float* __restrict__ partials,
+                      BnGeom g, int pix_per_cta, int n_ranges) {
+  constexpr int SC = kSliceGroups * 8;
+  constexpr int kWin = kPool ? 4 : 1;
+  constexpr int kU = kPool ? 2 : 4;      // items in flight per thread
+  __shared__ float s_part[kBn2Threads / 32][2 * SC];
+  __shared__ unsigned int s_last;
+  pdl_launch_dependents();
+  const int slice = blockIdx.x / n_ranges, range = blockIdx.x % n_ranges;
+  const int lg = threadIdx.x % kSliceGroups, prow = threadIdx.x / kSliceGroups;
+  const int cg = slice * kSliceGroups + lg;
+  const int c0 = slice * SC;
+  const int out_pix = g.N * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
+  const int p_begin = range * pix_per_cta;
+  int p_end = p_begin + pix_per_cta;
+  if (p_end > out_pix) p_end = out_pix;
+  pdl_wait();
+  float sc[8], sh[8], a1[8], a2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = cg * 8 + j;
+    const float mean = __ldg(saved + c), rstd = __ldg(saved + g.C + c);
+    sc[j] = __ldg(gamma + c) * rstd;
+    sh[j] = __ldg(beta + c) - mean * sc[j];
+    a1[j] = a2[j] = 0.f;
+  }
+  for (int base = p_begin + prow; base < p_end; base += kBn2Rows * kU) {
+    uint4 v[kU][kWin], d[kU];
+    int ipix[kU];
+    bool ok[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int opix = base + u * kBn2Rows;
+      ok[u] = opix < p_end;
+      if (ok[u]) ipix[u] = bn2_load<kPool>(x, dy, g, opix, cg, v[u], d[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      if (!ok[u]) continue;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float gr, xa;
+        if (!kPool) {
+          xa = bf16_at(v[u][0], j);
+          gr = (fmaf(xa, sc[j], sh[j]) > 0.f) ? bf16_at(d[u], j) : 0.f;
+        } else {
+          float best = 0.f;
+          xa = 0.f;
+          bool hit = false;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float xv = bf16_at(v[u][q], j);
+            const float z = fmaf(xv, sc[j], sh[j]);
+            if (z > best) {
+              best = z;
+              xa = xv;
+              hit = true;
+            }
+          }
+          gr = hit ? bf16_at(d[u], j) : 0.f;
+        }
+        a1[j] += gr;
+        a2[j] = fmaf(gr, xa, a2[j]);
+      }
+    }
+  }
+  // fixed-order tree: lanes l, l^8, l^16 (same channel group), then the 8 warps, then the ranges
+  const int warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    a1[j] += __shfl_xor_sync(0xffffffffu, a1[j], 8);
+    a2[j] += __shfl_xor_sync(0xffffffffu, a2[j], 8);
+    a1[j] += __shfl_xor_sync(0xffffffffu, a1[j], 16);
+    a2[j] += __shfl_xor_sync(0xffffffffu, a2[j], 16);
+  }
+  if (lane_id() < static_cast<uint32_t>(kSliceGroups)) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      s_part[warp][lg * 8 + j] = a1[j];
+      s_part[warp][SC + lg * 8 + j] = a2[j];
+    }
+  }
+  __syncthreads();
+  float* my_partial = partials + (static_cast<long long>(slice) * n_ranges + range) * (2 * SC);
+  if (threadIdx.x < 2 * SC) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kBn2Threads / 32; ++w) t += s_part[w][threadIdx.x];
+    __stcg(my_partial + threadIdx.x, t);
+  }
+  // ticket: the last CTA of this slice to get here folds the slice's partials (in range order)
+  unsigned int* counter = reinterpret_cast<unsigned int*>(sums + 2 * g.C) + slice;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) == static_cast<unsigned int>(n_ranges - 1)) ? 1u : 0u;
+  __syncthreads();
+  if (s_last == 0u) return;
+  __threadfence();
+  // 256 threads: thread t < 128 owns value t over the even ranges, t >= 128 value t-128 over the odd ones
+  {
+    const int val = threadIdx.x % (2 * SC), par = threadIdx.x / (2 * SC);
+    const float* src = partials + static_cast<long long>(slice) * n_ranges * (2 * SC) + val;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    int r = par;
+    for (; r + 14 < n_ranges; r += 16) {
+      float t[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) t[k] = __ldcg(src + static_cast<long long>(r + 2 * k) * (2 * SC));
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += t[k];
+    }
+    for (; r < n_ranges; r += 2) acc[0] += __ldcg(src + static_cast<long long>(r) * (2 * SC));
+    acc[0] += acc[4]; acc[1] += acc[5]; acc[2] += acc[6]; acc[3] += acc[7];
+    s_part[par][val] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * SC) {
+    const int which = threadIdx.x / SC, c = threadIdx.x % SC;
+    sums[which * g.C + c0 + c] = s_part[0][threadIdx.x] + s_part[1][threadIdx.x];
+  }
+  if (threadIdx.x == 0) *counter = 0u;   // ready for the next launch (graph replay)
+}
+
+template <bool kPool>
+__global__ void __launch_bounds__(kBn2Threads, 2)
+bn_bwd2_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                     const float* __restrict__ saved, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx,
+                     float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias, BnGeom g,
+                     int pix_per_cta, int n_ranges) {
+  constexpr int kWin = kPool ? 4 : 1;
+  constexpr int kU = kPool ? 2 : 4;
+  pdl_launch_dependents();
+  const int slice = blockIdx.x / n_ranges, range = blockIdx.x % n_ranges;
+  const int lg = threadIdx.x % kSliceGroups, prow = threadIdx.x / kSliceGroups;
+  const int cg = slice * kSliceGroups + lg;
+  const int out_pix = g.N * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
+  const int p_begin = range * pix_per_cta;
+  int p_end = p_begin + pix_per_cta;
+  if (p_end > out_pix) p_end = out_pix;
+  const float count = static_cast<float>(static_cast<long long>(g.N) * g.H * g.W);
+  const float inv_count = 1.f / count;
+  pdl_wait();
+  float sc[8], sh[8], cA[8], cB[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = cg * 8 + j;
+    const float mean = __ldg(saved + c), rstd = __ldg(saved + g.C + c);
+    sc[j] = __ldg(gamma + c) * rstd;
+    sh[j] = __ldg(beta + c) - mean * sc[j];
+    const float sum_g = __ldcg(sums + c);
+    const float sum_gxhat = rstd * (__ldcg(sums + g.C + c) - mean * sum_g);
+    cA[j] = -sc[j] * rstd * sum_gxhat * inv_count;
+    cB[j] = -sc[j] * sum_g * inv_count - cA[j] * mean;
+    if (range == 0 && prow == 0) {
+      if (dbeta != nullptr) dbeta[c] = sum_g;
+      if (dgamma != nullptr) dgamma[c] = sum_gxhat;
+      // sum over all pixels of dx, from the sums (sum x = mean * count)
+      if (dbias != nullptr) dbias[c] = fmaf(sc[j], sum_g, fmaf(cA[j], mean * count, cB[j] * count));
+    }
+  }
+  for (int base = p_begin + prow; base < p_end; base += kBn2Rows * kU) {
+    uint4 v[kU][kWin], d[kU];
+    int ipix[kU];
+    bool ok[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int opix = base + u * kBn2Rows;
+      ok[u] = opix < p_end;
+      if (ok[u]) ipix[u] = bn2_load<kPool>(x, dy, g, opix, cg, v[u], d[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      if (!ok[u]) continue;
+      if (!kPool) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xv = bf16_at(v[u][0], j);
+          const float gr = (fmaf(xv, sc[j], sh[j]) > 0.f) ? bf16_at(d[u], j) : 0.f;
+          o[j] = fmaf(sc[j], gr, fmaf(cA[j], xv, cB[j]));
+        }
+        store8(dx + static_cast<size_t>(ipix[u]) * g.C + cg * 8, o);
+      } else {
+        int arg[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float best = 0.f;
+          arg[j] = -1;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float z = fmaf(bf16_at(v[u][q], j), sc[j], sh[j]);
+            if (z > best) {
+              best = z;
+              arg[j] = q;
+            }
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float o[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float gr = (arg[j] == q) ? bf16_at(d[u], j) : 0.f;
+            o[j] = fmaf(sc[j], gr, fmaf(cA[j], bf16_at(v[u][q], j), cB[j]));
+          }
+          store8(dx + static_cast<size_t>(ipix[u] + (q >> 1) * g.W + (q & 1)) * g.C + cg * 8, o);
+        }
+      }
+    }
+  }
+}
+
+template <bool kPool>
+static int launch_bn_bwd2(const __nv_bfloat16* x, const __nv_bfloat16* dy, const float* saved, const float* gamma,
+                          const float* beta, float* sums, float* partials, long long partial_elems,
+                          __nv_bfloat16* dx, float* dgamma, float* dbeta, float* dbias, BnGeom g, long long out_pix,
+                          cudaStream_t stream) {
+  const Bn2Plan pl = bn2_plan(out_pix, g.C);
+  const long long need = static_cast<long long>(pl.n_slices) * pl.n_ranges * 2 * kSliceGroups * 8;
+  DDPB_REQUIRE(partials != nullptr && partial_elems >= need,
+               "bn_relu_pool_bwd: the partial-sum buffer holds %lld floats, this shape needs %lld "
+               "(ddpb_bn_bwd_partials_elems)", partial_elems, need);
+  DDPB_REQUIRE(pl.n_slices <= 32, "bn_relu_pool_bwd: at most 2048 channels");
+  DDPB_REQUIRE(static_cast<long long>(g.N) * g.H * g.W * g.C < (1LL << 31), "bn_relu_pool_bwd: tensor too large");
+  const int grid = pl.n_slices * pl.n_ranges;
+  const float* sums_c = sums;
+  DDPB_CHECK_CUDA(launch_pdl(bn_bwd2_reduce_kernel<kPool>, grid, kBn2Threads, 0, stream, x, dy, saved, gamma, beta,
+                             sums, partials, g, pl.pix_per_cta, pl.n_ranges));
+  DDPB_CHECK_CUDA(launch_pdl(bn_bwd2_apply_kernel<kPool>, grid, kBn2Threads, 0, stream, x, dy, saved, gamma, beta,
+                             sums_c, dx, dgamma, dbeta, dbias, g, pl.pix_per_cta, pl.n_ranges));
+  return 0;
+}
+
+// 0: two-kernel path with float atomics (round 1); 1: fused cooperative kernel, one CTA per SM; 2: fused
+// cooperative, up to two CTAs per SM; 3 (default): deterministic two-kernel path above -- falls back to 2
+// when the caller gives no partial-sum buffer
+static int g_bn_fused = 3;
 
 // Tries the fused cooperative kernel; returns -1 if the shape does not fit in shared memory.
 template <bool kPool>
@@ -698,14 +998,25 @@ int bn_relu_pool_fwd_launch(const void* x, const float* stats, const float* gamm
 extern "C" void ddpb_bn_bwd_set_fused(int enabled) { g_bn_fused = enabled; }
 
 // Backward of the fused block.  dy: gradient w.r.t. the (pooled) output, bf16.
-// sums: fp32 scratch of 2*C + 32 floats that MUST be zero on entry (the per-channel sums are
-// accumulated into the first 2*C; the word after them is the fused kernel's grid barrier).
+// sums: fp32 scratch of 2*C + 32 floats that MUST be zero on entry (per-channel sums in the first
+// 2*C; the words after them are ticket counters / the cooperative kernel's grid barrier.  The default
+// path leaves the counters zero again, the older paths do not).
+// partials / partial_elems: scratch of ddpb_bn_bwd_partials_elems() floats for the default
+// deterministic path (no zeroing needed); null selects the cooperative kernel of round 1.
 // dx: [N*H*W][C] bf16 gradient w.r.t. the raw conv output.  dgamma/dbeta/dbias: fp32 [C]
-// (dbias may be null; it is cleared by pass 1 and accumulated by pass 2).
+// (dbias may be null).
+// Floats of partial-sum scratch the default (deterministic two-kernel) backward wants for this shape.
+extern "C" long long ddpb_bn_bwd_partials_elems(int N, int H, int W, int C, int pool) {
+  if (C <= 0 || C % (kSliceGroups * 8) != 0) return 0;
+  const long long out_pix = static_cast<long long>(N) * (pool ? H / 2 : H) * (pool ? W / 2 : W);
+  const Bn2Plan pl = bn2_plan(out_pix, C);
+  return static_cast<long long>(pl.n_slices) * pl.n_ranges * 2 * kSliceGroups * 8;
+}
+
 extern "C" int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float* saved, const float* gamma,
                                      const float* beta, float* sums, void* dx, float* dgamma, float* dbeta,
-                                     float* dbias, int N, int H, int W, int C, int pool, float eps,
-                                     cudaStream_t stream) {
+                                     float* dbias, float* partials, long long partial_elems, int N, int H, int W,
+                                     int C, int pool, float eps, cudaStream_t stream) {
   DDPB_BN_CHECK_GEOM("bn_relu_pool_bwd");
   BnGeom g{N, H, W, C, pool, eps};
   DDPB_REQUIRE((C / 8) <= kBnThreads && kBnThreads % (C / 8) == 0,
@@ -715,6 +1026,13 @@ extern "C" int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float*
   const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
   const __nv_bfloat16* dyb = static_cast<const __nv_bfloat16*>(dy);
   __nv_bfloat16* dxb = static_cast<__nv_bfloat16*>(dx);
+  if (g_bn_fused >= 3 && partials != nullptr && C % (kSliceGroups * 8) == 0) {
+    const long long out_pix = items / (C / 8);
+    return pool ? launch_bn_bwd2<true>(xb, dyb, saved, gamma, beta, sums, partials, partial_elems, dxb, dgamma, dbeta,
+                                       dbias, g, out_pix, stream)
+                : launch_bn_bwd2<false>(xb, dyb, saved, gamma, beta, sums, partials, partial_elems, dxb, dgamma, dbeta,
+                                        dbias, g, out_pix, stream);
+  }
   if (g_bn_fused) {
     const int rc = pool ? launch_bn_bwd_fused<true>(xb, dyb, saved, gamma, beta, sums, dxb, dgamma, dbeta, dbias, g,
                                                     items, stream)

@@ -101,6 +101,36 @@ extern "C" int ddpb_stamp(unsigned long long* slot, cudaStream_t stream) {
   return 0;
 }
 
+namespace ddpb {
+// One thread: bump a device-side sequence number and store {sequence, value bits} as ONE 8-byte word
+// into mapped pinned host memory.  The host polls that word: when the sequence number it expects
+// shows up, the value next to it is the one written with it (an aligned 8-byte store reaches host
+// memory as one transaction).  Lets a training loop read every step's loss without a D2H copy call
+// or a stream synchronisation, and without waiting for the rest of the step (the loss is known
+// after the classifier, long before backward ends).
+__global__ void publish_scalar_kernel(const float* __restrict__ value, unsigned int* __restrict__ dev_seq,
+                                      unsigned long long* host_slot) {
+  const unsigned int seq = *dev_seq + 1u;
+  *dev_seq = seq;
+  const unsigned long long word =
+      (static_cast<unsigned long long>(seq) << 32) | static_cast<unsigned long long>(__float_as_uint(*value));
+  asm volatile("st.global.relaxed.sys.u64 [%0], %1;" ::"l"(host_slot), "l"(word) : "memory");
+  __threadfence_system();
+}
+}  // namespace ddpb
+
+// value: device fp32 scalar; dev_seq: device counter (starts at 0, owned by the caller); host_slot:
+// 8-byte aligned word in pinned (mapped) host memory, device-accessible address.  After this point of
+// the stream has executed, *host_slot == (new sequence number << 32) | bits of *value.
+extern "C" int ddpb_publish_scalar(const float* value, unsigned int* dev_seq, unsigned long long* host_slot,
+                                   cudaStream_t stream) {
+  DDPB_REQUIRE(value != nullptr && dev_seq != nullptr && host_slot != nullptr, "publish_scalar: null argument");
+  DDPB_REQUIRE(reinterpret_cast<uintptr_t>(host_slot) % 8 == 0, "publish_scalar: host slot must be 8-byte aligned");
+  ddpb::publish_scalar_kernel<<<1, 1, 0, stream>>>(value, dev_seq, host_slot);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // Programmatic dependent launch between consecutive kernels: 1 on (default), 0 off.
 extern "C" void ddpb_set_pdl(int on) { ddpb::g_pdl = on ? 1 : 0; }
 extern "C" int ddpb_get_pdl() { return ddpb::pdl_enabled() ? 1 : 0; }

@@ -200,6 +200,12 @@ class VGGEngine:
                     need_f = max(need_f, K.conv_fprop_scratch_elems(n, L.H, L.W, L.c_out, L.c_in, 9))
         self.wgrad_scratch = torch.empty(need_w, **f32)
         self.fprop_scratch = torch.empty(need_f, **f32)
+        # --- partial sums of the BatchNorm backward (one buffer, the layers run one after the other)
+        need_p = 1
+        for L in self.layers:
+            for n in {B, max(1, B // 2), max(1, B // 4), 1} | set(range(1, B + 1, max(1, B // 16))):
+                need_p = max(need_p, K.bn_bwd_partials_elems(n, L.H, L.W, L.c_out, L.pool))
+        self.bn_partials = torch.empty(need_p + 8192, **f32)
         self.image_hw = image_hw
         self._tl = None
         self._tl_labels = []
@@ -313,7 +319,7 @@ class VGGEngine:
             K.bn_relu_pool_bwd(self.conv_out[li], self.dact[li], self.saved[li], a.flat_master(L.p_g),
                                a.flat_master(L.p_beta), N, L.H, L.W, L.c_out, L.pool, sums=self.bsums[li],
                                dx=self.dconv[li], dgamma=a.flat_grad(L.p_g), dbeta=a.flat_grad(L.p_beta),
-                               dbias=a.flat_grad(L.p_b))
+                               dbias=a.flat_grad(L.p_b), partials=self.bn_partials)
             self.mark(f"L{li} bn bwd")
             cols = 9 * L.c_in
             if side_stream is not None:
@@ -361,10 +367,7 @@ class VGGEngine:
                 n += 2              # split-K finalize + separate BatchNorm forward
             if li > 0 and K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_out, L.c_in, 9):
                 n += 1
-            # bn bwd: one cooperative kernel when the layer's data fits in shared memory, else two passes
-            slot = 5 if L.pool else 2
-            out_pix = B * L.H * L.W // (4 if L.pool else 1)
-            n += 1 if out_pix * (L.c_out // 8) * slot * 16 <= K.sm_count() * 200 * 1024 else 2
+            n += 2                  # BatchNorm backward: reduce + apply
             n += 1                  # wgrad
             if K.conv_wgrad_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps):
                 n += 1              # split-K reduce

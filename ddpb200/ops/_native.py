@@ -44,9 +44,11 @@ _SIGNATURES = {
     "ddpb_bn_relu_pool_fwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int,
                               c_float, c_void],
     "ddpb_bn_relu_pool_bwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void,
-                              c_int, c_int, c_int, c_int, c_int, c_float, c_void],
+                              c_void, c_ll, c_int, c_int, c_int, c_int, c_int, c_float, c_void],
+    "ddpb_bn_bwd_partials_elems": [c_int, c_int, c_int, c_int, c_int],
     "ddpb_bn_bwd_set_fused": [c_int],
     "ddpb_stamp": [c_void, c_void],
+    "ddpb_publish_scalar": [c_void, c_void, c_void, c_void],
     "ddpb_conv_wgrad_set_mode": [c_int],
     "ddpb_set_pdl": [c_int],
     "ddpb_get_pdl": [],

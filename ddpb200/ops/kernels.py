@@ -194,6 +194,14 @@ def stamp(slot: torch.Tensor, stream=None) -> None:
     nat.check(nat.load().ddpb_stamp(nat.ptr(slot), _s(stream)), "ddpb_stamp")
 
 
+def publish_scalar(value: torch.Tensor, dev_seq: torch.Tensor, host_slot: torch.Tensor, stream=None) -> None:
+    """Stores (++dev_seq << 32 | bits of value) into ``host_slot`` (pinned int64[1]) from the device."""
+    assert value.is_cuda and value.dtype == torch.float32 and dev_seq.is_cuda and dev_seq.dtype == torch.int32
+    assert host_slot.is_pinned() and host_slot.dtype == torch.int64
+    nat.check(nat.load().ddpb_publish_scalar(nat.ptr(value), nat.ptr(dev_seq), nat.ptr(host_slot), _s(stream)),
+              "ddpb_publish_scalar")
+
+
 def sm_count() -> int:
     return int(nat.load().ddpb_sm_count())
 
@@ -210,19 +218,31 @@ def get_pdl() -> bool:
 
 
 def bn_bwd_set_fused(mode: bool | int) -> None:
-    """0/False: two-kernel BatchNorm backward; 1: fused cooperative kernel with one CTA per SM
-    (room for a co-resident gradient-sync CTA); 2/True... default is 2: up to two CTAs per SM."""
+    """3 (default): two ordinary kernels, fixed-order sums (deterministic, no float atomics);
+    2/True: fused cooperative kernel, up to two CTAs per SM; 1: same with one CTA per SM;
+    0/False: the two-pass kernels with float atomics of round 1."""
     nat.load().ddpb_bn_bwd_set_fused(2 if mode is True else int(mode))
 
 
+def bn_bwd_partials_elems(N, H, W, C_, pool: bool) -> int:
+    return int(nat.load().ddpb_bn_bwd_partials_elems(N, H, W, C_, int(pool)))
+
+
 def bn_relu_pool_bwd(x, dy, saved, gamma, beta, N, H, W, C_, pool: bool, *, sums=None, dx=None, dgamma=None,
-                     dbeta=None, dbias=None, eps=BN_EPS, stream=None):
-    """O5+O6+O7 backward.  ``sums`` (fp32, 2*C + 32 elements) must be zero on entry."""
+                     dbeta=None, dbias=None, partials: torch.Tensor | None | bool = True, eps=BN_EPS, stream=None):
+    """O5+O6+O7 backward.  ``sums`` (fp32, 2*C + 32 elements) must be zero on entry.  ``partials``:
+    fp32 scratch of bn_bwd_partials_elems() for the deterministic default path (True = allocate,
+    None/False = use the cooperative one-kernel variant)."""
     nat.require_cuda(x, dy, saved, gamma, beta)
     dev = x.device
     if sums is None:
         sums = torch.zeros(2 * C_ + 32, dtype=torch.float32, device=dev)
     assert sums.numel() >= 2 * C_ + 32, "bn backward scratch needs 2*C + 32 zeroed floats"
+    if partials is True:
+        need = bn_bwd_partials_elems(N, H, W, C_, pool)
+        partials = torch.empty(need, dtype=torch.float32, device=dev) if need else None
+    elif partials is False:
+        partials = None
     if dx is None:
         dx = torch.empty(N * H * W, C_, dtype=torch.bfloat16, device=dev)
     if dgamma is None:
@@ -231,7 +251,8 @@ def bn_relu_pool_bwd(x, dy, saved, gamma, beta, N, H, W, C_, pool: bool, *, sums
         dbeta = torch.empty(C_, dtype=torch.float32, device=dev)
     rc = nat.load().ddpb_bn_relu_pool_bwd(nat.ptr(x), nat.ptr(dy), nat.ptr(saved), nat.ptr(gamma), nat.ptr(beta),
                                           nat.ptr(sums), nat.ptr(dx), nat.ptr(dgamma), nat.ptr(dbeta),
-                                          nat.ptr(dbias), N, H, W, C_, int(pool), eps, _s(stream))
+                                          nat.ptr(dbias), nat.ptr(partials), _numel(partials), N, H, W, C_, int(pool),
+                                          eps, _s(stream))
     nat.check(rc, "ddpb_bn_relu_pool_bwd")
     return dx, dgamma, dbeta
 

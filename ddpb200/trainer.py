@@ -139,9 +139,6 @@ class Trainer:
             # per step with it, 0.831 without; profiles/r1_call45_*)
             K.set_pdl(not (self.distributed and self.mode == "ddp"))
         if self.distributed and self.mode == "ddp":
-            # fused BatchNorm backward is a cooperative launch: with two CTAs per SM it fills the
-            # register file and would have to wait for every overlapped reduction to finish
-            K.bn_bwd_set_fused(1)
             self._broadcast_parameters()
 
     def _broadcast_parameters(self):

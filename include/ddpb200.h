@@ -27,6 +27,11 @@ int ddpb_get_pdl(void);
 /* Diagnostics: a one-thread kernel writes %globaltimer (ns) to *slot at this point of the stream. */
 int ddpb_stamp(unsigned long long* slot, void* stream);
 
+/* Loss read-back without a copy call (part1/main.py:80 reads loss.item() every iteration, SURVEY.md
+ * Q8): a one-thread kernel bumps *dev_seq and stores (sequence << 32 | bits of *value) as one 8-byte
+ * word into pinned host memory; the host polls the word for the sequence number it expects. */
+int ddpb_publish_scalar(const float* value, unsigned int* dev_seq, unsigned long long* host_slot, void* stream);
+
 /* ---- convolution (K1, K2, K5, K6) ----------------------------------------------------------- */
 /* O1: nn.Conv2d(3x3, stride 1, pad 1, bias) forward, part1/model.py:18-23.
  * y[N*H*W][C_out] = conv(x[N][H][W][C_in], w[C_out][taps*C_in]) (+bias), bf16 out.
@@ -107,10 +112,17 @@ void ddpb_conv_debug_mode(int mode);   /* timing probes, wrong results: bit 0 sk
 int ddpb_channel_stats(const void* x, float* stats, long long P, int C, void* stream);
 int ddpb_bn_relu_pool_fwd(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
                           float* saved_mean_rstd, int N, int H, int W, int C, int pool, float eps, void* stream);
-/* O5+O6+O7 backward.  sums: fp32 scratch of 2*C + 32 floats that must be ZERO on entry. */
+/* O5+O6+O7 backward.  sums: fp32 scratch of 2*C + 32 floats that must be ZERO on entry.  partials:
+ * ddpb_bn_bwd_partials_elems() floats of scratch (contents irrelevant) for the default path: two
+ * ordinary kernels, every sum taken in a fixed order (dgamma / dbeta bitwise reproducible, no float
+ * atomics), dbias evaluated from the sums.  partials == null: the cooperative one-kernel variant.
+ * ddpb_bn_bwd_set_fused: 3 default, 2 / 1 cooperative (two / one CTA per SM), 0 two-pass with atomics. */
 int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float* saved_mean_rstd, const float* gamma,
-                          const float* beta, float* sums, void* dx, float* dgamma, float* dbeta, float* dbias, int N,
-                          int H, int W, int C, int pool, float eps, void* stream);
+                          const float* beta, float* sums, void* dx, float* dgamma, float* dbeta, float* dbias,
+                          float* partials, long long partial_elems, int N, int H, int W, int C, int pool, float eps,
+                          void* stream);
+long long ddpb_bn_bwd_partials_elems(int N, int H, int W, int C, int pool);
+void ddpb_bn_bwd_set_fused(int mode);
 
 /* ---- classifier + loss (K7, K8, K15) --------------------------------------------------------- */
 /* O9+O10+O15: Linear(512,10) + CrossEntropyLoss(mean) + top-1, part1/model.py:40,45,

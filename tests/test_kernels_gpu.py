@@ -187,11 +187,13 @@ def test_conv_wgrad_first_layer_compact():
     assert _rel_err(dw, ref) < 2e-3
 
 
-@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("fused", [3, 2, 0])
 @pytest.mark.parametrize("pool", [False, True])
-@pytest.mark.parametrize("geom", [(8, 32, 32, 64), (8, 8, 8, 256), (16, 2, 2, 512), (64, 16, 16, 128)])
+@pytest.mark.parametrize("geom", [(8, 32, 32, 64), (8, 8, 8, 256), (16, 2, 2, 512), (64, 16, 16, 128), (5, 4, 4, 512),
+                                  (256, 2, 2, 512)])
 def test_bn_relu_pool_fwd_bwd(geom, pool, fused):
-    """fused=True: single cooperative kernel (slice parked in shared memory); False: two passes."""
+    """fused=3 (default): two ordinary kernels with fixed-order sums; 2: single cooperative kernel (slice
+    parked in shared memory); 0: two passes with float atomics."""
     N, H, W, C = geom
     K.bn_bwd_set_fused(fused)
     x = (torch.randn(N * H * W, C, device=DEV) * 1.5 + 0.3).bfloat16()
@@ -205,12 +207,19 @@ def test_bn_relu_pool_fwd_bwd(geom, pool, fused):
     Po = y.shape[0]
     dy = torch.randn(Po, C, device=DEV).bfloat16()
     dbias = torch.full((C,), 7.0, device=DEV)
-    dx, dgamma, dbeta = K.bn_relu_pool_bwd(x, dy, saved, gamma, beta, N, H, W, C, pool, dbias=dbias)
+    sums = torch.zeros(2 * C + 32, device=DEV)
+    dx, dgamma, dbeta = K.bn_relu_pool_bwd(x, dy, saved, gamma, beta, N, H, W, C, pool, dbias=dbias, sums=sums)
     rdx, rdg, rdb = R.bn_relu_pool_bwd(x, dy, gamma, beta, N, H, W, pool)
     assert _rel_err(dx, rdx) < 2e-2
     assert _rel_err(dgamma, rdg) < 5e-3
     assert _rel_err(dbeta, rdb) < 5e-3
-    K.bn_bwd_set_fused(True)
+    if fused == 3:
+        # fixed summation order: bitwise reproducible, and the ticket counters are left at zero so the
+        # same scratch serves the next launch (CUDA-graph replay) without a memset
+        assert int(sums[2 * C:].view(torch.int32).abs().sum()) == 0
+        dx2, dg2, db2 = K.bn_relu_pool_bwd(x, dy, saved, gamma, beta, N, H, W, C, pool, sums=sums)
+        assert torch.equal(dx, dx2) and torch.equal(dgamma, dg2) and torch.equal(dbeta, db2)
+    K.bn_bwd_set_fused(3)
     # conv-bias gradient = column sums of dx: mathematically zero (SURVEY.md §2.5 numerics note)
     assert dbias.abs().max().item() < 1e-2 * dy.float().abs().sum(0).max().item()
 
