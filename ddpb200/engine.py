@@ -286,7 +286,7 @@ class VGGEngine:
                         self.labels[:N], logits=self.logits, row_loss=self.row_loss)
         self.mark("fc fwd")
 
-    def backward(self, N: int, after_layer=None, side_stream=None, reduce_loss: bool = False):
+    def backward(self, N: int, after_layer=None, side_stream=None, reduce_loss: bool = False, on_loss_ready=None):
         """dlogits[:N] -> every gradient in the arena.
 
         ``reduce_loss``: the classifier's backward kernel also writes ``loss`` / ``correct`` from
@@ -311,6 +311,8 @@ class VGGEngine:
                  **(dict(row_loss=self.row_loss[:N], row_correct=self.row_correct[:N], loss=self.loss,
                          correct=self.correct) if reduce_loss else {}))
         self.mark("fc bwd")
+        if on_loss_ready is not None:
+            on_loss_ready()             # ``loss`` / ``correct`` are final from here on (reduce_loss)
         if after_layer is not None:
             after_layer(last + 1, [])   # the classifier is parameter group len(layers)
         for li in range(last, -1, -1):

@@ -117,15 +117,29 @@ def train_model(model, *args, rank: int | None = None, world_size: int | None = 
     device = trainer.device
     running_loss = 0.0
     total_time = 0
-    for batch_idx, (data, target, aug) in enumerate(_batches(train_loader)):
+    # The loop keeps the reference's shape (timer after the batch is fetched, loss read every iteration,
+    # Q6/Q8) but is software pipelined on CUDA: while step i computes, the host gathers batch i+1 and
+    # its host->device copy runs on the copy stream (Trainer.prefetch); the loss comes back through
+    # pinned memory (Trainer.last_loss) without draining the stream.
+    batches = _batches(train_loader)
+    nxt = next(batches, None)
+    if nxt is not None and device.type == "cuda":
+        trainer.prefetch(*nxt)
+    batch_idx = -1
+    while nxt is not None:
+        batch_idx += 1
         if max_iters is not None and batch_idx >= max_iters:
             break
+        data, target, aug = nxt
         start_time = time.perf_counter_ns()
         if device.type != "cuda":
             data, target = data.to(device), target.to(device)
         # zero_grad / forward / loss / backward / [sync] / optimizer.step, fused
-        loss = trainer.step(data, target, aug)
-        running_loss += loss.item()
+        trainer.step(data, target, aug)
+        nxt = next(batches, None)
+        if nxt is not None and device.type == "cuda" and (max_iters is None or batch_idx + 1 < max_iters):
+            trainer.prefetch(*nxt)
+        running_loss += trainer.last_loss()
         if batch_idx % 20 == 19:
             print(f"[{epoch + 1}, {batch_idx + 1:5d}] loss: {running_loss / 20:.3f}")
             running_loss = 0.0

@@ -127,10 +127,23 @@ class Trainer:
         self.update_stream = torch.cuda.Stream(device=self.device) if self.overlap_sgd else None
         B = self.batch_size
         hw = self.engine.image_hw
-        self.in_u8 = torch.zeros(B, hw, hw, 3, dtype=torch.uint8, device=self.device)
-        self.in_aug = torch.zeros(B, 4, dtype=torch.int8, device=self.device)
-        self.in_f32 = torch.zeros(B, 3, hw, hw, dtype=torch.float32, device=self.device)
+        # Two staging sets alternate between steps, so the host->device copy of batch i+1 (issued by
+        # prefetch() on the copy stream) runs while step i computes.  The fp32 staging buffer is only
+        # allocated when a float batch shows up.  Set 2 belongs to evaluate().
+        self._stage = [dict(u8=torch.zeros(B, hw, hw, 3, dtype=torch.uint8, device=self.device),
+                            aug=torch.zeros(B, 4, dtype=torch.int8, device=self.device), f32=None,
+                            labels=torch.zeros(B, dtype=torch.int64, device=self.device),
+                            ready=None, free=None) for _ in range(3)]
+        self._slot = 0              # staging set the NEXT step reads
+        self._pending = None        # (slot, kind, with_aug, N, data object) filled by prefetch()
+        self.copy_stream = torch.cuda.Stream(device=self.device)
         self._capture_stream = torch.cuda.Stream(device=self.device)
+        # every step's loss is published to pinned host memory by a one-thread kernel right after the
+        # classifier (sequence number + value in one 8-byte word): last_loss() polls it instead of
+        # issuing a D2H copy and draining the stream
+        self._loss_host = torch.zeros(1, dtype=torch.int64).pin_memory()
+        self._loss_seq = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._steps_published = 0
         from .ops import kernels as K
 
         if os.environ.get("DDPB_PDL") is None:
@@ -140,6 +153,14 @@ class Trainer:
             K.set_pdl(not (self.distributed and self.mode == "ddp"))
         if self.distributed and self.mode == "ddp":
             self._broadcast_parameters()
+
+    @property
+    def in_u8(self):
+        return self._stage[self._slot]["u8"]
+
+    @property
+    def in_aug(self):
+        return self._stage[self._slot]["aug"]
 
     def _broadcast_parameters(self):
         """DDP's constructor-time parameter broadcast from rank 0, via the arena."""
@@ -156,6 +177,22 @@ class Trainer:
     def _sgd_args(self):
         a = self.engine.arena
         return (a.master, a.momentum, self.engine.shadow, self.lr, self.momentum, self.weight_decay)
+
+    def _publish_loss(self):
+        """Enqueued right after the classifier's backward kernel (which also reduces the loss): a
+        one-thread kernel on the weight-gradient branch stores the loss into pinned host memory."""
+        from .ops import kernels as K
+
+        main = torch.cuda.current_stream()
+        side = self.wgrad_stream
+        if side is None:
+            K.publish_scalar(self.engine.loss, self._loss_seq, self._loss_host)
+            return
+        ev = torch.cuda.Event()
+        ev.record(main)
+        side.wait_event(ev)
+        with torch.cuda.stream(side):
+            K.publish_scalar(self.engine.loss, self._loss_seq, self._loss_host)
 
     def _sgd_slice(self, off: int, n: int):
         """Plain (local) SGD update of arena range [off, off + n) on the current stream."""
@@ -174,17 +211,19 @@ class Trainer:
             self.symm.allreduce_avg(off, n, blocks=self.comm_blocks, slot_base=slot_base, use_mc=self.use_mc, sgd=sgd,
                                     stream=stream)
 
-    def _enqueue_iteration(self, kind: str, with_aug: bool, B: int | None = None):
+    def _enqueue_iteration(self, kind: str, with_aug: bool, B: int | None = None, slot: int = 0):
         """Everything between 'inputs are on the device' and 'parameters are updated'."""
         eng, a = self.engine, self.engine.arena
         B = self.batch_size if B is None else B
+        st = self._stage[slot]
+        eng.labels = st["labels"]
         # the input kernel also refreshes the first layer's padded filter pack; every other conv
         # operand is the SGD-maintained shadow
         eng.mark("step begin", reset=True)
         if kind == "u8":
-            eng.load_input_u8(self.in_u8[:B], self.in_aug[:B] if with_aug else None, pack=True)
+            eng.load_input_u8(st["u8"][:B], st["aug"][:B] if with_aug else None, pack=True)
         else:
-            eng.load_input_f32(self.in_f32[:B], pack=True)
+            eng.load_input_f32(st["f32"][:B], pack=True)
         eng.forward(B, with_loss=True, defer_loss=True)
         if not self.distributed:
             if self.overlap_sgd and self.update_stream is not None:
@@ -205,13 +244,13 @@ class Trainer:
                         self._sgd_slice(off, n)
                         eng.mark(f"sgd group {gi} (side)")
 
-                eng.backward(B, after_layer=after_layer, side_stream=self.wgrad_stream, reduce_loss=True)
+                eng.backward(B, on_loss_ready=self._publish_loss, after_layer=after_layer, side_stream=self.wgrad_stream, reduce_loss=True)
                 done = torch.cuda.Event()
                 done.record(upd)
                 main.wait_event(done)
                 eng.mark("sgd joined")
             else:
-                eng.backward(B, side_stream=self.wgrad_stream, reduce_loss=True)
+                eng.backward(B, on_loss_ready=self._publish_loss, side_stream=self.wgrad_stream, reduce_loss=True)
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
         elif self.mode == "ddp":
             # Early buckets: reduction only, few CTAs, on the side stream while backward continues.
@@ -241,7 +280,7 @@ class Trainer:
                         # update it now (a local kernel, no peer waits), not in the tail after backward
                         self._sgd_slice(off, n)
 
-            eng.backward(B, after_layer=after_layer, side_stream=self.wgrad_stream, reduce_loss=True)
+            eng.backward(B, on_loss_ready=self._publish_loss, after_layer=after_layer, side_stream=self.wgrad_stream, reduce_loss=True)
             done = torch.cuda.Event()
             done.record(self.comm_stream)
             main.wait_event(done)
@@ -254,7 +293,7 @@ class Trainer:
             if not self.fuse_sgd:
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
         else:
-            eng.backward(B, side_stream=self.wgrad_stream, reduce_loss=True)
+            eng.backward(B, on_loss_ready=self._publish_loss, side_stream=self.wgrad_stream, reduce_loss=True)
             if self.granularity == "param":
                 # one launch per parameter tensor, like the reference's python loop
                 for i in range(len(a.params)):
@@ -265,21 +304,46 @@ class Trainer:
             if not self.fuse_sgd:
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
 
-    def _stage_inputs(self, data: torch.Tensor, target: torch.Tensor, aug):
-        eng = self.engine
+    def _copy_into(self, slot: int, data: torch.Tensor, target: torch.Tensor, aug):
+        """Enqueues the copies of one batch into staging set ``slot`` on the CURRENT stream."""
+        st = self._stage[slot]
         N = data.shape[0]
         if N > self.batch_size or N < 1:
             raise ValueError(f"Trainer was built for batches of up to {self.batch_size}, got {N}")
         if data.dtype == torch.uint8:
-            self.in_u8[:N].copy_(data, non_blocking=True)
+            st["u8"][:N].copy_(data, non_blocking=True)
             if aug is not None:
-                self.in_aug[:N].copy_(aug, non_blocking=True)
+                st["aug"][:N].copy_(aug, non_blocking=True)
             kind = "u8"
         else:
-            self.in_f32[:N].copy_(data, non_blocking=True)
+            if st["f32"] is None:
+                hw = self.engine.image_hw
+                for t in self._stage:
+                    t["f32"] = torch.zeros(self.batch_size, 3, hw, hw, dtype=torch.float32, device=self.device)
+            st["f32"][:N].copy_(data, non_blocking=True)
             kind = "f32"
-        eng.labels[:N].copy_(target, non_blocking=True)
+        st["labels"][:N].copy_(target, non_blocking=True)
         return kind
+
+    def prefetch(self, data: torch.Tensor, target: torch.Tensor, aug: torch.Tensor | None = None) -> None:
+        """Starts the host->device copy of the NEXT step's batch on the copy stream, into the staging
+        set the running step does not use; the next ``step()`` (called with the same tensors or with
+        no arguments) only waits for that copy.  Call it right after ``step()``: the copy then runs
+        while the GPU computes.  Pinned host tensors make the copy asynchronous."""
+        if self.device.type != "cuda":
+            self._pending = (None, data, target, aug)
+            return
+        slot = self._slot
+        st = self._stage[slot]
+        cs = self.copy_stream
+        if st["free"] is not None:
+            cs.wait_event(st["free"])      # the step that last read this set has finished
+        with torch.cuda.stream(cs):
+            kind = self._copy_into(slot, data, target, aug)
+            ready = torch.cuda.Event()
+            ready.record(cs)
+        st["ready"] = ready
+        self._pending = (slot, kind, aug is not None, data.shape[0], data)
 
     def set_hyperparameters(self, lr: float | None = None, momentum: float | None = None,
                             weight_decay: float | None = None) -> None:
@@ -303,39 +367,80 @@ class Trainer:
             g = src.param_groups[0]
             self.set_hyperparameters(g["lr"], g.get("momentum", 0.0), g.get("weight_decay", 0.0))
 
-    def step(self, data: torch.Tensor, target: torch.Tensor, aug: torch.Tensor | None = None) -> torch.Tensor:
+    def step(self, data: torch.Tensor | None = None, target: torch.Tensor | None = None,
+             aug: torch.Tensor | None = None) -> torch.Tensor:
         """One training iteration.  ``data`` is either raw uint8 NHWC pixels (plus optional
         per-image crop/flip parameters ``aug``) or a normalised fp32 NCHW batch, on the host
-        (ideally pinned) or on the device.  Returns the mean loss as a 0-d device tensor that is
-        overwritten by the next call."""
+        (ideally pinned) or on the device; without arguments (or with the very tensors given to
+        ``prefetch``) the prefetched batch is used.  Returns the mean loss as a 0-d device tensor
+        that is overwritten by the next call; ``last_loss()`` gives the same number on the host
+        without a copy or a stream synchronisation."""
         self._refresh_hyper()
         if self.device.type != "cuda":
+            if data is None:
+                _, data, target, aug = self._pending
+            self._pending = None
             return self._step_cpu(data, target, aug)
-        kind = self._stage_inputs(data, target, aug)
-        with_aug = aug is not None
-        key = f"{kind}:{int(with_aug)}"
-        N = data.shape[0]
+        main = torch.cuda.current_stream()
+        pend, self._pending = self._pending, None
+        if pend is not None and (data is None or data is pend[4]):
+            slot, kind, with_aug, N, _ = pend
+            main.wait_event(self._stage[slot]["ready"])
+        else:
+            if data is None:
+                raise ValueError("step() without arguments needs a preceding prefetch()")
+            slot = self._slot
+            kind = self._copy_into(slot, data, target, aug)
+            with_aug, N = aug is not None, data.shape[0]
+        key = f"{kind}:{int(with_aug)}:{slot}"
         if not self.use_graph or N != self.batch_size:
             # ragged last batch of an epoch (or graphs disabled): plain launches
-            self._enqueue_iteration(kind, with_aug, N)
+            self._enqueue_iteration(kind, with_aug, N, slot)
         else:
             g = self._graphs.get(key)
             if g is None:
-                g = self._capture(key, kind, with_aug)
+                g = self._capture(key, kind, with_aug, slot)
             else:
                 g.replay()
+        free = torch.cuda.Event()
+        free.record(main)
+        self._stage[slot]["free"] = free
+        self._slot = slot ^ 1
+        self._steps_published += 1
         self.iteration += 1
         return self.engine.loss
 
-    def _capture(self, key, kind, with_aug):
+    def last_loss(self) -> float:
+        """Mean loss of the most recent ``step()`` on the host.  The step itself stores it into pinned
+        host memory right after the classifier, so this returns as soon as that store has landed --
+        typically while the step's backward pass is still running -- instead of draining the
+        stream like ``loss.item()`` (/root/reference/part1/main.py:80 reads the loss every iteration)."""
+        if self.device.type != "cuda":
+            return float(self._cpu_last_loss)
+        import struct
+        import time
+
+        want = self._steps_published & 0xFFFFFFFF
+        view = self._loss_host.numpy()
+        t0 = None
+        while True:
+            word = int(view[0]) & 0xFFFFFFFFFFFFFFFF
+            if (word >> 32) == want:
+                return struct.unpack("<f", struct.pack("<I", word & 0xFFFFFFFF))[0]
+            if t0 is None:
+                t0 = time.perf_counter()
+            elif time.perf_counter() - t0 > 120.0:
+                raise RuntimeError("last_loss(): the step did not publish its loss within 120 s")
+
+    def _capture(self, key, kind, with_aug, slot):
         # The first call runs eagerly (it also performs one-time kernel attribute set-up) and
         # IS the iteration; the graph is captured afterwards from a snapshot-free sequence: the
         # capture itself executes nothing.
-        self._enqueue_iteration(kind, with_aug)
+        self._enqueue_iteration(kind, with_aug, None, slot)
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=self._capture_stream):
-            self._enqueue_iteration(kind, with_aug)
+            self._enqueue_iteration(kind, with_aug, None, slot)
         self._graphs[key] = g
         return g
 
@@ -351,13 +456,13 @@ class Trainer:
             raise ValueError("evaluation batch larger than the engine was sized for")
         # pack=True: the first layer's padded filter pack is refreshed by the input kernel; after a
         # training step it still holds the filters from BEFORE that step's update
-        eng.labels[:N].copy_(target, non_blocking=True)
-        if data.dtype == torch.uint8:
-            self.in_u8[:N].copy_(data, non_blocking=True)
-            eng.load_input_u8(self.in_u8[:N], None, pack=True)
+        kind = self._copy_into(2, data, target, None)      # evaluation has its own staging set
+        st = self._stage[2]
+        eng.labels = st["labels"]
+        if kind == "u8":
+            eng.load_input_u8(st["u8"][:N], None, pack=True)
         else:
-            self.in_f32[:N].copy_(data, non_blocking=True)
-            eng.load_input_f32(self.in_f32[:N], pack=True)
+            eng.load_input_f32(st["f32"][:N], pack=True)
         eng.forward(N, with_loss=True, want_dlogits=False)
         return eng.loss.clone(), eng.correct.clone()
 
@@ -417,6 +522,7 @@ class Trainer:
                 self.reducer.finalize()
         self.optimizer.step()
         self.iteration += 1
+        self._cpu_last_loss = float(loss.detach())
         return loss.detach()
 
     def _evaluate_cpu(self, data, target):

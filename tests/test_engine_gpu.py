@@ -313,3 +313,36 @@ def test_scratch_is_sized_for_every_batch_up_to_the_maximum():
     img, lab = _batch(232, seed=9)
     l = tr.step(img, lab).item()        # 1000 % 256 = 232: one of the sizes that used to overrun
     assert l == l
+
+
+def test_prefetch_and_published_loss_match_the_plain_call():
+    """Trainer.prefetch / step() / last_loss(): the software-pipelined loop of train_model gives the same
+    losses and parameters as step(data, target, aug) + loss.item(), batch by batch."""
+    batches = [tuple(t.pin_memory() for t in _batch(32, seed=s)) for s in range(5)]
+
+    def run(pipelined):
+        torch.manual_seed(11)
+        model = ddpb200.VGG11().to(DEV)
+        tr = ddpb200.Trainer(model, mode="single", batch_size=32, lr=0.02)
+        out = []
+        if pipelined:
+            tr.prefetch(*batches[0])
+        for i, (img, lab) in enumerate(batches):
+            if pipelined:
+                dev_loss = tr.step()
+                if i + 1 < len(batches):
+                    tr.prefetch(*batches[i + 1])
+                host = tr.last_loss()
+                assert host == dev_loss.item()          # same fp32 bits, read two ways
+                out.append(host)
+            else:
+                out.append(tr.step(img, lab).item())
+        torch.cuda.synchronize()
+        return out, [p.detach().clone() for p in model.parameters()]
+
+    la, pa = run(False)
+    lb, pb = run(True)
+    # two runs are not bitwise equal (the forward BatchNorm statistics are accumulated with float
+    # atomics, DESIGN.md par. 7a), so compare within the run-to-run noise
+    assert all(abs(a - b) < 1e-2 * abs(a) for a, b in zip(la, lb)), (la, lb)
+    assert _cos(torch.cat([p.flatten() for p in pa]), torch.cat([p.flatten() for p in pb])) > 0.9999
