@@ -36,7 +36,7 @@ class Trainer:
                  bucket_layout: str = "reference", first_bucket_bytes: int | None = None,
                  bucket_bytes: int | None = None, symm_backend: str | None = None,
                  fuse_sgd: bool = True, overlap_wgrad: bool = True, comm_threads: int = 512, optimizer=None,
-                 overlap_sgd: bool = True):
+                 overlap_sgd: bool = True, debug_poison_grads: bool = False):
         if mode not in MODES:
             raise ValueError(f"mode must be one of {MODES}")
         if granularity not in ("fused", "param"):
@@ -54,6 +54,10 @@ class Trainer:
         # parameter group ('single') / each reduced bucket ('ddp') runs on a side stream while the
         # rest of backward continues, instead of as one 30 us pass over all 9.2 M parameters at the end.
         self.overlap_sgd = overlap_sgd
+        # Race detector for the overlapped modes (tests): every iteration starts by filling the whole
+        # gradient arena with NaN.  The backward kernels overwrite all of it, so a reduction or an SGD
+        # update that ran BEFORE its gradients were final would pick up NaNs and poison the parameters.
+        self.debug_poison_grads = debug_poison_grads
         # CTA size of the reductions that overlap backward (mode 'ddp').  256-thread CTAs would fit on
         # an SM next to a persistent conv CTA, but measured on 2 GPUs (profiles/r1_call30_*) the lost
         # reduction throughput costs more than the co-residency gains: 512-thread CTAs stay default.
@@ -147,10 +151,11 @@ class Trainer:
         from .ops import kernels as K
 
         if os.environ.get("DDPB_PDL") is None:
-            # programmatic dependent launch: +0.6% on one GPU, but in 'ddp' mode the early-resident
-            # CTAs of the next kernel keep the overlapped reductions off the SMs (2 GPUs: 0.874 ms
-            # per step with it, 0.831 without; profiles/r1_call45_*)
-            K.set_pdl(not (self.distributed and self.mode == "ddp"))
+            # programmatic dependent launch: +0.6% on one GPU.  Round 1 had to switch it off in 'ddp' mode
+            # (early-resident CTAs kept the overlapped reductions off the SMs while a cooperative
+            # BatchNorm backward waited for all of them); with the two-kernel BatchNorm backward it helps
+            # there too (2 GPUs: 0.795 ms per step with it, 0.815 without; profiles/r2_call08_*)
+            K.set_pdl(True)
         if self.distributed and self.mode == "ddp":
             self._broadcast_parameters()
 
@@ -220,6 +225,9 @@ class Trainer:
         # the input kernel also refreshes the first layer's padded filter pack; every other conv
         # operand is the SGD-maintained shadow
         eng.mark("step begin", reset=True)
+        if self.debug_poison_grads:
+            for i in range(len(a.params)):      # (not the alignment padding, which no kernel writes)
+                a.flat_grad(i).fill_(float("nan"))
         if kind == "u8":
             eng.load_input_u8(st["u8"][:B], st["aug"][:B] if with_aug else None, pack=True)
         else:
@@ -275,21 +283,25 @@ class Trainer:
                 with torch.cuda.stream(self.comm_stream):
                     self.symm.allreduce_avg(off, n, blocks=self.comm_blocks, slot_base=bi * self.comm_blocks,
                                             use_mc=self.use_mc, sgd=None, threads=self.comm_threads)
+                    eng.mark(f"bucket {bi} reduced (comm)")
                     if early_sgd:
                         # the bucket's mean is final on this rank once its reduction kernel has ended:
                         # update it now (a local kernel, no peer waits), not in the tail after backward
                         self._sgd_slice(off, n)
+                        eng.mark(f"bucket {bi} sgd (comm)")
 
             eng.backward(B, on_loss_ready=self._publish_loss, after_layer=after_layer, side_stream=self.wgrad_stream, reduce_loss=True)
             done = torch.cuda.Event()
             done.record(self.comm_stream)
             main.wait_event(done)
+            eng.mark("comm joined")
             b = self.buckets[last_bi]
             off, n = a.range_of(b.first_param, b.last_param)
             wide = min(torch.cuda.get_device_properties(self.device).multi_processor_count, 128)
             self.symm.allreduce_avg(off, n, blocks=wide, slot_base=1024, use_mc=self.use_mc,
                                     sgd=self._sgd_args() if self.fuse_sgd else None,
                                     sgd_range=(off, n) if early_sgd else (0, a.numel))
+            eng.mark("last bucket reduced + sgd")
             if not self.fuse_sgd:
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
         else:

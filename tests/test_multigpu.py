@@ -18,21 +18,22 @@ import os, sys, torch, torch.distributed as dist
 sys.path.insert(0, os.environ["DDPB_ROOT"])
 import ddpb200
 mode, gran, mc = sys.argv[1], sys.argv[2], sys.argv[3] == "1"
+B = int(sys.argv[4]) if len(sys.argv) > 4 else 32
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
 torch.cuda.set_device(dev)
 dist.init_process_group("nccl", device_id=dev)
 torch.manual_seed(89395)
 model = ddpb200.VGG11().to(dev)
-tr = ddpb200.Trainer(model, mode=mode, batch_size=32, rank=rank, world_size=world, granularity=gran,
+tr = ddpb200.Trainer(model, mode=mode, batch_size=B, rank=rank, world_size=world, granularity=gran,
                      use_multicast=mc, fuse_sgd=False, use_graph=False)
 g = torch.Generator().manual_seed(100 + rank)
-img = torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, generator=g)
-lab = torch.randint(0, 10, (32,), generator=g)
+img = torch.randint(0, 256, (B, 32, 32, 3), dtype=torch.uint8, generator=g)
+lab = torch.randint(0, 10, (B,), generator=g)
 # 1) raw per-rank gradients (no sync): run fwd+bwd by hand
 eng = tr.engine
 eng.load_input_u8(img.to(dev), None); eng.labels.copy_(lab.to(dev))
-eng.forward(32, with_loss=True); eng.backward(32)
+eng.forward(B, with_loss=True); eng.backward(B)
 torch.cuda.synchronize()
 local = eng.arena.grad.clone()
 gathered = [torch.empty_like(local) for _ in range(world)]
@@ -58,23 +59,41 @@ tr2 = None
 torch.manual_seed(89395)
 model2 = ddpb200.VGG11().to(dev)
 tr.close()
-tr2 = ddpb200.Trainer(model2, mode=mode, batch_size=32, rank=rank, world_size=world, granularity=gran, use_multicast=mc)
-for it in range(4):
+# debug_poison_grads: the gradient arena is NaN at the start of every step, so a bucket reduction / SGD
+# update that outran its last weight gradient (the overlap race of mode 'ddp') would poison the parameters
+tr2 = ddpb200.Trainer(model2, mode=mode, batch_size=B, rank=rank, world_size=world, granularity=gran, use_multicast=mc,
+                      lr=0.02, debug_poison_grads=True)
+for it in range(6):
     loss = tr2.step(img, lab)
 torch.cuda.synchronize()
 assert loss.item() == loss.item()
 flat = tr2.engine.arena.master.clone()
+assert bool(torch.isfinite(flat).all()), "a reduction read gradients that were not final (NaN poison reached the parameters)"
 allp = [torch.empty_like(flat) for _ in range(world)]
 dist.all_gather(allp, flat)
 assert all(torch.equal(allp[0], p) for p in allp), "parameters diverged across ranks"
-if rank == 0:
-    print(f"OK {mode} {gran} mc={tr2.use_mc} backend={tr2.symm.backend} err={err:.3e} loss={loss.item():.4f}")
+# 4) every mode computes the same update: compare with mode 'allreduce' (sync strictly after backward, the
+# reference's part2b order) run on the same data from the same seed.  Not bitwise: the forward BatchNorm
+# statistics use float atomics, so two runs differ in the last bits.
 tr2.close()
+torch.manual_seed(89395)
+model3 = ddpb200.VGG11().to(dev)
+tr3 = ddpb200.Trainer(model3, mode="allreduce", batch_size=B, rank=rank, world_size=world, use_multicast=mc, lr=0.02)
+for it in range(6):
+    tr3.step(img, lab)
+torch.cuda.synchronize()
+ref = tr3.engine.arena.master
+cos = float((flat.double() @ ref.double()) / (flat.double().norm() * ref.double().norm()))
+rel = float((flat - ref).norm() / ref.norm())
+assert cos > 0.999 and rel < 5e-2, (mode, cos, rel)   # two runs of the SAME mode differ by ~1e-2 (atomics + 6 steps)
+tr3.close()
+if rank == 0:
+    print(f"OK {mode} {gran} B={B} W={world} err={err:.3e} loss={loss.item():.4f} vs allreduce: cos={cos:.7f} rel={rel:.2e}")
 dist.destroy_process_group()
 '''
 
 
-def _run(mode, gran="fused", mc=False, world=None):
+def _run(mode, gran="fused", mc=False, world=None, batch=32):
     world = world or int(os.environ.get("DDPB_TEST_WORLD", "2"))
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
@@ -87,7 +106,7 @@ def _run(mode, gran="fused", mc=False, world=None):
         sk.bind(("127.0.0.1", 0))
         port = sk.getsockname()[1]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
-           "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), mode, gran, "1" if mc else "0"]
+           "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), mode, gran, "1" if mc else "0", str(batch)]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "OK " + mode in res.stdout
@@ -105,3 +124,11 @@ def test_allreduce_per_parameter_granularity():
 @pytest.mark.parametrize("mode", ["allreduce", "gather_scatter", "ddp"])
 def test_sync_modes_multicast(mode):
     _run(mode, mc=True)
+
+
+@pytest.mark.parametrize("mode", ["allreduce", "gather_scatter", "ddp"])
+def test_three_ranks_batch_85(mode):
+    """world_size = 3: int(256 / 3) = 85 images per rank, global batch 255
+    (/root/reference/part2/part2b/main.py:177; the report's figures include N = 3).  The reduction
+    slices (n/4 * rank / world) are uneven and the ragged batch runs outside the 128-pixel tiles."""
+    _run(mode, world=3, batch=85, mc=torch.cuda.device_count() >= 3)
