@@ -62,6 +62,8 @@ def parse():
     ap.add_argument("--no-overlap-sgd", action="store_true",
                     help="one SGD pass after backward instead of per-group / per-bucket updates on a side stream")
     ap.add_argument("--symm-backend", default=None)
+    ap.add_argument("--no-extra", action="store_true",
+                    help="skip the extra_configs block (strong-scaling runs of BASELINE.json configs 2-4)")
     return ap.parse_args()
 
 
@@ -119,40 +121,28 @@ def synthetic_host_batches(n_batches, batch, seed, pinned=True):
 # =========================================================================================
 # our arm
 # =========================================================================================
-def run_ours(a):
+def _measure_ours(a, mode, scaling, steps, warmup, granularity, world, rank, local_rank, device):
+    """Builds a Trainer for one (mode, scaling) config, times ``steps`` steps twice (batch resident on the
+    device / end to end from pinned host memory) and returns the numbers (max over ranks)."""
     import torch
     import torch.distributed as dist
 
     import ddpb200
     from ddpb200.utils.timing import ClockSampler, max_over_ranks
 
-    rank, local_rank, world = env_rank()
-    assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}"
-    device = torch.device("cuda", local_rank)
-    torch.cuda.set_device(device)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=device)
-    per_gpu = a.per_gpu_batch if a.scaling == "weak" else max(1, 256 // world)
-    global_batch = per_gpu * world
-    mode = a.mode if world > 1 else "single"
-
+    per_gpu = a.per_gpu_batch if scaling == "weak" else max(1, 256 // world)
+    mode = mode if world > 1 else "single"
     torch.manual_seed(89395)
-    if a.no_pdl:
-        from ddpb200.ops import kernels as _K
-        _K.set_pdl(False)
-    if a.conv_mode >= 0:
-        from ddpb200.ops import kernels as _K3
-        _K3.conv_force(a.conv_mode, -1, -1)
     model = ddpb200.VGG11().to(device)
     trainer = ddpb200.Trainer(model, mode=mode, batch_size=per_gpu, lr=0.1, momentum=0.9, weight_decay=1e-4,
-                              rank=rank, world_size=world, granularity=a.granularity,
+                              rank=rank, world_size=world, granularity=granularity,
                               use_multicast=False if a.no_multicast else "auto", use_graph=not a.no_graph,
                               comm_blocks=a.comm_blocks, symm_backend=a.symm_backend, bucket_layout=a.bucket_layout,
                               fuse_sgd=not a.no_fuse_sgd, comm_threads=a.comm_threads,
                               overlap_wgrad=not a.no_overlap_wgrad, overlap_sgd=not a.no_overlap_sgd,
                               first_bucket_bytes=None if a.bucket_mb is None else int(min(1.0, a.bucket_mb) * 2**20),
                               bucket_bytes=None if a.bucket_mb is None else int(a.bucket_mb * 2**20))
-    if a.bn_fused is not None:   # (after the Trainer, whose 'ddp' mode picks its own default)
+    if a.bn_fused is not None:
         from ddpb200.ops import kernels as _K2
         _K2.bn_bwd_set_fused(a.bn_fused)
     n_rot = 8
@@ -186,53 +176,104 @@ def run_ours(a):
         wall = (time.perf_counter() - t0) * 1e3
         return s.elapsed_time(e), wall, last
 
-    for it in range(max(a.warmup, 3)):
+    for it in range(max(warmup, 3)):
         img, lab, aug = dev_batches[it % n_rot]
         trainer.step(img, lab, aug)
     first_loss = float(trainer.engine.loss.item())
     with ClockSampler(local_rank, uuid=_gpu_uuid(local_rank)) as clocks:
-        dev_ms, _, _ = timed(dev_batches, a.steps, readback=False)
+        dev_ms, _, _ = timed(dev_batches, steps, readback=False)
     # end to end from pinned host memory (a few extra warm-up steps for the copy path)
     for it in range(3):
         img, lab, aug = host[it % n_rot]
         trainer.step(img, lab, aug)
         trainer.last_loss()
-    e2e_dev_ms, e2e_wall_ms, last_loss = timed(host, a.steps, readback=True)
-
+    e2e_dev_ms, e2e_wall_ms, last_loss = timed(host, steps, readback=True)
     dev_ms = max_over_ranks(dev_ms, device)
     e2e_ms = max_over_ranks(max(e2e_dev_ms, e2e_wall_ms), device)
+    eng = trainer.engine
+    act_mb = sum(t.numel() * 2 for ts in (eng.conv_out, eng.act, eng.dconv, eng.dact) for t in ts) / 1e6
+    out = dict(mode=mode, scaling=scaling, per_gpu=per_gpu, global_batch=per_gpu * world, steps=steps,
+               warmup=max(warmup, 3), ms_step=dev_ms / steps, e2e_ms_step=e2e_ms / steps,
+               launches=trainer.kernel_launches_per_step(), clocks=clocks.summary(), first_loss=first_loss,
+               last_loss=last_loss, h2d=world * sum(t.numel() * t.element_size() for t in host[0]),
+               ws_mb=act_mb + eng.operand0.numel() * 2 / 1e6 + 3 * eng.arena.numel * 4 / 1e6,
+               sync=None if world == 1 else {"backend": trainer.symm.backend, "multicast": trainer.use_mc,
+                                             "granularity": granularity,
+                                             "bucket_layout": a.bucket_layout if mode == "ddp" else None,
+                                             "comm_blocks": trainer.comm_blocks,
+                                             "buckets_floats": [b.numel for b in trainer.buckets] if mode == "ddp" else None})
+    trainer.close()
+    del trainer, model
+    torch.cuda.empty_cache()
+    return out
+
+
+def _extra_list(world):
+    """BASELINE.json configs 2-4: the reference report's strong-scaling experiment (global batch 256 =
+    int(256 / world) per rank, /root/reference/part2/part2b/main.py:177) in each sync mode."""
+    if world == 1:
+        return []
+    return [("strong", "ddp", "fused"), ("allreduce_strong", "allreduce", "fused"),
+            ("allreduce_param_strong", "allreduce", "param"), ("gather_scatter_strong", "gather_scatter", "fused")]
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+
+    rank, local_rank, world = env_rank()
+    assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}"
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    if a.no_pdl:
+        os.environ["DDPB_PDL"] = "0"     # (the Trainer leaves an explicit setting alone)
+        from ddpb200.ops import kernels as _K
+        _K.set_pdl(False)
+    if a.conv_mode >= 0:
+        from ddpb200.ops import kernels as _K3
+        _K3.conv_force(a.conv_mode, -1, -1)
+    m = _measure_ours(a, a.mode, a.scaling, a.steps, a.warmup, a.granularity, world, rank, local_rank, device)
+    extras = {}
+    if not a.no_extra:
+        for name, mode, gran in _extra_list(world):
+            x = _measure_ours(a, mode, "strong", min(a.steps, 30), min(a.warmup, 5), gran, world, rank, local_rank, device)
+            extras[name] = {"mode": x["mode"], "granularity": gran, "global_batch": x["global_batch"],
+                            "per_gpu_batch": x["per_gpu"], "ms_per_step": round(x["ms_step"], 4),
+                            "images_per_s": round(x["global_batch"] / (x["ms_step"] * 1e-3), 1),
+                            "e2e_ms_per_step": round(x["e2e_ms_step"], 4),
+                            "e2e_images_per_s": round(x["global_batch"] / (x["e2e_ms_step"] * 1e-3), 1),
+                            "steps": x["steps"], "warmup": x["warmup"]}
     if rank == 0:
-        ms_step = dev_ms / a.steps
-        value = global_batch / (ms_step * 1e-3)
-        e2e_value = global_batch / (e2e_ms / a.steps * 1e-3)
-        eng = trainer.engine
-        act_mb = sum(t.numel() * 2 for ts in (eng.conv_out, eng.act, eng.dconv, eng.dact) for t in ts) / 1e6
-        ws_mb = act_mb + eng.operand0.numel() * 2 / 1e6 + 3 * eng.arena.numel * 4 / 1e6
+        mode = m["mode"]
+        value = m["global_batch"] / (m["ms_step"] * 1e-3)
+        e2e_value = m["global_batch"] / (m["e2e_ms_step"] * 1e-3)
         pub = PUBLISHED_IMAGES_PER_S.get(world)
         par = "single" if world == 1 else {"ddp": "dp", "allreduce": "dp-allreduce", "gather_scatter": "dp-gather-scatter"}[mode]
         emit({
             "metric": "VGG-11 CIFAR-10 images/sec (ms/iter max over ranks)", "value": round(value, 1),
-            "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
-            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": a.scaling,
+            "unit": "images/s", "n_gpus": world, "steps": m["steps"], "warmup": m["warmup"],
+            "ms_per_step": round(m["ms_step"], 4), "higher_is_better": True, "scaling": a.scaling,
             "vs_baseline": round(value / pub, 2) if pub else None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
-            "config": {"model": "VGG-11 (3x32x32, 10 classes, BatchNorm batch stats)", "global_batch": global_batch,
-                       "per_gpu_batch": per_gpu, "seq_len": None, "parallelism": f"{par}{world}", "mode": mode,
+            "config": {"model": "VGG-11 (3x32x32, 10 classes, BatchNorm batch stats)", "global_batch": m["global_batch"],
+                       "per_gpu_batch": m["per_gpu"], "seq_len": None, "parallelism": f"{par}{world}", "mode": mode,
                        "optimizer": "SGD lr=0.1 momentum=0.9 wd=1e-4 (inside the timed step)",
-                       "sync": None if world == 1 else {"backend": trainer.symm.backend, "multicast": trainer.use_mc,
-                                                       "granularity": a.granularity, "bucket_layout": a.bucket_layout if mode == "ddp" else None, "comm_blocks": trainer.comm_blocks, "buckets_floats": [b.numel for b in trainer.buckets] if mode == "ddp" else None},
+                       "sync": m["sync"],
                        "cuda_graph": not a.no_graph, "programmatic_dependent_launch": bool(_pdl_state()),
                        "conv_mode": "automatic" if a.conv_mode < 0 else a.conv_mode,
-                       "l2": f"no explicit flush: working set {ws_mb:.0f} MB/step > 126 MB L2; inputs rotate over {n_rot} device batches",
+                       "l2": f"no explicit flush: working set {m['ws_mb']:.0f} MB/step > 126 MB L2; inputs rotate over 8 device batches",
                        "baseline_ref": "BASELINE.md §1: published CPU/Gloo images/s for this worker count"},
-            "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "ms_per_step": round(e2e_ms / a.steps, 4),
-                    "h2d_bytes_per_step": world * sum(t.numel() * t.element_size() for t in host[0]),
-                    "d2h_bytes_per_step": world * 8, "api": "ddpb200.Trainer.prefetch(next pinned uint8 NHWC, labels, aug) / step() / last_loss() -- the loop of ddpb200.train.train_model; the loss word (sequence + fp32) is written to pinned host memory by the step"},
-            "gpu_launches": trainer.kernel_launches_per_step() * a.steps,
-            "gpu_launches_per_step": trainer.kernel_launches_per_step(),
-            "clocks": clocks.summary(),
-            "loss_first": first_loss, "loss_last": last_loss,
+            "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "ms_per_step": round(m["e2e_ms_step"], 4),
+                    "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": world * 8,
+                    "api": "ddpb200.Trainer.prefetch(next pinned uint8 NHWC, labels, aug) / step() / last_loss() -- "
+                           "the loop of ddpb200.train.train_model; every step copies its batch host->device (copy "
+                           "stream, overlapping the previous step) and stores its loss word (sequence + fp32) into "
+                           "pinned host memory, which the host reads every step"},
+            "gpu_launches": m["launches"] * m["steps"], "gpu_launches_per_step": m["launches"],
+            "clocks": m["clocks"], "loss_first": m["first_loss"], "loss_last": m["last_loss"],
+            "extra_configs": extras,
         })
-    trainer.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -248,10 +289,25 @@ def find_reference():
 
 
 def import_reference_main(ref_root: Path, part: str):
+    """Imports baseline/_ref/<part>/main.py as a module, unmodified -- except part2/part2a, which does not
+    parse as committed (a stray '/' after the closing bracket at line 70): for that file the
+    one character is dropped IN MEMORY (the copy on disk stays byte-identical; baseline/PATCHES.md)."""
     d = ref_root / part
     sys.path.insert(0, str(d))          # the script does `import model as mdl`
     sys.modules.pop("model", None)
-    spec = importlib.util.spec_from_file_location(f"ref_{part.replace('/', '_')}_main", d / "main.py")
+    name = f"ref_{part.replace('/', '_')}_main"
+    if part == "part2/part2a":
+        import types
+
+        src = (d / "main.py").read_text()
+        lines = src.splitlines(keepends=True)
+        assert lines[69].rstrip("\r\n") == "            ])/", f"unexpected line 70: {lines[69]!r}"
+        lines[69] = lines[69].replace("])/", "])", 1)
+        mod = types.ModuleType(name)
+        mod.__file__ = str(d / "main.py")
+        exec(compile("".join(lines), str(d / "main.py"), "exec"), mod.__dict__)
+        return mod
+    spec = importlib.util.spec_from_file_location(name, d / "main.py")
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     return mod
@@ -286,6 +342,64 @@ class TimedLoader:
         self.wall_ms = (time.perf_counter() - self.wall0) * 1e3
 
 
+_REF_MODS = {}
+
+
+def _measure_reference(a, ref_root, part, scaling, steps, warmup, world, rank, local_rank, device):
+    """Runs the reference's own train_model (its DDP / sync_gradients, NCCL, cuDNN) for one config."""
+    import contextlib
+    import io
+    import random
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from ddpb200.ops.reference import CIFAR_MEAN, CIFAR_STD
+    from ddpb200.utils.timing import ClockSampler, max_over_ranks
+
+    per_gpu = a.per_gpu_batch if scaling == "weak" else max(1, 256 // world)
+    # get_rank() is evaluated when the module's parse_arguments runs, not at import: importing is safe
+    ref = _REF_MODS.get(part)
+    if ref is None:
+        ref = _REF_MODS[part] = import_reference_main(ref_root, part)
+    ref.device = str(device)                      # the scripts read this module global (main.py:15)
+    random.seed(ref.seed)
+    torch.manual_seed(ref.seed)
+    np.random.seed(ref.seed)
+    criterion = torch.nn.CrossEntropyLoss().to(device)
+    model = ref.mdl.VGG11()
+    model.to(device)
+    net = ref.DDP(model) if part == "part3" else model
+    optimizer = ref.optim.SGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0001)
+    mean, std = CIFAR_MEAN.view(1, 3, 1, 1), CIFAR_STD.view(1, 3, 1, 1)
+    host = []
+    for img, lab, _ in synthetic_host_batches(8, per_gpu, seed=1234 + rank, pinned=False):
+        x = ((img.permute(0, 3, 1, 2).float() / 255.0 - mean) / std).contiguous().pin_memory()
+        host.append((x, lab.pin_memory()))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    warm = max(warmup, 3)
+    loader = TimedLoader(host, warm, steps, barrier)
+    sink = io.StringIO()
+    with ClockSampler(local_rank, uuid=_gpu_uuid(local_rank)) as clocks, contextlib.redirect_stdout(sink):
+        if part in ("part1", "part3"):
+            ref.train_model(net, loader, optimizer, criterion, 0)
+        else:
+            ref.train_model(net, rank, world, loader, optimizer, criterion, 0)
+    dev_ms = loader.start.elapsed_time(loader.end)
+    ms = max_over_ranks(max(dev_ms, loader.wall_ms), device)
+    out = dict(part=part, per_gpu=per_gpu, global_batch=per_gpu * world, steps=steps, warmup=warm, ms_step=ms / steps,
+               clocks=clocks.summary(), h2d=world * sum(t.numel() * t.element_size() for t in host[0]))
+    del net, model, optimizer
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_reference(a):
     ref_root = find_reference()
     if ref_root is None:
@@ -299,82 +413,52 @@ def run_reference(a):
     except Exception as e:  # noqa: BLE001
         emit({"impl": "reference", "unavailable": f"import failed: {e}"})
         return
-    from ddpb200.ops.reference import CIFAR_MEAN, CIFAR_STD
-    from ddpb200.utils.timing import ClockSampler, max_over_ranks
-
     rank, local_rank, world = env_rank()
     device = torch.device("cuda", local_rank)
     torch.cuda.set_device(device)
-    per_gpu = a.per_gpu_batch if a.scaling == "weak" else max(1, 256 // world)
-    global_batch = per_gpu * world
-    part = "part1" if world == 1 else {"ddp": "part3", "allreduce": "part2/part2b", "single": "part3",
-                                       "gather_scatter": "part2/part2a"}[a.mode]
-    if part == "part2/part2a":
-        emit({"impl": "reference", "unavailable": "part2/part2a/main.py has a syntax error at line 70 as committed"})
-        return
-    # get_rank() is evaluated when the module's parse_arguments runs, not at import: importing is safe
-    ref = import_reference_main(ref_root, part)
-    ref.device = str(device)                      # the scripts read this module global (main.py:15)
+    parts = {"ddp": "part3", "allreduce": "part2/part2b", "single": "part3", "gather_scatter": "part2/part2a"}
+    part = "part1" if world == 1 else parts[a.mode]
     if world > 1:
-        ref.init_distributed_setup(os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"], rank, world, "nccl")
-    import random
-
-    import numpy as np
-
-    random.seed(ref.seed)
-    torch.manual_seed(ref.seed)
-    np.random.seed(ref.seed)
-    criterion = torch.nn.CrossEntropyLoss().to(device)
-    model = ref.mdl.VGG11()
-    model.to(device)
-    net = model
-    if part == "part3":
-        net = ref.DDP(model)
-    optimizer = ref.optim.SGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0001)
-
-    mean, std = CIFAR_MEAN.view(1, 3, 1, 1), CIFAR_STD.view(1, 3, 1, 1)
-    host = []
-    for img, lab, _ in synthetic_host_batches(8, per_gpu, seed=1234 + rank, pinned=False):
-        x = ((img.permute(0, 3, 1, 2).float() / 255.0 - mean) / std).contiguous().pin_memory()
-        host.append((x, lab.pin_memory()))
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(device)
-
-    warm = max(a.warmup, 3)
-    loader = TimedLoader(host, warm, a.steps, barrier)
-    import contextlib
-    import io
-
-    sink = io.StringIO()
-    with ClockSampler(local_rank, uuid=_gpu_uuid(local_rank)) as clocks, contextlib.redirect_stdout(sink):
-        if part == "part1" or part == "part3":
-            ref.train_model(net, loader, optimizer, criterion, 0)
-        else:
-            ref.train_model(net, rank, world, loader, optimizer, criterion, 0)
-    dev_ms = loader.start.elapsed_time(loader.end)
-    ms = max_over_ranks(max(dev_ms, loader.wall_ms), device)
+        # the reference's own bootstrap (identical in 2a / 2b / 3: part2/part2b/main.py:52-58), with its
+        # `backend` parameter set to nccl
+        boot = import_reference_main(ref_root, "part3")
+        _REF_MODS["part3"] = boot
+        boot.init_distributed_setup(os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"], rank, world, "nccl")
+    m = _measure_reference(a, ref_root, part, a.scaling, a.steps, a.warmup, world, rank, local_rank, device)
+    extras = {}
+    if not a.no_extra:
+        for name, mode, gran in _extra_list(world):
+            if gran == "param" and mode == "allreduce":
+                continue      # the reference's part2b IS per parameter: one row ("allreduce_strong") covers it
+            x = _measure_reference(a, ref_root, parts[mode], "strong", min(a.steps, 30), min(a.warmup, 5), world, rank,
+                                   local_rank, device)
+            extras[name] = {"script": f"baseline/_ref/{x['part']}/main.py train_model()", "global_batch": x["global_batch"],
+                            "per_gpu_batch": x["per_gpu"], "ms_per_step": round(x["ms_step"], 4),
+                            "images_per_s": round(x["global_batch"] / (x["ms_step"] * 1e-3), 1),
+                            "e2e_ms_per_step": round(x["ms_step"], 4),
+                            "e2e_images_per_s": round(x["global_batch"] / (x["ms_step"] * 1e-3), 1),
+                            "steps": x["steps"], "warmup": x["warmup"],
+                            "patch": "line 70: stray '/' dropped in memory (baseline/PATCHES.md)" if "part2a" in x["part"] else None}
+        if "allreduce_strong" in extras:
+            extras["allreduce_param_strong"] = dict(extras["allreduce_strong"])
     if rank == 0:
-        ms_step = ms / a.steps
-        value = global_batch / (ms_step * 1e-3)
+        ms_step = m["ms_step"]
+        value = m["global_batch"] / (ms_step * 1e-3)
         pub = PUBLISHED_IMAGES_PER_S.get(world)
         emit({
             "metric": "VGG-11 CIFAR-10 images/sec (ms/iter max over ranks)", "value": round(value, 1),
-            "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": warm, "ms_per_step": round(ms_step, 4),
+            "unit": "images/s", "n_gpus": world, "steps": m["steps"], "warmup": m["warmup"], "ms_per_step": round(ms_step, 4),
             "higher_is_better": True, "scaling": a.scaling, "vs_baseline": round(value / pub, 2) if pub else None,
             "dtype": "fp32 (cuDNN TF32 convolutions, torch defaults)", "data": "synthetic", "impl": "reference",
-            "config": {"model": "VGG-11 (reference model.py, unmodified)", "global_batch": global_batch,
-                       "per_gpu_batch": per_gpu, "seq_len": None, "parallelism": f"{'single' if world == 1 else 'dp'}{world}",
+            "config": {"model": "VGG-11 (reference model.py, unmodified)", "global_batch": m["global_batch"],
+                       "per_gpu_batch": m["per_gpu"], "seq_len": None, "parallelism": f"{'single' if world == 1 else 'dp'}{world}",
                        "script": f"baseline/_ref/{part}/main.py train_model()", "backend": None if world == 1 else "nccl",
                        "l2": "no explicit flush; inputs rotate over 8 pinned host batches"},
             "e2e": {"value": round(value, 1), "unit": "images/s", "ms_per_step": round(ms_step, 4),
-                    "h2d_bytes_per_step": world * sum(t.numel() * t.element_size() for t in host[0]),
-                    "d2h_bytes_per_step": world * 4,
+                    "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": world * 4,
                     "note": "the reference's loop copies each batch host->device and calls loss.item() itself, "
                             "so its only number is end to end"},
-            "gpu_launches": 0, "clocks": clocks.summary(),
+            "gpu_launches": 0, "clocks": m["clocks"], "extra_configs": extras,
         })
     if world > 1:
         dist.destroy_process_group()
