@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--mode", choices=["ddp", "allreduce", "gather_scatter", "single"], default="ddp")
     ap.add_argument("--scaling", choices=["weak", "strong"], default="weak")
     ap.add_argument("--per-gpu-batch", type=int, default=256)
-    ap.add_argument("--granularity", choices=["fused", "param"], default="fused")
+    ap.add_argument("--granularity", choices=["fused", "param", "param_launches"], default="fused")
     ap.add_argument("--no-multicast", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch")

@@ -42,7 +42,7 @@ def build_parser(distributed: bool) -> argparse.ArgumentParser:
         p.add_argument("--backend", default=None, help="process-group backend (default: nccl with GPUs, else gloo)")
         p.add_argument("--spawn", action="store_true",
                        help="convenience: start all --num-nodes ranks of this host from one command")
-        p.add_argument("--sync-granularity", choices=["fused", "param"], default="fused",
+        p.add_argument("--sync-granularity", choices=["fused", "param", "param_launches"], default="fused",
                        help="'param' launches one sync kernel per parameter tensor, like the reference's loop")
         p.add_argument("--no-multicast", action="store_true", help="do not use NVLS multimem instructions")
     p.add_argument("--device", default=None, help="cuda | cpu (default: cuda when available)")

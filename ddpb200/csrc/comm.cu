@@ -266,13 +266,168 @@ allreduce_avg_kernel(const CommCtx c, long long off, long long n4, int slot_base
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// K10 + batched table (SURVEY.md par. 8): MANY ranges in ONE launch with ONE pair of cross-GPU
+// barriers.  The reference's part2b issues 34 blocking all-reduces per iteration, 32 of them <= 2 KB
+// (/root/reference/part2/part2b/main.py:101-103); launched one by one here, each pays two ~12 us
+// barriers (1.6 ms per step at 2 GPUs, profiles/r2_call10_*).  This kernel takes the whole list:
+//   * "small" ranges (the host puts them first; at most kHold float4 per thread in total) are reduced
+//     ONE-SHOT: every rank reduces every element itself -- one multimem.ld_reduce through the switch,
+//     or W peer loads summed in rank order -- keeps the mean in registers across the closing barrier,
+//     then writes it to its OWN buffer and applies the SGD update from the same registers.  No remote
+//     stores, no local grid barrier, no second pass over the data;
+//   * the other ranges use the two-shot slice scheme of allreduce_avg_kernel.
+// ------------------------------------------------------------------------------------------
+constexpr int kMaxRanges = 64;
+constexpr int kHold = 4;
+struct RangeTable {
+  long long off[kMaxRanges];   // floats, multiple of 4
+  int n4[kMaxRanges];          // float4 per range
+  int pre4[kMaxRanges + 1];    // prefix sums of n4 over the small ranges
+  int count, small_count;
+};
+
+__device__ __forceinline__ void sgd_apply4(const SgdArgs& s, long long e, const float4& g) {
+  float4 pv = *reinterpret_cast<const float4*>(s.p + e);
+  float4 mv = *reinterpret_cast<const float4*>(s.m + e);
+  float4 gg;
+  gg.x = fmaf(s.wd, pv.x, g.x);
+  gg.y = fmaf(s.wd, pv.y, g.y);
+  gg.z = fmaf(s.wd, pv.z, g.z);
+  gg.w = fmaf(s.wd, pv.w, g.w);
+  mv.x = fmaf(s.mu, mv.x, gg.x);
+  mv.y = fmaf(s.mu, mv.y, gg.y);
+  mv.z = fmaf(s.mu, mv.z, gg.z);
+  mv.w = fmaf(s.mu, mv.w, gg.w);
+  pv.x = fmaf(-s.lr, mv.x, pv.x);
+  pv.y = fmaf(-s.lr, mv.y, pv.y);
+  pv.z = fmaf(-s.lr, mv.z, pv.z);
+  pv.w = fmaf(-s.lr, mv.w, pv.w);
+  *reinterpret_cast<float4*>(s.p + e) = pv;
+  *reinterpret_cast<float4*>(s.m + e) = mv;
+  if (s.shadow != nullptr)
+    *reinterpret_cast<uint2*>(s.shadow + e) = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+}
+
+template <bool kMc>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_multi_kernel(const CommCtx c, const __grid_constant__ RangeTable tab, int slot_base, SgdArgs sgd) {
+  const int slot = slot_base + blockIdx.x;
+  const float inv_w = 1.f / static_cast<float>(c.world);
+  const long long T = static_cast<long long>(gridDim.x) * blockDim.x;
+  const long long g = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  const int small_total4 = tab.pre4[tab.small_count];
+  peer_barrier(c, slot);   // every rank's gradients for all ranges are complete
+  // ---- one-shot part: chunk idx of the concatenated small ranges -> this thread's registers
+  float4 held[kHold];
+  long long held_e[kHold];
+#pragma unroll
+  for (int h = 0; h < kHold; ++h) {
+    const long long idx = g + h * T;
+    held_e[h] = -1;
+    if (idx < small_total4) {
+      int r = 0;
+      while (idx >= tab.pre4[r + 1]) ++r;
+      const long long e = tab.off[r] + 4 * (idx - tab.pre4[r]);
+      float4 acc;
+      if (kMc) {
+        acc = mc_ld_reduce(c.mc + e);
+      } else {
+        acc = ld_sys(c.buf[0] + e);
+        for (int q = 1; q < c.world; ++q) {   // rank order: identical rounding on every rank
+          const float4 v = ld_sys(c.buf[q] + e);
+          acc.x += v.x;
+          acc.y += v.y;
+          acc.z += v.z;
+          acc.w += v.w;
+        }
+      }
+      acc.x *= inv_w;
+      acc.y *= inv_w;
+      acc.z *= inv_w;
+      acc.w *= inv_w;
+      held[h] = acc;
+      held_e[h] = e;
+    }
+  }
+  // ---- two-shot part: rank r owns slice r of every large range
+  for (int r = tab.small_count; r < tab.count; ++r) {
+    const long long off = tab.off[r], n4 = tab.n4[r];
+    const long long lo = n4 * c.rank / c.world, hi = n4 * (c.rank + 1) / c.world;
+    for (long long i = lo + g; i < hi; i += T) {
+      const long long e = off + 4 * i;
+      float4 acc;
+      if (kMc) {
+        acc = mc_ld_reduce(c.mc + e);
+      } else {
+        acc = ld_sys(c.buf[0] + e);
+        for (int q = 1; q < c.world; ++q) {
+          const float4 v = ld_sys(c.buf[q] + e);
+          acc.x += v.x;
+          acc.y += v.y;
+          acc.z += v.z;
+          acc.w += v.w;
+        }
+      }
+      acc.x *= inv_w;
+      acc.y *= inv_w;
+      acc.z *= inv_w;
+      acc.w *= inv_w;
+      if (kMc) {
+        mc_st(c.mc + e, acc);
+      } else {
+        for (int q = 0; q < c.world; ++q) st_sys(c.buf[q] + e, acc);
+      }
+    }
+  }
+  peer_barrier(c, slot);   // everyone has read the small ranges; every large slice has landed everywhere
+#pragma unroll
+  for (int h = 0; h < kHold; ++h) {
+    if (held_e[h] >= 0) {
+      *reinterpret_cast<float4*>(c.buf[c.rank] + held_e[h]) = held[h];
+      if (sgd.p != nullptr) sgd_apply4(sgd, held_e[h], held[h]);
+    }
+  }
+  if (sgd.p != nullptr && tab.small_count < tab.count) {
+    local_grid_barrier(c);
+    for (int r = tab.small_count; r < tab.count; ++r) sgd_range(c, sgd, tab.off[r], tab.n4[r]);
+  }
+}
+
 // part2a: the root pulls every rank's gradients, averages, pushes the mean to everyone.
 template <bool kMc>
 __global__ void __launch_bounds__(kCommThreads)
 reduce_root_bcast_kernel(const CommCtx c, long long off, long long n4, int slot_base, int root, SgdArgs sgd) {
   const int slot = slot_base + blockIdx.x;
   peer_barrier(c, slot);
-  if (c.rank == root) {
+  if (c.rank == root && kMc && c.world > 2) {
+    // NVLS: the switch sums all ranks' copies on the way to the root (one inbound stream of S bytes
+    // instead of W-1 peer reads) and fans the mean out again with one multicast store per element.
+    // With two ranks there is only one peer to read and the plain loads are faster (2 GPUs: 0.839 vs
+    // 0.878 ms per step, profiles/r2_call11_*)
+    const float inv_w = 1.f / static_cast<float>(c.world);
+    constexpr int kU = 4;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * kU;
+    for (long long base = blockIdx.x * static_cast<long long>(blockDim.x) * kU + threadIdx.x; base < n4;
+         base += stride) {
+      float4 acc[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = base + static_cast<long long>(u) * blockDim.x;
+        if (i < n4) acc[u] = mc_ld_reduce(c.mc + off + 4 * i);
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = base + static_cast<long long>(u) * blockDim.x;
+        if (i >= n4) continue;
+        acc[u].x *= inv_w;
+        acc[u].y *= inv_w;
+        acc[u].z *= inv_w;
+        acc[u].w *= inv_w;
+        mc_st(c.mc + off + 4 * i, acc[u]);
+      }
+    }
+  } else if (c.rank == root) {
     const float inv_w = 1.f / static_cast<float>(c.world);
     constexpr int kU = 1;   // the loads from all peers are issued together (see allreduce_avg_kernel)
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * kU;
@@ -414,6 +569,55 @@ extern "C" int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int r
     allreduce_avg_kernel<true><<<blocks, threads, 0, stream>>>(c, off, n / 4, slot_base, s);
   else
     allreduce_avg_kernel<false><<<blocks, threads, 0, stream>>>(c, off, n / 4, slot_base, s);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Many ranges, one launch (see allreduce_multi_kernel).  offs / ns: `count` ranges in floats (multiples
+// of 4, pairwise disjoint).  Ranges of at most small_max floats are reduced one-shot as long as their
+// total fits in the threads' registers (4 float4 per thread); the rest two-shot.  p / m / shadow as for
+// ddpb_allreduce_avg: the SGD update covers exactly the listed ranges.
+extern "C" int ddpb_allreduce_multi(const void* const* bufs, const void* mc, int rank, int world,
+                                    const long long* offs, const long long* ns, int count, long long small_max,
+                                    int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow, float lr,
+                                    float momentum, float weight_decay, cudaStream_t stream) {
+  CommCtx c;
+  if (int rc = fill_ctx(&c, bufs, mc, rank, world)) return rc;
+  DDPB_REQUIRE(count >= 1 && count <= kMaxRanges, "comm: 1..%d ranges per launch (got %d)", kMaxRanges, count);
+  DDPB_REQUIRE(!use_mc || c.mc != nullptr, "comm: multicast requested but no multicast mapping");
+  if (int rc = check_range(0, 0, blocks, slot_base)) return rc;
+  RangeTable tab;
+  const long long hold_cap = static_cast<long long>(blocks) * kCommThreads * kHold;   // float4
+  long long small4 = 0;
+  int ns_small = 0;
+  bool is_small[kMaxRanges];
+  for (int i = 0; i < count; ++i) {
+    if (int rc = check_range(offs[i], ns[i], blocks, slot_base)) return rc;
+    DDPB_REQUIRE(ns[i] / 4 < (1LL << 31), "comm: range too long");
+    is_small[i] = ns[i] <= small_max && small4 + ns[i] / 4 <= hold_cap;
+    if (is_small[i]) {
+      small4 += ns[i] / 4;
+      ++ns_small;
+    }
+  }
+  int k = 0;
+  tab.pre4[0] = 0;
+  for (int pass = 0; pass < 2; ++pass)
+    for (int i = 0; i < count; ++i)
+      if (is_small[i] == (pass == 0)) {
+        tab.off[k] = offs[i];
+        tab.n4[k] = static_cast<int>(ns[i] / 4);
+        if (pass == 0) tab.pre4[k + 1] = tab.pre4[k] + tab.n4[k];
+        ++k;
+      }
+  for (int i = ns_small; i < kMaxRanges; ++i) tab.pre4[i + 1] = tab.pre4[ns_small];
+  tab.count = count;
+  tab.small_count = ns_small;
+  SgdArgs s{p, m, static_cast<__nv_bfloat16*>(shadow), lr, momentum, weight_decay, 0, 0};
+  if (use_mc)
+    allreduce_multi_kernel<true><<<blocks, kCommThreads, 0, stream>>>(c, tab, slot_base, s);
+  else
+    allreduce_multi_kernel<false><<<blocks, kCommThreads, 0, stream>>>(c, tab, slot_base, s);
   DDPB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

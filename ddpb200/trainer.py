@@ -39,8 +39,8 @@ class Trainer:
                  overlap_sgd: bool = True, debug_poison_grads: bool = False):
         if mode not in MODES:
             raise ValueError(f"mode must be one of {MODES}")
-        if granularity not in ("fused", "param"):
-            raise ValueError("granularity must be 'fused' or 'param'")
+        if granularity not in ("fused", "param", "param_launches"):
+            raise ValueError("granularity must be 'fused', 'param' or 'param_launches'")
         self.model, self.mode = model, mode
         self.batch_size = batch_size
         self.lr, self.momentum, self.weight_decay = lr, momentum, weight_decay
@@ -298,15 +298,26 @@ class Trainer:
             b = self.buckets[last_bi]
             off, n = a.range_of(b.first_param, b.last_param)
             wide = min(torch.cuda.get_device_properties(self.device).multi_processor_count, 128)
-            self.symm.allreduce_avg(off, n, blocks=wide, slot_base=1024, use_mc=self.use_mc,
-                                    sgd=self._sgd_args() if self.fuse_sgd else None,
-                                    sgd_range=(off, n) if early_sgd else (0, a.numel))
+            if early_sgd and n <= self.symm.SMALL_MAX_FLOATS:
+                # small tail bucket (the first layers): one-shot reduction, mean and SGD update from
+                # registers -- no remote stores, no local grid barrier
+                self.symm.allreduce_multi([(off, n)], blocks=wide, slot_base=1024, use_mc=self.use_mc,
+                                          sgd=self._sgd_args())
+            else:
+                self.symm.allreduce_avg(off, n, blocks=wide, slot_base=1024, use_mc=self.use_mc,
+                                        sgd=self._sgd_args() if self.fuse_sgd else None,
+                                        sgd_range=(off, n) if early_sgd else (0, a.numel))
             eng.mark("last bucket reduced + sgd")
             if not self.fuse_sgd:
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
         else:
             eng.backward(B, on_loss_ready=self._publish_loss, side_stream=self.wgrad_stream, reduce_loss=True)
-            if self.granularity == "param":
+            if self.granularity == "param" and self.mode == "allreduce":
+                # the reference's 34 per-parameter all-reduces (part2b/main.py:101-103) as ONE launch over a
+                # table of 34 ranges: the 32 small tensors one-shot, the big filters two-shot
+                self.symm.allreduce_multi([a.range_of(i, i) for i in range(len(a.params))], blocks=self.comm_blocks,
+                                          use_mc=self.use_mc, sgd=self._sgd_args() if self.fuse_sgd else None)
+            elif self.granularity in ("param", "param_launches"):
                 # one launch per parameter tensor, like the reference's python loop
                 for i in range(len(a.params)):
                     off, n = a.range_of(i, i)
@@ -489,7 +500,8 @@ class Trainer:
             early = self.overlap_sgd and self.fuse_sgd
             n += len(self.buckets) + (len(self.buckets) - 1 if early else 0) + (0 if self.fuse_sgd else 1)
         else:
-            n += (len(self.engine.arena.params) if self.granularity == "param" else 1) + (0 if self.fuse_sgd else 1)
+            per_param = self.granularity == "param_launches" or (self.granularity == "param" and self.mode != "allreduce")
+            n += (len(self.engine.arena.params) if per_param else 1) + (0 if self.fuse_sgd else 1)
         return n
 
     def close(self):

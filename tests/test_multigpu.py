@@ -43,6 +43,10 @@ expect = torch.stack(gathered).mean(0)
 n = eng.arena.numel
 if mode == "gather_scatter":
     tr.symm.reduce_root_bcast(0, n, root=0, blocks=tr.comm_blocks, use_mc=tr.use_mc)
+elif gran == "param":
+    # the reference's 34 per-parameter all-reduces as one launch: small tensors one-shot, big ones two-shot
+    tr.symm.allreduce_multi([eng.arena.range_of(i, i) for i in range(len(eng.arena.params))], blocks=tr.comm_blocks,
+                            use_mc=tr.use_mc)
 else:
     tr.symm.allreduce_avg(0, n, blocks=tr.comm_blocks, use_mc=tr.use_mc)
 torch.cuda.synchronize()
@@ -117,8 +121,9 @@ def test_sync_modes_p2p(mode):
     _run(mode)
 
 
-def test_allreduce_per_parameter_granularity():
-    _run("allreduce", gran="param")
+@pytest.mark.parametrize("mc", [False, True])
+def test_allreduce_per_parameter_granularity(mc):
+    _run("allreduce", gran="param", mc=mc)
 
 
 @pytest.mark.parametrize("mode", ["allreduce", "gather_scatter", "ddp"])
