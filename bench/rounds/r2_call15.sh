@@ -1,0 +1,10 @@
+#!/bin/bash
+# round 2, call 15: persistent conv with the smem-staged TMA-store epilogue: tests, layer times, phase probe, bench
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_kernels_gpu.py tests/test_engine_gpu.py -m gpu -x -q -p no:cacheprovider > gpurun_out/r2c15_pytest.log 2>&1; echo "rc=$?"; tail -6 gpurun_out/r2c15_pytest.log | cut -c1-250
+timeout 200 python bench/layer_graph_times.py > gpurun_out/r2c15_layers.log 2>&1; cat gpurun_out/r2c15_layers.log
+timeout 200 python bench/conv_probe2.py 2,0 > gpurun_out/r2c15_probe_fwd.log 2>&1; cat gpurun_out/r2c15_probe_fwd.log
+timeout 200 python bench/conv_probe2.py --dgrad 2,0 > gpurun_out/r2c15_probe_dgrad.log 2>&1; cat gpurun_out/r2c15_probe_dgrad.log
+for v in "" ""; do
+  timeout 200 python bench.py --steps 40 --warmup 10 $v 2> gpurun_out/r2c15_bench.err | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('$v', d['ms_per_step'], d['e2e']['ms_per_step'], d['loss_last'])"
+done

@@ -594,8 +594,8 @@ static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint,
 }
 
 template <int BLOCK_N, bool kDgrad>
-static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const FpropParams& p, int m_tiles,
-                        int splits, cudaStream_t stream) {
+static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& /*to*/, const FpropParams& p,
+                        int m_tiles, int splits, cudaStream_t stream) {
   using Cfg = FpropCfg<BLOCK_N>;
   static bool configured = false;
   if (!configured) {
@@ -609,8 +609,8 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const Fpro
 }
 
 template <int BLOCK_N, bool kDgrad>
-static int launch_pair(const CUtensorMap& tx, const CUtensorMap& tw, const FpropParams& p, int m_tiles,
-                       int splits, cudaStream_t stream) {
+static int launch_pair(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& /*to*/, const FpropParams& p,
+                       int m_tiles, int splits, cudaStream_t stream) {
   using Cfg = PairCfg<BLOCK_N>;
   static bool configured = false;
   if (!configured) {
@@ -737,6 +737,18 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B))
       return 3;
   }
+  CUtensorMap to;
+  {
+    // output tiles leave through TMA stores: boxes of 32 rows x 64 (or, for 64-wide tiles, 32) columns
+    const uint32_t box_cols = block_n >= 128 ? 64 : 32;
+    uint64_t dims[2] = {(uint64_t)C_out, (uint64_t)P};
+    uint64_t strides[1] = {(uint64_t)C_out * 2};
+    uint32_t box[2] = {box_cols, 32};
+    if (encode_tmap(&to, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, y, dims, strides, box,
+                    box_cols == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B))
+      return 3;
+  }
   FpropParams p;
   p.out = static_cast<__nv_bfloat16*>(y);
   p.bias = bias;
@@ -783,17 +795,17 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
 #define DDPB_CONV_DISPATCH(FN)                                                     \
   if (!dgrad) {                                                                    \
     switch (block_n) {                                                             \
-      case 64: rc = (pl.pair == 2 ? launch_persist<64, false>(tx, tw, p, m_tiles, splits, stream)          \
-                                    : launch_fprop<64, false>(tx, tw, p, m_tiles, splits, stream)); break; \
-      case 128: rc = FN<128, false>(tx, tw, p, m_tiles, splits, stream); break;    \
-      default: rc = FN<256, false>(tx, tw, p, m_tiles, splits, stream); break;     \
+      case 64: rc = (pl.pair == 2 ? launch_persist<64, false>(tx, tw, to, p, m_tiles, splits, stream)          \
+                                    : launch_fprop<64, false>(tx, tw, to, p, m_tiles, splits, stream)); break; \
+      case 128: rc = FN<128, false>(tx, tw, to, p, m_tiles, splits, stream); break;    \
+      default: rc = FN<256, false>(tx, tw, to, p, m_tiles, splits, stream); break;     \
     }                                                                              \
   } else {                                                                         \
     switch (block_n) {                                                             \
-      case 64: rc = (pl.pair == 2 ? launch_persist<64, true>(tx, tw, p, m_tiles, splits, stream)           \
-                                    : launch_fprop<64, true>(tx, tw, p, m_tiles, splits, stream)); break;  \
-      case 128: rc = FN<128, true>(tx, tw, p, m_tiles, splits, stream); break;     \
-      default: rc = FN<256, true>(tx, tw, p, m_tiles, splits, stream); break;      \
+      case 64: rc = (pl.pair == 2 ? launch_persist<64, true>(tx, tw, to, p, m_tiles, splits, stream)           \
+                                    : launch_fprop<64, true>(tx, tw, to, p, m_tiles, splits, stream)); break;  \
+      case 128: rc = FN<128, true>(tx, tw, to, p, m_tiles, splits, stream); break;     \
+      default: rc = FN<256, true>(tx, tw, to, p, m_tiles, splits, stream); break;      \
     }                                                                              \
   }
   if (pl.pair == 1) {

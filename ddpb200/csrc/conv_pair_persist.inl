@@ -386,8 +386,8 @@ conv_pair_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
 }
 
 template <int BLOCK_N, bool kDgrad>
-static int launch_pair_persist(const CUtensorMap& tx, const CUtensorMap& tw, const FpropParams& p, int m_tiles,
-                               int splits, cudaStream_t stream) {
+static int launch_pair_persist(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& /*to*/,
+                               const FpropParams& p, int m_tiles, int splits, cudaStream_t stream) {
   using Cfg = PairPersistCfg<BLOCK_N>;
   DDPB_REQUIRE(splits == 1, "conv: the persistent CTA-pair kernel does not split K");
   static bool configured = false;

@@ -19,14 +19,28 @@ struct PersistCfg {
   static constexpr int kABytes = kBlockM * kBlockK * 2;
   static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
+  // Epilogue staging: each of the 8 epilogue warps owns two swizzled boxes of 32 rows x kBoxCols bf16
+  // columns.  A drained accumulator chunk goes registers -> box (16-byte shared stores, conflict
+  // free under the TMA swizzle) -> one TMA store per box, instead of 32 lanes each storing 16 bytes
+  // to 32 different rows of global memory (the epilogue was bound by those partial-line stores:
+  // 2 us per 32-column chunk per warp, profiles/r2_call02_*).  The channel statistics are column
+  // sums read back from the box (32 conflict-free shared loads per lane) instead of two 31-shuffle
+  // transposes per chunk.
+  static constexpr int kBoxCols = (BLOCK_N >= 128) ? 64 : 32;          // columns per box (128 / 64 byte rows)
+  static constexpr int kBoxBytes = 32 * kBoxCols * 2;                  // 4 KB / 2 KB
+  static constexpr int kStagingBytes = 8 * 2 * kBoxBytes;              // 64 KB / 32 KB
+  static constexpr int kStatsBytes = 4 * 2 * BLOCK_N * 4;      // [quarter][sum, sumsq][column]
+  static constexpr int kBiasBytes = 8 * (BLOCK_N / 2) * 4;     // warp-private copies of the bias slice
+  static constexpr int kFixedBytes = 1024 + kStagingBytes + kStatsBytes + kBiasBytes + 512;
 #ifdef DDPB_PERSIST_STAGES
   static constexpr int kStages = DDPB_PERSIST_STAGES;
 #else
-  static constexpr int kStages = kRingBytes / kStageBytes;     // 8 / 6 / 4 for BLOCK_N = 64 / 128 / 256
+  // the rest of the 227 KB is the operand ring: 7 / 4 / 3 stages for BLOCK_N = 64 / 128 / 256.  The main
+  // loop is bound by the tensor pipe's operand fetch, not by the loads (skipping them changes nothing,
+  // profiles/r2_call02_*), so a shallower ring than round 1's 192 KB costs nothing.
+  static constexpr int kStages = (227 * 1024 - kFixedBytes) / kStageBytes;
 #endif
-  static constexpr int kStatsBytes = 4 * 2 * BLOCK_N * 4;      // [quarter][sum, sumsq][column]
-  static constexpr int kBiasBytes = 8 * (BLOCK_N / 2) * 4;     // warp-private copies of the bias slice
-  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kStatsBytes + kBiasBytes + 512;
+  static constexpr int kSmemBytes = kFixedBytes + kStages * kStageBytes;
   // accumulators in TMEM: as many as fit in 512 columns, at most 4.  With short reductions
   // (first layers: 1 or 9 k-steps per tile) the MMA -> epilogue -> MMA hand-off latency, not the
   // work, bounds a 2-deep ring; 4 buffers let the MMA warp run three tiles ahead.
@@ -71,15 +85,16 @@ __device__ __forceinline__ void persist_grid_barrier(unsigned int* word, const c
 template <int BLOCK_N, bool kDgrad>
 __global__ void __launch_bounds__(512, 1)   // 512, not 320: caps the kernel at 128 registers per thread
 conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
-                    const FpropParams p, int m_tiles, int n_tiles, int splits) {
+                    const __grid_constant__ CUtensorMap tmap_out, const FpropParams p, int m_tiles, int n_tiles,
+                    int splits) {
   using Cfg = PersistCfg<BLOCK_N>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
-  float* s_stats = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes);
-  float* s_bias = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes);
-  uint64_t* bars =
-      reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes + Cfg::kBiasBytes);
+  uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;    // 1024-byte aligned (stages are multiples of 8 KB)
+  float* s_stats = reinterpret_cast<float*>(staging + Cfg::kStagingBytes);
+  float* s_bias = reinterpret_cast<float*>(staging + Cfg::kStagingBytes + Cfg::kStatsBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes + Cfg::kStatsBytes + Cfg::kBiasBytes);
   uint64_t* full_bar = bars;                         // [kStages]
   uint64_t* empty_bar = bars + Cfg::kStages;         // [kStages]
   uint64_t* tmem_full = bars + 2 * Cfg::kStages;     // [kAccBufs]
@@ -95,6 +110,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmap_x);
     tma_prefetch_desc(&tmap_w);
+    tma_prefetch_desc(&tmap_out);
   }
   if (warp == 1) {
     if (elect_one()) {
@@ -214,28 +230,38 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     const int chunk0 = half * kMyChunks;
     float* my_bias = s_bias + ew * (BLOCK_N / 2);
     const int row = q * 32 + lane_id();
-    // Per-channel statistics are accumulated in shared memory across this CTA's tiles and
-    // flushed with atomics only when the column block changes (or at the end): with one flush
-    // per tile the 2*C_out atomic addresses were hit by every tile of the layer and serialised
-    // in L2 (first layer: 2048 tiles onto 128 addresses).
+    // Per-channel statistics: every lane keeps running sums of "its" columns of each box in registers
+    // across this CTA's tiles; they go to shared memory and on to global atomics only when the column
+    // block changes (or at the end): with one flush per tile the 2*C_out atomic addresses were hit by
+    // every tile of the layer and serialised in L2 (first layer: 2048 tiles onto 128 addresses).
     const bool do_stats = (p.partial == nullptr) && (p.stats != nullptr);
-    // BLOCK_N = 64 (one 32-column chunk per warp; first layer: 2048 tiles of one k-step each, i.e.
-    // epilogue bound): keep the running sums per THREAD in registers and do the cross-lane
-    // reduction once per flush instead of once per tile (measured: statistics were 36% of that
-    // layer's kernel time, profiles/r1_call26_*).
-    constexpr bool kRegStats = (kMyChunks == 1);
-    float racc1[kRegStats ? 32 : 1], racc2[kRegStats ? 32 : 1];
+    constexpr int kBoxCols = Cfg::kBoxCols;
+    constexpr int kBoxes = kMyChunks * 32 / kBoxCols;        // boxes per tile and warp: 1 / 1 / 2
+    constexpr int kChunksPerBox = kBoxCols / 32;             // 1 / 2 / 2
+    constexpr int kColsPerLane = kBoxCols / 32;              // columns of a box whose sums a lane keeps
+    constexpr int kRowBytes = kBoxCols * 2;                  // 64 / 128: the TMA swizzle span
+    float racc1[kBoxes][kColsPerLane], racc2[kBoxes][kColsPerLane];
 #pragma unroll
-    for (int j = 0; j < (kRegStats ? 32 : 1); ++j) racc1[j] = racc2[j] = 0.f;
+    for (int b = 0; b < kBoxes; ++b)
+#pragma unroll
+      for (int j = 0; j < kColsPerLane; ++j) racc1[b][j] = racc2[b][j] = 0.f;
+    const uint32_t my_boxes = smem_u32(staging) + static_cast<uint32_t>(ew) * 2u * Cfg::kBoxBytes;
+    // byte offset of 16-byte chunk k of row r inside a box, as the TMA swizzle lays it out
+    auto box_off = [&](int r, int k) -> uint32_t {
+      const int sw = (kRowBytes == 128) ? (r & 7) : ((r >> 1) & 3);
+      return static_cast<uint32_t>(r * kRowBytes + ((k ^ sw) << 4));
+    };
+    uint32_t box_count = 0;
     auto flush_stats = [&](int n_tile_done) {
-      if constexpr (kRegStats) {
-        const float s1 = warp_transpose_reduce(racc1);
-        const float s2 = warp_transpose_reduce(racc2);
-        s_stats[(q * 2 + 0) * BLOCK_N + chunk0 * 32 + lane_id()] += s1;
-        s_stats[(q * 2 + 1) * BLOCK_N + chunk0 * 32 + lane_id()] += s2;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) racc1[j] = racc2[j] = 0.f;
-      }
+      for (int b = 0; b < kBoxes; ++b)
+#pragma unroll
+        for (int j = 0; j < kColsPerLane; ++j) {
+          const int col = chunk0 * 32 + b * kBoxCols + static_cast<int>(lane_id()) * kColsPerLane + j;
+          s_stats[(q * 2 + 0) * BLOCK_N + col] += racc1[b][j];
+          s_stats[(q * 2 + 1) * BLOCK_N + col] += racc2[b][j];
+          racc1[b][j] = racc2[b][j] = 0.f;
+        }
       asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps
       for (int c = threadIdx.x - 64; c < 2 * BLOCK_N; c += 256) {
         const int which = c / BLOCK_N, col = c - which * BLOCK_N;
@@ -291,47 +317,60 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           }
         }
       } else {
-        __nv_bfloat16* out_row = p.out + pix * p.C_out + it.n_tile * BLOCK_N;
 #pragma unroll 1
-        for (int c = 0; c < kMyChunks; ++c) {
-          uint32_t raw[32];
-          tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
-          tmem_ld_wait();
-          float v[32];
+        for (int b = 0; b < kBoxes; ++b) {
+          const uint32_t box = my_boxes + (box_count & 1u) * Cfg::kBoxBytes;
+          ++box_count;
+          // the TMA store issued from this buffer two boxes ago must have finished READING it
+          if (lane_id() == 0) bulk_wait_read<1>();
+          __syncwarp();
+          const int r = static_cast<int>(lane_id());
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float x = __uint_as_float(raw[j]);
-            if (p.bias != nullptr) x += my_bias[c * 32 + j];   // same address in every lane: broadcast
-            v[j] = valid ? bf16_round(x) : 0.f;
-          }
-          if (valid) {
-            uint4* dst = reinterpret_cast<uint4*>(out_row + (chunk0 + c) * 32);
+          for (int cc = 0; cc < kChunksPerBox; ++cc) {
+            const int c = b * kChunksPerBox + cc;
+            uint32_t raw[32];
+            tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
+            tmem_ld_wait();
+            uint32_t pk[16];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 o;
-              o.x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
-              o.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
-              o.z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]);
-              o.w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
-              dst[j] = o;
-            }
-          }
-          if (p.stats != nullptr) {
-            if constexpr (kRegStats) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                racc1[j] += v[j];
-                racc2[j] = fmaf(v[j], v[j], racc2[j]);
+            for (int j = 0; j < 16; ++j) {
+              float x0 = __uint_as_float(raw[2 * j]), x1 = __uint_as_float(raw[2 * j + 1]);
+              if (p.bias != nullptr) {
+                x0 += my_bias[c * 32 + 2 * j];         // same address in every lane: broadcast
+                x1 += my_bias[c * 32 + 2 * j + 1];
               }
-            } else {
-              float sq[32];
+              pk[j] = valid ? pack_bf16x2(x0, x1) : 0u;   // rows past the end add zeros to the channel sums
+            }
 #pragma unroll
-              for (int j = 0; j < 32; ++j) sq[j] = v[j] * v[j];
-              const float s1 = warp_transpose_reduce(v);
-              const float s2 = warp_transpose_reduce(sq);
-              // entry (q, column) belongs to exactly this lane of this warp: plain accumulate
-              s_stats[(q * 2 + 0) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] += s1;
-              s_stats[(q * 2 + 1) * BLOCK_N + (chunk0 + c) * 32 + lane_id()] += s2;
+            for (int k = 0; k < 4; ++k)
+              st_shared_v4(box + box_off(r, cc * 4 + k), pk[4 * k], pk[4 * k + 1], pk[4 * k + 2], pk[4 * k + 3]);
+          }
+          fence_proxy_async();      // this lane's generic-proxy writes -> visible to the TMA engine
+          __syncwarp();
+          if (lane_id() == 0) {
+            // rows past P are clipped by the tensor map, so a ragged last tile needs no masking
+            tma_store_2d_saddr(&tmap_out, box, it.n_tile * BLOCK_N + chunk0 * 32 + b * kBoxCols,
+                               it.m_tile * kBlockM + q * 32);
+            bulk_commit();
+          }
+          if (do_stats) {
+            // column sums of the box just written (the stored, rounded values: what BatchNorm will see)
+            const int word = (kColsPerLane == 2) ? r : (r >> 1);      // 4-byte word of the row this lane reads
+            const int k16 = word >> 2, w4 = (word & 3) << 2;
+#pragma unroll 8
+            for (int rr = 0; rr < 32; ++rr) {
+              const uint32_t wv = ld_shared_u32(box + box_off(rr, k16) + w4);
+              if (kColsPerLane == 2) {
+                const float lo = __uint_as_float(wv << 16), hi = __uint_as_float(wv & 0xffff0000u);
+                racc1[b][0] += lo;
+                racc2[b][0] = fmaf(lo, lo, racc2[b][0]);
+                racc1[b][kColsPerLane - 1] += hi;
+                racc2[b][kColsPerLane - 1] = fmaf(hi, hi, racc2[b][kColsPerLane - 1]);
+              } else {
+                const float x = __uint_as_float((r & 1) ? (wv & 0xffff0000u) : (wv << 16));
+                racc1[b][0] += x;
+                racc2[b][0] = fmaf(x, x, racc2[b][0]);
+              }
             }
           }
         }
@@ -341,6 +380,13 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&tmem_empty[buf]);
     }
+    // every box this warp handed to the TMA engine is in global memory before anyone (the BatchNorm
+    // tail after the grid barrier, or the next kernel) reads the tiles back
+    if (lane_id() == 0) {
+      bulk_wait<0>();
+      fence_proxy_async_all();
+    }
+    __syncwarp();
     if (do_stats && cur_n >= 0) flush_stats(cur_n);
     if (threadIdx.x == 64) dbg_stamp(p, 4);
   }
@@ -507,8 +553,8 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
 }
 
 template <int BLOCK_N, bool kDgrad>
-static int launch_persist(const CUtensorMap& tx, const CUtensorMap& tw, const FpropParams& p, int m_tiles,
-                          int splits, cudaStream_t stream) {
+static int launch_persist(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& to, const FpropParams& p,
+                          int m_tiles, int splits, cudaStream_t stream) {
   using Cfg = PersistCfg<BLOCK_N>;
   static bool configured = false;
   if (!configured) {
@@ -521,6 +567,6 @@ static int launch_persist(const CUtensorMap& tx, const CUtensorMap& tw, const Fp
   int grid = sm_count();
   if (grid > items) grid = items;
   DDPB_CHECK_CUDA(launch_pdl(conv_persist_kernel<BLOCK_N, kDgrad>, grid, kPersistThreads, Cfg::kSmemBytes, stream, tx,
-                             tw, p, m_tiles, n_tiles, splits));
+                             tw, to, p, m_tiles, n_tiles, splits));
   return 0;
 }
