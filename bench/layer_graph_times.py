@@ -58,10 +58,8 @@ def main():
     ap.add_argument("--conv-mode", type=int, default=-1,
                     help="conv kernel: -1 automatic, 0 one tile per CTA, 1 CTA pair, 2 persistent, 3 persistent CTA pair")
     ap.add_argument("--block-n", type=int, default=-1, help="force the tile width of fprop / dgrad")
-    ap.add_argument("--wgrad-mode", type=int, default=0, help="0 one tap per CTA, 1 tap-fused cluster, 2 CTA pair")
     a = ap.parse_args()
     K.conv_force(a.conv_mode, a.block_n, -1)
-    K.conv_wgrad_set_mode(a.wgrad_mode)
     N, reps = a.batch, a.reps
     K.bn_bwd_set_fused(a.bn_fused)
     tot = dict(fwd=0.0, bn_bwd=0.0, wgrad=0.0, dgrad=0.0)

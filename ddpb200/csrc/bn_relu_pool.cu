@@ -902,6 +902,205 @@ static int launch_bn_bwd2(const __nv_bfloat16* x, const __nv_bfloat16* dy, const
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------
+// Channel-owner backward for the small late layers (default path when the layer fits): ONE ordinary
+// launch, no grid-wide synchronisation at all.  A CTA owns 8 channels and ALL pixels of the layer, so
+// the per-channel sums are complete inside the CTA: it streams its (x window, dy) items into shared
+// memory with every load in flight at once, reduces in a fixed order (registers -> warp shuffles ->
+// the 8 warps), and produces dx from the parked data.  Used when a CTA's slice is at most 48 KB (batch 256:
+// layers 6 and 7; smaller batches: more layers), where two latency-bound launches become one.
+// Deterministic like the two-kernel path.
+// ------------------------------------------------------------------------------------------
+constexpr int kBnOwnThreads = 256;
+
+template <bool kPool>
+__global__ void __launch_bounds__(kBnOwnThreads, 1)
+bn_bwd_owner_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                    const float* __restrict__ saved, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma,
+                    float* __restrict__ dbeta, float* __restrict__ dbias, BnGeom g) {
+  constexpr int kSlot = kPool ? 5 : 2;   // uint4 words parked per item: x window + dy
+  constexpr int kWin = kPool ? 4 : 1;
+  extern __shared__ uint4 s_data[];
+  __shared__ float s_coef[4][8];                        // scale, shift, A, Bc
+  __shared__ float s_red[kBnOwnThreads / 32][16];
+  __shared__ float s_tot[16];
+  pdl_launch_dependents();
+  const int cg = blockIdx.x;                            // this CTA's 8 channels
+  const int out_pix = g.N * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
+  pdl_wait();
+  // ---- phase 1a: every global load of the CTA, straight into shared memory
+  for (int i = threadIdx.x; i < out_pix; i += kBnOwnThreads) {
+    uint4 v[kWin], d;
+    bn2_load<kPool>(x, dy, g, i, cg, v, d);
+    uint4* slot = s_data + static_cast<size_t>(i) * kSlot;
+#pragma unroll
+    for (int q = 0; q < kWin; ++q) slot[q] = v[q];
+    slot[kSlot - 1] = d;
+  }
+  if (threadIdx.x < 8) {
+    const int c = cg * 8 + threadIdx.x;
+    const float mean = saved[c], rstd = saved[g.C + c];
+    const float sc = gamma[c] * rstd;
+    s_coef[0][threadIdx.x] = sc;
+    s_coef[1][threadIdx.x] = beta[c] - mean * sc;
+  }
+  __syncthreads();
+  float sc[8], sh[8], a1[8], a2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = s_coef[0][j];
+    sh[j] = s_coef[1][j];
+    a1[j] = a2[j] = 0.f;
+  }
+  // ---- phase 1b: per-channel sums from this thread's own slots
+  for (int i = threadIdx.x; i < out_pix; i += kBnOwnThreads) {
+    const uint4* slot = s_data + static_cast<size_t>(i) * kSlot;
+    const uint4 d = slot[kSlot - 1];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float gr, xa;
+      if (!kPool) {
+        xa = bf16_at(slot[0], j);
+        gr = (fmaf(xa, sc[j], sh[j]) > 0.f) ? bf16_at(d, j) : 0.f;
+      } else {
+        float best = 0.f;
+        xa = 0.f;
+        bool hit = false;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float xv = bf16_at(slot[q], j);
+          const float z = fmaf(xv, sc[j], sh[j]);
+          if (z > best) {
+            best = z;
+            xa = xv;
+            hit = true;
+          }
+        }
+        gr = hit ? bf16_at(d, j) : 0.f;
+      }
+      a1[j] += gr;
+      a2[j] = fmaf(gr, xa, a2[j]);
+    }
+  }
+  // fixed-order block reduction
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+      a1[j] += __shfl_xor_sync(0xffffffffu, a1[j], off);
+      a2[j] += __shfl_xor_sync(0xffffffffu, a2[j], off);
+    }
+  }
+  if (lane_id() == 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      s_red[threadIdx.x >> 5][j] = a1[j];
+      s_red[threadIdx.x >> 5][8 + j] = a2[j];
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 16) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kBnOwnThreads / 32; ++w) t += s_red[w][threadIdx.x];
+    s_tot[threadIdx.x] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    const int c = cg * 8 + threadIdx.x;
+    const float count = static_cast<float>(static_cast<long long>(g.N) * g.H * g.W);
+    const float mean = saved[c], rstd = saved[g.C + c];
+    const float scale = s_coef[0][threadIdx.x];
+    const float sum_g = s_tot[threadIdx.x];
+    const float sum_gxhat = rstd * (s_tot[8 + threadIdx.x] - mean * sum_g);
+    const float A = -scale * rstd * sum_gxhat / count;
+    const float Bc = -scale * sum_g / count - A * mean;
+    s_coef[2][threadIdx.x] = A;
+    s_coef[3][threadIdx.x] = Bc;
+    if (dbeta != nullptr) dbeta[c] = sum_g;
+    if (dgamma != nullptr) dgamma[c] = sum_gxhat;
+    if (dbias != nullptr) dbias[c] = fmaf(scale, sum_g, fmaf(A, mean * count, Bc * count));
+  }
+  __syncthreads();
+  float cA[8], cB[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    cA[j] = s_coef[2][j];
+    cB[j] = s_coef[3][j];
+  }
+  // ---- phase 2: dx from the parked data
+  for (int i = threadIdx.x; i < out_pix; i += kBnOwnThreads) {
+    const uint4* slot = s_data + static_cast<size_t>(i) * kSlot;
+    const uint4 d = slot[kSlot - 1];
+    int base = i;
+    if (kPool) {
+      const int Ho = g.H >> 1, Wo = g.W >> 1;
+      const int wo = i % Wo, t = i / Wo;
+      base = ((t / Ho) * g.H + 2 * (t % Ho)) * g.W + 2 * wo;
+    }
+    if (!kPool) {
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xv = bf16_at(slot[0], j);
+        const float gr = (fmaf(xv, sc[j], sh[j]) > 0.f) ? bf16_at(d, j) : 0.f;
+        o[j] = fmaf(sc[j], gr, fmaf(cA[j], xv, cB[j]));
+      }
+      store8(dx + static_cast<size_t>(base) * g.C + cg * 8, o);
+    } else {
+      int arg[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float best = 0.f;
+        arg[j] = -1;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float z = fmaf(bf16_at(slot[q], j), sc[j], sh[j]);
+          if (z > best) {
+            best = z;
+            arg[j] = q;
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float gr = (arg[j] == q) ? bf16_at(d, j) : 0.f;
+          o[j] = fmaf(sc[j], gr, fmaf(cA[j], bf16_at(slot[q], j), cB[j]));
+        }
+        store8(dx + static_cast<size_t>(base + (q >> 1) * g.W + (q & 1)) * g.C + cg * 8, o);
+      }
+    }
+  }
+}
+
+// Measured at batch 256 (profiles/r2_call16_*): layers 6 / 7 (32 / 20 KB per CTA) 9.4 -> 6.1 and 10.2 -> 5.8 us,
+// but layers 4 / 5 (128 / 80 KB, 16 items per thread on only 64 CTAs) got 2 us SLOWER than the two-kernel path.
+constexpr int kBnOwnMaxSmem = 48 * 1024;
+
+// Returns -1 when the layer is not a channel-owner case (too many pixels for one CTA's shared memory,
+// or too few channel groups to be worth it).
+template <bool kPool>
+static int launch_bn_bwd_owner(const __nv_bfloat16* x, const __nv_bfloat16* dy, const float* saved, const float* gamma,
+                               const float* beta, __nv_bfloat16* dx, float* dgamma, float* dbeta, float* dbias,
+                               BnGeom g, long long out_pix, cudaStream_t stream) {
+  const size_t smem = static_cast<size_t>(out_pix) * (kPool ? 5 : 2) * 16;
+  if (smem > static_cast<size_t>(kBnOwnMaxSmem) || g.C / 8 < 32 || out_pix < 1) return -1;
+  if (static_cast<long long>(g.N) * g.H * g.W * g.C >= (1LL << 31)) return -1;
+  static bool configured = false;
+  if (!configured) {
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_owner_kernel<kPool>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kBnOwnMaxSmem));
+    configured = true;
+  }
+  DDPB_CHECK_CUDA(launch_pdl(bn_bwd_owner_kernel<kPool>, g.C / 8, kBnOwnThreads, smem, stream, x, dy, saved, gamma,
+                             beta, dx, dgamma, dbeta, dbias, g));
+  return 0;
+}
+
 // 0: two-kernel path with float atomics (round 1); 1: fused cooperative kernel, one CTA per SM; 2: fused
 // cooperative, up to two CTAs per SM; 3 (default): deterministic two-kernel path above -- falls back to 2
 // when the caller gives no partial-sum buffer
@@ -1026,6 +1225,15 @@ extern "C" int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float*
   const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
   const __nv_bfloat16* dyb = static_cast<const __nv_bfloat16*>(dy);
   __nv_bfloat16* dxb = static_cast<__nv_bfloat16*>(dx);
+  if (g_bn_fused >= 3) {
+    // small late layers: one launch, a CTA owns 8 channels and every pixel
+    const long long out_pix = items / (C / 8);
+    const int rc = pool ? launch_bn_bwd_owner<true>(xb, dyb, saved, gamma, beta, dxb, dgamma, dbeta, dbias, g, out_pix,
+                                                    stream)
+                        : launch_bn_bwd_owner<false>(xb, dyb, saved, gamma, beta, dxb, dgamma, dbeta, dbias, g, out_pix,
+                                                     stream);
+    if (rc >= 0) return rc;
+  }
   if (g_bn_fused >= 3 && partials != nullptr && C % (kSliceGroups * 8) == 0) {
     const long long out_pix = items / (C / 8);
     return pool ? launch_bn_bwd2<true>(xb, dyb, saved, gamma, beta, sums, partials, partial_elems, dxb, dgamma, dbeta,

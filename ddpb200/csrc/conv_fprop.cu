@@ -20,6 +20,7 @@
 // that BatchNorm needs (O4), so the conv output is not re-read for statistics.
 #include "common.cuh"
 #include <stdlib.h>
+#include <type_traits>
 
 namespace ddpb {
 
@@ -62,7 +63,6 @@ struct FpropParams {
   __nv_bfloat16* act;    // [P or P/4][C_out]
   float* saved;          // [2][C_out] mean, rstd for the backward pass
   unsigned int* grid_sync;  // one zeroed word: all CTAs meet here once the statistics are complete
-  unsigned int* fin_sync;   // persistent kernel, split-K: zeroed word -> partials are summed in-kernel (null: off)
   int H, W, pool;
   float eps;
 };
@@ -301,156 +301,6 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   }
 }
 
-// ------------------------------------------------------------------------------------------
-// CTA-pair variant (tcgen05 cta_group::2).  The kernels above are bound by how fast one SM
-// can pull operand tiles out of L2 (ncu: ~45 B/clk/SM, tensor pipe 38% busy at 128x128
-// tiles).  Here two CTAs of a (2,1,1) cluster share one M = 256 MMA: each loads its own 128
-// pixel rows of A but only HALF of the filter tile B, so the bytes per flop an SM must ingest
-// drop by up to 2x (BLOCK_N = 256: 32 KB per 128x256x64 instead of 32 KB per 128x128x64).
-//   * both CTAs: TMA producer (own A tile + own half of B) signalling the LEADER's full barrier
-//   * leader only: MMA issue; tcgen05.commit multicasts "slot free" / "accumulator ready" to
-//     the barriers of both CTAs
-//   * both CTAs: epilogue over their own 128 TMEM lanes
-// ------------------------------------------------------------------------------------------
-template <int BLOCK_N>
-struct PairCfg {
-  static constexpr int kStages = (BLOCK_N >= 256) ? 5 : 6;
-  static constexpr int kABytes = kBlockM * kBlockK * 2;            // 16 KB: this CTA's pixels
-  static constexpr int kBBytes = (BLOCK_N / 2) * kBlockK * 2;      // this CTA's half of the filters
-  static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStatsBytes = 4 * 2 * BLOCK_N * 4;
-  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kStatsBytes + 256;
-};
-
-template <int BLOCK_N, bool kDgrad>
-__global__ void __launch_bounds__(kConvThreads)
-conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
-                 const FpropParams p) {
-  using Cfg = PairCfg<BLOCK_N>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* tiles = smem;
-  float* s_stats = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes);
-  uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + Cfg::kStages;
-  uint64_t* tmem_full_bar = bars + 2 * Cfg::kStages;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * Cfg::kStages + 1);
-
-  const int warp = threadIdx.x >> 5;
-  const uint32_t rank = cluster_ctarank();     // 0 = leader
-  const int m_tile = blockIdx.x;               // the pair covers m-tiles (2i, 2i+1)
-  const int n_tile = blockIdx.y;
-  const int cchunks = p.C_in / kBlockK;
-  const int total_k = p.taps * cchunks;
-  const int k_begin = static_cast<int>(static_cast<long long>(total_k) * blockIdx.z / gridDim.z);
-  const int k_end = static_cast<int>(static_cast<long long>(total_k) * (blockIdx.z + 1) / gridDim.z);
-  const int num_k = k_end - k_begin;
-
-  pdl_launch_dependents();
-  if (warp == 0 && elect_one()) {
-    tma_prefetch_desc(&tmap_x);
-    tma_prefetch_desc(&tmap_w);
-  }
-  if (warp == 1) {
-    if (elect_one()) {
-      for (int i = 0; i < Cfg::kStages; ++i) {
-        mbar_init(&full_bar[i], 1);    // the leader's producer arrives (with the byte count of BOTH CTAs)
-        mbar_init(&empty_bar[i], 1);   // one multicast commit from the leader's MMA thread
-      }
-      mbar_init(tmem_full_bar, 1);
-      fence_mbar_init();
-    }
-    __syncwarp();
-    tmem_alloc_pair(tmem_ptr_smem, BLOCK_N);
-    tmem_relinquish_pair();
-  }
-  if (threadIdx.x == 0) dbg_stamp(p, 0);
-  tc_fence_before();
-  cluster_sync_all();   // both CTAs' barriers exist before anything is signalled across the pair
-  tc_fence_after();
-  pdl_wait();
-  const uint32_t tmem_base = *tmem_ptr_smem;
-  if (threadIdx.x == 0) dbg_stamp(p, 1);
-
-  if (warp == 0) {
-    // ===================== TMA producer (both CTAs) =====================
-    if (elect_one()) {
-      const int n_img = (m_tile / p.hblocks) * p.bn;
-      const int h0 = (m_tile % p.hblocks) * p.bh;
-      const int b_row0 = n_tile * BLOCK_N + static_cast<int>(rank) * (BLOCK_N / 2);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int k = k_begin; k < k_end; ++k) {
-        const int tap = k / cchunks;
-        const int cc = k - tap * cchunks;
-        int dr = 0, ds = 0;
-        if (p.taps == 9) {
-          dr = tap / 3 - 1;
-          ds = tap % 3 - 1;
-        }
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* a_dst = tiles + stage * Cfg::kStageBytes;
-        uint8_t* b_dst = a_dst + Cfg::kABytes;
-        if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
-        tma_load_4d_pair(a_dst, &tmap_x, &full_bar[stage], cc * kBlockK, ds, h0 + dr, n_img);
-        if (!kDgrad) {
-          tma_load_2d_pair(b_dst, &tmap_w, &full_bar[stage], tap * p.C_in + cc * kBlockK, b_row0);
-        } else {
-#pragma unroll
-          for (int j = 0; j < BLOCK_N / 128; ++j)
-            tma_load_2d_pair(b_dst + j * 8192, &tmap_w, &full_bar[stage],
-                             (p.taps - 1 - tap) * p.C_out + b_row0 + j * 64, cc * kBlockK);
-        }
-        if (++stage == Cfg::kStages) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (leader CTA only) =====================
-    if (rank == 0 && elect_one()) {
-      constexpr uint32_t idesc = make_idesc_bf16(2 * kBlockM, BLOCK_N, 0, kDgrad ? 1 : 0);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int k = 0; k < num_k; ++k) {
-        mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        const uint32_t a_addr = smem_u32(tiles + stage * Cfg::kStageBytes);
-        const uint32_t b_addr = a_addr + Cfg::kABytes;
-#pragma unroll
-        for (int kk = 0; kk < kBlockK / kUmmaK; ++kk) {
-          const uint64_t adesc = make_smem_desc_sw128(a_addr + kk * kUmmaK * 2, 16, 1024);
-          const uint64_t bdesc = kDgrad ? make_smem_desc_sw128(b_addr + kk * kUmmaK * 128, 8192, 1024)
-                                        : make_smem_desc_sw128(b_addr + kk * kUmmaK * 2, 16, 1024);
-          umma_f16_pair(tmem_base, adesc, bdesc, idesc, (k | kk) != 0);
-        }
-        umma_commit_pair(&empty_bar[stage], 0x3);   // slot free in BOTH CTAs
-        if (++stage == Cfg::kStages) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-      umma_commit_pair(tmem_full_bar, 0x3);         // accumulators ready in BOTH CTAs
-      if (p.dbg != nullptr) {
-        mbar_wait(tmem_full_bar, 0);
-        dbg_stamp(p, 2);
-      }
-    }
-  } else {
-    conv_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, s_stats, warp, m_tile, n_tile);
-  }
-
-  tc_fence_before();
-  cluster_sync_all();   // nobody frees TMEM or exits while the peer may still signal / read
-  if (threadIdx.x == 0) dbg_stamp(p, 3);
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc_pair(tmem_base, BLOCK_N);
-  }
-}
-
 // Split-K finalize: y = bf16(sum_s partial[s] + bias); stats += (sum y, sum y^2) per channel.
 // One thread = one pixel x 8 channels; 256 % (C_out/8) == 0 keeps a thread on its channels.
 __global__ void __launch_bounds__(256)
@@ -527,7 +377,7 @@ splitk_finalize_kernel(const float* __restrict__ partial, const float* __restric
 // model and takes the cheapest.
 // ------------------------------------------------------------------------------------------
 struct ConvPlan {
-  int pair;      // kernel: 0 = one tile per CTA, 1 = CTA pair (cta_group::2), 2 = persistent
+  int pair;      // kernel: 0 = one tile per CTA, 2 = persistent, 3 = persistent CTA pair (cta_group::2)
   int block_n;
   int splits;
 };
@@ -566,7 +416,7 @@ static ConvPlan plan_conv_mode(int mode, long long P, int C_out, int total_k, in
   for (int bi = 0; bi < 3; ++bi) {
     const int bn = bns[bi];
     if (C_out % bn != 0) continue;
-    if ((mode == 1 || mode == 3) && bn < 128) continue;   // a CTA pair splits B in halves of >= 64 rows
+    if (mode == 3 && bn < 128) continue;   // a CTA pair splits B in halves of >= 64 rows
     if (block_n_hint != 0 && bn != block_n_hint) continue;
     if (g_force_block_n >= 0 && bn != g_force_block_n) continue;
     for (int splits = 1; splits <= 8; ++splits) {
@@ -585,7 +435,7 @@ static ConvPlan plan_conv_mode(int mode, long long P, int C_out, int total_k, in
 }
 
 static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint, bool allow_split) {
-  const int mode = g_force_pair >= 0 ? g_force_pair : 2;
+  const int mode = (g_force_pair == 0 || g_force_pair == 3) ? g_force_pair : 2;
   bool found = false;
   const ConvPlan pl = plan_conv_mode(mode, P, C_out, total_k, block_n_hint, allow_split, &found);
   // mode 3 (persistent CTA pair) has no 64-wide tile and no split-K: such shapes use mode 2
@@ -605,34 +455,6 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUte
   }
   dim3 grid(m_tiles, p.C_out / BLOCK_N, splits);
   DDPB_CHECK_CUDA(launch_pdl(conv_fprop_kernel<BLOCK_N, kDgrad>, grid, kConvThreads, Cfg::kSmemBytes, stream, tx, tw, p));
-  return 0;
-}
-
-template <int BLOCK_N, bool kDgrad>
-static int launch_pair(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& /*to*/, const FpropParams& p,
-                       int m_tiles, int splits, cudaStream_t stream) {
-  using Cfg = PairCfg<BLOCK_N>;
-  static bool configured = false;
-  if (!configured) {
-    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_pair_kernel<BLOCK_N, kDgrad>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    configured = true;
-  }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((m_tiles + 1) / 2 * 2, p.C_out / BLOCK_N, splits);   // even: CTA pairs along M
-  cfg.blockDim = dim3(kConvThreads);
-  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[2];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[1].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  DDPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_pair_kernel<BLOCK_N, kDgrad>, tx, tw, p));
   return 0;
 }
 
@@ -687,8 +509,7 @@ struct BnTail {
 // Returns 0 on success; *fused_bn (if given) tells whether the BatchNorm tail ran inside the conv kernel.
 static int conv_impl(int dgrad, const void* x, const void* w, const float* bias, void* y, float* stats, int N, int H,
                      int W, int C_in, int C_out, int taps, int block_n, float* scratch, long long scratch_elems,
-                     cudaStream_t stream, const BnTail* bn_tail = nullptr, int* fused_bn = nullptr,
-                     unsigned int* fin_sync = nullptr) {
+                     cudaStream_t stream, const BnTail* bn_tail = nullptr, int* fused_bn = nullptr) {
   const char* name = dgrad ? "conv_dgrad" : "conv_fprop";
   DDPB_REQUIRE(taps == 1 || taps == 9, "%s: taps must be 1 or 9 (got %d)", name, taps);
   DDPB_REQUIRE(C_in % 64 == 0 && C_in > 0, "%s: reduction channels must be a multiple of 64 (got %d)", name, C_in);
@@ -710,7 +531,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
     pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, false);
   }
   block_n = pl.block_n;
-  const int b_rows = (pl.pair == 1 || pl.pair == 3) ? block_n / 2 : block_n;   // filter rows one CTA loads per k-step
+  const int b_rows = (pl.pair == 3) ? block_n / 2 : block_n;   // filter rows one CTA loads per k-step
 
   CUtensorMap tx, tw;
   {
@@ -766,18 +587,13 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   p.act = nullptr;
   p.saved = nullptr;
   p.grid_sync = nullptr;
-  p.fin_sync = nullptr;
   p.H = H;
   p.W = W;
   p.pool = 0;
   p.eps = 0.f;
   if (fused_bn != nullptr) *fused_bn = 0;
-  // split-K partials summed inside the persistent kernel (after a grid barrier) when the caller
-  // provides the barrier word and a thread can own one 8-channel group
-  const bool fin_in_kernel = pl.pair == 2 && pl.splits > 1 && fin_sync != nullptr && kPersistThreads % (C_out / 8) == 0;
-  if (fin_in_kernel) p.fin_sync = fin_sync;
   // BatchNorm tail inside the kernel: persistent kernel, whole 2x2 windows per tile
-  if (bn_tail != nullptr && stats != nullptr && (pl.pair == 2 || pl.pair == 3) && (pl.splits == 1 || fin_in_kernel) &&
+  if (bn_tail != nullptr && stats != nullptr && (pl.pair == 2 || pl.pair == 3) && pl.splits == 1 &&
       (!bn_tail->pool || bh % 2 == 0)) {
     p.gamma = bn_tail->gamma;
     p.beta = bn_tail->beta;
@@ -808,9 +624,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
       default: rc = FN<256, true>(tx, tw, to, p, m_tiles, splits, stream); break;      \
     }                                                                              \
   }
-  if (pl.pair == 1) {
-    DDPB_CONV_DISPATCH(launch_pair)
-  } else if (pl.pair == 2) {
+  if (pl.pair == 2) {
     DDPB_CONV_DISPATCH(launch_persist)
   } else if (pl.pair == 3) {
     DDPB_CONV_DISPATCH(launch_pair_persist)
@@ -818,7 +632,10 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
     DDPB_CONV_DISPATCH(launch_fprop)
   }
 #undef DDPB_CONV_DISPATCH
-  if (rc != 0 || splits == 1 || fin_in_kernel) return rc;
+  if (rc != 0 || splits == 1) return rc;
+  // (one channel-owner launch doing finalize + statistics + BatchNorm for the small split-K layers was tried and
+  // removed: 64 CTAs pulling the fp32 partial tiles in 32-byte pieces took 27-28 us against 25 us for the
+  // finalize + BatchNorm kernels, profiles/r2_call16_*)
   const long long items = static_cast<long long>(p.P) * (C_out / 8);
   long long blocks = (items + 255) / 256;
   if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
@@ -856,14 +673,10 @@ extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const fl
                                           cudaStream_t stream) {
   BnTail bn{gamma, beta, act, saved, pool, eps};
   int fused = 0;
-  // words 2*C_out (BatchNorm barrier) and 2*C_out + 1 (split-K finalize barrier) of `stats`
-  // Off by default: summing the split-K partials inside the kernel (two grid barriers) measured
-  // 8 us per step SLOWER than the finalize + BatchNorm kernels with programmatic launch overlap
-  // (profiles/r1_call40_*); DDPB_FWD_FIN_IN_KERNEL=1 selects it.
-  static const int fin_in_kernel = [] { const char* e = getenv("DDPB_FWD_FIN_IN_KERNEL"); return e ? atoi(e) : 0; }();
+  // (summing the split-K partials inside the persistent kernel after a second grid barrier was tried and
+  // removed: 8 us per step slower than separate kernels with programmatic launch overlap, profiles/r1_call40_*)
   if (int rc = conv_impl(0, x, w, bias, conv_out, stats, N, H, W, C_in, C_out, taps, 0, scratch,
-                         scratch != nullptr ? scratch_elems : 0, stream, &bn, &fused,
-                         fin_in_kernel ? reinterpret_cast<unsigned int*>(stats + 2 * C_out) + 1 : nullptr))
+                         scratch != nullptr ? scratch_elems : 0, stream, &bn, &fused))
     return rc;
   if (fused) return 0;
   return bn_relu_pool_fwd_launch(conv_out, stats, gamma, beta, act, saved, N, H, W, C_out, pool, eps, stream);
@@ -871,12 +684,9 @@ extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const fl
 
 // Data gradient of the 3x3 convolution (O2).  dy: [N][H][W][C_out] bf16; w: the SAME bf16 pack
 // fprop uses, [C_out][9][C_in]; dx: [N*H*W][C_in] bf16.  scratch: as for fprop, sized with
-// ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n).  sync: one 32-bit word of
-// device memory that is ZERO on entry (left non-zero), or null; with it a split-K launch sums its
-// partial tiles inside the same kernel instead of launching a finalize kernel.
+// ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n).
 extern "C" int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out,
-                               int block_n, float* scratch, long long scratch_elems, unsigned int* sync,
-                               cudaStream_t stream) {
+                               int block_n, float* scratch, long long scratch_elems, cudaStream_t stream) {
   return conv_impl(1, dy, w, nullptr, dx, nullptr, N, H, W, C_out, C_in, 9, block_n, scratch,
-                   scratch != nullptr ? scratch_elems : 0, stream, nullptr, nullptr, sync);
+                   scratch != nullptr ? scratch_elems : 0, stream);
 }

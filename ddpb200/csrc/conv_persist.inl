@@ -398,57 +398,6 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 
-  // ===================== in-kernel split-K finalize =====================
-  // With p.fin_sync the partial tiles in p.partial are summed here, after a grid-wide barrier,
-  // instead of by a second kernel: y = bf16(sum_s partial[s] + bias), statistics accumulated.
-  // One thread owns one 8-channel group (blockDim % (C_out/8) == 0, checked by the host) and
-  // walks pixels with a grid stride, so its running sums stay in registers.
-  if (p.fin_sync != nullptr) {
-    persist_grid_barrier(p.fin_sync, "split-K finalize");
-    const int groups = p.C_out / 8;
-    const int rows_per_pass = blockDim.x / groups;
-    const int g = threadIdx.x % groups, r = threadIdx.x / groups;
-    float bv[8], s1[8], s2[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      bv[j] = p.bias != nullptr ? __ldg(p.bias + g * 8 + j) : 0.f;
-      s1[j] = s2[j] = 0.f;
-    }
-    for (long long pix = static_cast<long long>(blockIdx.x) * rows_per_pass + r; pix < p.P;
-         pix += static_cast<long long>(gridDim.x) * rows_per_pass) {
-      float v[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = bv[j];   // same summation order as splitk_finalize_kernel
-#pragma unroll 4
-      for (int sp = 0; sp < splits; ++sp) {
-        const float4* src =
-            reinterpret_cast<const float4*>(p.partial + (static_cast<long long>(sp) * p.P + pix) * p.C_out + g * 8);
-        const float4 a = __ldcg(src), b = __ldcg(src + 1);   // written by other SMs: L2, not L1
-        v[0] += a.x; v[1] += a.y; v[2] += a.z; v[3] += a.w;
-        v[4] += b.x; v[5] += b.y; v[6] += b.z; v[7] += b.w;
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        v[j] = bf16_round(v[j]);
-        s1[j] += v[j];
-        s2[j] = fmaf(v[j], v[j], s2[j]);
-      }
-      store8(p.out + pix * p.C_out + g * 8, v);
-    }
-    if (p.stats != nullptr) {
-      float* s_acc = reinterpret_cast<float*>(tiles);   // the operand ring is idle
-      for (int c = threadIdx.x; c < 2 * p.C_out; c += blockDim.x) s_acc[c] = 0.f;
-      __syncthreads();
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        atomicAdd(&s_acc[g * 8 + j], s1[j]);
-        atomicAdd(&s_acc[p.C_out + g * 8 + j], s2[j]);
-      }
-      __syncthreads();
-      for (int c = threadIdx.x; c < 2 * p.C_out; c += blockDim.x) atomicAdd(p.stats + c, s_acc[c]);
-    }
-  }
-
   // ===================== fused BatchNorm + ReLU (+ pool) =====================
   // The conv output of this layer is only ever consumed by its BatchNorm, whose statistics
   // were accumulated by the epilogues above.  Instead of a second kernel, all CTAs meet at a
@@ -477,19 +426,22 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     }
     __syncthreads();
     constexpr int kGroups = BLOCK_N / 8;                 // 16-byte channel groups per tile row
-    constexpr int kUnroll = 4;                           // items per thread in flight (memory-level parallelism)
     const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
     const int out_rows = p.pool ? kBlockM / 4 : kBlockM; // output pixels per tile
     const int per_tile = out_rows * kGroups;
-    const int nwin = p.pool ? 4 : 1;
     // flat index over ALL of this CTA's tiles, so a thread always has kUnroll independent items
     // in flight (a single tile is only 256..1024 items: fewer than the block has threads)
     const int out_tiles = m_tiles * n_tiles;             // (with split-K, several items share a tile)
     const int my_tiles = (out_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
     const long long my_total = static_cast<long long>(my_tiles) * per_tile;
-    {
+    // The pass is latency bound (the tiles come back from L2), so what counts is 16-byte loads in flight per
+    // thread: 4 items x 4 window loads with pooling, 8 items x 1 load without (measured: the un-pooled
+    // layers ran this pass at 1.8 TB/s with 4 loads in flight, profiles/r2_call15_*)
+    auto bn_tail_pass = [&](auto unroll_tag, auto win_tag) {
+      constexpr int kUnroll = decltype(unroll_tag)::value;   // items per thread in flight
+      constexpr int kWinLoads = decltype(win_tag)::value;    // loads per item
       for (long long base = threadIdx.x; base < my_total; base += static_cast<long long>(blockDim.x) * kUnroll) {
-        uint4 raw[kUnroll][4];
+        uint4 raw[kUnroll][kWinLoads];
         long long opix[kUnroll];
         int chv[kUnroll];
         bool ok[kUnroll];
@@ -521,9 +473,8 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           ok[u] = ok[u] && in00 < p.P;
           if (ok[u]) {
 #pragma unroll
-            for (int d = 0; d < 4; ++d)
-              if (d < nwin)
-                raw[u][d] = __ldcg(reinterpret_cast<const uint4*>(p.out + (in00 + (d >> 1) * p.W + (d & 1)) * p.C_out + chv[u]));
+            for (int d = 0; d < kWinLoads; ++d)
+              raw[u][d] = __ldcg(reinterpret_cast<const uint4*>(p.out + (in00 + (d >> 1) * p.W + (d & 1)) * p.C_out + chv[u]));
           }
         }
         // 2) normalise, rectify, pool, store
@@ -534,8 +485,8 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] = 0.f;   // ReLU floor
 #pragma unroll
-          for (int d = 0; d < 4; ++d) {
-            if (d < nwin) {
+          for (int d = 0; d < kWinLoads; ++d) {
+            {
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 const uint32_t wv = (j < 2) ? raw[u][d].x : (j < 4) ? raw[u][d].y : (j < 6) ? raw[u][d].z : raw[u][d].w;
@@ -547,7 +498,11 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           store8(p.act + opix[u] * p.C_out + chv[u], o);
         }
       }
-    }
+    };
+    if (p.pool)
+      bn_tail_pass(std::integral_constant<int, 4>{}, std::integral_constant<int, 4>{});
+    else
+      bn_tail_pass(std::integral_constant<int, 8>{}, std::integral_constant<int, 1>{});
   }
   if (threadIdx.x == 0) dbg_stamp(p, 3);
 }

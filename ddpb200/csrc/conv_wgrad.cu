@@ -25,12 +25,11 @@ constexpr int kWgThreads = 192;
 constexpr int kWgPix = 64;                    // pixels per pipeline stage
 constexpr int kWgBoxBytes = kWgPix * 128;     // one (64 ch x 64 px) box = 8 KB
 
-// kDeep = false: <= 97 KB of shared memory, two CTAs per SM share the tensor pipe (the ring of one
-// CTA is latency bound: ~1.1 us TMA round trip over 3 stages).  kDeep = true: for grids of at
-// most one CTA per SM, the whole shared memory is one ring twice as deep.
-template <int BLOCK_N, bool kDeep = false>
+// <= 97 KB of shared memory: two CTAs per SM share the tensor pipe (the ring of one CTA is latency
+// bound: ~1.1 us TMA round trip over 3 stages).
+template <int BLOCK_N>
 struct WgradCfg {
-  static constexpr int kStages = ((BLOCK_N >= 128) ? 3 : 4) * (kDeep ? 2 : 1);
+  static constexpr int kStages = (BLOCK_N >= 128) ? 3 : 4;
   static constexpr int kABytes = 2 * kWgBoxBytes;                 // M = 128 channels of dY
   static constexpr int kBBytes = (BLOCK_N / 64) * kWgBoxBytes;    // N channels of X
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -49,11 +48,11 @@ struct WgradParams {
   int dup_m;            // C_out == 64: both halves of M read the same 64 channels
 };
 
-template <int BLOCK_N, bool kDeep>
+template <int BLOCK_N>
 __global__ void __launch_bounds__(kWgThreads)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x,
                   const WgradParams p) {
-  using Cfg = WgradCfg<BLOCK_N, kDeep>;
+  using Cfg = WgradCfg<BLOCK_N>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
@@ -248,44 +247,32 @@ wgrad_reduce_rows_kernel(const float* __restrict__ ws, float* __restrict__ out, 
   }
 }
 
-template <int BLOCK_N, bool kDeep>
-static int launch_wgrad_cfg(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
-                            cudaStream_t stream) {
-  using Cfg = WgradCfg<BLOCK_N, kDeep>;
-  static bool configured = false;
-  if (!configured) {
-    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BLOCK_N, kDeep>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    configured = true;
-  }
-  dim3 grid(p.taps * p.m_tiles * p.n_tiles, splits);
-  DDPB_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BLOCK_N, kDeep>, grid, kWgThreads, Cfg::kSmemBytes, stream, tdy, tx, p));
-  return 0;
-}
-
 template <int BLOCK_N>
 static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
                         cudaStream_t stream) {
-  // Off by default: alone the deep ring is faster, but inside the training step a 198 KB CTA cannot
-  // share an SM with the main stream's BatchNorm-backward CTAs and the step got 15 us SLOWER
-  // (profiles/r1_call38_wgrad_deep_ring.txt).  DDPB_WGRAD_DEEP=1 selects it for standalone use.
-  static const int deep_ok = [] { const char* e = getenv("DDPB_WGRAD_DEEP"); return e ? atoi(e) : 0; }();
-  const long long ctas = static_cast<long long>(p.taps) * p.m_tiles * p.n_tiles * splits;
-  if (deep_ok && ctas <= sm_count()) return launch_wgrad_cfg<BLOCK_N, true>(tdy, tx, p, splits, stream);
-  return launch_wgrad_cfg<BLOCK_N, false>(tdy, tx, p, splits, stream);
+  using Cfg = WgradCfg<BLOCK_N>;
+  static bool configured = false;
+  if (!configured) {
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Cfg::kSmemBytes));
+    configured = true;
+  }
+  dim3 grid(p.taps * p.m_tiles * p.n_tiles, splits);
+  DDPB_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BLOCK_N>, grid, kWgThreads, Cfg::kSmemBytes, stream, tdy, tx, p));
+  return 0;
 }
 
-#include "conv_wgrad_taps.inl"
-#include "conv_wgrad_pair.inl"
-
-// Launch plan.  fused: the tap-fused cluster kernel (3x3 layers with C_out % 128 == 0) with
-// `cluster` CTAs per thread-block cluster and `groups` clusters per tile (global partial tiles
-// only when groups > 1); otherwise the one-tap kernel with `groups` pixel splits.
+// Launch plan: the one-tap kernel with `groups` pixel splits.
+//
+// Tried and removed (measured slower at the training shapes, batch 256; the logs stay under profiles/):
+//   * three taps per CTA with the split reduction over distributed shared memory inside a cluster:
+//     187-197 us for the eight layers against 159 us (r1_call43_wgrad_tap_fused.txt);
+//   * a cta_group::2 kernel (256 output channels x 128/256 input channels per CTA pair): 197 us against
+//     160 us (r2_call01_pair_modes_layer_times.txt) -- it doubles the partial-tile volume;
+//   * the whole shared memory as one deep ring for one CTA per SM: faster alone, 15 us slower inside the
+//     step (r1_call38_wgrad_deep_ring.txt).
 struct WgPlan {
-  bool fused;
-  bool pair;      // CTA-pair kernel (mode 2): tiles of 256 output channels x block_n input channels
   int block_n;
-  int cluster;
   int groups;
 };
 
@@ -307,56 +294,12 @@ static int legacy_splits(int P, int tiles) {
   return splits;
 }
 
-// 0 (default): one-tap kernel, global split reduction.  1: tap-fused cluster kernel.  Measured on
-// B200 at batch 256 (profiles/r1_call43_wgrad_tap_fused.txt): the fused kernel is correct and
-// deterministic but SLOWER -- 187 us (cluster 1) / 197 us (cluster 4) against 159 us for the eight
-// layers, 0.740 vs 0.697 ms per training step.  One 192 KB CTA per SM loses the overlap two
-// 97 KB CTAs give each other (prologue, epilogue, TMEM drain), and the MMA count is unchanged.
-static int g_wgrad_mode = -1;
-
 static WgPlan plan_wgrad(int N, int H, int W, int C_in, int C_out, int taps) {
-  if (g_wgrad_mode < 0) {
-    const char* e = getenv("DDPB_WGRAD_TAPS");
-    g_wgrad_mode = e ? atoi(e) : 0;
-  }
-  const int fused_ok = g_wgrad_mode == 1;
   WgPlan pl;
-  pl.pair = false;
-  const int P = N * H * W;
-  if (g_wgrad_mode == 2 && taps == 9 && C_out % 256 == 0 && C_in % 128 == 0) {
-    // CTA pairs: 2 x tiles x splits CTAs of <= 97 KB, two per SM -> about one wave
-    pl.pair = true;
-    pl.fused = false;
-    pl.block_n = (C_in % 256 == 0) ? 256 : 128;
-    pl.cluster = 1;
-    const int tiles = taps * (C_out / 256) * (C_in / pl.block_n);
-    const int pix_blocks = (P + kWgPix - 1) / kWgPix;
-    int splits = sm_count() / tiles;
-    if (splits > pix_blocks / 8) splits = pix_blocks / 8;
-    if (splits > 256) splits = 256;
-    if (splits < 1) splits = 1;
-    pl.groups = splits;
-    return pl;
-  }
   pl.block_n = (C_in % 128 == 0) ? 128 : 64;
   const int m_tiles = (C_out + 127) / 128;
   const int n_tiles = C_in / pl.block_n;
-  pl.fused = fused_ok && taps == 9 && C_out % 128 == 0;
-  if (!pl.fused) {
-    pl.cluster = 1;
-    pl.groups = legacy_splits(P, taps * m_tiles * n_tiles);
-    return pl;
-  }
-  // one CTA per SM (its ring fills the shared memory): as many pixel splits as there are SMs per
-  // tile, at least 8 pipeline steps each; up to four of them share a cluster
-  const int tiles = kWg3Taps * m_tiles * n_tiles;
-  const int pix_blocks = (P + kWgPix - 1) / kWgPix;
-  int total = sm_count() / tiles;
-  if (total > pix_blocks / 8) total = pix_blocks / 8;
-  if (total < 1) total = 1;
-  static const int max_cluster = [] { const char* e = getenv("DDPB_WGRAD_CLUSTER"); return e ? atoi(e) : 4; }();
-  pl.cluster = (total >= 4 && max_cluster >= 4) ? 4 : ((total >= 2 && max_cluster >= 2) ? 2 : 1);
-  pl.groups = total / pl.cluster;
+  pl.groups = legacy_splits(N * H * W, taps * m_tiles * n_tiles);
   return pl;
 }
 
@@ -364,15 +307,9 @@ static WgPlan plan_wgrad(int N, int H, int W, int C_in, int C_out, int taps) {
 
 using namespace ddpb;
 
-// 0: one-tap kernel (default); 1: tap-fused kernel with the split reduction inside a cluster;
-// 2: CTA-pair (cta_group::2) kernel where the shape allows (C_out % 256 == 0, C_in % 128 == 0).
-// Changes ddpb_conv_wgrad_scratch_elems() for later calls.
-extern "C" void ddpb_conv_wgrad_set_mode(int mode) { ddpb::g_wgrad_mode = (mode >= 0 && mode <= 2) ? mode : 0; }
-
 // Number of pixel splits the launcher will use for this shape (so callers can size scratch).
 extern "C" int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps) {
-  const WgPlan pl = plan_wgrad(N, H, W, C_in, C_out, taps);
-  return pl.cluster * pl.groups;
+  return plan_wgrad(N, H, W, C_in, C_out, taps).groups;
 }
 
 // Floats of scratch a launch with this plan writes.  `dense`: dw takes every column with no row padding
@@ -410,10 +347,7 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
   const WgPlan pl = plan_wgrad(N, H, W, C_in, C_out, taps);
   const int block_n = pl.block_n;
   const int splits = pl.groups;   // partial tiles in global memory
-  DDPB_REQUIRE(!pl.fused || dw_cols_valid == taps * C_in, "conv_wgrad: a 3x3 layer's dw must take all %d columns",
-               taps * C_in);
-  const bool direct = (splits == 1 && C_out >= 128 && dw_cols_valid == taps * C_in &&
-                       (pl.fused || dw_ld == taps * C_in));
+  const bool direct = (splits == 1 && C_out >= 128 && dw_cols_valid == taps * C_in && dw_ld == taps * C_in);
   DDPB_REQUIRE(dw_cols_valid > 0 && dw_cols_valid <= taps * C_in && dw_ld >= dw_cols_valid,
                "conv_wgrad: bad dw layout (cols_valid %d, ld %d, taps*C_in %d)", dw_cols_valid, dw_ld, taps * C_in);
   {
@@ -448,7 +382,7 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
   p.C_in = C_in;
   p.C_out = C_out;
   p.taps = taps;
-  p.m_tiles = pl.pair ? C_out / 256 : (C_out + 127) / 128;
+  p.m_tiles = (C_out + 127) / 128;
   p.n_tiles = C_in / block_n;
   p.bh = bh;
   p.bn = bn;
@@ -464,16 +398,8 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
     p.out = scratch;
     p.out_split_stride = rows * taps * C_in;
   }
-  int rc;
-  if (pl.pair)
-    rc = (block_n == 256) ? launch_wgrad_pair<256>(tdy, tx, p, splits, stream)
-                          : launch_wgrad_pair<128>(tdy, tx, p, splits, stream);
-  else if (pl.fused)
-    rc = (block_n == 128) ? launch_wgrad3<128>(tdy, tx, p, pl.cluster, pl.groups, stream)
-                          : launch_wgrad3<64>(tdy, tx, p, pl.cluster, pl.groups, stream);
-  else
-    rc = (block_n == 128) ? launch_wgrad<128>(tdy, tx, p, splits, stream)
-                          : launch_wgrad<64>(tdy, tx, p, splits, stream);
+  const int rc = (block_n == 128) ? launch_wgrad<128>(tdy, tx, p, splits, stream)
+                                  : launch_wgrad<64>(tdy, tx, p, splits, stream);
   if (rc) return rc;
   if (!direct) {
     const bool dense = (dw_cols_valid == taps * C_in && dw_ld == taps * C_in && C_out >= 128);

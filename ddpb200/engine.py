@@ -209,7 +209,6 @@ class VGGEngine:
         self.image_hw = image_hw
         self._tl = None
         self._tl_labels = []
-        self.dgrad_sum_in_kernel = os.environ.get("DDPB_DGRAD_FIN_IN_KERNEL", "0") == "1"
         if share_from is None:
             self.repack(full=True)
             _register_engine(self)
@@ -340,13 +339,8 @@ class VGGEngine:
                              cols_valid=cols, out_ld=cols, scratch=self.wgrad_scratch)
                 self.mark(f"L{li} wgrad")
             if li > 0:
-                # sync: a spare zeroed word of this layer's statistics slot lets a split-K dgrad sum its
-                # partial tiles in-kernel.  Off by default: a kernel with a grid barrier cannot start
-                # until every SM has room, and the weight-gradient CTAs of the side stream hold some
-                # (measured 0.691 -> 0.718 ms/step with it, profiles/r1_call39_*).
-                sync = self.bsums[li][2 * L.c_out + 16:2 * L.c_out + 17] if self.dgrad_sum_in_kernel else None
                 K.conv_dgrad(self.dconv[li], self.w_f[li], N, L.H, L.W, L.c_in, L.c_out, out=self.dact[li - 1],
-                             scratch=self.fprop_scratch, sync=sync)
+                             scratch=self.fprop_scratch)
                 self.mark(f"L{li} dgrad")
             if after_layer is not None:
                 after_layer(li, side_events[-1:] if side_stream is not None else [])
@@ -369,7 +363,9 @@ class VGGEngine:
                 n += 2              # split-K finalize + separate BatchNorm forward
             if li > 0 and K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_out, L.c_in, 9):
                 n += 1
-            n += 2                  # BatchNorm backward: reduce + apply
+            out_pix = B * L.H * L.W // (4 if L.pool else 1)
+            owner = L.c_out // 8 >= 32 and out_pix * (5 if L.pool else 2) * 16 <= 48 * 1024
+            n += 1 if owner else 2  # BatchNorm backward: channel-owner kernel, or reduce + apply
             n += 1                  # wgrad
             if K.conv_wgrad_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps):
                 n += 1              # split-K reduce

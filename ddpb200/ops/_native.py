@@ -49,7 +49,6 @@ _SIGNATURES = {
     "ddpb_bn_bwd_set_fused": [c_int],
     "ddpb_stamp": [c_void, c_void],
     "ddpb_publish_scalar": [c_void, c_void, c_void, c_void],
-    "ddpb_conv_wgrad_set_mode": [c_int],
     "ddpb_set_pdl": [c_int],
     "ddpb_get_pdl": [],
     "ddpb_fc_ce_fwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_int,
@@ -57,8 +56,7 @@ _SIGNATURES = {
     "ddpb_fc_bwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_void,
                     c_void, c_void],
     "ddpb_sgd_step": [c_void, c_void, c_void, c_void, c_ll, c_float, c_float, c_float, c_float, c_void],
-    "ddpb_conv_dgrad": [c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_void, c_ll, c_void,
-                        c_void],
+    "ddpb_conv_dgrad": [c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_void, c_ll, c_void],
     "ddpb_pack_weights": [c_int, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void],
     "ddpb_first_layer_operand_f32": [c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_int, c_void],
     "ddpb_first_layer_operand_u8": [c_void, c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_int, c_void,

@@ -102,10 +102,8 @@ def conv_bn_relu_pool_fwd(x, w, bias, gamma, beta, N, H, W, C_in, C_out, taps, p
 
 def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, C_in: int, C_out: int, *,
                out: torch.Tensor | None = None, block_n: int = 0, scratch: torch.Tensor | None | bool = True,
-               sync: torch.Tensor | None = None, stream=None) -> torch.Tensor:
-    """O2: dx[P, C_in] from dy[P, C_out] and the SAME bf16 filter pack fprop uses ([C_out, 9*C_in]).
-    ``sync``: a ZEROED 4-byte tensor (left non-zero); with it a split-K launch sums its partial tiles
-    inside the conv kernel instead of launching a finalize kernel."""
+               stream=None) -> torch.Tensor:
+    """O2: dx[P, C_in] from dy[P, C_out] and the SAME bf16 filter pack fprop uses ([C_out, 9*C_in])."""
     nat.require_cuda(dy, w_fprop)
     assert dy.dtype == torch.bfloat16 and w_fprop.dtype == torch.bfloat16
     assert dy.numel() >= N * H * W * C_out and w_fprop.numel() == C_out * 9 * C_in
@@ -116,9 +114,8 @@ def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, 
         scratch = torch.empty(need, dtype=torch.float32, device=dy.device) if need else None
     elif scratch is False:
         scratch = None
-    assert sync is None or (sync.is_cuda and sync.element_size() == 4 and sync.numel() >= 1)
     rc = nat.load().ddpb_conv_dgrad(nat.ptr(dy), nat.ptr(w_fprop), nat.ptr(out), N, H, W, C_in, C_out, block_n,
-                                    nat.ptr(scratch), _numel(scratch), nat.ptr(sync), _s(stream))
+                                    nat.ptr(scratch), _numel(scratch), _s(stream))
     nat.check(rc, "ddpb_conv_dgrad")
     return out
 
@@ -132,13 +129,6 @@ def conv_wgrad_scratch_elems(N, H, W, C_in, C_out, taps=9, cols_valid: int | Non
     cols_valid = taps * C_in if cols_valid is None else cols_valid
     out_ld = cols_valid if out_ld is None else out_ld
     return int(nat.load().ddpb_conv_wgrad_scratch_elems_ld(N, H, W, C_in, C_out, taps, cols_valid, out_ld))
-
-
-def conv_wgrad_set_mode(mode: int) -> None:
-    """0: one-tap weight-gradient kernel with a global split reduction (default, measured faster);
-    1: three taps per CTA, pixel splits summed through distributed shared memory in a cluster;
-    2: CTA-pair (cta_group::2) kernel for C_out % 256 == 0 and C_in % 128 == 0 (experimental)."""
-    nat.load().ddpb_conv_wgrad_set_mode(int(mode))
 
 
 def conv_wgrad_splits(N, H, W, C_in, C_out, taps=9) -> int:

@@ -59,11 +59,9 @@ int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const float* bias, 
 
 /* O2: data gradient of the same convolution (autograd of part1/model.py:18-23).
  * dx[N*H*W][C_in] from dy[..][C_out] and the SAME filter pack fprop reads (no transposed copy).
- * scratch sized with ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n).
- * sync: one zeroed 32-bit device word (left non-zero) or null; with it a split-K launch sums its
- * partial tiles inside the same kernel after a grid barrier instead of in a second kernel. */
+ * scratch sized with ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n). */
 int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out, int block_n,
-                    float* scratch, long long scratch_elems, unsigned int* sync, void* stream);
+                    float* scratch, long long scratch_elems, void* stream);
 
 /* O3: weight gradient.  dw (fp32 [C_out][dw_ld]) gets its first dw_cols_valid (<= taps*C_in)
  * columns per row.  scratch: scratch_elems floats of device memory for the split reduction over
@@ -77,13 +75,6 @@ long long ddpb_conv_wgrad_scratch_elems(int N, int H, int W, int C_in, int C_out
 long long ddpb_conv_wgrad_scratch_elems_ld(int N, int H, int W, int C_in, int C_out, int taps, int dw_cols_valid,
                                            int dw_ld);
 int ddpb_conv_wgrad_splits(int N, int H, int W, int C_in, int C_out, int taps);
-/* 0 (default): one tap per CTA, split reduction through global memory.  1: three taps per CTA and
- * the split reduction over distributed shared memory inside a thread-block cluster (measured
- * slower on B200 at the training shapes; kept selectable).  2: CTA-pair kernel (cta_group::2,
- * 256 output channels x 128/256 input channels per pair) where C_out % 256 == 0 and
- * C_in % 128 == 0 -- experimental, see docs/NEXT.md.  Changes the scratch size. */
-void ddpb_conv_wgrad_set_mode(int mode);
-
 /* No counterpart in the reference.  ddpb_conv_wgrad for callers that must not allocate device
  * memory (a loop that cannot take cudaMalloc's device-wide synchronisation, a process whose
  * memory was handed to another allocator, a host application that forbids allocator calls):
@@ -98,9 +89,9 @@ int ddpb_conv_wgrad_static(const void* dy, const void* x, float* dw, int N, int 
                            int taps, int dw_cols_valid, int dw_ld, void* stream);
 long long ddpb_conv_wgrad_static_max_elems(void);
 
-/* Tuning / profiling hooks for the conv launch planner (kernel: 0 one tile per CTA, 1 CTA
- * pair with cta_group::2, 2 persistent, 3 persistent CTA pair -- no split-K, no 64-wide tile:
- * such shapes fall back to 2; -1 = automatic = 2). */
+/* Tuning / profiling hooks for the conv launch planner (kernel: 0 one tile per CTA, 2 persistent,
+ * 3 persistent CTA pair with cta_group::2 -- no split-K, no 64-wide tile: such shapes fall back
+ * to 2; -1 = automatic = 2). */
 void ddpb_conv_force(int kernel, int block_n, int splits);
 void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3);
 void ddpb_conv_debug_timing(unsigned long long* per_cta_stamps);   /* 8 slots per CTA, see bench/conv_probe2.py */

@@ -89,19 +89,26 @@ def test_conv_dgrad_via_rotated_filters(shape):
     assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
 
 
-# CTA-pair (cta_group::2) kernel, every legal tile / split combination, fprop and dgrad
-PAIR_CASES = [((8, 8, 8, 128, 256), 128, 1), ((8, 8, 8, 128, 256), 256, 1), ((8, 8, 8, 256, 256), 256, 2),
+# every legal tile / split combination, fprop and dgrad
+BASE_CASES = [((8, 8, 8, 128, 256), 128, 1), ((8, 8, 8, 128, 256), 256, 1), ((8, 8, 8, 256, 256), 256, 2),
               ((3, 8, 8, 128, 128), 128, 1), ((4, 16, 16, 64, 128), 128, 1), ((32, 4, 4, 256, 512), 256, 3),
               ((37, 2, 2, 512, 512), 128, 4), ((2, 32, 32, 64, 128), 128, 1)]
 
 
-PERSIST_CASES = PAIR_CASES + [((4, 32, 32, 64, 64), 64, 1), ((64, 8, 8, 128, 128), 128, 1),
+PERSIST_CASES = BASE_CASES + [((4, 32, 32, 64, 64), 64, 1), ((64, 8, 8, 128, 128), 128, 1),
                               ((300, 4, 4, 256, 256), 128, 2), ((8, 32, 32, 64, 128), 64, 1)]
 
+# persistent CTA-pair kernel (cta_group::2; no split-K, tiles of 128 / 256 columns): one pair tile per cluster, an
+# odd number of 128-pixel tiles, several tiles per cluster (accumulator ring wraps: 4 buffers at 128 columns, 2 at 256)
+PAIR_PERSIST_CASES = [((8, 8, 8, 128, 256), 128, 1), ((8, 8, 8, 128, 256), 256, 1), ((3, 8, 8, 128, 128), 128, 1),
+                      ((512, 16, 16, 64, 128), 128, 1), ((1024, 8, 8, 128, 256), 256, 1), ((256, 4, 4, 256, 512), 256, 1)]
 
-@pytest.mark.parametrize("case", [(1, c) for c in PAIR_CASES] + [(2, c) for c in PERSIST_CASES])
+
+@pytest.mark.parametrize("case", [(0, c) for c in BASE_CASES] + [(2, c) for c in PERSIST_CASES] +
+                         [(3, c) for c in PAIR_PERSIST_CASES])
 def test_conv_kernel_variants_fprop_and_dgrad(case):
-    """mode 1 = CTA pair (cta_group::2), mode 2 = persistent kernel; both against the oracle."""
+    """mode 0 = one tile per CTA, mode 2 = persistent kernel (the default), mode 3 = persistent CTA pair
+    (cta_group::2, opt-in: measured no faster, DESIGN.md par. 7); all against the oracle."""
     mode, ((N, H, W, Ci, Co), bn, splits) = case
     x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
     w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
@@ -109,6 +116,7 @@ def test_conv_kernel_variants_fprop_and_dgrad(case):
     dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
     try:
         K.conv_force(mode, bn, splits)
+        assert tuple(K.conv_plan(N, H, W, Ci, Co, 9))[:2] == (mode, bn)
         stats = torch.zeros(2, Co, device=DEV)
         y = K.conv_fprop(x, w, b, N, H, W, Ci, Co, stats=stats)
         dx = K.conv_dgrad(dy, w, N, H, W, Ci, Co) if Ci % bn == 0 else None
@@ -131,23 +139,6 @@ def test_conv_dgrad_from_fprop_pack(shape):
     assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
 
 
-@pytest.mark.parametrize("shape", [(256, 2, 2, 512, 512), (96, 2, 2, 512, 256), (64, 4, 4, 128, 512)])
-def test_conv_dgrad_split_k_summed_in_kernel(shape):
-    """With a zeroed sync word the split-K partial tiles are summed inside the persistent kernel
-    (grid barrier) -- same result as the separate finalize kernel, twice in a row."""
-    N, H, W, Ci, Co = shape
-    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
-    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Co) ** 0.5).bfloat16()
-    assert K.conv_fprop_scratch_elems(N, H, W, Co, Ci, 9) > 0, "shape is meant to split K"
-    ref = K.conv_dgrad(dy, w, N, H, W, Ci, Co)
-    for _ in range(2):
-        sync = torch.zeros(1, dtype=torch.int32, device=DEV)
-        dx = K.conv_dgrad(dy, w, N, H, W, Ci, Co, sync=sync)
-        assert sync.item() != 0, "the in-kernel finalize did not run"
-        assert torch.equal(dx, ref)
-    assert _rel_err(dx, R.conv_dgrad(dy, w, N, H, W, Ci, Co)) < 1e-2
-
-
 @pytest.mark.parametrize("shape", CONV_SHAPES + [(64, 32, 32, 64, 128)])
 def test_conv_wgrad(shape):
     N, H, W, Ci, Co = shape
@@ -160,21 +151,16 @@ def test_conv_wgrad(shape):
 
 @pytest.mark.parametrize("shape", [(256, 8, 8, 128, 256), (256, 8, 8, 256, 256), (256, 4, 4, 256, 512),
                                    (256, 4, 4, 512, 512), (256, 2, 2, 512, 512), (100, 16, 16, 64, 128)])
-def test_conv_wgrad_tap_fused_cluster_reduction(shape):
-    """The training shapes: three taps per CTA, pixel splits summed through distributed shared
-    memory inside a cluster (plus global groups for the long pixel ranges); deterministic."""
+def test_conv_wgrad_training_shapes_deterministic(shape):
+    """The training shapes at batch 256 (split reductions of 1..32 partial tiles): fixed summation
+    order, so two launches agree bitwise."""
     N, H, W, Ci, Co = shape
     x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
     dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
     ref = R.conv_wgrad(dy, x, N, H, W, Ci, Co)
-    try:
-        K.conv_wgrad_set_mode(1)
-        dw = K.conv_wgrad(dy, x, N, H, W, Ci, Co)
-        assert _rel_err(dw, ref) < 2e-3
-        assert torch.equal(dw, K.conv_wgrad(dy, x, N, H, W, Ci, Co))
-    finally:
-        K.conv_wgrad_set_mode(0)
-    assert _rel_err(K.conv_wgrad(dy, x, N, H, W, Ci, Co), ref) < 2e-3   # default kernel, same shapes
+    dw = K.conv_wgrad(dy, x, N, H, W, Ci, Co)
+    assert _rel_err(dw, ref) < 2e-3
+    assert torch.equal(dw, K.conv_wgrad(dy, x, N, H, W, Ci, Co))
 
 
 def test_conv_wgrad_first_layer_compact():
@@ -418,3 +404,28 @@ def test_conv_wgrad_padded_dw_goes_through_scratch_even_without_a_split():
     rc = nat.load().ddpb_conv_wgrad(nat.ptr(dy), nat.ptr(x), nat.ptr(out), nat.ptr(small), small.numel(), N, H, W, Ci,
                                     Co, 9, 9 * Ci, ld, nat.stream_ptr(None))
     assert rc != 0 and b"scratch" in nat.load().ddpb_last_error()
+
+
+@pytest.mark.parametrize("pool", [False, True])
+@pytest.mark.parametrize("case", [((16, 16, 16, 64, 128), 128), ((37, 8, 8, 128, 256), 256), ((256, 8, 8, 256, 256), 256),
+                                  ((64, 4, 4, 256, 512), 128)])
+def test_persistent_cta_pair_conv_with_batchnorm_tail(case, pool):
+    """Mode 3 (persistent cta_group::2 kernel, opt-in) with the BatchNorm + ReLU (+pool) tail after the grid barrier."""
+    (N, H, W, Ci, Co), bn = case
+    torch.manual_seed(1)
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
+    b = torch.randn(Co, device=DEV) * 0.1
+    gamma = torch.rand(Co, device=DEV) + 0.5
+    beta = torch.randn(Co, device=DEV) * 0.2
+    try:
+        K.conv_force(3, bn, 1)
+        conv_out, act, saved = K.conv_bn_relu_pool_fwd(x, w, b, gamma, beta, N, H, W, Ci, Co, 9, pool)
+        torch.cuda.synchronize()
+    finally:
+        K.conv_force(-1, -1, -1)
+    assert _rel_err(conv_out, R.conv_fprop(x, w, b, N, H, W, Ci, Co)) < 1e-2
+    assert _rel_err(act, R.bn_relu_pool_fwd(conv_out, gamma, beta, N, H, W, pool)) < 1e-2
+    cf = conv_out.float()
+    assert torch.allclose(saved[0], cf.mean(0), rtol=1e-3, atol=1e-3)
+    assert torch.allclose(saved[1], (cf.var(0, unbiased=False) + 1e-5).rsqrt(), rtol=2e-3)
