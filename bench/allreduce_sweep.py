@@ -62,9 +62,40 @@ def main():
         row["ours_busbw_gbs"] = bus / best / 1e3
         row["nccl_busbw_gbs"] = bus / row["nccl_us"] / 1e3
         row["ours_frac_of_nvlink_770"] = row["ours_busbw_gbs"] / NVLINK_GBS
+        # Rooflines (bytes that must cross one GPU's NVLink per direction / 770 GB/s):
+        #   two-shot over peer memory: 2 (W-1)/W S;   NVLS (ld_reduce of the own slice + multicast store): S + S/W
+        #   (SURVEY.md par. 5.8) -- the NVLS kernel is scored against ITS OWN, lower, roof
+        roof_p2p_us = bus / NVLINK_GBS / 1e3
+        roof_nvls_us = (nbytes + nbytes / world) / NVLINK_GBS / 1e3
+        nvls = [v for k, v in row.items() if k.startswith("ours_nvls")]
+        p2p = [v for k, v in row.items() if k.startswith("ours_p2p")]
+        row["roof_p2p_two_shot_us"], row["roof_nvls_us"] = roof_p2p_us, roof_nvls_us
+        if nvls:
+            row["ours_nvls_frac_of_nvls_roof"] = roof_nvls_us / min(nvls)
+        row["ours_p2p_frac_of_p2p_roof"] = roof_p2p_us / min(p2p)
+        # the batched multi-range kernel on the reference's per-parameter shape is timed once below
         rows.append(row)
+    # the reference's part2b shape: 34 per-parameter all-reduces (32 of them <= 2 KB) -- one launch per tensor
+    # versus the batched table kernel (one launch, small tensors one-shot)
+    import ddpb200
+    from ddpb200.engine import ALIGN
+
+    sizes = [p.numel() for p in ddpb200.VGG11().parameters()]
+    ranges, off = [], 0
+    for nel in sizes:
+        ranges.append((off, (nel + 3) // 4 * 4))
+        off += (nel + ALIGN - 1) // ALIGN * ALIGN
+    mc = symm.has_multicast
+    per_param = {
+        "what": "34 parameter tensors of VGG-11 (part2b shape)",
+        "one_launch_per_tensor_us": timed(lambda: [symm.allreduce_avg(o, n, blocks=32, use_mc=mc) for o, n in ranges], iters=10),
+        "batched_table_kernel_us": timed(lambda: symm.allreduce_multi(ranges, blocks=128, use_mc=mc), iters=30),
+        "one_fused_range_us": timed(lambda: symm.allreduce_avg(0, off, blocks=128 if not mc else 32, use_mc=mc), iters=30),
+        "nccl_34_calls_us": timed(lambda: [dist.all_reduce(nccl_buf[o:o + n]) for o, n in ranges], iters=10),
+    }
     if rank == 0:
-        out = {"world": world, "backend": symm.backend, "multicast": symm.has_multicast, "rows": rows}
+        out = {"world": world, "backend": symm.backend, "multicast": symm.has_multicast, "rows": rows,
+               "per_parameter": per_param}
         print(json.dumps(out, indent=1))
         p = Path(os.environ.get("DDPB_SWEEP_OUT", "gpurun_out/allreduce_sweep.json"))
         p.parent.mkdir(parents=True, exist_ok=True)

@@ -631,7 +631,7 @@ static Bn2Plan bn2_plan(long long out_pix, int C) {
   Bn2Plan pl;
   pl.n_slices = C / (kSliceGroups * 8);
   // one resident wave (two CTAs per SM over all slices), at least two 32-pixel passes per CTA
-  long long ranges = (2LL * sm_count()) / pl.n_slices;
+  long long ranges = (static_cast<long long>(DDPB_BN2_WAVES) * sm_count()) / pl.n_slices;
   const long long max_ranges = (out_pix + 2 * kBn2Rows - 1) / (2 * kBn2Rows);
   if (ranges > max_ranges) ranges = max_ranges;
   if (ranges < 1) ranges = 1;
@@ -664,8 +664,17 @@ __device__ __forceinline__ int bn2_load(const __nv_bfloat16* __restrict__ x, con
   return base;
 }
 
+#ifndef DDPB_BN2_REDUCE_MINB
+#define DDPB_BN2_REDUCE_MINB 3
+#endif
+#ifndef DDPB_BN2_APPLY_MINB
+#define DDPB_BN2_APPLY_MINB 2
+#endif
+#ifndef DDPB_BN2_WAVES
+#define DDPB_BN2_WAVES 2
+#endif
 template <bool kPool>
-__global__ void __launch_bounds__(kBn2Threads, 3)
+__global__ void __launch_bounds__(kBn2Threads, DDPB_BN2_REDUCE_MINB)
 bn_bwd2_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                       const float* __restrict__ saved, const float* __restrict__ gamma,
                       const float* __restrict__ beta, float* __restrict__ sums, float* __restrict__ partials,
@@ -792,7 +801,7 @@ bn_bwd2_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
 }
 
 template <bool kPool>
-__global__ void __launch_bounds__(kBn2Threads, 2)
+__global__ void __launch_bounds__(kBn2Threads, DDPB_BN2_APPLY_MINB)
 bn_bwd2_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                      const float* __restrict__ saved, const float* __restrict__ gamma,
                      const float* __restrict__ beta, const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx,
