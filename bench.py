@@ -55,8 +55,8 @@ def parse():
     ap.add_argument("--conv-mode", type=int, default=-1,
                     help="conv kernel of fprop/dgrad: -1 automatic (persistent), 1 CTA pair, 3 persistent CTA pair")
     ap.add_argument("--comm-blocks", type=int, default=None)
-    ap.add_argument("--bucket-layout", choices=["per_layer", "reference", "balanced"], default="reference")
-    ap.add_argument("--comm-threads", type=int, default=512)
+    ap.add_argument("--bucket-layout", choices=["per_layer", "reference", "balanced"], default="balanced")
+    ap.add_argument("--comm-threads", type=int, default=None)
     ap.add_argument("--bucket-mb", type=float, default=None, help="explicit bucket cap in MiB (first bucket: min(1, cap))")
     ap.add_argument("--no-fuse-sgd", action="store_true", help="run SGD as its own full-width kernel after the sync")
     ap.add_argument("--no-overlap-sgd", action="store_true",

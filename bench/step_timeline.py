@@ -20,7 +20,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--no-overlap-wgrad", action="store_true")
     ap.add_argument("--mode", default="ddp", help="sync mode when launched under torchrun with several ranks")
-    ap.add_argument("--bucket-layout", default="reference")
+    ap.add_argument("--bucket-layout", default="balanced")
     a = ap.parse_args()
     import os
 

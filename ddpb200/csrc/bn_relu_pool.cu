@@ -620,6 +620,17 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
 //           A*sum(x) + Bc*P evaluated from the sums: analytically zero (BatchNorm removes the channel
 //           mean; SURVEY.md par. 2.5), numerically fp32 rounding noise like the reference's value.
 // ------------------------------------------------------------------------------------------
+// CTAs per SM the two kernels are compiled for / resident waves of the launch (measured: 3 / 2 / 2 is best,
+// more CTAs per SM spill and run 1.5-1.8x slower, profiles/r2_call18_*)
+#ifndef DDPB_BN2_REDUCE_MINB
+#define DDPB_BN2_REDUCE_MINB 3
+#endif
+#ifndef DDPB_BN2_APPLY_MINB
+#define DDPB_BN2_APPLY_MINB 2
+#endif
+#ifndef DDPB_BN2_WAVES
+#define DDPB_BN2_WAVES 2
+#endif
 constexpr int kBn2Threads = 256;
 constexpr int kBn2Rows = kBn2Threads / kSliceGroups;   // 32 output pixels per CTA pass
 
@@ -664,15 +675,6 @@ __device__ __forceinline__ int bn2_load(const __nv_bfloat16* __restrict__ x, con
   return base;
 }
 
-#ifndef DDPB_BN2_REDUCE_MINB
-#define DDPB_BN2_REDUCE_MINB 3
-#endif
-#ifndef DDPB_BN2_APPLY_MINB
-#define DDPB_BN2_APPLY_MINB 2
-#endif
-#ifndef DDPB_BN2_WAVES
-#define DDPB_BN2_WAVES 2
-#endif
 template <bool kPool>
 __global__ void __launch_bounds__(kBn2Threads, DDPB_BN2_REDUCE_MINB)
 bn_bwd2_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,

@@ -61,27 +61,42 @@ __device__ __forceinline__ uint32_t cas_acquire_sys(uint32_t* addr, uint32_t cmp
   return old;
 }
 
-// Cross-GPU barrier for one CTA: thread p signals peer p and waits for peer p's signal.
-// Flags toggle 0 -> 1 -> 0, so the pad needs no reset between launches or graph replays.
+__device__ __forceinline__ void st_release_sys_u32(uint32_t* addr, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* addr) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+
+// Cross-GPU barrier for one CTA.  Word [slot][q] of a rank's signal pad is written only by rank q; word
+// [slot][own rank] is the rank's own barrier count for that slot.  Barrier number e of a slot: every rank
+// stores e into "its" word on every peer (a posted release store: no round trip, unlike the CAS toggle of
+// round 1, whose remote atomics cost ~12 us per barrier) and waits until every peer's word in its own pad
+// has reached e.  The counts only grow, so a rank that runs ahead into barrier e + 1 cannot disturb a peer
+// still waiting for e; all ranks issue the same barrier sequence per slot, and the state lives in the pad,
+// so CUDA-graph replays continue the count.  (Wrap-around after 2^32 barriers per slot is handled by the
+// signed difference.)
 __device__ __forceinline__ void peer_barrier(const CommCtx& c, int slot) {
   __syncthreads();
   if (threadIdx.x < c.world) {
     const int peer = threadIdx.x;
-    __threadfence_system();
-    uint32_t* theirs = c.sig[peer] + slot * kMaxRanks + c.rank;
-    uint32_t* mine = c.sig[c.rank] + slot * kMaxRanks + peer;
-    const unsigned long long t0 = global_timer_ns();
-    uint32_t spins = 0;
-    while (cas_release_sys(theirs, 0u, 1u) != 0u) {
-      if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_COMM_TIMEOUT_NS) {
-        printf("ddpb200: rank %d timed out signalling rank %d (slot %d)\n", c.rank, peer, slot);
-        __trap();
-      }
-    }
-    while (cas_acquire_sys(mine, 1u, 0u) != 1u) {
-      if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_COMM_TIMEOUT_NS) {
-        printf("ddpb200: rank %d timed out waiting for rank %d (slot %d)\n", c.rank, peer, slot);
-        __trap();
+    uint32_t* mine = c.sig[c.rank] + slot * kMaxRanks;
+    const uint32_t epoch = mine[c.rank] + 1u;      // same value in every participating thread
+    __syncwarp(__activemask());
+    __threadfence_system();                        // this CTA's earlier writes (ordered by the barrier above)
+    if (peer == c.rank) {
+      mine[c.rank] = epoch;
+    } else {
+      st_release_sys_u32(c.sig[peer] + slot * kMaxRanks + c.rank, epoch);
+      const unsigned long long t0 = global_timer_ns();
+      uint32_t spins = 0;
+      while (static_cast<int32_t>(ld_acquire_sys_u32(mine + peer) - epoch) < 0) {
+        if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_COMM_TIMEOUT_NS) {
+          printf("ddpb200: rank %d timed out waiting for rank %d (slot %d, barrier %u)\n", c.rank, peer, slot, epoch);
+          __trap();
+        }
       }
     }
     __threadfence_system();

@@ -25,11 +25,12 @@ constexpr int kWgThreads = 192;
 constexpr int kWgPix = 64;                    // pixels per pipeline stage
 constexpr int kWgBoxBytes = kWgPix * 128;     // one (64 ch x 64 px) box = 8 KB
 
-// <= 97 KB of shared memory: two CTAs per SM share the tensor pipe (the ring of one CTA is latency
-// bound: ~1.1 us TMA round trip over 3 stages).
-template <int BLOCK_N>
+// kDeep = false: <= 97 KB of shared memory, two CTAs per SM share the tensor pipe (the ring of one CTA is
+// latency bound: ~1.1 us TMA round trip over 3 stages).  kDeep = true, for grids of at most one CTA per SM
+// (nobody to share with): the ring is twice as deep.
+template <int BLOCK_N, bool kDeep = false>
 struct WgradCfg {
-  static constexpr int kStages = (BLOCK_N >= 128) ? 3 : 4;
+  static constexpr int kStages = ((BLOCK_N >= 128) ? 3 : 4) * (kDeep ? 2 : 1);
   static constexpr int kABytes = 2 * kWgBoxBytes;                 // M = 128 channels of dY
   static constexpr int kBBytes = (BLOCK_N / 64) * kWgBoxBytes;    // N channels of X
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -48,11 +49,11 @@ struct WgradParams {
   int dup_m;            // C_out == 64: both halves of M read the same 64 channels
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool kDeep>
 __global__ void __launch_bounds__(kWgThreads)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x,
                   const WgradParams p) {
-  using Cfg = WgradCfg<BLOCK_N>;
+  using Cfg = WgradCfg<BLOCK_N, kDeep>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
@@ -247,19 +248,33 @@ wgrad_reduce_rows_kernel(const float* __restrict__ ws, float* __restrict__ out, 
   }
 }
 
-template <int BLOCK_N>
-static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
-                        cudaStream_t stream) {
-  using Cfg = WgradCfg<BLOCK_N>;
+template <int BLOCK_N, bool kDeep>
+static int launch_wgrad_cfg(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
+                            cudaStream_t stream) {
+  using Cfg = WgradCfg<BLOCK_N, kDeep>;
   static bool configured = false;
   if (!configured) {
-    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BLOCK_N, kDeep>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes));
     configured = true;
   }
   dim3 grid(p.taps * p.m_tiles * p.n_tiles, splits);
-  DDPB_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BLOCK_N>, grid, kWgThreads, Cfg::kSmemBytes, stream, tdy, tx, p));
+  DDPB_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BLOCK_N, kDeep>, grid, kWgThreads, Cfg::kSmemBytes, stream, tdy, tx, p));
   return 0;
+}
+
+static int g_wgrad_deep = -1;   // -1: environment DDPB_WGRAD_DEEP (default on), 0 / 1
+
+template <int BLOCK_N>
+static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
+                        cudaStream_t stream) {
+  if (g_wgrad_deep < 0) {
+    const char* e = getenv("DDPB_WGRAD_DEEP");
+    g_wgrad_deep = e ? atoi(e) : 1;
+  }
+  const long long ctas = static_cast<long long>(p.taps) * p.m_tiles * p.n_tiles * splits;
+  if (g_wgrad_deep && ctas <= sm_count()) return launch_wgrad_cfg<BLOCK_N, true>(tdy, tx, p, splits, stream);
+  return launch_wgrad_cfg<BLOCK_N, false>(tdy, tx, p, splits, stream);
 }
 
 // Launch plan: the one-tap kernel with `groups` pixel splits.

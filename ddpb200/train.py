@@ -44,8 +44,9 @@ class DistributedDataParallel(nn.Module):
     are slices of the flat gradient arena, reduced by a peer-memory kernel on a side stream."""
 
     def __init__(self, module: nn.Module, bucket_cap_mb: float | None = None):
-        """bucket_cap_mb=None: torch DDP's default layout (1 MiB first bucket, 25 MiB cap), as in the
-        reference; a number selects that cap instead."""
+        """bucket_cap_mb=None: the Trainer's default bucket layout ("balanced": measured faster on NVLink than
+        torch DDP's 1 MiB / 25 MiB default, which the reference ran with and which ``bucket_cap_mb=25`` or
+        ``Trainer(bucket_layout="reference")`` selects); a number selects that cap in torch's scheme."""
         super().__init__()
         self.module = module
         self.bucket_cap_mb = bucket_cap_mb

@@ -33,9 +33,9 @@ class Trainer:
     def __init__(self, model, mode: str = "single", batch_size: int = 256, lr: float = 0.1, momentum: float = 0.9,
                  weight_decay: float = 1e-4, rank: int = 0, world_size: int = 1, granularity: str = "fused",
                  use_multicast: bool | str = "auto", use_graph: bool = True, comm_blocks: int | None = None,
-                 bucket_layout: str = "reference", first_bucket_bytes: int | None = None,
+                 bucket_layout: str = "balanced", first_bucket_bytes: int | None = None,
                  bucket_bytes: int | None = None, symm_backend: str | None = None,
-                 fuse_sgd: bool = True, overlap_wgrad: bool = True, comm_threads: int = 512, optimizer=None,
+                 fuse_sgd: bool = True, overlap_wgrad: bool = True, comm_threads: int | None = None, optimizer=None,
                  overlap_sgd: bool = True, debug_poison_grads: bool = False):
         if mode not in MODES:
             raise ValueError(f"mode must be one of {MODES}")
@@ -58,10 +58,10 @@ class Trainer:
         # gradient arena with NaN.  The backward kernels overwrite all of it, so a reduction or an SGD
         # update that ran BEFORE its gradients were final would pick up NaNs and poison the parameters.
         self.debug_poison_grads = debug_poison_grads
-        # CTA size of the reductions that overlap backward (mode 'ddp').  256-thread CTAs would fit on
-        # an SM next to a persistent conv CTA, but measured on 2 GPUs (profiles/r1_call30_*) the lost
-        # reduction throughput costs more than the co-residency gains: 512-thread CTAs stay default.
-        self.comm_threads = comm_threads
+        # CTA size of the reductions that overlap backward (mode 'ddp'): 32 CTAs of 256 threads -- the same
+        # number of threads as round 1's 16 x 512, spread over twice as many SMs with half the footprint
+        # each (2 GPUs, balanced buckets: 0.754 ms per step against 0.772 with 16 x 512, profiles/r2_call23_*)
+        self.comm_threads = comm_threads if comm_threads is not None else (256 if mode == "ddp" else 512)
         self.device = next(model.parameters()).device
         self.distributed = world_size > 1 and mode != "single"
         self.iteration = 0
@@ -70,13 +70,14 @@ class Trainer:
         # on CPU it is also the object that is stepped, so its state_dict carries the momentum.
         self._hyper_source = optimizer
         self._graphs: dict[str, torch.cuda.CUDAGraph] = {}
-        # Bucket layout of mode 'ddp'.  "reference" (default) = torch DDP's defaults (1 MiB first
-        # bucket, 25 MiB cap: 9.46 / 27.16 / 0.31 MB for VGG-11).  "per_layer" closes a bucket after
-        # every parameter group.  Measured on 2 and 8 B200s (profiles/r1_call20*, r1_call21*) the
-        # three-bucket layout wins: NVLink moves all 36.9 MB in ~0.1 ms, so what matters is how
-        # few reduction kernels (two cross-GPU barriers each, CTAs taken from backward) run,
-        # not how early they start; re-measured with the final kernels in profiles/r1_call46_*.
-        # Explicit byte caps override both.
+        # Bucket layout of mode 'ddp'.  "balanced" (default): {fc, L7} {L6..L4} {L3, L2} {L1, L0} -- ~20 MiB
+        # middle buckets and a small last one.  "reference" = torch DDP's defaults, which the reference ran
+        # with (1 MiB first bucket, 25 MiB cap: 9.46 / 27.16 / 0.31 MB for VGG-11): its 27 MB bucket is only
+        # complete after layer 2's dgrad, so its reduction and SGD pass pile up on the memory-bound end of
+        # backward (profiles/r2_call09_2gpu_ddp_timeline_reference.txt).  "per_layer" closes a bucket after
+        # every parameter group.  2 GPUs, ms per step: balanced 0.761-0.772, reference 0.800-0.807,
+        # per_layer 0.830 (profiles/r2_call23_*; in round 1, with CAS barriers and a cooperative BatchNorm
+        # backward, reference was the best of the three).  Explicit byte caps override the layout.
         if bucket_layout not in ("per_layer", "reference", "balanced"):
             raise ValueError("bucket_layout must be 'per_layer', 'reference' or 'balanced'")
         tail_bytes = 0
@@ -121,10 +122,9 @@ class Trainer:
             use_multicast = bool(self.symm is not None and self.symm.has_multicast)
         self.use_mc = bool(use_multicast and self.symm is not None and self.symm.has_multicast)
         sms = torch.cuda.get_device_properties(self.device).multi_processor_count
-        # 2a / 2b reductions own the GPU (full width).  'ddp': CTAs of the reductions that overlap backward.  Each thread keeps four 16-byte
-        # requests in flight, so 16 CTAs already move a bucket in time and leave the SMs to backward
-        # (2 GPUs: 8 / 16 / 32 / 64 CTAs -> 0.797 / 0.787 / 0.802 / 0.826 ms per step, profiles/r1_call48_*)
-        self.comm_blocks = comm_blocks if comm_blocks is not None else (16 if self.mode == "ddp" else min(sms, 128))
+        # 2a / 2b reductions own the GPU (full width).  'ddp': CTAs of the reductions that overlap backward
+        # (2 GPUs, reference buckets, 512 threads: 8 / 16 / 32 CTAs -> 0.951 / 0.807 / 0.773 ms, profiles/r2_call23_*)
+        self.comm_blocks = comm_blocks if comm_blocks is not None else (32 if self.mode == "ddp" else min(sms, 128))
         self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1) if self.mode == "ddp" else None
         # wgrad runs on its own branch, concurrently with dgrad / the next BatchNorm backward
         self.wgrad_stream = torch.cuda.Stream(device=self.device) if self.overlap_wgrad else None
