@@ -263,6 +263,9 @@ static int launch_wgrad_cfg(const CUtensorMap& tdy, const CUtensorMap& tx, const
   return 0;
 }
 
+// Deep ring for single-wave grids: 159 -> 147 us for the eight layers, 0.681 -> 0.669 ms per step
+// (profiles/r2_call22_*).  Round 1 had measured it slower inside the step, because a 193 KB CTA kept the
+// then-cooperative BatchNorm backward from starting; that kernel is an ordinary launch now.
 static int g_wgrad_deep = -1;   // -1: environment DDPB_WGRAD_DEEP (default on), 0 / 1
 
 template <int BLOCK_N>
@@ -283,9 +286,7 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Wgr
 //   * three taps per CTA with the split reduction over distributed shared memory inside a cluster:
 //     187-197 us for the eight layers against 159 us (r1_call43_wgrad_tap_fused.txt);
 //   * a cta_group::2 kernel (256 output channels x 128/256 input channels per CTA pair): 197 us against
-//     160 us (r2_call01_pair_modes_layer_times.txt) -- it doubles the partial-tile volume;
-//   * the whole shared memory as one deep ring for one CTA per SM: faster alone, 15 us slower inside the
-//     step (r1_call38_wgrad_deep_ring.txt).
+//     160 us (r2_call01_pair_modes_layer_times.txt) -- it doubles the partial-tile volume.
 struct WgPlan {
   int block_n;
   int groups;
