@@ -620,6 +620,31 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
 //           A*sum(x) + Bc*P evaluated from the sums: analytically zero (BatchNorm removes the channel
 //           mean; SURVEY.md par. 2.5), numerically fp32 rounding noise like the reference's value.
 // ------------------------------------------------------------------------------------------
+// Pooling window of 4 x (8 channels, packed bf16): the element that wins the max-pool AFTER BatchNorm is the
+// largest x where gamma * rstd > 0 and the smallest where it is < 0, so it can be found on the raw bf16 values
+// with packed max instructions (sign bit flipped for the channels with a negative scale) instead of four
+// fp32 fma + compare + select chains per channel.  flip: 0x8000 in the halves whose scale is negative.
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+  const __nv_bfloat162 r = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+  return *reinterpret_cast<const uint32_t*>(&r);
+}
+__device__ __forceinline__ uint4 window_best(const uint4 (&v)[4], const uint4& flip) {
+  uint4 r;
+  r.x = bf16x2_max(bf16x2_max(v[0].x ^ flip.x, v[1].x ^ flip.x), bf16x2_max(v[2].x ^ flip.x, v[3].x ^ flip.x)) ^ flip.x;
+  r.y = bf16x2_max(bf16x2_max(v[0].y ^ flip.y, v[1].y ^ flip.y), bf16x2_max(v[2].y ^ flip.y, v[3].y ^ flip.y)) ^ flip.y;
+  r.z = bf16x2_max(bf16x2_max(v[0].z ^ flip.z, v[1].z ^ flip.z), bf16x2_max(v[2].z ^ flip.z, v[3].z ^ flip.z)) ^ flip.z;
+  r.w = bf16x2_max(bf16x2_max(v[0].w ^ flip.w, v[1].w ^ flip.w), bf16x2_max(v[2].w ^ flip.w, v[3].w ^ flip.w)) ^ flip.w;
+  return r;
+}
+__device__ __forceinline__ uint4 sign_flip_mask(const float (&sc)[8]) {
+  uint4 f;
+  f.x = (sc[0] < 0.f ? 0x8000u : 0u) | (sc[1] < 0.f ? 0x80000000u : 0u);
+  f.y = (sc[2] < 0.f ? 0x8000u : 0u) | (sc[3] < 0.f ? 0x80000000u : 0u);
+  f.z = (sc[4] < 0.f ? 0x8000u : 0u) | (sc[5] < 0.f ? 0x80000000u : 0u);
+  f.w = (sc[6] < 0.f ? 0x8000u : 0u) | (sc[7] < 0.f ? 0x80000000u : 0u);
+  return f;
+}
+
 // CTAs per SM the two kernels are compiled for / resident waves of the launch (measured: 3 / 2 / 2 is best,
 // more CTAs per SM spill and run 1.5-1.8x slower, profiles/r2_call18_*)
 #ifndef DDPB_BN2_REDUCE_MINB
@@ -705,6 +730,8 @@ bn_bwd2_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
     sh[j] = __ldg(beta + c) - mean * sc[j];
     a1[j] = a2[j] = 0.f;
   }
+  const uint4 flip = sign_flip_mask(sc);
+  (void)flip;
   for (int base = p_begin + prow; base < p_end; base += kBn2Rows * kU) {
     uint4 v[kU][kWin], d[kU];
     int ipix[kU];
@@ -718,28 +745,12 @@ bn_bwd2_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
       if (!ok[u]) continue;
+      uint4 xb;                       // the window element that survives pool + ReLU, 8 channels packed
+      if constexpr (kPool) xb = window_best(v[u], flip); else xb = v[u][0];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        float gr, xa;
-        if (!kPool) {
-          xa = bf16_at(v[u][0], j);
-          gr = (fmaf(xa, sc[j], sh[j]) > 0.f) ? bf16_at(d[u], j) : 0.f;
-        } else {
-          float best = 0.f;
-          xa = 0.f;
-          bool hit = false;
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float xv = bf16_at(v[u][q], j);
-            const float z = fmaf(xv, sc[j], sh[j]);
-            if (z > best) {
-              best = z;
-              xa = xv;
-              hit = true;
-            }
-          }
-          gr = hit ? bf16_at(d[u], j) : 0.f;
-        }
+        const float xa = bf16_at(xb, j);
+        const float gr = (fmaf(xa, sc[j], sh[j]) > 0.f) ? bf16_at(d[u], j) : 0.f;
         a1[j] += gr;
         a2[j] = fmaf(gr, xa, a2[j]);
       }
@@ -840,6 +851,8 @@ bn_bwd2_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
       if (dbias != nullptr) dbias[c] = fmaf(sc[j], sum_g, fmaf(cA[j], mean * count, cB[j] * count));
     }
   }
+  const uint4 flip = sign_flip_mask(sc);
+  (void)flip;
   for (int base = p_begin + prow; base < p_end; base += kBn2Rows * kU) {
     uint4 v[kU][kWin], d[kU];
     int ipix[kU];
@@ -853,7 +866,7 @@ bn_bwd2_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
       if (!ok[u]) continue;
-      if (!kPool) {
+      if constexpr (!kPool) {
         float o[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -863,27 +876,29 @@ bn_bwd2_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
         }
         store8(dx + static_cast<size_t>(ipix[u]) * g.C + cg * 8, o);
       } else {
-        int arg[8];
+        // route dy to the window element that won the max-pool: packed compare against the winner, first match wins
+        const uint4 xb = window_best(v[u], flip);
+        float gsel[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float best = 0.f;
-          arg[j] = -1;
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float z = fmaf(bf16_at(v[u][q], j), sc[j], sh[j]);
-            if (z > best) {
-              best = z;
-              arg[j] = q;
-            }
-          }
-        }
+        for (int j = 0; j < 8; ++j) gsel[j] = (fmaf(bf16_at(xb, j), sc[j], sh[j]) > 0.f) ? bf16_at(d[u], j) : 0.f;
+        uint32_t found[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
+          const uint32_t vw[4] = {v[u][q].x, v[u][q].y, v[u][q].z, v[u][q].w};
+          const uint32_t bw[4] = {xb.x, xb.y, xb.z, xb.w};
+          uint32_t m[4];
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            const uint32_t eq = __heq2_mask(*reinterpret_cast<const __nv_bfloat162*>(&vw[w]),
+                                            *reinterpret_cast<const __nv_bfloat162*>(&bw[w]));
+            m[w] = eq & ~found[w];
+            found[w] |= eq;
+          }
           float o[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float gr = (arg[j] == q) ? bf16_at(d[u], j) : 0.f;
-            o[j] = fmaf(sc[j], gr, fmaf(cA[j], bf16_at(v[u][q], j), cB[j]));
+            const bool sel = ((m[j >> 1] >> ((j & 1) * 16)) & 1u) != 0u;
+            o[j] = fmaf(sc[j], sel ? gsel[j] : 0.f, fmaf(cA[j], bf16_at(v[u][q], j), cB[j]));
           }
           store8(dx + static_cast<size_t>(ipix[u] + (q >> 1) * g.W + (q & 1)) * g.C + cg * 8, o);
         }
