@@ -37,6 +37,16 @@ nat.register_optional("ddpb_reduce_root_bcast", [c_void, c_void, c_int, c_int, c
 nat.register_optional("ddpb_broadcast", [c_void, c_void, c_int, c_int, c_int, c_ll, c_ll, c_int, c_int, c_int,
                                          c_void])
 nat.register_optional("ddpb_peer_barrier", [c_void, c_int, c_int, c_int, c_int, c_void])
+nat.register_optional("ddpb_vmm_granularity", [c_int, C.POINTER(c_ll)])
+nat.register_optional("ddpb_vmm_create", [c_ll, C.POINTER(C.c_ulonglong), C.POINTER(c_int)])
+nat.register_optional("ddpb_vmm_import", [c_int, C.POINTER(C.c_ulonglong)])
+nat.register_optional("ddpb_vmm_map", [C.c_ulonglong, c_ll, C.POINTER(c_void)])
+nat.register_optional("ddpb_vmm_unmap", [c_void, c_ll])
+nat.register_optional("ddpb_vmm_release", [C.c_ulonglong])
+nat.register_optional("ddpb_vmm_close_fd", [c_int])
+nat.register_optional("ddpb_mc_create", [c_int, c_ll, C.POINTER(C.c_ulonglong), C.POINTER(c_int)])
+nat.register_optional("ddpb_mc_add_device", [C.c_ulonglong])
+nat.register_optional("ddpb_mc_bind", [C.c_ulonglong, C.c_ulonglong, c_ll])
 nat.register_optional("ddpb_ipc_alloc", [c_ll, C.POINTER(c_void), c_void])
 nat.register_optional("ddpb_ipc_open", [c_void, C.POINTER(c_void)])
 nat.register_optional("ddpb_ipc_close", [c_void])
@@ -92,7 +102,8 @@ class SymmetricBuffer:
         self._ipc_local = 0
         prefer = prefer or os.environ.get("DDPB_SYMM_BACKEND", "auto")
         errors = []
-        for name in (["symm_mem", "ipc"] if prefer == "auto" else [prefer]):
+        self._vmm = None
+        for name in (["symm_mem", "vmm", "ipc"] if prefer == "auto" else [prefer]):
             try:
                 getattr(self, "_init_" + name)()
                 self.backend = name
@@ -141,6 +152,119 @@ class SymmetricBuffer:
         except Exception:  # noqa: BLE001
             self.multicast_ptr = 0
         self.payload = raw[SIGNAL_PAD_BYTES // 4:]
+
+    def _exchange_fds(self, mine: list[int], owner: int | None = None) -> list[list[int]]:
+        """File descriptors cannot travel through torch.distributed: every owning rank serves its
+        descriptors over a Unix-domain socket (SCM_RIGHTS) to the others, one owner after the other.
+        Returns, per rank, the descriptors received from it (this rank's own are returned as given;
+        with ``owner`` only that rank sends)."""
+        import socket
+        import tempfile
+        import uuid
+
+        token = [uuid.uuid4().hex if self.rank == 0 else None]
+        dist.broadcast_object_list(token, src=dist.get_global_rank(self.group, 0), group=self.group)
+        base = os.path.join(tempfile.gettempdir(), f"ddpb200_{token[0]}")
+        got: list[list[int]] = [[] for _ in range(self.world)]
+        owners = range(self.world) if owner is None else [owner]
+        for r in owners:
+            path = f"{base}_{r}.sock"
+            if r == self.rank:
+                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                srv.bind(path)
+                srv.listen(self.world)
+                dist.barrier(self.group)
+                for _ in range(self.world - 1):
+                    conn, _ = srv.accept()
+                    socket.send_fds(conn, [b"x"], list(mine))
+                    conn.recv(1)              # the peer has its duplicates
+                    conn.close()
+                srv.close()
+                os.unlink(path)
+                got[r] = list(mine)
+            else:
+                dist.barrier(self.group)
+                c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                c.connect(path)
+                _, fds, _, _ = socket.recv_fds(c, 16, len(mine) if owner is None else 8)
+                c.send(b"k")
+                c.close()
+                got[r] = list(fds)
+            dist.barrier(self.group)
+        return got
+
+    def _init_vmm(self) -> None:
+        """Own bootstrap (csrc/vmm.cu): cuMemCreate + POSIX-fd export, every peer's allocation mapped with
+        cuMemMap, and an NVLS multicast object (cuMulticastCreate / AddDevice / BindMem) mapped as the
+        multimem alias -- what torch's symmetric memory provides, without depending on it."""
+        lib = nat.load()
+        ok, err = True, None
+        st = dict(handles=[], maps=[], mc_handle=0, mc_ptr=0, size=0)
+        try:
+            with torch.cuda.device(self.device):
+                gran = c_ll()
+                nat.check(lib.ddpb_vmm_granularity(self.world, C.byref(gran)), "ddpb_vmm_granularity")
+                size = (self.bytes + gran.value - 1) // gran.value * gran.value
+                h, fd = C.c_ulonglong(), c_int()
+                nat.check(lib.ddpb_vmm_create(size, C.byref(h), C.byref(fd)), "ddpb_vmm_create")
+                st.update(size=size, local=h.value, local_fd=fd.value)
+        except Exception as e:  # noqa: BLE001
+            ok, err = False, e
+        self._agree(ok, "vmm allocation")
+        if err is not None:
+            raise err
+        fds = self._exchange_fds([st["local_fd"]])
+        self.ptrs = []
+        with torch.cuda.device(self.device):
+            for r in range(self.world):
+                if r == self.rank:
+                    hr = st["local"]
+                else:
+                    imp = C.c_ulonglong()
+                    nat.check(lib.ddpb_vmm_import(fds[r][0], C.byref(imp)), "ddpb_vmm_import")
+                    os.close(fds[r][0])
+                    hr = imp.value
+                ptr = c_void()
+                nat.check(lib.ddpb_vmm_map(hr, st["size"], C.byref(ptr)), "ddpb_vmm_map")
+                st["handles"].append(hr)
+                st["maps"].append(ptr.value)
+                self.ptrs.append(ptr.value)
+            lib.ddpb_vmm_close_fd(st["local_fd"])
+            # NVLS multicast alias; a box without it (no NVSwitch, old driver) keeps the peer mappings only
+            mc_ok = True
+            try:
+                mh, mfd = C.c_ulonglong(), c_int(-1)
+                if self.rank == 0:
+                    nat.check(lib.ddpb_mc_create(self.world, st["size"], C.byref(mh), C.byref(mfd)), "ddpb_mc_create")
+            except Exception:  # noqa: BLE001
+                mc_ok = False
+            flag = torch.tensor([1 if mc_ok else 0], device=self.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+            if int(flag.item()) == 1 and self.world > 1:
+                got = self._exchange_fds([mfd.value] if self.rank == 0 else [], owner=0)
+                if self.rank != 0:
+                    nat.check(lib.ddpb_vmm_import(got[0][0], C.byref(mh)), "ddpb_vmm_import (multicast)")
+                    os.close(got[0][0])
+                else:
+                    lib.ddpb_vmm_close_fd(mfd.value)
+                try:
+                    nat.check(lib.ddpb_mc_add_device(mh.value), "ddpb_mc_add_device")
+                except Exception:  # noqa: BLE001
+                    mc_ok = False
+                flag = torch.tensor([1 if mc_ok else 0], device=self.device)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)   # also: every device is added
+                if int(flag.item()) == 1:
+                    nat.check(lib.ddpb_mc_bind(mh.value, st["local"], st["size"]), "ddpb_mc_bind")
+                    dist.barrier(self.group)
+                    mptr = c_void()
+                    nat.check(lib.ddpb_vmm_map(mh.value, st["size"], C.byref(mptr)), "ddpb_vmm_map (multicast)")
+                    st.update(mc_handle=mh.value, mc_ptr=mptr.value)
+                    self.multicast_ptr = mptr.value
+        self._vmm = st
+        local = self.ptrs[self.rank]
+        whole = _tensor_from_ptr(local, self.bytes // 4, self.device, self)
+        whole.zero_()
+        self.payload = _tensor_from_ptr(local + SIGNAL_PAD_BYTES, self.payload_floats, self.device, self)
 
     def _init_ipc(self) -> None:
         lib = nat.load()
@@ -229,6 +353,22 @@ class SymmetricBuffer:
         nat.check(rc, "ddpb_peer_barrier")
 
     def close(self) -> None:
+        if self.backend == "vmm" and self._vmm is not None:
+            torch.cuda.synchronize(self.device)
+            dist.barrier(self.group)
+            lib, st = nat.load(), self._vmm
+            with torch.cuda.device(self.device):
+                if st["mc_ptr"]:
+                    lib.ddpb_vmm_unmap(C.c_void_p(st["mc_ptr"]), st["size"])
+                for p in st["maps"]:
+                    lib.ddpb_vmm_unmap(C.c_void_p(p), st["size"])
+                dist.barrier(self.group)
+                for h in st["handles"]:
+                    lib.ddpb_vmm_release(C.c_ulonglong(h))
+                if st["mc_handle"]:
+                    lib.ddpb_vmm_release(C.c_ulonglong(st["mc_handle"]))
+            self._vmm = None
+            self.multicast_ptr = 0
         if self.backend == "ipc" and self._ipc_local:
             torch.cuda.synchronize(self.device)
             dist.barrier(self.group)

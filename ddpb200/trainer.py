@@ -216,8 +216,11 @@ class Trainer:
             self.symm.allreduce_avg(off, n, blocks=self.comm_blocks, slot_base=slot_base, use_mc=self.use_mc, sgd=sgd,
                                     stream=stream)
 
-    def _enqueue_iteration(self, kind: str, with_aug: bool, B: int | None = None, slot: int = 0):
-        """Everything between 'inputs are on the device' and 'parameters are updated'."""
+    def _enqueue_iteration(self, kind: str, with_aug: bool, B: int | None = None, slot: int = 0,
+                           one_bucket: bool = False):
+        """Everything between 'inputs are on the device' and 'parameters are updated'.
+        ``one_bucket`` (mode 'ddp'): reduce all gradients as ONE bucket after backward, which is what
+        torch's Reducer does in iteration 0 before it has seen the gradient-ready order."""
         eng, a = self.engine, self.engine.arena
         B = self.batch_size if B is None else B
         st = self._stage[slot]
@@ -259,6 +262,13 @@ class Trainer:
                 eng.mark("sgd joined")
             else:
                 eng.backward(B, on_loss_ready=self._publish_loss, side_stream=self.wgrad_stream, reduce_loss=True)
+                eng.sgd(self.lr, self.momentum, self.weight_decay)
+        elif self.mode == "ddp" and one_bucket:
+            eng.backward(B, on_loss_ready=self._publish_loss, side_stream=self.wgrad_stream, reduce_loss=True)
+            wide = min(torch.cuda.get_device_properties(self.device).multi_processor_count, 128)
+            self.symm.allreduce_avg(0, a.numel, blocks=wide, slot_base=1024, use_mc=self.use_mc,
+                                    sgd=self._sgd_args() if self.fuse_sgd else None)
+            if not self.fuse_sgd:
                 eng.sgd(self.lr, self.momentum, self.weight_decay)
         elif self.mode == "ddp":
             # Early buckets: reduction only, few CTAs, on the side stream while backward continues.
@@ -416,9 +426,10 @@ class Trainer:
             kind = self._copy_into(slot, data, target, aug)
             with_aug, N = aug is not None, data.shape[0]
         key = f"{kind}:{int(with_aug)}:{slot}"
+        first = self.iteration == 0 and self.mode == "ddp"
         if not self.use_graph or N != self.batch_size:
             # ragged last batch of an epoch (or graphs disabled): plain launches
-            self._enqueue_iteration(kind, with_aug, N, slot)
+            self._enqueue_iteration(kind, with_aug, N, slot, one_bucket=first)
         else:
             g = self._graphs.get(key)
             if g is None:
@@ -459,7 +470,7 @@ class Trainer:
         # The first call runs eagerly (it also performs one-time kernel attribute set-up) and
         # IS the iteration; the graph is captured afterwards from a snapshot-free sequence: the
         # capture itself executes nothing.
-        self._enqueue_iteration(kind, with_aug, None, slot)
+        self._enqueue_iteration(kind, with_aug, None, slot, one_bucket=self.iteration == 0 and self.mode == "ddp")
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=self._capture_stream):

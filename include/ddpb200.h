@@ -168,7 +168,20 @@ int ddpb_reduce_root_bcast(const void* const* bufs, const void* mc, int rank, in
 int ddpb_broadcast(const void* const* bufs, const void* mc, int rank, int world, int root, long long off,
                    long long n, int blocks, int slot_base, int use_mc, void* stream);
 int ddpb_peer_barrier(const void* const* bufs, int rank, int world, int blocks, int slot_base, void* stream);
-/* CUDA IPC bootstrap of the symmetric buffer (process-group rendezvous, part2b/main.py:52-58). */
+/* Own VMM + NVLS multicast bootstrap of the symmetric buffer (csrc/vmm.cu; the counterpart of the Gloo
+ * rendezvous at part2b/main.py:52-58).  Handles cross processes as POSIX file descriptors; sizes must be
+ * multiples of ddpb_vmm_granularity().  All calls act on the current device. */
+int ddpb_vmm_granularity(int ndev, long long* bytes_out);
+int ddpb_vmm_create(long long bytes, unsigned long long* handle, int* fd);   /* cuMemCreate + export */
+int ddpb_vmm_import(int fd, unsigned long long* handle);                     /* allocation or multicast object */
+int ddpb_vmm_map(unsigned long long handle, long long bytes, void** ptr);    /* reserve + map + read-write access */
+int ddpb_vmm_unmap(void* ptr, long long bytes);
+int ddpb_vmm_release(unsigned long long handle);
+int ddpb_vmm_close_fd(int fd);
+int ddpb_mc_create(int ndev, long long bytes, unsigned long long* handle, int* fd);   /* one rank */
+int ddpb_mc_add_device(unsigned long long mc_handle);                                  /* every rank, before any bind */
+int ddpb_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, long long bytes);
+/* CUDA IPC bootstrap of the symmetric buffer (last fallback: peer mappings only, no multicast). */
 int ddpb_ipc_alloc(long long bytes, void** ptr, void* handle64);
 int ddpb_ipc_open(const void* handle64, void** ptr);
 int ddpb_ipc_close(void* ptr);

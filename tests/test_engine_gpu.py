@@ -235,6 +235,28 @@ def test_matches_precision_matched_oracle(n):
             assert _relnorm(eng.act[li][:Po].float(), nchw_to_nhwc2d(z.bfloat16().float())) < 1e-3, f"block {li}"
             Ho = L.H // 2 if blk.pool else L.H
             y = eng.act[li][:Po].float().view(n, Ho, Ho, -1).permute(0, 3, 1, 2).contiguous()
+    # ---- per layer BACKWARD, teacher forced (tight): every kernel of the backward chain against the fp32
+    # restatement of its op, fed with the ENGINE's own upstream gradient and stored activations, so a wrong dX /
+    # dW / BatchNorm gradient cannot hide behind the loose end-to-end cosine above
+    from ddpb200.ops import reference as R
+
+    a = eng.arena
+    for li in range(len(eng.layers) - 1, -1, -1):
+        L = eng.layers[li]
+        P = n * L.H * L.W
+        Po = P // 4 if L.pool else P
+        gamma, beta = a.flat_master(L.p_g), a.flat_master(L.p_beta)
+        dconv_ref, dg_ref, db_ref = R.bn_relu_pool_bwd(eng.conv_out[li][:P], eng.dact[li][:Po], gamma, beta, n, L.H, L.W,
+                                                       L.pool)
+        assert _relnorm(eng.dconv[li][:P].float(), dconv_ref) < 6e-3, f"BatchNorm backward dx, layer {li}"
+        assert _relnorm(a.flat_grad(L.p_g), dg_ref) < 2e-3 and _relnorm(a.flat_grad(L.p_beta), db_ref) < 2e-3, li
+        x_in = eng.operand0 if li == 0 else eng.act[li - 1]
+        dw_ref = R.conv_wgrad(eng.dconv[li][:P], x_in[:P], n, L.H, L.W, L.c_in_eff, L.c_out, L.taps)
+        cols = 27 if li == 0 else 9 * L.c_in
+        assert _relnorm(a.flat_grad(L.p_w).view(L.c_out, cols), dw_ref[:, :cols]) < 2e-3, f"wgrad, layer {li}"
+        if li > 0:
+            dx_ref = R.conv_dgrad(eng.dconv[li][:P], eng.w_f[li], n, L.H, L.W, L.c_in, L.c_out)
+            assert _relnorm(eng.dact[li - 1][:P].float(), dx_ref) < 6e-3, f"dgrad, layer {li}"
 
 
 @pytest.mark.parametrize("factory,batch", [(ddpb200.VGG16, 24), (ddpb200.VGG13, 40)])

@@ -79,6 +79,7 @@ assert all(torch.equal(allp[0], p) for p in allp), "parameters diverged across r
 # 4) every mode computes the same update: compare with mode 'allreduce' (sync strictly after backward, the
 # reference's part2b order) run on the same data from the same seed.  Not bitwise: the forward BatchNorm
 # statistics use float atomics, so two runs differ in the last bits.
+bk = (tr2.symm.backend, tr2.use_mc)
 tr2.close()
 torch.manual_seed(89395)
 model3 = ddpb200.VGG11().to(dev)
@@ -92,18 +93,21 @@ rel = float((flat - ref).norm() / ref.norm())
 assert cos > 0.999 and rel < 5e-2, (mode, cos, rel)   # two runs of the SAME mode differ by ~1e-2 (atomics + 6 steps)
 tr3.close()
 if rank == 0:
-    print(f"OK {mode} {gran} B={B} W={world} err={err:.3e} loss={loss.item():.4f} vs allreduce: cos={cos:.7f} rel={rel:.2e}")
+    print(f"OK {mode} {gran} B={B} W={world} backend={bk[0]} mc={bk[1]} err={err:.3e} loss={loss.item():.4f} "
+          f"vs allreduce: cos={cos:.7f} rel={rel:.2e}")
 dist.destroy_process_group()
 '''
 
 
-def _run(mode, gran="fused", mc=False, world=None, batch=32):
+def _run(mode, gran="fused", mc=False, world=None, batch=32, backend=None):
     world = world or int(os.environ.get("DDPB_TEST_WORLD", "2"))
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     script = Path(os.environ.get("TMPDIR", "/tmp")) / "ddpb_mgpu_worker.py"
     script.write_text(WORKER)
     env = dict(os.environ, DDPB_ROOT=str(ROOT))
+    if backend is not None:
+        env["DDPB_SYMM_BACKEND"] = backend
     import socket
 
     with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as sk:   # a port that is free right now
@@ -114,6 +118,7 @@ def _run(mode, gran="fused", mc=False, world=None, batch=32):
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "OK " + mode in res.stdout
+    return res.stdout
 
 
 @pytest.mark.parametrize("mode", ["allreduce", "gather_scatter", "ddp"])
@@ -137,3 +142,12 @@ def test_three_ranks_batch_85(mode):
     (/root/reference/part2/part2b/main.py:177; the report's figures include N = 3).  The reduction
     slices (n/4 * rank / world) are uneven and the ragged batch runs outside the 128-pixel tiles."""
     _run(mode, world=3, batch=85, mc=torch.cuda.device_count() >= 3)
+
+
+@pytest.mark.parametrize("mode", ["allreduce", "ddp"])
+def test_own_vmm_multicast_bootstrap(mode):
+    """Backend "vmm" (csrc/vmm.cu): cuMemCreate / POSIX-fd exchange / cuMemMap for the peer mappings and an
+    own NVLS multicast object (cuMulticastCreate / AddDevice / BindMem) instead of torch's symmetric memory;
+    the multimem kernels must run on it and give the same results."""
+    out = _run(mode, mc=True, backend="vmm")
+    assert "backend=vmm" in out and "mc=True" in out, out[-500:]
