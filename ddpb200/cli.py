@@ -53,6 +53,8 @@ def build_parser(distributed: bool) -> argparse.ArgumentParser:
     p.add_argument("--max-iters", type=int, default=None, help="stop each epoch after this many iterations")
     p.add_argument("--train-size", type=int, default=None, help="synthetic train-set size")
     p.add_argument("--test-size", type=int, default=None, help="synthetic test-set size")
+    p.add_argument("--device-augment", action="store_true",
+                   help="draw the random crop / flip parameters on the GPU inside the step (Philox) instead of on the host")
     p.add_argument("--no-graph", action="store_true", help="launch kernels one by one instead of a CUDA graph")
     p.add_argument("--save", default=None, help="write a state_dict checkpoint here after training")
     p.add_argument("--resume", default=None, help="load a checkpoint written by --save before training")

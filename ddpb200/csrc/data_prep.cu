@@ -217,3 +217,118 @@ extern "C" int ddpb_first_layer_operand_u8(const unsigned char* src, const signe
   DDPB_CHECK_CUDA(launch_prep<true>(src, aug, out, p, k, stream));
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// Device-side random numbers for the input pipeline (SURVEY.md par. 8, K16): Philox4x32-10, a
+// counter-based generator -- value = f(seed, step, image, word) -- so a captured step that reads its
+// step number from a device counter draws fresh numbers on every graph replay without any host input.
+// The reference draws on CPU workers (torchvision RandomCrop / RandomHorizontalFlip,
+// /root/reference/part1/main.py:23-26).
+// ------------------------------------------------------------------------------------------
+namespace ddpb {
+
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+  constexpr uint32_t kM0 = 0xD2511F53u, kM1 = 0xCD9E8D57u, kW0 = 0x9E3779B9u, kW1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(kM0, ctr.x), lo0 = kM0 * ctr.x;
+    const uint32_t hi1 = __umulhi(kM1, ctr.z), lo1 = kM1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += kW0;
+    key.y += kW1;
+  }
+  return ctr;
+}
+
+// aug[n] = {crop offset y in [0, 2 pad], crop offset x in [0, 2 pad], flip in {0, 1}, 0}; one block, any N.
+// *step is read by every thread first and bumped by one thread at the end: the next launch (or graph
+// replay) draws the next set.
+__global__ void __launch_bounds__(256)
+draw_augmentation_kernel(signed char* __restrict__ aug, int N, int pad, unsigned long long seed,
+                         unsigned int* __restrict__ step) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const unsigned int s = *step;
+  __syncthreads();
+  const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+  const uint32_t span = 2u * static_cast<uint32_t>(pad) + 1u;
+  for (int n = threadIdx.x; n < N; n += blockDim.x) {
+    const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(n), s, 0x41554721u /* "AUG!" stream */, 0u), key);
+    char4 a;
+    a.x = static_cast<signed char>(__umulhi(r.x, span));   // unbiased enough: span << 2^32
+    a.y = static_cast<signed char>(__umulhi(r.y, span));
+    a.z = static_cast<signed char>(r.z >> 31);
+    a.w = 0;
+    reinterpret_cast<char4*>(aug)[n] = a;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *step = s + 1u;
+}
+
+// Synthetic CIFAR-shaped batch generated on the device: label = uniform class, image = a smooth per-class
+// colour template (a 4x4x3 grid drawn from the seed, bilinearly interpolated) + Gaussian noise of sigma 0.25,
+// clamped to [0, 1] and quantised to uint8 -- the construction of ddpb200.data.synthetic_cifar10 with its own
+// random stream.  One thread per pixel.
+__global__ void __launch_bounds__(256)
+synthetic_batch_kernel(unsigned char* __restrict__ img, long long* __restrict__ labels, int N, int H, int W,
+                       int classes, unsigned long long seed, unsigned int* __restrict__ step) {
+  const unsigned int s = *step;
+  const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+  const long long pix = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (pix >= static_cast<long long>(N) * H * W) return;
+  const int n = static_cast<int>(pix / (H * W)), hw = static_cast<int>(pix % (H * W));
+  const int h = hw / W, w = hw % W;
+  const uint4 rl = philox4x32_10(make_uint4(static_cast<uint32_t>(n), s, 0x4C41424Cu /* labels */, 0u), key);
+  const int label = static_cast<int>(__umulhi(rl.x, static_cast<uint32_t>(classes)));
+  if (hw == 0) labels[n] = label;
+  // template value at (h, w): bilinear over a 4x4 grid whose nodes depend on (seed, class) only
+  const float gy = (h + 0.5f) * 4.f / H - 0.5f, gx = (w + 0.5f) * 4.f / W - 0.5f;
+  const int y0 = max(0, min(3, static_cast<int>(floorf(gy)))), x0 = max(0, min(3, static_cast<int>(floorf(gx))));
+  const int y1 = min(3, y0 + 1), x1 = min(3, x0 + 1);
+  const float fy = fminf(fmaxf(gy - y0, 0.f), 1.f), fx = fminf(fmaxf(gx - x0, 0.f), 1.f);
+  auto node = [&](int y, int x) {   // three channel values in [0, 1)
+    const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(label), static_cast<uint32_t>(y * 4 + x), 0x54454D50u, 0u), key);
+    return make_float3(r.x * 2.3283064e-10f, r.y * 2.3283064e-10f, r.z * 2.3283064e-10f);
+  };
+  const float3 a = node(y0, x0), b = node(y0, x1), c = node(y1, x0), d = node(y1, x1);
+  const uint4 rn = philox4x32_10(make_uint4(static_cast<uint32_t>(pix), static_cast<uint32_t>(pix >> 32) ^ s, 0x4E4F4953u, 1u), key);
+  // Box-Muller: two uniforms -> two normals; the third channel takes one of a second pair
+  const float u0 = (rn.x + 1.f) * 2.3283064e-10f, u1 = rn.y * 2.3283064e-10f;
+  const float u2 = (rn.z + 1.f) * 2.3283064e-10f, u3 = rn.w * 2.3283064e-10f;
+  const float m0 = sqrtf(-2.f * __logf(u0)), m1 = sqrtf(-2.f * __logf(u2));
+  const float nz[3] = {m0 * __cosf(6.2831853f * u1), m0 * __sinf(6.2831853f * u1), m1 * __cosf(6.2831853f * u3)};
+  const float t[3] = {(a.x * (1 - fx) + b.x * fx) * (1 - fy) + (c.x * (1 - fx) + d.x * fx) * fy,
+                      (a.y * (1 - fx) + b.y * fx) * (1 - fy) + (c.y * (1 - fx) + d.y * fx) * fy,
+                      (a.z * (1 - fx) + b.z * fx) * (1 - fy) + (c.z * (1 - fx) + d.z * fx) * fy};
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch) {
+    const float v = fminf(fmaxf(t[ch] + 0.25f * nz[ch], 0.f), 1.f);
+    img[pix * 3 + ch] = static_cast<unsigned char>(v * 255.f);
+  }
+}
+
+__global__ void bump_counter_kernel(unsigned int* step) { *step += 1u; }
+
+}  // namespace ddpb
+
+// O16 random draws on the device.  aug: int8 [N][4] (crop y, crop x, flip, 0); step: device counter (starts
+// wherever the caller set it) that this launch reads and increments.
+extern "C" int ddpb_draw_augmentation(signed char* aug, int N, int pad, unsigned long long seed, unsigned int* step,
+                                      cudaStream_t stream) {
+  DDPB_REQUIRE(aug != nullptr && step != nullptr && N >= 1 && pad >= 0 && pad <= 60, "draw_augmentation: bad arguments");
+  DDPB_CHECK_CUDA(launch_pdl(ddpb::draw_augmentation_kernel, 1, 256, 0, stream, aug, N, pad, seed, step));
+  return 0;
+}
+
+// Synthetic uint8 NHWC batch + int64 labels generated on the device (no host data at all); increments *step.
+extern "C" int ddpb_synthetic_batch(unsigned char* img, long long* labels, int N, int H, int W, int classes,
+                                    unsigned long long seed, unsigned int* step, cudaStream_t stream) {
+  DDPB_REQUIRE(img != nullptr && labels != nullptr && step != nullptr && N >= 1 && classes >= 1, "synthetic_batch: bad arguments");
+  const long long pixels = static_cast<long long>(N) * H * W;
+  ddpb::synthetic_batch_kernel<<<static_cast<int>((pixels + 255) / 256), 256, 0, stream>>>(img, labels, N, H, W, classes,
+                                                                                           seed, step);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  ddpb::bump_counter_kernel<<<1, 1, 0, stream>>>(step);
+  DDPB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

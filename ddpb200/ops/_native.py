@@ -61,6 +61,8 @@ _SIGNATURES = {
     "ddpb_first_layer_operand_f32": [c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_int, c_void],
     "ddpb_first_layer_operand_u8": [c_void, c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_int, c_void,
                                     c_void, c_int, c_void],
+    "ddpb_draw_augmentation": [c_void, c_int, c_int, C.c_ulonglong, c_void, c_void],
+    "ddpb_synthetic_batch": [c_void, c_void, c_int, c_int, c_int, c_int, C.c_ulonglong, c_void, c_void],
 }
 _RESTYPES = {
     "ddpb_last_error": C.c_char_p,

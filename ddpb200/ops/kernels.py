@@ -347,6 +347,40 @@ _MEAN3 = (C.c_float * 3)(125.3 / 255.0, 123.0 / 255.0, 113.9 / 255.0)  # part1/m
 _STD3 = (C.c_float * 3)(63.0 / 255.0, 62.1 / 255.0, 66.7 / 255.0)      # part1/main.py:21
 
 
+def draw_augmentation(aug: torch.Tensor, step: torch.Tensor, *, seed: int, pad: int = 4, n: int | None = None,
+                      stream=None) -> torch.Tensor:
+    """Draws RandomCrop(32, pad) offsets and RandomHorizontalFlip bits for ``n`` images on the device
+    (Philox4x32-10, counter = (step, image)) into ``aug`` (int8 [N][4]); ``step`` (int32 [1], device) is read
+    and incremented, so a captured launch draws anew on every replay.  The reference draws them on CPU
+    DataLoader workers (/root/reference/part1/main.py:23-26)."""
+    nat.require_cuda(aug)
+    assert aug.dtype == torch.int8 and aug.dim() == 2 and aug.shape[1] == 4 and aug.is_contiguous()
+    assert step.dtype == torch.int32 and step.numel() == 1 and step.is_cuda
+    n = aug.shape[0] if n is None else n
+    assert 1 <= n <= aug.shape[0]
+    nat.check(nat.load().ddpb_draw_augmentation(nat.ptr(aug), n, pad, seed & 0xFFFFFFFFFFFFFFFF, nat.ptr(step),
+                                                _s(stream)), "ddpb_draw_augmentation")
+    return aug
+
+
+def synthetic_batch(n: int, step: torch.Tensor, *, seed: int, hw: int = 32, classes: int = 10, out=None,
+                    stream=None):
+    """A synthetic CIFAR-shaped batch generated on the device: (uint8 [n][hw][hw][3], int64 [n]).  Class
+    templates depend on ``seed`` only; labels and noise on (seed, step).  Increments ``step``."""
+    nat.require_cuda(step)
+    assert step.dtype == torch.int32 and step.numel() == 1
+    if out is None:
+        out = (torch.empty(n, hw, hw, 3, dtype=torch.uint8, device=step.device),
+               torch.empty(n, dtype=torch.int64, device=step.device))
+    img, lab = out
+    assert img.dtype == torch.uint8 and img.is_contiguous() and img.shape == (n, hw, hw, 3)
+    assert lab.dtype == torch.int64 and lab.is_contiguous() and lab.shape == (n,)
+    nat.check(nat.load().ddpb_synthetic_batch(nat.ptr(img), nat.ptr(lab), n, hw, hw, classes,
+                                              seed & 0xFFFFFFFFFFFFFFFF, nat.ptr(step), _s(stream)),
+              "ddpb_synthetic_batch")
+    return img, lab
+
+
 def first_layer_operand_u8(x_nhwc_u8: torch.Tensor, aug: torch.Tensor | None = None, *, out=None, pad: int = 4,
                            w0_master=None, w0_packed=None, stream=None) -> torch.Tensor:
     """O16: crop/flip/normalise raw uint8 NHWC pixels and emit the layer-0 GEMM operand."""

@@ -213,13 +213,14 @@ def run(part: str, argv=None) -> None:
     root = args.data_root if args.data_root is not None else ("./../data" if part in ("part1", "part3") else "./../../data")
     train_loader, test_loader = create_data_loaders(rank, world_size, batch_size, root=root,
                                                     synthetic=True if args.synthetic else None,
-                                                    train_size=args.train_size, test_size=args.test_size)
+                                                    train_size=args.train_size, test_size=args.test_size,
+                                                    augment=not args.device_augment)
     model = VGG11()
     model.to(device)
     blob = load_checkpoint(args.resume, model) if args.resume else None
     net = DistributedDataParallel(model) if part == "part3" else model
     optimizer = SGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0001)
-    kw = dict(use_graph=not args.no_graph)
+    kw = dict(use_graph=not args.no_graph, device_augment=args.device_augment)
     if distributed:
         kw.update(granularity=args.sync_granularity, use_multicast=False if args.no_multicast else "auto")
     if blob is not None and "optimizer" in blob:

@@ -36,7 +36,8 @@ class Trainer:
                  bucket_layout: str = "balanced", first_bucket_bytes: int | None = None,
                  bucket_bytes: int | None = None, symm_backend: str | None = None,
                  fuse_sgd: bool = True, overlap_wgrad: bool = True, comm_threads: int | None = None, optimizer=None,
-                 overlap_sgd: bool = True, debug_poison_grads: bool = False):
+                 overlap_sgd: bool = True, debug_poison_grads: bool = False, device_augment: bool = False,
+                 augment_seed: int = 0, augment_pad: int = 4):
         if mode not in MODES:
             raise ValueError(f"mode must be one of {MODES}")
         if granularity not in ("fused", "param", "param_launches"):
@@ -58,6 +59,12 @@ class Trainer:
         # gradient arena with NaN.  The backward kernels overwrite all of it, so a reduction or an SGD
         # update that ran BEFORE its gradients were final would pick up NaNs and poison the parameters.
         self.debug_poison_grads = debug_poison_grads
+        # device_augment: uint8 batches given WITHOUT crop/flip draws get them drawn on the GPU inside the
+        # captured step (Philox keyed by augment_seed and the rank, counter = step number kept on the
+        # device), so the host sends 3 KiB of pixels per image and nothing else.
+        self.device_augment = device_augment
+        self.augment_seed = (int(augment_seed) * 0x9E3779B97F4A7C15 + rank) & 0xFFFFFFFFFFFFFFFF
+        self.augment_pad = augment_pad
         # CTA size of the reductions that overlap backward (mode 'ddp'): 32 CTAs of 256 threads -- the same
         # number of threads as round 1's 16 x 512, spread over twice as many SMs with half the footprint
         # each (2 GPUs, balanced buckets: 0.754 ms per step against 0.772 with 16 x 512, profiles/r2_call23_*)
@@ -148,6 +155,7 @@ class Trainer:
         self._loss_host = torch.zeros(1, dtype=torch.int64).pin_memory()
         self._loss_seq = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._steps_published = 0
+        self._aug_step = torch.zeros(1, dtype=torch.int32, device=self.device)   # Philox counter of the draws
         from .ops import kernels as K
 
         if os.environ.get("DDPB_PDL") is None:
@@ -216,7 +224,7 @@ class Trainer:
             self.symm.allreduce_avg(off, n, blocks=self.comm_blocks, slot_base=slot_base, use_mc=self.use_mc, sgd=sgd,
                                     stream=stream)
 
-    def _enqueue_iteration(self, kind: str, with_aug: bool, B: int | None = None, slot: int = 0,
+    def _enqueue_iteration(self, kind: str, with_aug: int, B: int | None = None, slot: int = 0,
                            one_bucket: bool = False):
         """Everything between 'inputs are on the device' and 'parameters are updated'.
         ``one_bucket`` (mode 'ddp'): reduce all gradients as ONE bucket after backward, which is what
@@ -232,6 +240,10 @@ class Trainer:
             for i in range(len(a.params)):      # (not the alignment padding, which no kernel writes)
                 a.flat_grad(i).fill_(float("nan"))
         if kind == "u8":
+            if with_aug == 2:       # draws made on the device (device_augment)
+                from .ops import kernels as K
+
+                K.draw_augmentation(st["aug"], self._aug_step, seed=self.augment_seed, pad=self.augment_pad, n=B)
             eng.load_input_u8(st["u8"][:B], st["aug"][:B] if with_aug else None, pack=True)
         else:
             eng.load_input_f32(st["f32"][:B], pack=True)
@@ -358,6 +370,12 @@ class Trainer:
         st["labels"][:N].copy_(target, non_blocking=True)
         return kind
 
+    def _aug_kind(self, kind: str, aug) -> int:
+        """0: no augmentation, 1: the caller's draws, 2: draws made on the device inside the step."""
+        if aug is not None:
+            return 1
+        return 2 if (self.device_augment and kind == "u8") else 0
+
     def prefetch(self, data: torch.Tensor, target: torch.Tensor, aug: torch.Tensor | None = None) -> None:
         """Starts the host->device copy of the NEXT step's batch on the copy stream, into the staging
         set the running step does not use; the next ``step()`` (called with the same tensors or with
@@ -376,7 +394,7 @@ class Trainer:
             ready = torch.cuda.Event()
             ready.record(cs)
         st["ready"] = ready
-        self._pending = (slot, kind, aug is not None, data.shape[0], data)
+        self._pending = (slot, kind, self._aug_kind(kind, aug), data.shape[0], data)
 
     def set_hyperparameters(self, lr: float | None = None, momentum: float | None = None,
                             weight_decay: float | None = None) -> None:
@@ -424,7 +442,7 @@ class Trainer:
                 raise ValueError("step() without arguments needs a preceding prefetch()")
             slot = self._slot
             kind = self._copy_into(slot, data, target, aug)
-            with_aug, N = aug is not None, data.shape[0]
+            with_aug, N = self._aug_kind(kind, aug), data.shape[0]
         key = f"{kind}:{int(with_aug)}:{slot}"
         first = self.iteration == 0 and self.mode == "ddp"
         if not self.use_graph or N != self.batch_size:
@@ -544,6 +562,13 @@ class Trainer:
         return data
 
     def _step_cpu(self, data, target, aug=None):
+        if aug is None and self.device_augment and data.dtype == torch.uint8:
+            g = torch.Generator().manual_seed((self.augment_seed + self.iteration) & 0x7FFFFFFFFFFFFFFF)
+            n, span = data.shape[0], 2 * self.augment_pad + 1
+            aug = torch.zeros(n, 4, dtype=torch.int8)
+            aug[:, 0] = torch.randint(0, span, (n,), generator=g).to(torch.int8)
+            aug[:, 1] = torch.randint(0, span, (n,), generator=g).to(torch.int8)
+            aug[:, 2] = torch.randint(0, 2, (n,), generator=g).to(torch.int8)
         data = self._to_float_batch(data, aug)
         self.optimizer.zero_grad()
         loss = F.cross_entropy(self.model(data), target)

@@ -145,6 +145,16 @@ int ddpb_first_layer_operand_u8(const unsigned char* src_nhwc, const signed char
                                 int W, const float* mean3, const float* std3, int pad, const float* w0_master,
                                 void* w0_packed, int c_out0, void* stream);
 
+/* Device-side random numbers for the input pipeline (Philox4x32-10 keyed by seed, counter = (*step, image)).
+ * aug: int8 [N][4] = {crop y in [0, 2 pad], crop x in [0, 2 pad], flip, 0}, the layout
+ * ddpb_first_layer_operand_u8 reads.  *step (device counter) is read and then incremented by the launch, so a
+ * CUDA graph that contains it draws a fresh set on every replay. */
+int ddpb_draw_augmentation(signed char* aug, int N, int pad, unsigned long long seed, unsigned int* step, void* stream);
+/* Synthetic CIFAR-shaped batch generated on the device: uint8 NHWC pixels (per-class smooth colour template +
+ * Gaussian noise) and int64 labels; increments *step. */
+int ddpb_synthetic_batch(unsigned char* img_nhwc, long long* labels, int N, int H, int W, int classes,
+                         unsigned long long seed, unsigned int* step, void* stream);
+
 /* ---- gradient synchronisation over NVLink peer memory (K10-K14) ------------------------------ */
 /* bufs: `world` base pointers of the symmetric buffers ([64 KiB signal pad | fp32 payload]) as
  * mapped in this process; mc: NVLS multicast mapping of the same buffer or null; off/n: payload

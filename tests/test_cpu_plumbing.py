@@ -294,3 +294,26 @@ def test_resume_restores_momentum_and_lr_changes_are_followed(tmp_path):
     # lr = 0: parameters must not move (momentum buffers do not matter with lr 0)
     for a, b in zip(before, m3.parameters()):
         assert torch.equal(a, b)
+
+
+def test_device_augment_option_on_the_cpu_path():
+    """--device-augment / Trainer(device_augment=True): loaders stop drawing, the trainer draws (on CPU with a
+    torch generator keyed by seed, rank and iteration): deterministic, and different between ranks."""
+    import ddpb200
+    from ddpb200.data import create_data_loaders
+
+    assert cli.parse_all(False, ["--device-augment"]).device_augment is True
+    assert cli.parse_all(False, []).device_augment is False
+    train_loader, _ = create_data_loaders(0, 1, 8, root=None, synthetic=True, train_size=32, test_size=8, augment=False)
+    img, lab, aug = next(iter(train_loader.raw()))
+    assert aug is None and img.dtype == torch.uint8
+
+    def run(rank, device_augment=True):
+        torch.manual_seed(1)
+        tr = ddpb200.Trainer(ddpb200.VGG11(), mode="single", batch_size=8, lr=0.01, device_augment=device_augment,
+                             augment_seed=5, rank=rank)
+        return [float(tr.step(img, lab)) for _ in range(2)]
+
+    assert run(0) == run(0)
+    assert run(0) != run(1)
+    assert run(0) != run(0, device_augment=False)

@@ -370,3 +370,89 @@ def test_prefetch_and_published_loss_match_the_plain_call():
     assert abs(la[0] - lb[0]) < 2e-3 * abs(la[0]), (la, lb)
     assert all(abs(a - b) < 0.15 * abs(a) for a, b in zip(la, lb)), (la, lb)
     assert _cos(torch.cat([p.flatten() for p in pa]), torch.cat([p.flatten() for p in pb])) > 0.99
+
+
+def test_device_side_augmentation_draws():
+    """K16 random numbers on the device: ranges, uniformity, determinism in (seed, step), a fresh set on every
+    launch, and the drawn parameters fed to the input kernel give what the CPU restatement gives."""
+    from ddpb200.ops import kernels as K
+
+    n, pad = 4096, 4
+    aug = torch.zeros(n, 4, dtype=torch.int8, device=DEV)
+    step = torch.zeros(1, dtype=torch.int32, device=DEV)
+    a0 = K.draw_augmentation(aug, step, seed=1234, pad=pad).clone()
+    a1 = K.draw_augmentation(aug, step, seed=1234, pad=pad).clone()
+    assert int(step) == 2
+    assert int(a0[:, :2].min()) == 0 and int(a0[:, :2].max()) == 2 * pad
+    assert set(a0[:, 2].unique().tolist()) == {0, 1} and int(a0[:, 3].abs().max()) == 0
+    assert not torch.equal(a0, a1)                                  # the counter moved
+    # every one of the 9 offsets ~ n/9 times, flips ~ n/2 (6 sigma of a binomial)
+    for col, k in ((0, 9), (1, 9), (2, 2)):
+        cnt = torch.bincount(a0[:, col].long(), minlength=k).float()
+        sigma = (n * (1 / k) * (1 - 1 / k)) ** 0.5
+        assert float((cnt - n / k).abs().max()) < 6 * sigma, cnt
+    assert abs(float(torch.corrcoef(torch.stack([a0[:, 0].float(), a0[:, 1].float()]))[0, 1])) < 0.08
+    step.zero_()
+    assert torch.equal(K.draw_augmentation(aug, step, seed=1234, pad=pad), a0)      # same (seed, step)
+    step.zero_()
+    assert not torch.equal(K.draw_augmentation(aug, step, seed=1235, pad=pad), a0)  # another seed
+    # a partial batch leaves the rest alone
+    aug.fill_(7)
+    step.zero_()
+    K.draw_augmentation(aug, step, seed=1234, pad=pad, n=100)
+    assert torch.equal(aug[:100], a0[:100]) and int((aug[100:] != 7).sum()) == 0
+    # the draws drive the input kernel exactly as host-made ones do
+    img, _ = _batch(64, seed=3)
+    from ddpb200.ops import reference as R
+
+    out = K.first_layer_operand_u8(img.to(DEV), a0[:64].contiguous())
+    ref = R.first_layer_operand(augment_normalize_u8(img, a0[:64].cpu(), pad)).bfloat16()
+    assert (out.float().cpu() - ref.float()).abs().max().item() < 2e-2
+
+
+def test_trainer_draws_its_augmentation_inside_the_captured_step():
+    """Trainer(device_augment=True): uint8 batches without draws get them from the device generator, a new
+    set on every CUDA-graph replay, different per rank seed, and training still learns."""
+    img, lab = _batch(64, seed=5)
+    img, lab = img.pin_memory(), lab.pin_memory()
+    torch.manual_seed(3)
+    model = ddpb200.VGG11().to(DEV)
+    tr = ddpb200.Trainer(model, mode="single", batch_size=64, lr=0.01, device_augment=True, augment_seed=9)
+    seen, losses = [], []
+    for _ in range(6):
+        slot = tr._slot
+        losses.append(tr.step(img, lab).item())
+        seen.append(tr._stage[slot]["aug"].clone())
+    assert int(tr._aug_step) == 6
+    assert len({tuple(a.flatten().tolist()) for a in seen}) == 6     # eager, capture and replays all differ
+    assert all(int(a[:, :2].max()) <= 8 and int(a.min()) >= 0 for a in seen)
+    assert losses[-1] < losses[0]
+    # host-made draws still win when they are given
+    aug = torch.zeros(64, 4, dtype=torch.int8)
+    aug[:, 0] = 4
+    aug[:, 1] = 4
+    slot = tr._slot
+    tr.step(img, lab, aug.pin_memory())
+    assert torch.equal(tr._stage[slot]["aug"].cpu(), aug) and int(tr._aug_step) == 6
+
+
+def test_device_synthetic_batch():
+    from ddpb200.ops import kernels as K
+
+    step = torch.zeros(1, dtype=torch.int32, device=DEV)
+    img0, lab0 = K.synthetic_batch(512, step, seed=7)
+    img1, lab1 = K.synthetic_batch(512, step, seed=7)
+    assert int(step) == 2 and img0.shape == (512, 32, 32, 3) and img0.dtype == torch.uint8
+    assert int(lab0.min()) >= 0 and int(lab0.max()) <= 9 and len(lab0.unique()) == 10
+    assert not torch.equal(lab0, lab1) and not torch.equal(img0, img1)
+    step.zero_()
+    img2, lab2 = K.synthetic_batch(512, step, seed=7)
+    assert torch.equal(img0, img2) and torch.equal(lab0, lab2)
+    # images of one class share a template: their means are closer to the class mean than to other classes'
+    x = img0.float().view(512, -1) / 255
+    means = torch.stack([x[lab0 == c].mean(0) for c in range(10)])
+    d = torch.cdist(x, means)
+    assert float((d.argmin(1) == lab0).float().mean()) > 0.95
+    # noise of about sigma 0.25 (clamping trims it a little)
+    resid = (x - means[lab0]).std()
+    assert 0.12 < float(resid) < 0.3
