@@ -5,7 +5,7 @@ thread), 4 epilogue loop done, 5 past the grid barrier, 3 exit.  Printed: median
 microseconds since the earliest start.  ``--probe`` also runs the producer-skip probes
 (ddpb_conv_debug_mode 1 = no B loads, 2 = no A loads, 3 = neither): numerically wrong, timing only.
 
-    python bench/conv_probe2.py [--probe] [--dgrad] [mode,block_n ...]     e.g. 2,0 3,256 3,128
+    python bench/conv_probe2.py [--probe] [--dgrad] [--tail-l2] [mode,block_n ...]     e.g. 2,0 3,256 3,128
 """
 import sys
 from pathlib import Path
@@ -25,6 +25,7 @@ args = [a for a in sys.argv[1:] if not a.startswith("--")]
 cfgs = [tuple(int(v) for v in c.split(",")) for c in (args or ["2,0", "3,256", "3,128"])]
 probes = [0, 1, 2, 3] if "--probe" in sys.argv else [0]
 dgrad = "--dgrad" in sys.argv
+K.conv_tail_from_tmem("--tail-l2" not in sys.argv)     # fused BatchNorm tail from TMEM (default) or from the stored tiles
 sms = torch.cuda.get_device_properties(0).multi_processor_count
 for li, (S, Ci, Co, taps, pool) in enumerate(LAYERS):
     P = N * S * S

@@ -58,12 +58,14 @@ def main():
     ap.add_argument("--conv-mode", type=int, default=-1,
                     help="conv kernel: -1 automatic, 0 one tile per CTA, 1 CTA pair, 2 persistent, 3 persistent CTA pair")
     ap.add_argument("--block-n", type=int, default=-1, help="force the tile width of fprop / dgrad")
+    ap.add_argument("--tail-l2", action="store_true", help="fused BatchNorm tail from the stored tiles, not from TMEM")
     a = ap.parse_args()
     K.conv_force(a.conv_mode, a.block_n, -1)
+    K.conv_tail_from_tmem(not a.tail_l2)
     N, reps = a.batch, a.reps
     K.bn_bwd_set_fused(a.bn_fused)
     tot = dict(fwd=0.0, bn_bwd=0.0, wgrad=0.0, dgrad=0.0)
-    print(f"batch {N}, pdl {K.get_pdl()}, bn fused mode {a.bn_fused}, conv mode {a.conv_mode}, block_n {a.block_n}; "
+    print(f"batch {N}, pdl {K.get_pdl()}, bn fused mode {a.bn_fused}, tail from {'L2' if a.tail_l2 else 'TMEM'}, conv mode {a.conv_mode}, block_n {a.block_n}; "
           "microseconds per call in a graph")
     for li, (S, Ci, Co, pool) in enumerate(LAYERS):
         H = W = S

@@ -367,6 +367,15 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n, int a_mn_ma
          (static_cast<uint32_t>(m >> 4) << 24);
 }
 
+// First 1024-byte aligned address of the dynamic shared memory (SWIZZLE_128B tiles need it).  Written as
+// "shared symbol + offset", not as a round trip through uintptr_t: after such a cast the compiler no longer
+// knows the address space and every access through the pointer becomes a generic LD.E / ST.E instead of
+// LDS / STS.
+__device__ __forceinline__ uint8_t* align_smem_1k(uint8_t* smem_raw) {
+  const uint32_t base = static_cast<uint32_t>(__cvta_generic_to_shared(smem_raw));
+  return smem_raw + ((1024u - (base & 1023u)) & 1023u);
+}
+
 // ---- small math helpers --------------------------------------------------------------
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
@@ -375,6 +384,10 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
   __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&v);
   return __bfloat1622float2(h);
+}
+__device__ __forceinline__ uint32_t bf16x2_max_u32(uint32_t a, uint32_t b) {   // packed max of two bf16 pairs
+  const __nv_bfloat162 r = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+  return *reinterpret_cast<const uint32_t*>(&r);
 }
 __device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 

@@ -65,6 +65,8 @@ struct FpropParams {
   unsigned int* grid_sync;  // one zeroed word: all CTAs meet here once the statistics are complete
   int H, W, pool;
   float eps;
+  int tail_tmem;         // persistent kernel: the BatchNorm tail re-reads the accumulators from TMEM (every tile of a CTA
+                         // still has its own accumulator buffer) instead of the bf16 tiles from L2
 };
 
 __device__ __forceinline__ void dbg_stamp(const FpropParams& p, int slot) {
@@ -162,7 +164,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   using Cfg = FpropCfg<BLOCK_N>;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operand tiles need 1024-byte alignment.
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1k(smem_raw);
   uint8_t* tiles = smem;
   float* s_stats = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes);
@@ -383,6 +385,7 @@ struct ConvPlan {
 };
 
 static int g_force_pair = -1, g_force_block_n = -1, g_force_splits = -1;
+static int g_tail_tmem = 1;   // BatchNorm tail of the persistent kernel from TMEM where possible (0: always from L2)
 static unsigned long long* g_dbg = nullptr;
 static int g_dbg_mode = 0;
 
@@ -468,6 +471,11 @@ extern "C" void ddpb_conv_force(int pair, int block_n, int splits) {
   g_force_block_n = block_n;
   g_force_splits = splits;
 }
+
+// Tuning hook: 1 (default) = the fused BatchNorm tail reads the accumulators back from TMEM where that is
+// faster (one tile per CTA), 2 = wherever the shape allows it, 0 = it always re-reads the stored bf16 tiles
+// from L2.  All give the same output.
+extern "C" void ddpb_conv_tail_from_tmem(int on) { g_tail_tmem = on; }
 
 // Profiling hook: device buffer of 8 x (number of CTAs) uint64 that every conv CTA stamps with
 // %globaltimer at start / after set-up / when its accumulator is complete / at exit (null = off).
@@ -591,6 +599,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   p.W = W;
   p.pool = 0;
   p.eps = 0.f;
+  p.tail_tmem = 0;
   if (fused_bn != nullptr) *fused_bn = 0;
   // BatchNorm tail inside the kernel: persistent kernel, whole 2x2 windows per tile
   if (bn_tail != nullptr && stats != nullptr && (pl.pair == 2 || pl.pair == 3) && pl.splits == 1 &&
@@ -603,6 +612,20 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
     p.pool = bn_tail->pool;
     p.eps = bn_tail->eps;
     if (fused_bn != nullptr) *fused_bn = 1;
+    // Tail from TMEM: possible when no accumulator buffer is recycled (tiles per CTA <= buffers) and, with
+    // pooling, a warp's 32 accumulator rows hold whole 2x2 windows (W a power of two <= 16: the window is
+    // lanes l, l^1, l^W, l^W^1).  Measured per layer at batch 256 (profiles/r2_call32_*): with one tile per CTA
+    // the tail takes 4.9 / 3.6 / 3.6 / 3.1 us from TMEM against 8.5 / 4.1 / 4.3 / 3.4 us from L2 (layers 2-5);
+    // with four tiles per CTA (layer 1) 6.2 against 5.4 us: the pass is bound by the shared-memory pipe
+    // (per-column coefficients are broadcast loads) and uses 8 of the 10 warps.  g_tail_tmem = 2 forces it
+    // wherever it is possible (tests).
+    const long long items = static_cast<long long>((p.P + kBlockM - 1) / kBlockM) * (C_out / block_n);
+    const long long grid = items < sm_count() ? items : sm_count();
+    const int acc_bufs = (512 / block_n) < 4 ? (512 / block_n) : 4;
+    const long long per_cta = (items + grid - 1) / grid;
+    const bool pool_ok = !bn_tail->pool || (W >= 2 && W <= 16 && (W & (W - 1)) == 0 && H % 2 == 0);
+    if (pl.pair == 2 && pool_ok && ((g_tail_tmem == 1 && per_cta == 1) || (g_tail_tmem == 2 && per_cta <= acc_bufs)))
+      p.tail_tmem = 1;
   }
   const int m_tiles = (p.P + kBlockM - 1) / kBlockM;
   const int splits = pl.splits;

@@ -51,7 +51,7 @@ conv_pair_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
                          const FpropParams p, int m_tiles, int n_tiles) {
   using Cfg = PairPersistCfg<BLOCK_N>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1k(smem_raw);
   uint8_t* tiles = smem;
   float* s_stats = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes);
   float* s_bias = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kStatsBytes);

@@ -89,7 +89,7 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                     int splits) {
   using Cfg = PersistCfg<BLOCK_N>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1k(smem_raw);
   uint8_t* tiles = smem;
   uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;    // 1024-byte aligned (stages are multiples of 8 KB)
   float* s_stats = reinterpret_cast<float*>(staging + Cfg::kStagingBytes);
@@ -336,8 +336,9 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             for (int j = 0; j < 16; ++j) {
               float x0 = __uint_as_float(raw[2 * j]), x1 = __uint_as_float(raw[2 * j + 1]);
               if (p.bias != nullptr) {
-                x0 += my_bias[c * 32 + 2 * j];         // same address in every lane: broadcast
-                x1 += my_bias[c * 32 + 2 * j + 1];
+                const float2 bb = *reinterpret_cast<const float2*>(my_bias + c * 32 + 2 * j);   // one broadcast load
+                x0 += bb.x;
+                x1 += bb.y;
               }
               pk[j] = valid ? pack_bf16x2(x0, x1) : 0u;   // rows past the end add zeros to the channel sums
             }
@@ -391,9 +392,10 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     if (threadIdx.x == 64) dbg_stamp(p, 4);
   }
 
+  const bool tail_tmem = (p.act != nullptr) && (p.tail_tmem != 0);   // the accumulators are read once more below
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == 1 && !tail_tmem) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
@@ -417,8 +419,13 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       var = fmaxf(var, 0.f);
       const float rstd = rsqrtf(var + p.eps);
       const float sc = p.gamma[c] * rstd;
-      s_scale[c] = sc;
-      s_shift[c] = p.beta[c] - mean * sc;
+      if (tail_tmem) {     // {scale, shift} of a column pair in one 16-byte word (one broadcast load per pair)
+        s_scale[(c >> 1) * 4 + (c & 1) * 2] = sc;
+        s_scale[(c >> 1) * 4 + (c & 1) * 2 + 1] = p.beta[c] - mean * sc;
+      } else {
+        s_scale[c] = sc;
+        s_shift[c] = p.beta[c] - mean * sc;
+      }
       if (blockIdx.x == 0 && p.saved != nullptr) {
         p.saved[c] = mean;
         p.saved[p.C_out + c] = rstd;
@@ -499,7 +506,76 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         }
       }
     };
-    if (p.pool)
+    if (tail_tmem) {
+      // Every tile of this CTA still sits in its own TMEM buffer: the eight epilogue warps read their rows
+      // again (+bias, rounded to bf16 exactly as stored), normalise, rectify and pool across lanes -- the 32
+      // rows of a warp are whole 2x2 windows: lanes l, l^1 (next column), l^W (next image row).  Same values
+      // as the pass over the stored tiles below, without the trip through L2.
+      if (warp >= 2) {
+        tc_fence_after();
+        const int ew = warp - 2, q = warp & 3, half = ew >> 2;
+        constexpr int kMyChunks = BLOCK_N / 64;
+        const int chunk0 = half * kMyChunks;
+        const int lane = static_cast<int>(lane_id());
+        const int row = q * 32 + lane;
+        const bool writer = !p.pool || ((lane & 1) == 0 && (lane & p.W) == 0);
+        const int Ho = p.H / 2, Wo = p.W / 2;
+        float* my_bias = s_bias + ew * (BLOCK_N / 2);
+        int local = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++local) {
+          const PersistItem it = persist_item(item, m_tiles, n_tiles);
+          const int pix = it.m_tile * kBlockM + row;      // (P is an int)
+          const bool valid = pix < p.P;
+          long long opix = pix;
+          if (p.pool) {
+            const int w = pix % p.W, t = pix / p.W;
+            const int h = t % p.H;
+            opix = (static_cast<long long>(t / p.H) * Ho + h / 2) * Wo + w / 2;
+          }
+          __syncwarp();
+#pragma unroll
+          for (int c = 0; c < kMyChunks; ++c)
+            my_bias[c * 32 + lane] = (p.bias != nullptr) ? __ldg(p.bias + it.n_tile * BLOCK_N + (chunk0 + c) * 32 + lane) : 0.f;
+          __syncwarp();
+          const uint32_t t_addr = tmem_base + local * BLOCK_N + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+          for (int c = 0; c < kMyChunks; ++c) {
+            const int col0 = it.n_tile * BLOCK_N + (chunk0 + c) * 32;
+            uint32_t raw[32];
+            tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
+            tmem_ld_wait();
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              // the shared-memory pipe is what bounds this pass: one 8-byte and one 16-byte broadcast load per pair
+              const float2 bb = *reinterpret_cast<const float2*>(my_bias + c * 32 + 2 * j);
+              const float4 cf = *reinterpret_cast<const float4*>(s_scale + (col0 + 2 * j) * 2);
+              const uint32_t xb = pack_bf16x2(__uint_as_float(raw[2 * j]) + bb.x, __uint_as_float(raw[2 * j + 1]) + bb.y);
+              const float y0 = fmaxf(fmaf(__uint_as_float(xb << 16), cf.x, cf.y), 0.f);
+              const float y1 = fmaxf(fmaf(__uint_as_float(xb & 0xffff0000u), cf.z, cf.w), 0.f);
+              pk[j] = pack_bf16x2(y0, y1);
+            }
+            if (p.pool) {        // rounding is monotonic: the max of the rounded values is the rounded max
+#pragma unroll
+              for (int j = 0; j < 16; ++j) pk[j] = bf16x2_max_u32(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 1));
+#pragma unroll
+              for (int j = 0; j < 16; ++j) pk[j] = bf16x2_max_u32(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], p.W));
+            }
+            if (valid && writer) {
+              uint4* dst = reinterpret_cast<uint4*>(p.act + opix * p.C_out + col0);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) dst[k] = make_uint4(pk[4 * k], pk[4 * k + 1], pk[4 * k + 2], pk[4 * k + 3]);
+            }
+          }
+        }
+        tc_fence_before();
+      }
+      __syncthreads();
+      if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, Cfg::kTmemCols);
+      }
+    } else if (p.pool)
       bn_tail_pass(std::integral_constant<int, 4>{}, std::integral_constant<int, 4>{});
     else
       bn_tail_pass(std::integral_constant<int, 8>{}, std::integral_constant<int, 1>{});

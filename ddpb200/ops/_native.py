@@ -34,6 +34,7 @@ _SIGNATURES = {
     "ddpb_conv_force": [c_int, c_int, c_int],
     "ddpb_conv_debug_timing": [c_void],
     "ddpb_conv_debug_mode": [c_int],
+    "ddpb_conv_tail_from_tmem": [c_int],
     "ddpb_conv_plan": [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void],
     "ddpb_conv_wgrad_splits": [c_int, c_int, c_int, c_int, c_int, c_int],
     "ddpb_conv_wgrad_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int],

@@ -32,6 +32,12 @@ def conv_force(pair: int = -1, block_n: int = -1, splits: int = -1) -> None:
     nat.load().ddpb_conv_force(pair, block_n, splits)
 
 
+def conv_tail_from_tmem(on: bool | int) -> None:
+    """Tuning hook: fused BatchNorm tail of the persistent conv kernel from TMEM (1, default: with one tile per
+    CTA; 2: wherever the shape allows) or from the stored tiles in L2 (0)."""
+    nat.load().ddpb_conv_tail_from_tmem(int(on))
+
+
 def conv_plan(N, H, W, C_in, C_out, taps=9, block_n=0) -> tuple[int, int, int]:
     """(cta_pair, block_n, splits) the planner picks for this fprop-shaped problem."""
     out = (C.c_int * 3)()

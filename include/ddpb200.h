@@ -95,6 +95,9 @@ long long ddpb_conv_wgrad_static_max_elems(void);
 void ddpb_conv_force(int kernel, int block_n, int splits);
 void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3);
 void ddpb_conv_debug_timing(unsigned long long* per_cta_stamps);   /* 8 slots per CTA, see bench/conv_probe2.py */
+void ddpb_conv_tail_from_tmem(int on);   /* fused BatchNorm tail re-reads the accumulators from TMEM: 1 (default) with one
+                                            tile per CTA, 2 wherever the shape allows, 0 never (stored tiles from L2).
+                                            Same output. */
 void ddpb_conv_debug_mode(int mode);   /* timing probes, wrong results: bit 0 skip B loads, bit 1 skip A loads */
 
 /* ---- BatchNorm + ReLU (+ MaxPool) (K3, K4) -------------------------------------------------- */

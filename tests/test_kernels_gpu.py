@@ -429,3 +429,38 @@ def test_persistent_cta_pair_conv_with_batchnorm_tail(case, pool):
     cf = conv_out.float()
     assert torch.allclose(saved[0], cf.mean(0), rtol=1e-3, atol=1e-3)
     assert torch.allclose(saved[1], (cf.var(0, unbiased=False) + 1e-5).rsqrt(), rtol=2e-3)
+
+
+@pytest.mark.parametrize("pool", [False, True])
+@pytest.mark.parametrize("shape", [(256, 16, 16, 64, 128), (256, 8, 8, 128, 256), (256, 8, 8, 256, 256), (256, 4, 4, 256, 512),
+                                   (256, 4, 4, 512, 512), (64, 16, 16, 64, 128), (37, 8, 8, 128, 256), (5, 4, 4, 256, 512),
+                                   (3, 2, 2, 512, 512), (8, 32, 32, 64, 64)])
+def test_batchnorm_tail_from_tmem_equals_the_tail_from_l2(shape, pool):
+    """The fused BatchNorm tail reads the accumulators back from TMEM when every tile of a CTA still has its
+    buffer (several tiles per CTA at 16x16, ragged last tiles, pooling across lanes for W = 2..16; 32x32 and
+    recycled buffers fall back to the stored tiles).  Same rounding points as the pass over the stored tiles:
+    the two agree to the run-to-run noise of the statistics, and both match the ATen composition."""
+    N, H, W, Ci, Co = shape
+    torch.manual_seed(2)
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
+    b = torch.randn(Co, device=DEV) * 0.1
+    gamma = (torch.rand(Co, device=DEV) + 0.5) * torch.where(torch.rand(Co, device=DEV) < 0.3, -1.0, 1.0)
+    beta = torch.randn(Co, device=DEV) * 0.2
+    out = {}
+    try:
+        for mode in (2, 0):           # 2: from TMEM wherever the shape allows (also several tiles per CTA)
+            K.conv_tail_from_tmem(mode)
+            K.conv_force(-1, -1, 1)       # no split-K: the tail runs inside the kernel
+            conv_out, act, saved = K.conv_bn_relu_pool_fwd(x, w, b, gamma, beta, N, H, W, Ci, Co, 9, pool)
+            torch.cuda.synchronize()
+            out[mode] = (conv_out.clone(), act.clone(), saved.clone())
+    finally:
+        K.conv_tail_from_tmem(1)
+        K.conv_force(-1, -1, -1)
+    assert torch.equal(out[0][0], out[2][0])                       # the conv output itself is deterministic
+    assert torch.allclose(out[0][2], out[2][2], rtol=1e-5, atol=1e-6)
+    diff = (out[0][1].float() - out[2][1].float()).abs()
+    assert float(diff.max()) <= 2 ** -6 * float(out[0][1].float().abs().max()) and float((diff > 0).float().mean()) < 1e-3
+    for mode in (0, 2):
+        assert _rel_err(out[mode][1], R.bn_relu_pool_fwd(out[mode][0], gamma, beta, N, H, W, pool)) < 1e-2
