@@ -25,8 +25,11 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--max-splits", type=int, default=8)
+    ap.add_argument("--dgrad-two-kernels", action="store_true", help="dgrad without sync words (what the engine does)")
+    ap.add_argument("--no-fuse-split", action="store_true", help="split-K summed by the second kernel, not inside the conv kernel")
     a = ap.parse_args()
     N, reps = a.batch, a.reps
+    K.conv_fuse_split(not a.no_fuse_split)
     gain = dict(fwd=0.0, dgrad=0.0)
     for li, (S, Ci, Co, pool) in enumerate(LAYERS):
         H = W = S
@@ -42,14 +45,14 @@ def main():
         stats = torch.zeros(reps + 2, 2 * Co + 32, device=dev)
         dconv = torch.randn(P, Co, device=dev).bfloat16()
         dx = torch.empty(P, max(Ci, 64), dtype=torch.bfloat16, device=dev)
-        scratch = torch.empty(a.max_splits * P * max(Co, Ci), device=dev)
+        scratch = torch.empty(a.max_splits * ((P + 127) // 128) * 128 * max(Co, Ci, 64), device=dev)
 
         def fwd(i):
             K.conv_bn_relu_pool_fwd(x, w, bias, gamma, beta, N, H, W, Cin_eff, Co, taps, pool, conv_out=conv_out,
                                     act=act, stats=stats[i], saved=saved, scratch=scratch)
 
         def dgrad(i):
-            K.conv_dgrad(dconv, w, N, H, W, Ci, Co, out=dx, scratch=scratch)
+            K.conv_dgrad(dconv, w, N, H, W, Ci, Co, out=dx, scratch=scratch, split_sync=None if a.dgrad_two_kernels else True)
 
         for what, fn, shape in (("fwd", fwd, (Cin_eff, Co, taps)), ("dgrad", dgrad, (Co, Ci, 9))):
             if what == "dgrad" and li == 0:

@@ -99,7 +99,7 @@ def main():
         if li > 0:
             dx = torch.empty(P, Ci, dtype=torch.bfloat16, device=dev)
             ds_ = torch.empty(max(1, K.conv_fprop_scratch_elems(N, H, W, Co, Ci, 9)), device=dev)
-            t_d = timed(lambda i: K.conv_dgrad(dconv, w, N, H, W, Ci, Co, out=dx, scratch=ds_), reps)
+            t_d = timed(lambda i: K.conv_dgrad(dconv, w, N, H, W, Ci, Co, out=dx, scratch=ds_, split_sync=None), reps)
         print(f"L{li} {S:2d}x{S:<2d} {Ci:3d}->{Co:3d} pool={int(pool)} | fwd(conv+bn) {t_f:6.1f} | bn_bwd {t_b:6.1f} | "
               f"wgrad {t_w:6.1f} (splits {K.conv_wgrad_splits(N, H, W, Cin_eff, Co, taps)}) | dgrad {t_d:6.1f}")
         for k, v in zip(("fwd", "bn_bwd", "wgrad", "dgrad"), (t_f, t_b, t_w, t_d)):

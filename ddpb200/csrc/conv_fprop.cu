@@ -20,6 +20,7 @@
 // that BatchNorm needs (O4), so the conv output is not re-read for statistics.
 #include "common.cuh"
 #include <stdlib.h>
+#include <cstdlib>
 #include <type_traits>
 
 namespace ddpb {
@@ -65,6 +66,11 @@ struct FpropParams {
   unsigned int* grid_sync;  // one zeroed word: all CTAs meet here once the statistics are complete
   int H, W, pool;
   float eps;
+  // Split-K summed inside the persistent kernel (split_sync != null): every epilogue warp takes a ticket per
+  // (tile, warp); the warp that draws the last ticket waits for the other splits' slices, adds them to its own
+  // accumulator in split order (so the result does not depend on who was last) and runs the normal epilogue.
+  // Two words per (tile, warp): tickets drawn, slices written; the last warp leaves both at zero.
+  unsigned int* split_sync;
   int tail_tmem;         // persistent kernel: the BatchNorm tail re-reads the accumulators from TMEM (every tile of a CTA
                          // still has its own accumulator buffer) instead of the bf16 tiles from L2
 };
@@ -382,10 +388,19 @@ struct ConvPlan {
   int pair;      // kernel: 0 = one tile per CTA, 2 = persistent, 3 = persistent CTA pair (cta_group::2)
   int block_n;
   int splits;
+  bool fused;    // split-K partial sums added up inside the persistent kernel (needs the caller's sync words)
 };
 
 static int g_force_pair = -1, g_force_block_n = -1, g_force_splits = -1;
-static int g_tail_tmem = 1;   // BatchNorm tail of the persistent kernel from TMEM where possible (0: always from L2)
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return (e != nullptr && e[0] != 0) ? atoi(e) : dflt;
+}
+// split-K summed inside the persistent kernel when the caller gives sync words (0: second kernel); environment
+// DDPB_FUSE_SPLIT / DDPB_TAIL_TMEM set the start values (A/B runs of bench.py), the hooks below change them
+static int g_fuse_split = env_int("DDPB_FUSE_SPLIT", 1);
+constexpr int kSplitSyncWords = 4096;   // two words per (output tile, epilogue warp): up to 256 tiles
+static int g_tail_tmem = env_int("DDPB_TAIL_TMEM", 1);   // BatchNorm tail of the persistent kernel from TMEM where possible (0: always from L2)
 static unsigned long long* g_dbg = nullptr;
 static int g_dbg_mode = 0;
 
@@ -393,7 +408,7 @@ static int g_dbg_mode = 0;
 // hook (profiles/r1_call11_conv_timeline.txt): a 64-deep k-step costs max(1.35 x tensor time,
 // stage bytes / 55 B per clk of operand ingest); draining a tile costs ~30 cycles per column
 // with eight epilogue warps and overlaps the next tile's main loop.
-static double plan_cost(int bn, int splits, long long P, int C_out, int total_k) {
+static double plan_cost(int bn, int splits, long long P, int C_out, int total_k, bool fused, bool with_tail) {
   const int m_tiles = static_cast<int>((P + kBlockM - 1) / kBlockM);
   const int items = m_tiles * (C_out / bn) * splits;
   const int sms = sm_count();
@@ -405,15 +420,22 @@ static double plan_cost(int bn, int splits, long long P, int C_out, int total_k)
   const int per_sm = (items + sms - 1) / sms;
   double t = per_sm * (mainloop > epi ? mainloop : epi) + (mainloop > epi ? epi : mainloop) + 2500.0;
   // split-K finalize: re-reads splits x P x C_out floats (L2-resident at these sizes) + a launch
-  if (splits > 1) t += 6000.0 + splits * static_cast<double>(P) * C_out * 4.0 / 3000.0;
+  // summed inside the kernel: the warp that draws the last ticket reads the other splits' slices of its tile
+  // (measured, profiles/r2_call34_*: ticket + wait for the slowest split + one L2 round trip per split and
+  // 32-column chunk, about 7 us at 4 splits: worth it where it keeps the BatchNorm tail inside the kernel)
+  if (splits > 1 && fused) t += 8000.0 + (splits - 1) * 2700.0;
+  else if (splits > 1) t += 6000.0 + splits * static_cast<double>(P) * C_out * 4.0 / 3000.0;
+  // a BatchNorm tail that cannot run inside the kernel (split-K summed by the second kernel) is a third launch
+  if (splits > 1 && !fused && with_tail) t += 8000.0;
   return t;
 }
 
 // Automatic choice: the persistent kernel with the cheapest (BLOCK_N, split-K); the
 // one-tile-per-CTA and CTA-pair kernels stay available through ddpb_conv_force (mode 0 / 1).
 static ConvPlan plan_conv_mode(int mode, long long P, int C_out, int total_k, int block_n_hint, bool allow_split,
-                               bool* found) {
-  ConvPlan best{mode, (C_out % 128 == 0) ? 128 : 64, 1};
+                               bool fuse_ok, bool with_tail, bool* found) {
+  ConvPlan best{mode, (C_out % 128 == 0) ? 128 : 64, 1, false};
+  const long long m_tiles = (P + kBlockM - 1) / kBlockM;
   double best_t = 1e30;
   const int bns[3] = {64, 128, 256};
   for (int bi = 0; bi < 3; ++bi) {
@@ -425,11 +447,18 @@ static ConvPlan plan_conv_mode(int mode, long long P, int C_out, int total_k, in
     for (int splits = 1; splits <= 8; ++splits) {
       if (g_force_splits >= 0 && splits != g_force_splits) continue;
       if (mode == 3 && splits > 1) continue;              // the persistent CTA-pair kernel does not split K
-      if (splits > 1 && (!allow_split || total_k / splits < 4 || C_out / 8 > 256 || 256 % (C_out / 8) != 0)) continue;
-      const double t = plan_cost(bn, splits, P, C_out, total_k);
+      if (splits > 1 && (!allow_split || total_k / splits < 4)) continue;
+      // in-kernel sum: persistent kernel, sync words for every (tile, warp); else the finalize kernel's thread mapping
+      // and one item per CTA: a warp waiting for the other splits' slices then only ever waits for warps whose
+      // single accumulator is already being produced (with several items per CTA, waits could chain through
+      // recycled accumulator buffers)
+      const bool fused = splits > 1 && fuse_ok && mode == 2 && m_tiles * (C_out / bn) * 16 <= kSplitSyncWords &&
+                         m_tiles * (C_out / bn) * splits <= sm_count();
+      if (splits > 1 && !fused && (C_out / 8 > 256 || 256 % (C_out / 8) != 0)) continue;
+      const double t = plan_cost(bn, splits, P, C_out, total_k, fused, with_tail);
       if (t < best_t) {
         best_t = t;
-        best = ConvPlan{mode, bn, splits};
+        best = ConvPlan{mode, bn, splits, fused};
       }
     }
   }
@@ -437,13 +466,20 @@ static ConvPlan plan_conv_mode(int mode, long long P, int C_out, int total_k, in
   return best;
 }
 
-static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint, bool allow_split) {
+static ConvPlan plan_conv(long long P, int C_out, int total_k, int block_n_hint, bool allow_split, bool fuse_ok,
+                          bool with_tail = false) {
   const int mode = (g_force_pair == 0 || g_force_pair == 3) ? g_force_pair : 2;
+  fuse_ok = fuse_ok && g_fuse_split != 0;
   bool found = false;
-  const ConvPlan pl = plan_conv_mode(mode, P, C_out, total_k, block_n_hint, allow_split, &found);
+  const ConvPlan pl = plan_conv_mode(mode, P, C_out, total_k, block_n_hint, allow_split, fuse_ok, with_tail, &found);
   // mode 3 (persistent CTA pair) has no 64-wide tile and no split-K: such shapes use mode 2
-  if (mode == 3 && !found) return plan_conv_mode(2, P, C_out, total_k, block_n_hint, allow_split, nullptr);
+  if (mode == 3 && !found) return plan_conv_mode(2, P, C_out, total_k, block_n_hint, allow_split, fuse_ok, with_tail, nullptr);
   return pl;
+}
+
+// floats of split-K scratch a plan needs: whole 128-row tiles per split (the in-kernel sum stores tile slices)
+static long long plan_scratch(const ConvPlan& pl, long long P, int C_out) {
+  return pl.splits > 1 ? pl.splits * ((P + kBlockM - 1) / kBlockM) * kBlockM * C_out : 0;
 }
 
 template <int BLOCK_N, bool kDgrad>
@@ -472,6 +508,13 @@ extern "C" void ddpb_conv_force(int pair, int block_n, int splits) {
   g_force_splits = splits;
 }
 
+// Words (uint32) of the `split_sync` buffer the conv entry points take: zero it ONCE; the kernels leave it zero.
+// Launches that may run concurrently need separate buffers.
+extern "C" int ddpb_conv_split_sync_words() { return kSplitSyncWords; }
+
+// Tuning hook: 0 = split-K partial sums always go through the second (finalize) kernel even with sync words.
+extern "C" void ddpb_conv_fuse_split(int on) { g_fuse_split = on; }
+
 // Tuning hook: 1 (default) = the fused BatchNorm tail reads the accumulators back from TMEM where that is
 // faster (one tile per CTA), 2 = wherever the shape allows it, 0 = it always re-reads the stored bf16 tiles
 // from L2.  All give the same output.
@@ -487,7 +530,7 @@ extern "C" void ddpb_conv_debug_mode(int mode) { g_dbg_mode = mode; }
 
 // What the planner picks for this shape: out3 = {pair, block_n, splits}.
 extern "C" void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3) {
-  const ConvPlan pl = plan_conv(static_cast<long long>(N) * H * W, C_out, taps * (C_in / 64), block_n, true);
+  const ConvPlan pl = plan_conv(static_cast<long long>(N) * H * W, C_out, taps * (C_in / 64), block_n, true, true);
   out3[0] = pl.pair;
   out3[1] = pl.block_n;
   out3[2] = pl.splits;
@@ -498,8 +541,14 @@ extern "C" long long ddpb_conv_fprop_scratch_elems(int N, int H, int W, int C_in
                                                    int block_n) {
   const long long P = static_cast<long long>(N) * H * W;
   if (C_out % 64 != 0 || C_in % 64 != 0) return 0;
-  const ConvPlan pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, true);
-  return pl.splits > 1 ? pl.splits * P * C_out : 0;
+  // enough for the plan with and the plan without the in-kernel sum (the caller may or may not pass sync words)
+  // and with / without a BatchNorm tail
+  long long need = 0;
+  for (int v = 0; v < 4; ++v) {
+    const long long a = plan_scratch(plan_conv(P, C_out, taps * (C_in / 64), block_n, true, (v & 1) != 0, (v & 2) != 0), P, C_out);
+    need = a > need ? a : need;
+  }
+  return need;
 }
 
 // Shared host path.  dgrad == 0: y[P][C_out] = conv(x[..C_in], w[C_out][taps*C_in]).
@@ -517,7 +566,8 @@ struct BnTail {
 // Returns 0 on success; *fused_bn (if given) tells whether the BatchNorm tail ran inside the conv kernel.
 static int conv_impl(int dgrad, const void* x, const void* w, const float* bias, void* y, float* stats, int N, int H,
                      int W, int C_in, int C_out, int taps, int block_n, float* scratch, long long scratch_elems,
-                     cudaStream_t stream, const BnTail* bn_tail = nullptr, int* fused_bn = nullptr) {
+                     unsigned int* split_sync, cudaStream_t stream, const BnTail* bn_tail = nullptr,
+                     int* fused_bn = nullptr) {
   const char* name = dgrad ? "conv_dgrad" : "conv_fprop";
   DDPB_REQUIRE(taps == 1 || taps == 9, "%s: taps must be 1 or 9 (got %d)", name, taps);
   DDPB_REQUIRE(C_in % 64 == 0 && C_in > 0, "%s: reduction channels must be a multiple of 64 (got %d)", name, C_in);
@@ -529,14 +579,15 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   DDPB_REQUIRE(block_n == 0 || C_out % block_n == 0, "%s: output channels %d not divisible by block_n %d", name,
                C_out, block_n);
   const long long P = static_cast<long long>(N) * H * W;
-  ConvPlan pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, scratch != nullptr);
+  const bool with_tail = bn_tail != nullptr && stats != nullptr;
+  ConvPlan pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, scratch != nullptr, split_sync != nullptr, with_tail);
   // The split-K choice is cost based, so a smaller batch can want MORE scratch than a larger one.  A plan
   // whose partial tiles do not fit in the caller's buffer is never launched: plan again without split-K.
-  if (pl.splits > 1 && static_cast<long long>(pl.splits) * P * C_out > scratch_elems) {
+  if (pl.splits > 1 && plan_scratch(pl, P, C_out) > scratch_elems) {
     DDPB_REQUIRE(g_force_splits < 0,
                  "%s: split-K x%d was forced but the scratch buffer holds %lld floats (needs %lld)", name, pl.splits,
-                 scratch_elems, static_cast<long long>(pl.splits) * P * C_out);
-    pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, false);
+                 scratch_elems, plan_scratch(pl, P, C_out));
+    pl = plan_conv(P, C_out, taps * (C_in / 64), block_n, false, false);
   }
   block_n = pl.block_n;
   const int b_rows = (pl.pair == 3) ? block_n / 2 : block_n;   // filter rows one CTA loads per k-step
@@ -600,9 +651,10 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
   p.pool = 0;
   p.eps = 0.f;
   p.tail_tmem = 0;
+  p.split_sync = pl.fused ? split_sync : nullptr;
   if (fused_bn != nullptr) *fused_bn = 0;
   // BatchNorm tail inside the kernel: persistent kernel, whole 2x2 windows per tile
-  if (bn_tail != nullptr && stats != nullptr && (pl.pair == 2 || pl.pair == 3) && pl.splits == 1 &&
+  if (bn_tail != nullptr && stats != nullptr && (pl.pair == 2 || pl.pair == 3) && (pl.splits == 1 || pl.fused) &&
       (!bn_tail->pool || bh % 2 == 0)) {
     p.gamma = bn_tail->gamma;
     p.beta = bn_tail->beta;
@@ -624,7 +676,8 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
     const int acc_bufs = (512 / block_n) < 4 ? (512 / block_n) : 4;
     const long long per_cta = (items + grid - 1) / grid;
     const bool pool_ok = !bn_tail->pool || (W >= 2 && W <= 16 && (W & (W - 1)) == 0 && H % 2 == 0);
-    if (pl.pair == 2 && pool_ok && ((g_tail_tmem == 1 && per_cta == 1) || (g_tail_tmem == 2 && per_cta <= acc_bufs)))
+    if (pl.pair == 2 && pl.splits == 1 && pool_ok &&
+        ((g_tail_tmem == 1 && per_cta == 1) || (g_tail_tmem == 2 && per_cta <= acc_bufs)))
       p.tail_tmem = 1;
   }
   const int m_tiles = (p.P + kBlockM - 1) / kBlockM;
@@ -655,7 +708,7 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
     DDPB_CONV_DISPATCH(launch_fprop)
   }
 #undef DDPB_CONV_DISPATCH
-  if (rc != 0 || splits == 1) return rc;
+  if (rc != 0 || splits == 1 || pl.fused) return rc;
   // (one channel-owner launch doing finalize + statistics + BatchNorm for the small split-K layers was tried and
   // removed: 64 CTAs pulling the fp32 partial tiles in 32-byte pieces took 27-28 us against 25 us for the
   // finalize + BatchNorm kernels, profiles/r2_call16_*)
@@ -676,9 +729,9 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
 // that does not fit in scratch_elems is replaced by one without split-K, never launched.
 extern "C" int ddpb_conv_fprop(const void* x, const void* w, const float* bias, void* y, float* stats,
                                int N, int H, int W, int C_in, int C_out, int taps, int block_n,
-                               float* scratch, long long scratch_elems, cudaStream_t stream) {
+                               float* scratch, long long scratch_elems, unsigned int* split_sync, cudaStream_t stream) {
   return conv_impl(0, x, w, bias, y, stats, N, H, W, C_in, C_out, taps, block_n, scratch,
-                   scratch != nullptr ? scratch_elems : 0, stream);
+                   scratch != nullptr ? scratch_elems : 0, split_sync, stream);
 }
 
 int bn_relu_pool_fwd_launch(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
@@ -693,13 +746,13 @@ extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const fl
                                           float* stats, const float* gamma, const float* beta, void* act,
                                           float* saved, int N, int H, int W, int C_in, int C_out, int taps,
                                           int pool, float eps, float* scratch, long long scratch_elems,
-                                          cudaStream_t stream) {
+                                          unsigned int* split_sync, cudaStream_t stream) {
   BnTail bn{gamma, beta, act, saved, pool, eps};
   int fused = 0;
   // (summing the split-K partials inside the persistent kernel after a second grid barrier was tried and
   // removed: 8 us per step slower than separate kernels with programmatic launch overlap, profiles/r1_call40_*)
   if (int rc = conv_impl(0, x, w, bias, conv_out, stats, N, H, W, C_in, C_out, taps, 0, scratch,
-                         scratch != nullptr ? scratch_elems : 0, stream, &bn, &fused))
+                         scratch != nullptr ? scratch_elems : 0, split_sync, stream, &bn, &fused))
     return rc;
   if (fused) return 0;
   return bn_relu_pool_fwd_launch(conv_out, stats, gamma, beta, act, saved, N, H, W, C_out, pool, eps, stream);
@@ -709,7 +762,8 @@ extern "C" int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const fl
 // fprop uses, [C_out][9][C_in]; dx: [N*H*W][C_in] bf16.  scratch: as for fprop, sized with
 // ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n).
 extern "C" int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out,
-                               int block_n, float* scratch, long long scratch_elems, cudaStream_t stream) {
+                               int block_n, float* scratch, long long scratch_elems, unsigned int* split_sync,
+                               cudaStream_t stream) {
   return conv_impl(1, dy, w, nullptr, dx, nullptr, N, H, W, C_out, C_in, 9, block_n, scratch,
-                   scratch != nullptr ? scratch_elems : 0, stream);
+                   scratch != nullptr ? scratch_elems : 0, split_sync, stream);
 }

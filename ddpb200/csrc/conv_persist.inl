@@ -82,7 +82,10 @@ __device__ __forceinline__ void persist_grid_barrier(unsigned int* word, const c
   __syncthreads();
 }
 
-template <int BLOCK_N, bool kDgrad>
+// kFuseSplit: split-K partial sums are added up inside the kernel (one item per CTA; see FpropParams::split_sync).
+// A separate instantiation: the ticket logic in the epilogue loop cost the first layer (14 short tiles per
+// CTA, epilogue bound) 4 us when it was a run-time branch.
+template <int BLOCK_N, bool kDgrad, bool kFuseSplit>
 __global__ void __launch_bounds__(512, 1)   // 512, not 320: caps the kernel at 128 registers per thread
 conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                     const __grid_constant__ CUtensorMap tmap_out, const FpropParams p, int m_tiles, int n_tiles,
@@ -234,7 +237,9 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     // across this CTA's tiles; they go to shared memory and on to global atomics only when the column
     // block changes (or at the end): with one flush per tile the 2*C_out atomic addresses were hit by
     // every tile of the layer and serialised in L2 (first layer: 2048 tiles onto 128 addresses).
-    const bool do_stats = (p.partial == nullptr) && (p.stats != nullptr);
+    constexpr bool fuse_split = kFuseSplit;
+    const bool do_stats = (p.partial == nullptr || fuse_split) && (p.stats != nullptr);
+    constexpr int kSliceVec = kMyChunks * 8 * 32;             // 16-byte words of one warp's fp32 slice of a tile
     constexpr int kBoxCols = Cfg::kBoxCols;
     constexpr int kBoxes = kMyChunks * 32 / kBoxCols;        // boxes per tile and warp: 1 / 1 / 2
     constexpr int kChunksPerBox = kBoxCols / 32;             // 1 / 2 / 2
@@ -291,7 +296,17 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       const uint32_t use = static_cast<uint32_t>(local / Cfg::kAccBufs);
       const long long pix = static_cast<long long>(it.m_tile) * kBlockM + row;
       const bool valid = pix < p.P;
-      const bool direct = (p.partial == nullptr);
+      bool direct = (p.partial == nullptr);
+      unsigned int* ticket = nullptr;
+      const int out_tile = it.n_tile * m_tiles + it.m_tile;
+      if (fuse_split) {
+        ticket = p.split_sync + (static_cast<long long>(out_tile) * 8 + ew) * 2;
+        unsigned int order = 0;
+        if (lane_id() == 0) order = atomicAdd(ticket, 1u);
+        order = __shfl_sync(0xffffffffu, order, 0);
+        direct = (order == static_cast<unsigned int>(splits - 1));     // last of this (tile, warp): sums and finishes it
+      }
+      const bool reduce_here = fuse_split && direct;
       // stage this warp's slice of the bias while the accumulator is still being produced
       if (direct && p.bias != nullptr) {
 #pragma unroll
@@ -302,7 +317,24 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       mbar_wait(&tmem_full[buf], use & 1);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + buf * BLOCK_N + (static_cast<uint32_t>(q * 32) << 16);
-      if (!direct) {
+      if (!direct && fuse_split) {
+        // this warp's 32 rows x BLOCK_N/2 columns, laid out [chunk][16-byte word][lane]: every store (and every load of
+        // the warp that sums) is one contiguous 512-byte run
+        uint4* dst = reinterpret_cast<uint4*>(p.partial) +
+                     ((static_cast<long long>(it.split) * (m_tiles * n_tiles) + out_tile) * 8 + ew) * kSliceVec + lane_id();
+#pragma unroll 1
+        for (int c = 0; c < kMyChunks; ++c) {
+          uint32_t raw[32];
+          tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            dst[(c * 8 + j) * 32] = make_uint4(raw[4 * j], raw[4 * j + 1], raw[4 * j + 2], raw[4 * j + 3]);
+        }
+        __threadfence();          // every lane's slice stores before the count below
+        __syncwarp();
+        if (lane_id() == 0) atomicAdd(ticket + 1, 1u);
+      } else if (!direct) {
         float* prow = p.partial + (static_cast<long long>(it.split) * p.P + pix) * p.C_out + it.n_tile * BLOCK_N;
 #pragma unroll 1
         for (int c = 0; c < kMyChunks; ++c) {
@@ -317,6 +349,26 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           }
         }
       } else {
+        if (reduce_here) {
+          if (lane_id() == 0) {
+            const unsigned long long t0 = global_timer_ns();
+            unsigned int seen, spins = 0;
+            do {
+              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(ticket + 1) : "memory");
+              if ((++spins & 0x3FFu) == 0 && global_timer_ns() - t0 > DDPB_WAIT_TIMEOUT_NS) {
+                printf("ddpb200: split-K reduction timed out (block %d, tile %d: %u of %d slices)\n", blockIdx.x, out_tile,
+                       seen, splits - 1);
+                __trap();
+              }
+            } while (seen < static_cast<unsigned int>(splits - 1));
+            ticket[0] = 0u;       // nobody else touches the pair any more in this launch: leave it zero for the next
+            ticket[1] = 0u;
+          }
+          __syncwarp();
+          __threadfence();
+        }
+        const uint4* slices = reinterpret_cast<const uint4*>(p.partial) + (static_cast<long long>(out_tile) * 8 + ew) * kSliceVec + lane_id();
+        const long long slice_stride = static_cast<long long>(m_tiles) * n_tiles * 8 * kSliceVec;    // between splits
 #pragma unroll 1
         for (int b = 0; b < kBoxes; ++b) {
           const uint32_t box = my_boxes + (box_count & 1u) * Cfg::kBoxBytes;
@@ -329,8 +381,38 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           for (int cc = 0; cc < kChunksPerBox; ++cc) {
             const int c = b * kChunksPerBox + cc;
             uint32_t raw[32];
-            tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
-            tmem_ld_wait();
+            if (!reduce_here) {
+              tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
+              tmem_ld_wait();
+            } else {
+              // sum over the splits in split order, this CTA's own accumulator at its position
+              float acc[32];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) acc[j] = 0.f;
+              auto add_slice = [&](int sp, float (&dst)[32]) {
+                const uint4* src = slices + sp * slice_stride + c * 8 * 32;
+                uint4 v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = __ldcg(src + j * 32);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  dst[4 * j] += __uint_as_float(v[j].x);
+                  dst[4 * j + 1] += __uint_as_float(v[j].y);
+                  dst[4 * j + 2] += __uint_as_float(v[j].z);
+                  dst[4 * j + 3] += __uint_as_float(v[j].w);
+                }
+              };
+#pragma unroll 1
+              for (int sp = 0; sp < it.split; ++sp) add_slice(sp, acc);
+              tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) acc[j] += __uint_as_float(raw[j]);
+#pragma unroll 1
+              for (int sp = it.split + 1; sp < splits; ++sp) add_slice(sp, acc);
+#pragma unroll
+              for (int j = 0; j < 32; ++j) raw[j] = __float_as_uint(acc[j]);
+            }
             uint32_t pk[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
@@ -440,7 +522,12 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     // in flight (a single tile is only 256..1024 items: fewer than the block has threads)
     const int out_tiles = m_tiles * n_tiles;             // (with split-K, several items share a tile)
     const int my_tiles = (out_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
-    const long long my_total = static_cast<long long>(my_tiles) * per_tile;
+    // without split-K a CTA normalises the tiles it wrote; with it (several CTAs per tile, all tiles final after the
+    // grid barrier) the flat item range of the whole layer is cut into one contiguous piece per CTA
+    constexpr bool spread = kFuseSplit;   // (the tail only runs with one split or with the in-kernel sum)
+    const long long all_total = static_cast<long long>(out_tiles) * per_tile;
+    const long long flat_lo = spread ? all_total * blockIdx.x / gridDim.x : 0;
+    const long long my_total = spread ? all_total * (blockIdx.x + 1) / gridDim.x - flat_lo : static_cast<long long>(my_tiles) * per_tile;
     // The pass is latency bound (the tiles come back from L2), so what counts is 16-byte loads in flight per
     // thread: 4 items x 4 window loads with pooling, 8 items x 1 load without (measured: the un-pooled
     // layers ran this pass at 1.8 TB/s with 4 loads in flight, profiles/r2_call15_*)
@@ -457,9 +544,9 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         for (int u = 0; u < kUnroll; ++u) {
           const long long flat = base + static_cast<long long>(u) * blockDim.x;
           ok[u] = flat < my_total;
-          const int tile_local = static_cast<int>(flat / per_tile);
-          const int w_item = static_cast<int>(flat - static_cast<long long>(tile_local) * per_tile);
-          const PersistItem it = persist_item(blockIdx.x + tile_local * gridDim.x, m_tiles, n_tiles);
+          const int tile_local = static_cast<int>((flat_lo + flat) / per_tile);
+          const int w_item = static_cast<int>(flat_lo + flat - static_cast<long long>(tile_local) * per_tile);
+          const PersistItem it = persist_item(spread ? tile_local : blockIdx.x + tile_local * gridDim.x, m_tiles, n_tiles);
           const int n_img0 = (it.m_tile / p.hblocks) * p.bn;
           const int h0 = (it.m_tile % p.hblocks) * p.bh;
           const int cgp = w_item % kGroups;
@@ -583,13 +670,13 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   if (threadIdx.x == 0) dbg_stamp(p, 3);
 }
 
-template <int BLOCK_N, bool kDgrad>
-static int launch_persist(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& to, const FpropParams& p,
-                          int m_tiles, int splits, cudaStream_t stream) {
+template <int BLOCK_N, bool kDgrad, bool kFuseSplit>
+static int launch_persist_impl(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& to, const FpropParams& p,
+                               int m_tiles, int splits, cudaStream_t stream) {
   using Cfg = PersistCfg<BLOCK_N>;
   static bool configured = false;
   if (!configured) {
-    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_persist_kernel<BLOCK_N, kDgrad>,
+    DDPB_CHECK_CUDA(cudaFuncSetAttribute(conv_persist_kernel<BLOCK_N, kDgrad, kFuseSplit>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured = true;
   }
@@ -597,7 +684,17 @@ static int launch_persist(const CUtensorMap& tx, const CUtensorMap& tw, const CU
   const int items = m_tiles * n_tiles * splits;
   int grid = sm_count();
   if (grid > items) grid = items;
-  DDPB_CHECK_CUDA(launch_pdl(conv_persist_kernel<BLOCK_N, kDgrad>, grid, kPersistThreads, Cfg::kSmemBytes, stream, tx,
-                             tw, to, p, m_tiles, n_tiles, splits));
+  DDPB_REQUIRE(!kFuseSplit || (grid == items && p.partial != nullptr && p.split_sync != nullptr),
+               "conv: the in-kernel split-K sum needs one item per CTA, scratch and sync words");
+  DDPB_CHECK_CUDA(launch_pdl(conv_persist_kernel<BLOCK_N, kDgrad, kFuseSplit>, grid, kPersistThreads, Cfg::kSmemBytes,
+                             stream, tx, tw, to, p, m_tiles, n_tiles, splits));
   return 0;
+}
+
+template <int BLOCK_N, bool kDgrad>
+static int launch_persist(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& to, const FpropParams& p,
+                          int m_tiles, int splits, cudaStream_t stream) {
+  if (p.split_sync != nullptr && splits > 1)
+    return launch_persist_impl<BLOCK_N, kDgrad, true>(tx, tw, to, p, m_tiles, splits, stream);
+  return launch_persist_impl<BLOCK_N, kDgrad, false>(tx, tw, to, p, m_tiles, splits, stream);
 }

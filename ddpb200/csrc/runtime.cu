@@ -140,4 +140,4 @@ extern "C" const char* ddpb_last_error() { return ddpb::last_error(); }
 extern "C" int ddpb_sm_count() { return ddpb::sm_count(); }
 
 // Library/ABI version: bump when an entry point's signature changes.
-extern "C" int ddpb_abi_version() { return 4; }
+extern "C" int ddpb_abi_version() { return 5; }

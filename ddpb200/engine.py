@@ -200,6 +200,9 @@ class VGGEngine:
                     need_f = max(need_f, K.conv_fprop_scratch_elems(n, L.H, L.W, L.c_out, L.c_in, 9))
         self.wgrad_scratch = torch.empty(need_w, **f32)
         self.fprop_scratch = torch.empty(need_f, **f32)
+        # sync words of the in-kernel split-K sums (zeroed once, left zero by every launch; fprop and dgrad
+        # run one after the other on the main stream, so one buffer serves both)
+        self.split_sync = torch.zeros(K.conv_split_sync_words(), dtype=torch.int32, device=dev)
         # --- partial sums of the BatchNorm backward (one buffer, the layers run one after the other)
         need_p = 1
         for L in self.layers:
@@ -270,7 +273,7 @@ class VGGEngine:
             K.conv_bn_relu_pool_fwd(x, self.w_f[li], a.flat_master(L.p_b), a.flat_master(L.p_g),
                                     a.flat_master(L.p_beta), N, L.H, L.W, L.c_in_eff, L.c_out, L.taps, L.pool,
                                     conv_out=self.conv_out[li], act=self.act[li], stats=self.stats[li],
-                                    saved=self.saved[li], scratch=self.fprop_scratch)
+                                    saved=self.saved[li], scratch=self.fprop_scratch, split_sync=self.split_sync)
             self.mark(f"L{li} conv+bn fwd")
             x = self.act[li]
         feat = x[:N]
@@ -340,7 +343,7 @@ class VGGEngine:
                 self.mark(f"L{li} wgrad")
             if li > 0:
                 K.conv_dgrad(self.dconv[li], self.w_f[li], N, L.H, L.W, L.c_in, L.c_out, out=self.dact[li - 1],
-                             scratch=self.fprop_scratch)
+                             scratch=self.fprop_scratch, split_sync=None)   # two-kernel split-K is faster here (no tail to fuse)
                 self.mark(f"L{li} dgrad")
             if after_layer is not None:
                 after_layer(li, side_events[-1:] if side_stream is not None else [])

@@ -28,9 +28,11 @@ _SIGNATURES = {
     "ddpb_abi_version": [],
     "ddpb_sm_count": [],
     "ddpb_conv_fprop": [c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
-                        c_void, c_ll, c_void],
+                        c_void, c_ll, c_void, c_void],
+    "ddpb_conv_split_sync_words": [],
+    "ddpb_conv_fuse_split": [c_int],
     "ddpb_conv_fprop_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int, c_int],
-    "ddpb_conv_bn_relu_pool_fwd": [c_void] * 9 + [c_int] * 7 + [c_float, c_void, c_ll, c_void],
+    "ddpb_conv_bn_relu_pool_fwd": [c_void] * 9 + [c_int] * 7 + [c_float, c_void, c_ll, c_void, c_void],
     "ddpb_conv_force": [c_int, c_int, c_int],
     "ddpb_conv_debug_timing": [c_void],
     "ddpb_conv_debug_mode": [c_int],
@@ -57,7 +59,7 @@ _SIGNATURES = {
     "ddpb_fc_bwd": [c_void, c_void, c_void, c_void, c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_void,
                     c_void, c_void],
     "ddpb_sgd_step": [c_void, c_void, c_void, c_void, c_ll, c_float, c_float, c_float, c_float, c_void],
-    "ddpb_conv_dgrad": [c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_void, c_ll, c_void],
+    "ddpb_conv_dgrad": [c_void, c_void, c_void, c_int, c_int, c_int, c_int, c_int, c_int, c_void, c_ll, c_void, c_void],
     "ddpb_pack_weights": [c_int, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void, c_void],
     "ddpb_first_layer_operand_f32": [c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_int, c_void],
     "ddpb_first_layer_operand_u8": [c_void, c_void, c_void, c_int, c_int, c_int, c_void, c_void, c_int, c_void,

@@ -45,6 +45,40 @@ def conv_plan(N, H, W, C_in, C_out, taps=9, block_n=0) -> tuple[int, int, int]:
     return tuple(out)
 
 
+_SPLIT_SYNC: dict = {}
+
+
+def conv_split_sync(device) -> torch.Tensor:
+    """The zeroed sync words the conv entry points use to add up split-K partial sums inside the kernel: one
+    cached buffer per device (the kernels leave it zero).  Launches that may run concurrently on several
+    streams need their own (``torch.zeros(conv_split_sync_words(), dtype=torch.int32)``)."""
+    key = torch.device(device)
+    if key.index is None:
+        key = torch.device("cuda", torch.cuda.current_device())
+    buf = _SPLIT_SYNC.get(key)
+    if buf is None:
+        buf = _SPLIT_SYNC[key] = torch.zeros(conv_split_sync_words(), dtype=torch.int32, device=key)
+    return buf
+
+
+def conv_split_sync_words() -> int:
+    return int(nat.load().ddpb_conv_split_sync_words())
+
+
+def conv_fuse_split(on: bool) -> None:
+    """Tuning hook: False = split-K partial sums always go through the second (finalize) kernel."""
+    nat.load().ddpb_conv_fuse_split(int(on))
+
+
+def _sync_arg(split_sync, device):
+    if split_sync is True:
+        return conv_split_sync(device)
+    if split_sync is False or split_sync is None:
+        return None
+    assert split_sync.dtype == torch.int32 and split_sync.numel() >= conv_split_sync_words() and split_sync.is_cuda
+    return split_sync
+
+
 def conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps=9, block_n=0) -> int:
     """fp32 elements of split-K scratch conv_fprop wants for this shape (0 = no split)."""
     return int(nat.load().ddpb_conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps, block_n))
@@ -52,7 +86,8 @@ def conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps=9, block_n=0) -> int:
 
 def conv_fprop(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, N: int, H: int, W: int, C_in: int,
                C_out: int, taps: int = 9, *, out: torch.Tensor | None = None, stats: torch.Tensor | None = None,
-               block_n: int = 0, scratch: torch.Tensor | None | bool = True, stream=None) -> torch.Tensor:
+               block_n: int = 0, scratch: torch.Tensor | None | bool = True, split_sync=True,
+               stream=None) -> torch.Tensor:
     """O1 (and O2 when fed dY and the rotated filters): y[P,C_out] = conv3x3(x) (+bias).
 
     ``stats`` (fp32 [2, C_out]) is accumulated with per-channel sum / sum of squares of y.
@@ -70,14 +105,15 @@ def conv_fprop(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, N: i
     elif scratch is False:
         scratch = None
     rc = nat.load().ddpb_conv_fprop(nat.ptr(x), nat.ptr(w), nat.ptr(bias), nat.ptr(out), nat.ptr(stats), N, H, W,
-                                    C_in, C_out, taps, block_n, nat.ptr(scratch), _numel(scratch), _s(stream))
+                                    C_in, C_out, taps, block_n, nat.ptr(scratch), _numel(scratch),
+                                    nat.ptr(_sync_arg(split_sync, x.device)), _s(stream))
     nat.check(rc, "ddpb_conv_fprop")
     return out
 
 
 def conv_bn_relu_pool_fwd(x, w, bias, gamma, beta, N, H, W, C_in, C_out, taps, pool: bool, *, conv_out=None, act=None,
                           stats=None, saved=None, scratch: torch.Tensor | None | bool = True, eps=BN_EPS,
-                          stream=None):
+                          split_sync=True, stream=None):
     """O1+O4+O6+O7: conv -> BatchNorm(batch stats) -> ReLU (-> 2x2 max-pool) in one call.  Returns
     (conv_out, act, saved).  ``stats``: zeroed fp32 scratch of 2*C_out + 32 elements."""
     nat.require_cuda(x, w, gamma, beta)
@@ -101,14 +137,14 @@ def conv_bn_relu_pool_fwd(x, w, bias, gamma, beta, N, H, W, C_in, C_out, taps, p
     rc = nat.load().ddpb_conv_bn_relu_pool_fwd(nat.ptr(x), nat.ptr(w), nat.ptr(bias), nat.ptr(conv_out), nat.ptr(stats),
                                                nat.ptr(gamma), nat.ptr(beta), nat.ptr(act), nat.ptr(saved), N, H, W,
                                                C_in, C_out, taps, int(pool), eps, nat.ptr(scratch), _numel(scratch),
-                                               _s(stream))
+                                               nat.ptr(_sync_arg(split_sync, dev)), _s(stream))
     nat.check(rc, "ddpb_conv_bn_relu_pool_fwd")
     return conv_out, act, saved
 
 
 def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, C_in: int, C_out: int, *,
                out: torch.Tensor | None = None, block_n: int = 0, scratch: torch.Tensor | None | bool = True,
-               stream=None) -> torch.Tensor:
+               split_sync=True, stream=None) -> torch.Tensor:
     """O2: dx[P, C_in] from dy[P, C_out] and the SAME bf16 filter pack fprop uses ([C_out, 9*C_in])."""
     nat.require_cuda(dy, w_fprop)
     assert dy.dtype == torch.bfloat16 and w_fprop.dtype == torch.bfloat16
@@ -121,7 +157,8 @@ def conv_dgrad(dy: torch.Tensor, w_fprop: torch.Tensor, N: int, H: int, W: int, 
     elif scratch is False:
         scratch = None
     rc = nat.load().ddpb_conv_dgrad(nat.ptr(dy), nat.ptr(w_fprop), nat.ptr(out), N, H, W, C_in, C_out, block_n,
-                                    nat.ptr(scratch), _numel(scratch), _s(stream))
+                                    nat.ptr(scratch), _numel(scratch), nat.ptr(_sync_arg(split_sync, dy.device)),
+                                    _s(stream))
     nat.check(rc, "ddpb_conv_dgrad")
     return out
 

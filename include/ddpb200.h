@@ -43,7 +43,7 @@ int ddpb_publish_scalar(const float* value, unsigned int* dev_seq, unsigned long
  * scratch_elems is replaced by one without split-K; nothing is ever written past the buffer. */
 int ddpb_conv_fprop(const void* x, const void* w, const float* bias, void* y, float* stats, int N, int H, int W,
                     int C_in, int C_out, int taps, int block_n, float* scratch, long long scratch_elems,
-                    void* stream);
+                    unsigned int* split_sync, void* stream);
 long long ddpb_conv_fprop_scratch_elems(int N, int H, int W, int C_in, int C_out, int taps, int block_n);
 
 /* O1+O4+O6+O7 in one call: convolution, then BatchNorm(batch statistics) + ReLU (+2x2 max-pool),
@@ -55,13 +55,13 @@ long long ddpb_conv_fprop_scratch_elems(int N, int H, int W, int C_in, int C_out
 int ddpb_conv_bn_relu_pool_fwd(const void* x, const void* w, const float* bias, void* conv_out, float* stats,
                                const float* gamma, const float* beta, void* act, float* saved_mean_rstd, int N, int H,
                                int W, int C_in, int C_out, int taps, int pool, float eps, float* scratch,
-                               long long scratch_elems, void* stream);
+                               long long scratch_elems, unsigned int* split_sync, void* stream);
 
 /* O2: data gradient of the same convolution (autograd of part1/model.py:18-23).
  * dx[N*H*W][C_in] from dy[..][C_out] and the SAME filter pack fprop reads (no transposed copy).
  * scratch sized with ddpb_conv_fprop_scratch_elems(N, H, W, C_out, C_in, 9, block_n). */
 int ddpb_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C_in, int C_out, int block_n,
-                    float* scratch, long long scratch_elems, void* stream);
+                    float* scratch, long long scratch_elems, unsigned int* split_sync, void* stream);
 
 /* O3: weight gradient.  dw (fp32 [C_out][dw_ld]) gets its first dw_cols_valid (<= taps*C_in)
  * columns per row.  scratch: scratch_elems floats of device memory for the split reduction over
@@ -95,6 +95,12 @@ long long ddpb_conv_wgrad_static_max_elems(void);
 void ddpb_conv_force(int kernel, int block_n, int splits);
 void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3);
 void ddpb_conv_debug_timing(unsigned long long* per_cta_stamps);   /* 8 slots per CTA, see bench/conv_probe2.py */
+/* split_sync (optional, may be null): ddpb_conv_split_sync_words() uint32 words, zeroed ONCE by the caller and left
+ * zero by every launch.  With it, split-K partial sums are added up inside the persistent kernel (the warp that
+ * draws the last ticket of a tile sums the slices in split order: deterministic) and the BatchNorm tail stays
+ * fused; without it a second kernel sums them.  Launches that can run concurrently need separate buffers. */
+int ddpb_conv_split_sync_words(void);
+void ddpb_conv_fuse_split(int on);       /* tuning: 0 = never sum split-K inside the kernel */
 void ddpb_conv_tail_from_tmem(int on);   /* fused BatchNorm tail re-reads the accumulators from TMEM: 1 (default) with one
                                             tile per CTA, 2 wherever the shape allows, 0 never (stored tiles from L2).
                                             Same output. */

@@ -464,3 +464,50 @@ def test_batchnorm_tail_from_tmem_equals_the_tail_from_l2(shape, pool):
     assert float(diff.max()) <= 2 ** -6 * float(out[0][1].float().abs().max()) and float((diff > 0).float().mean()) < 1e-3
     for mode in (0, 2):
         assert _rel_err(out[mode][1], R.bn_relu_pool_fwd(out[mode][0], gamma, beta, N, H, W, pool)) < 1e-2
+
+
+@pytest.mark.parametrize("case", [((256, 2, 2, 512, 512), 128, 4), ((256, 2, 2, 512, 512), 256, 8), ((256, 2, 2, 512, 512), 64, 2),
+                                  ((96, 2, 2, 512, 512), 128, 8), ((64, 4, 4, 256, 512), 128, 4), ((37, 4, 4, 512, 256), 256, 7),
+                                  ((8, 8, 8, 128, 256), 128, 3), ((3, 2, 2, 512, 512), 128, 5)])
+def test_split_k_summed_inside_the_persistent_kernel(case):
+    """Split-K with sync words: the warp that draws the last ticket of a tile sums the slices in split order, so
+    the output does not depend on which CTA finished last (bitwise repeatable), the BatchNorm tail stays fused,
+    and the sync words are zero again afterwards.  Oracle: ATen; cross-check: the two-kernel path."""
+    (N, H, W, Ci, Co), bn, splits = case
+    torch.manual_seed(4)
+    x = torch.randn(N * H * W, Ci, device=DEV).bfloat16()
+    w = (torch.randn(Co, 9 * Ci, device=DEV) / (9 * Ci) ** 0.5).bfloat16()
+    dy = torch.randn(N * H * W, Co, device=DEV).bfloat16()
+    b = torch.randn(Co, device=DEV) * 0.1
+    gamma, beta = torch.rand(Co, device=DEV) + 0.5, torch.randn(Co, device=DEV) * 0.2
+    sync = torch.zeros(K.conv_split_sync_words(), dtype=torch.int32, device=DEV)
+    scratch = torch.full((8 * ((N * H * W + 127) // 128) * 128 * max(Ci, Co),), float("nan"), device=DEV)
+    ref = R.conv_fprop(x, w, b, N, H, W, Ci, Co)
+    ref_dx = R.conv_dgrad(dy, w, N, H, W, Ci, Co)
+    try:
+        K.conv_force(-1, bn, splits)
+        assert K.conv_plan(N, H, W, Ci, Co, 9)[1:] == (bn, splits)
+        runs = []
+        for _ in range(3):
+            y = K.conv_fprop(x, w, b, N, H, W, Ci, Co, scratch=scratch, split_sync=sync)
+            conv_out, act, saved = K.conv_bn_relu_pool_fwd(x, w, b, gamma, beta, N, H, W, Ci, Co, 9, True, scratch=scratch,
+                                                           split_sync=sync)
+            dx = K.conv_dgrad(dy, w, N, H, W, Ci, Co, scratch=scratch, split_sync=sync) if Ci % bn == 0 else None
+            torch.cuda.synchronize()
+            assert int(sync.abs().sum()) == 0
+            runs.append((y.clone(), conv_out.clone(), None if dx is None else dx.clone(), act.clone()))
+        for r in runs[1:]:
+            assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][0])      # same bits every time, both entry points
+            assert r[2] is None or torch.equal(r[2], runs[0][2])
+        y, conv_out, dx, act = runs[0]
+        assert _rel_err(y, ref) < 1e-2
+        assert dx is None or _rel_err(dx, ref_dx) < 1e-2
+        assert _rel_err(act, R.bn_relu_pool_fwd(conv_out, gamma, beta, N, H, W, True)) < 1e-2
+        cf = conv_out.float()
+        assert torch.allclose(saved[0], cf.mean(0), rtol=1e-3, atol=1e-3)
+        # the two-kernel path (no sync words) sums in another order: equal up to fp32 rounding before the bf16 store
+        y2 = K.conv_fprop(x, w, b, N, H, W, Ci, Co, scratch=scratch, split_sync=None)
+        diff = (y2.float() - y.float()).abs()
+        assert float((diff > 0).float().mean()) < 2e-2 and float(diff.max()) <= 2 ** -7 * float(y.float().abs().max())
+    finally:
+        K.conv_force(-1, -1, -1)
