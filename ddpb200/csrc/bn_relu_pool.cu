@@ -18,7 +18,22 @@ struct BnGeom {
   int N, H, W, C;   // pre-pool geometry
   int pool;         // 1: 2x2/2 max-pool follows the ReLU
   float eps;
+  // a stride of 32 / 256 pooled output pixels as {step % Wo, step / Wo}, for the kernels that walk the pooled pixels
+  // incrementally (kernel parameters: no registers)
+  int d32[2], d256[2];
 };
+
+static BnGeom make_geom(int N, int H, int W, int C, int pool, float eps) {
+  BnGeom g{N, H, W, C, pool, eps, {0, 0}, {0, 0}};
+  const int Wo = W / 2;
+  if (pool && Wo > 0) {
+    g.d32[0] = 32 % Wo;
+    g.d32[1] = 32 / Wo;
+    g.d256[0] = 256 % Wo;
+    g.d256[1] = 256 / Wo;
+  }
+  return g;
+}
 
 // scale/shift per channel in shared memory: y = x*scale + shift.
 __device__ __forceinline__ void bn_coeffs_to_smem(const float* __restrict__ stats, const float* __restrict__ gamma,
@@ -681,18 +696,35 @@ static Bn2Plan bn2_plan(long long out_pix, int C) {
 // Loads one work item: dy of output pixel `opix` and the matching x window (1 pixel, or the 2x2 pooling
 // window whose first pixel index is returned).  32-bit pixel arithmetic (the host checks N*H*W*C < 2^31):
 // the 64-bit divisions of the older kernels cost more instructions than the rest of the item.
+// Position of a pooled output pixel, kept incrementally: a thread's items are kBn2Rows output pixels apart, so
+// (wo, ho, n) advance by constant amounts with two carries instead of three integer divisions per item (the
+// divisions were ~40% of the instructions of the pooled kernels, and the compute phase between two rounds of
+// loads, not the memory system, is what bounds them).
+struct Bn2Pos {
+  int wo, row;          // current output pixel: column, and row counted over all images (n * Ho + ho)
+};
+__device__ __forceinline__ Bn2Pos bn2_pos(const BnGeom& g, int opix) {
+  const int Wo = g.W >> 1;
+  Bn2Pos p;
+  p.wo = opix % Wo;
+  p.row = opix / Wo;
+  return p;
+}
+// step: g.d32 or g.d256 (the thread's stride in pooled pixels as {step % Wo, step / Wo}, from the host)
+__device__ __forceinline__ void bn2_advance(Bn2Pos& p, const BnGeom& g, const int (&step)[2]) {
+  const int Wo = g.W >> 1;
+  p.wo += step[0];
+  const int carry = p.wo >= Wo ? 1 : 0;
+  p.wo -= carry ? Wo : 0;
+  p.row += step[1] + carry;
+}
+
 template <bool kPool>
 __device__ __forceinline__ int bn2_load(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
-                                        const BnGeom& g, int opix, int cg, uint4 (&v)[kPool ? 4 : 1], uint4& d) {
+                                        const BnGeom& g, int opix, const Bn2Pos& pos, int cg,
+                                        uint4 (&v)[kPool ? 4 : 1], uint4& d) {
   int base = opix;
-  if (kPool) {
-    const int Ho = g.H >> 1, Wo = g.W >> 1;
-    const int wo = opix % Wo;
-    const int t = opix / Wo;
-    const int ho = t % Ho;
-    const int n = t / Ho;
-    base = (n * g.H + 2 * ho) * g.W + 2 * wo;
-  }
+  if (kPool) base = 2 * (pos.row * g.W + pos.wo);      // H is even: input row = 2 * (n * Ho + ho)
   d = ldg16(dy + static_cast<size_t>(opix) * g.C + cg * 8);
 #pragma unroll
   for (int q = 0; q < (kPool ? 4 : 1); ++q)
@@ -732,6 +764,8 @@ bn_bwd2_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
   }
   const uint4 flip = sign_flip_mask(sc);
   (void)flip;
+  Bn2Pos pos = {};
+  if (kPool) pos = bn2_pos(g, p_begin + prow);
   for (int base = p_begin + prow; base < p_end; base += kBn2Rows * kU) {
     uint4 v[kU][kWin], d[kU];
     int ipix[kU];
@@ -740,7 +774,8 @@ bn_bwd2_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
     for (int u = 0; u < kU; ++u) {
       const int opix = base + u * kBn2Rows;
       ok[u] = opix < p_end;
-      if (ok[u]) ipix[u] = bn2_load<kPool>(x, dy, g, opix, cg, v[u], d[u]);
+      if (ok[u]) ipix[u] = bn2_load<kPool>(x, dy, g, opix, pos, cg, v[u], d[u]);
+      if (kPool) bn2_advance(pos, g, g.d32);
     }
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
@@ -853,6 +888,8 @@ bn_bwd2_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
   }
   const uint4 flip = sign_flip_mask(sc);
   (void)flip;
+  Bn2Pos pos = {};
+  if (kPool) pos = bn2_pos(g, p_begin + prow);
   for (int base = p_begin + prow; base < p_end; base += kBn2Rows * kU) {
     uint4 v[kU][kWin], d[kU];
     int ipix[kU];
@@ -861,7 +898,8 @@ bn_bwd2_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
     for (int u = 0; u < kU; ++u) {
       const int opix = base + u * kBn2Rows;
       ok[u] = opix < p_end;
-      if (ok[u]) ipix[u] = bn2_load<kPool>(x, dy, g, opix, cg, v[u], d[u]);
+      if (ok[u]) ipix[u] = bn2_load<kPool>(x, dy, g, opix, pos, cg, v[u], d[u]);
+      if (kPool) bn2_advance(pos, g, g.d32);
     }
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
@@ -956,9 +994,13 @@ bn_bwd_owner_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   const int out_pix = g.N * (kPool ? g.H / 2 : g.H) * (kPool ? g.W / 2 : g.W);
   pdl_wait();
   // ---- phase 1a: every global load of the CTA, straight into shared memory
+  Bn2Pos pos = {};
+  static_assert(kBnOwnThreads == 256 && kBn2Rows == 32, "BnGeom carries the strides 32 and 256");
+  if (kPool) pos = bn2_pos(g, threadIdx.x);
   for (int i = threadIdx.x; i < out_pix; i += kBnOwnThreads) {
     uint4 v[kWin], d;
-    bn2_load<kPool>(x, dy, g, i, cg, v, d);
+    bn2_load<kPool>(x, dy, g, i, pos, cg, v, d);
+    if (kPool) bn2_advance(pos, g, g.d256);
     uint4* slot = s_data + static_cast<size_t>(i) * kSlot;
 #pragma unroll
     for (int q = 0; q < kWin; ++q) slot[q] = v[q];
@@ -1212,7 +1254,7 @@ extern "C" int ddpb_bn_relu_pool_fwd(const void* x, const float* stats, const fl
 int bn_relu_pool_fwd_launch(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
                             float* saved, int N, int H, int W, int C, int pool, float eps, cudaStream_t stream) {
   DDPB_BN_CHECK_GEOM("bn_relu_pool_fwd");
-  BnGeom g{N, H, W, C, pool, eps};
+  BnGeom g = make_geom(N, H, W, C, pool, eps);
   const long long items = static_cast<long long>(N) * (pool ? H / 2 : H) * (pool ? W / 2 : W) * (C / 8);
   DDPB_CHECK_CUDA(launch_pdl(bn_relu_pool_fwd_kernel, bn_grid(items), kBnThreads, 4 * C * sizeof(float), stream,
                              static_cast<const __nv_bfloat16*>(x), stats, gamma, beta, static_cast<__nv_bfloat16*>(y),
@@ -1243,7 +1285,7 @@ extern "C" int ddpb_bn_relu_pool_bwd(const void* x, const void* dy, const float*
                                      float* dbias, float* partials, long long partial_elems, int N, int H, int W,
                                      int C, int pool, float eps, cudaStream_t stream) {
   DDPB_BN_CHECK_GEOM("bn_relu_pool_bwd");
-  BnGeom g{N, H, W, C, pool, eps};
+  BnGeom g = make_geom(N, H, W, C, pool, eps);
   DDPB_REQUIRE((C / 8) <= kBnThreads && kBnThreads % (C / 8) == 0,
                "bn_relu_pool_bwd: C/8 must divide %d (got C=%d)", kBnThreads, C);
   const long long items = static_cast<long long>(N) * (pool ? H / 2 : H) * (pool ? W / 2 : W) * (C / 8);
