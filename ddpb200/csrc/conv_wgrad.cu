@@ -47,12 +47,13 @@ struct WgradParams {
   int m_tiles, n_tiles;
   int bh, bn, hblocks;  // 64-pixel box geometry of X
   int dup_m;            // C_out == 64: both halves of M read the same 64 channels
+  int rows_per_split;   // rows of `out` one split owns (the output tensor map stacks the splits along its rows)
 };
 
 template <int BLOCK_N, bool kDeep>
 __global__ void __launch_bounds__(kWgThreads)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x,
-                  const WgradParams p) {
+                  const __grid_constant__ CUtensorMap tmap_out, const WgradParams p) {
   using Cfg = WgradCfg<BLOCK_N, kDeep>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1k(smem_raw);
@@ -80,6 +81,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmap_dy);
     tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_out);
   }
   if (warp == 1) {
     if (elect_one()) {
@@ -156,16 +158,20 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
       umma_commit(tmem_full_bar);
     }
   } else {
+    // Epilogue through shared memory and TMA stores: a lane holds one output row (channel), so direct stores
+    // were 32 lanes x 16 bytes to 32 different rows per instruction (partial lines; the same pattern cost the
+    // fprop epilogue 2 us per 32-column chunk and warp).  The operand ring is idle once the accumulator is
+    // complete: each warp stages 32 rows x 32 fp32 columns (one 128-byte swizzle row per lane, conflict free)
+    // in two alternating 4 KB boxes of it and hands them to the TMA engine.
     const int q = warp & 3;
-    const int row = q * 32 + lane_id();       // output channel within the M tile
-    const int k_ch = m_tile * 128 + row;
-    const bool valid = p.dup_m ? (row < 64) : (k_ch < p.C_out);
-    float* out_row = p.out + static_cast<long long>(split) * p.out_split_stride +
-                     static_cast<long long>(k_ch) * p.out_ld + tap * p.C_in + n_tile * BLOCK_N;
+    const int r = static_cast<int>(lane_id());
     if (num_k > 0) {
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
     }
+    const uint32_t my_boxes = smem_u32(tiles) + static_cast<uint32_t>(q) * 8192u;
+    const int out_row = split * p.rows_per_split + m_tile * 128 + q * 32;
+    const int out_col = tap * p.C_in + n_tile * BLOCK_N;
 #pragma unroll 1
     for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
       uint32_t raw[32];
@@ -176,12 +182,22 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 #pragma unroll
         for (int j = 0; j < 32; ++j) raw[j] = 0u;
       }
-      if (valid) {
-        uint4* dst = reinterpret_cast<uint4*>(out_row + chunk * 32);
+      const uint32_t box = my_boxes + (chunk & 1) * 4096u;
+      if (lane_id() == 0) bulk_wait_read<1>();     // the store issued from this box two chunks ago has read it
+      __syncwarp();
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dst[j] = make_uint4(raw[4 * j], raw[4 * j + 1], raw[4 * j + 2], raw[4 * j + 3]);
+      for (int k = 0; k < 8; ++k)
+        st_shared_v4(box + r * 128 + ((k ^ (r & 7)) << 4), raw[4 * k], raw[4 * k + 1], raw[4 * k + 2], raw[4 * k + 3]);
+      fence_proxy_async();
+      __syncwarp();
+      if (lane_id() == 0) {
+        // (C_out == 64: rows 64..127 of the tile are duplicates and land in the unused half of the split's scratch)
+        tma_store_2d_saddr(&tmap_out, box, out_col + chunk * 32, out_row);
+        bulk_commit();
       }
     }
+    if (lane_id() == 0) bulk_wait<0>();     // shared memory must outlive the reads; the writes are done at kernel end
+    __syncwarp();
   }
 
   tc_fence_before();
@@ -249,8 +265,8 @@ wgrad_reduce_rows_kernel(const float* __restrict__ ws, float* __restrict__ out, 
 }
 
 template <int BLOCK_N, bool kDeep>
-static int launch_wgrad_cfg(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
-                            cudaStream_t stream) {
+static int launch_wgrad_cfg(const CUtensorMap& tdy, const CUtensorMap& tx, const CUtensorMap& to, const WgradParams& p,
+                            int splits, cudaStream_t stream) {
   using Cfg = WgradCfg<BLOCK_N, kDeep>;
   static bool configured = false;
   if (!configured) {
@@ -259,7 +275,7 @@ static int launch_wgrad_cfg(const CUtensorMap& tdy, const CUtensorMap& tx, const
     configured = true;
   }
   dim3 grid(p.taps * p.m_tiles * p.n_tiles, splits);
-  DDPB_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BLOCK_N, kDeep>, grid, kWgThreads, Cfg::kSmemBytes, stream, tdy, tx, p));
+  DDPB_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BLOCK_N, kDeep>, grid, kWgThreads, Cfg::kSmemBytes, stream, tdy, tx, to, p));
   return 0;
 }
 
@@ -269,15 +285,15 @@ static int launch_wgrad_cfg(const CUtensorMap& tdy, const CUtensorMap& tx, const
 static int g_wgrad_deep = -1;   // -1: environment DDPB_WGRAD_DEEP (default on), 0 / 1
 
 template <int BLOCK_N>
-static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradParams& p, int splits,
-                        cudaStream_t stream) {
+static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const CUtensorMap& to, const WgradParams& p,
+                        int splits, cudaStream_t stream) {
   if (g_wgrad_deep < 0) {
     const char* e = getenv("DDPB_WGRAD_DEEP");
     g_wgrad_deep = e ? atoi(e) : 1;
   }
   const long long ctas = static_cast<long long>(p.taps) * p.m_tiles * p.n_tiles * splits;
-  if (g_wgrad_deep && ctas <= sm_count()) return launch_wgrad_cfg<BLOCK_N, true>(tdy, tx, p, splits, stream);
-  return launch_wgrad_cfg<BLOCK_N, false>(tdy, tx, p, splits, stream);
+  if (g_wgrad_deep && ctas <= sm_count()) return launch_wgrad_cfg<BLOCK_N, true>(tdy, tx, to, p, splits, stream);
+  return launch_wgrad_cfg<BLOCK_N, false>(tdy, tx, to, p, splits, stream);
 }
 
 // Launch plan: the one-tap kernel with `groups` pixel splits.
@@ -414,8 +430,21 @@ static int wgrad_impl(const void* dy, const void* x, float* dw, float* scratch, 
     p.out = scratch;
     p.out_split_stride = rows * taps * C_in;
   }
-  const int rc = (block_n == 128) ? launch_wgrad<128>(tdy, tx, p, splits, stream)
-                                  : launch_wgrad<64>(tdy, tx, p, splits, stream);
+  p.rows_per_split = direct ? 0 : static_cast<int>(rows);
+  // output (dw itself, or the splits' partial tiles stacked along the rows): fp32 [rows][taps * C_in], written in
+  // boxes of 32 rows x 32 columns (128-byte swizzle rows)
+  CUtensorMap to;
+  {
+    DDPB_REQUIRE((reinterpret_cast<uintptr_t>(p.out) & 15u) == 0, "conv_wgrad: dw / scratch must be 16-byte aligned");
+    uint64_t dims[2] = {(uint64_t)taps * C_in, direct ? (uint64_t)C_out : (uint64_t)splits * rows};
+    uint64_t strides[1] = {(uint64_t)taps * C_in * 4};
+    uint32_t box[2] = {32, 32};
+    if (encode_tmap(&to, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, p.out, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B))
+      return 3;
+  }
+  const int rc = (block_n == 128) ? launch_wgrad<128>(tdy, tx, to, p, splits, stream)
+                                  : launch_wgrad<64>(tdy, tx, to, p, splits, stream);
   if (rc) return rc;
   if (!direct) {
     const bool dense = (dw_cols_valid == taps * C_in && dw_ld == taps * C_in && C_out >= 128);
