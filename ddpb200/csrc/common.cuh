@@ -205,6 +205,12 @@ __device__ __forceinline__ void tma_store_2d_saddr(const CUtensorMap* map, uint3
                "r"(src_saddr), "r"(c0), "r"(c1)
                : "memory");
 }
+__device__ __forceinline__ void tma_store_3d_saddr(const CUtensorMap* map, uint32_t src_saddr, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(src_saddr), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // at most N of this thread's bulk groups may still be READING their shared-memory source
 template <int N>

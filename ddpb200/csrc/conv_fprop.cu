@@ -629,6 +629,16 @@ static int conv_impl(int dgrad, const void* x, const void* w, const float* bias,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B))
       return 3;
   }
+  if (pl.pair == 2 && pl.splits > 1 && !pl.fused) {
+    // persistent kernel, split-K summed by the second kernel: no bf16 tile is stored by this launch, and the
+    // same parameter slot carries the fp32 map of the partial buffer [split][P][C_out], boxes of 32 x 32
+    uint64_t dims[3] = {(uint64_t)C_out, (uint64_t)P, (uint64_t)pl.splits};
+    uint64_t strides[2] = {(uint64_t)C_out * 4, (uint64_t)P * C_out * 4};
+    uint32_t box[3] = {32, 32, 1};
+    if (encode_tmap(&to, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, scratch, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B))
+      return 3;
+  }
   FpropParams p;
   p.out = static_cast<__nv_bfloat16*>(y);
   p.bias = bias;

@@ -335,17 +335,31 @@ conv_persist_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         __syncwarp();
         if (lane_id() == 0) atomicAdd(ticket + 1, 1u);
       } else if (!direct) {
-        float* prow = p.partial + (static_cast<long long>(it.split) * p.P + pix) * p.C_out + it.n_tile * BLOCK_N;
+        // two-kernel split-K: fp32 partial tiles [split][P][C_out], written as 32 x 32 boxes through shared memory
+        // and TMA stores (tmap_out is the 3-d fp32 map of the partial buffer in this mode).  Direct stores were
+        // 32 lanes x 16 bytes to 32 different rows per instruction, as in the old wgrad epilogue.
+        constexpr bool kTwoBufs = Cfg::kBoxBytes >= 4096;     // a 32 x 32 fp32 box is 4 KB: two fit only for BLOCK_N >= 128
+        const int r = static_cast<int>(lane_id());
 #pragma unroll 1
         for (int c = 0; c < kMyChunks; ++c) {
           uint32_t raw[32];
           tmem_ld_32x32(t_addr + (chunk0 + c) * 32, raw);
           tmem_ld_wait();
-          if (valid) {
-            uint4* dst = reinterpret_cast<uint4*>(prow + (chunk0 + c) * 32);
+          const uint32_t box = my_boxes + (kTwoBufs ? (box_count & 1u) * 4096u : 0u);
+          ++box_count;
+          if (lane_id() == 0) {
+            if (kTwoBufs) bulk_wait_read<1>(); else bulk_wait_read<0>();
+          }
+          __syncwarp();
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-              dst[j] = make_uint4(raw[4 * j], raw[4 * j + 1], raw[4 * j + 2], raw[4 * j + 3]);
+          for (int k = 0; k < 8; ++k)
+            st_shared_v4(box + r * 128 + ((k ^ (r & 7)) << 4), raw[4 * k], raw[4 * k + 1], raw[4 * k + 2], raw[4 * k + 3]);
+          fence_proxy_async();
+          __syncwarp();
+          if (lane_id() == 0) {
+            // rows past P are clipped by the map (per split: the split index is its own dimension)
+            tma_store_3d_saddr(&tmap_out, box, it.n_tile * BLOCK_N + (chunk0 + c) * 32, it.m_tile * kBlockM + q * 32, it.split);
+            bulk_commit();
           }
         }
       } else {
