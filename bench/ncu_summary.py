@@ -2,9 +2,9 @@
 list, DDPB_NCU_REPS=1): per kernel the duration, tensor-pipe and DRAM utilisation, DRAM bytes against the
 algorithmic bytes, and the roofline fraction against MEASURED_PEAKS.json (cuBLAS bf16 burst rate for a kernel
 timed alone, copy bandwidth).  ncu serialises and cold-starts every launch: read shares, not absolutes;
-the in-graph times are in profiles/r2_call16_* / r2_call22_*.
+the in-graph times are in profiles/r2_call43_layer_times_*.
 
-    python bench/ncu_summary.py profiles/r2_call17_ncu_raw_metrics.csv > profiles/r2_ncu_summary.txt
+    python bench/ncu_summary.py profiles/r2_call46_ncu_raw_metrics.csv > profiles/r2_ncu_summary.txt
 """
 import csv
 import json
@@ -47,8 +47,8 @@ def bn(li, passes_x, passes_dy, writes_dx):
 ROWS = [("input kernel (crop/flip/normalise -> layer-0 operand)", 0, N * 32 * 32 * 3 + N * 32 * 32 * 64 * 2),
         ("fwd L0 conv+BN (persistent, 64-wide)",) + conv(0, "fwd"), ("fwd L1 conv+BN (128-wide)",) + conv(1, "fwd"),
         ("fwd L3 conv+BN (256-wide)",) + conv(3, "fwd"), ("fwd L5 conv+BN (128-wide)",) + conv(5, "fwd"),
-        ("fwd L7 conv, split-K x4",) + conv(7, "fwd")[:1] + (N * 4 * 512 * 2 + 512 * 4608 * 2 + 4 * N * 4 * 512 * 4,),
-        ("fwd L7 split-K finalize", 0, 5 * N * 4 * 512 * 4), ("fwd L7 BatchNorm forward", 0, N * 4 * 512 * 2 * 1.25),
+        ("fwd L7 conv+BN, split-K x4 summed in the kernel",) + conv(7, "fwd")[:1] +
+        (N * 4 * 512 * 2 + 512 * 4608 * 2 + 2 * 3 * N * 4 * 512 * 4 + 2 * N * 4 * 512 * 2 * 1.25,),
         ("dgrad L1 (64-wide)",) + conv(1, "dgrad"), ("dgrad L3 (256-wide)",) + conv(3, "dgrad"),
         ("dgrad L5 (128-wide)",) + conv(5, "dgrad"),
         ("dgrad L7 split-K x4",) + conv(7, "dgrad")[:1] + (N * 4 * 512 * 2 + 512 * 4608 * 2 + 4 * N * 4 * 512 * 4,),

@@ -61,7 +61,7 @@ for w in which:
         if op == "fwd":
             K.conv_bn_relu_pool_fwd(x, wt, bias, gamma, beta, N, H, W, Cin, Co, taps, pool)
         elif op == "dgrad":
-            K.conv_dgrad(dy, wt, N, H, W, Ci, Co)
+            K.conv_dgrad(dy, wt, N, H, W, Ci, Co, split_sync=None)     # as the engine calls it: two-kernel split-K
         elif op == "wgrad":
             cols = 27 if li == 0 else 9 * Ci
             K.conv_wgrad(dy, x, N, H, W, Cin, Co, taps, cols_valid=cols, out_ld=cols)
