@@ -423,7 +423,9 @@ static double plan_cost(int bn, int splits, long long P, int C_out, int total_k,
   // summed inside the kernel: the warp that draws the last ticket reads the other splits' slices of its tile
   // (measured, profiles/r2_call34_*: ticket + wait for the slowest split + one L2 round trip per split and
   // 32-column chunk, about 7 us at 4 splits: worth it where it keeps the BatchNorm tail inside the kernel)
-  if (splits > 1 && fused) t += 8000.0 + (splits - 1) * 2700.0;
+  if (splits > 1 && fused) t += 8000.0 + (splits - 1) * 2700.0 + (bn == 64 ? 4500.0 : 0.0);
+  // (64-wide: the model above is ~2 us optimistic for the fused 64 x2 plan of layers 6 / 7, measured 22.1 / 22.9 us
+  // against 20.5 / 21.5 us for 128 x4, profiles/r2_call37_*)
   else if (splits > 1) t += 6000.0 + splits * static_cast<double>(P) * C_out * 4.0 / 3000.0;
   // a BatchNorm tail that cannot run inside the kernel (split-K summed by the second kernel) is a third launch
   if (splits > 1 && !fused && with_tail) t += 8000.0;
@@ -534,6 +536,18 @@ extern "C" void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int tap
   out3[0] = pl.pair;
   out3[1] = pl.block_n;
   out3[2] = pl.splits;
+}
+
+// The same with the caller's situation spelled out: with_tail = the fused conv + BatchNorm entry point,
+// with_sync = sync words are passed.  out4 = {pair, block_n, splits, split-K summed inside the kernel}.
+extern "C" void ddpb_conv_plan_ex(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int with_tail,
+                                  int with_sync, int* out4) {
+  const ConvPlan pl = plan_conv(static_cast<long long>(N) * H * W, C_out, taps * (C_in / 64), block_n, true,
+                                with_sync != 0, with_tail != 0);
+  out4[0] = pl.pair;
+  out4[1] = pl.block_n;
+  out4[2] = pl.splits;
+  out4[3] = pl.fused ? 1 : 0;
 }
 
 // Floats of scratch ddpb_conv_fprop wants for this shape (0: it will not split K).

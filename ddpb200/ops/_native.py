@@ -38,6 +38,7 @@ _SIGNATURES = {
     "ddpb_conv_debug_mode": [c_int],
     "ddpb_conv_tail_from_tmem": [c_int],
     "ddpb_conv_plan": [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void],
+    "ddpb_conv_plan_ex": [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void],
     "ddpb_conv_wgrad_splits": [c_int, c_int, c_int, c_int, c_int, c_int],
     "ddpb_conv_wgrad_scratch_elems": [c_int, c_int, c_int, c_int, c_int, c_int],
     "ddpb_conv_wgrad_scratch_elems_ld": [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int],

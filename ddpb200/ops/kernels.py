@@ -79,6 +79,14 @@ def _sync_arg(split_sync, device):
     return split_sync
 
 
+def conv_plan_ex(N, H, W, C_in, C_out, taps=9, block_n=0, *, with_tail=False, with_sync=False) -> tuple[int, int, int, int]:
+    """(kernel, block_n, splits, fused split-K) for a given call situation: ``with_tail`` = the fused
+    conv + BatchNorm entry point, ``with_sync`` = sync words passed.  Host only (works without a GPU)."""
+    out = (C.c_int * 4)()
+    nat.load().ddpb_conv_plan_ex(N, H, W, C_in, C_out, taps, block_n, int(with_tail), int(with_sync), out)
+    return tuple(out)
+
+
 def conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps=9, block_n=0) -> int:
     """fp32 elements of split-K scratch conv_fprop wants for this shape (0 = no split)."""
     return int(nat.load().ddpb_conv_fprop_scratch_elems(N, H, W, C_in, C_out, taps, block_n))

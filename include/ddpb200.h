@@ -94,6 +94,10 @@ long long ddpb_conv_wgrad_static_max_elems(void);
  * to 2; -1 = automatic = 2). */
 void ddpb_conv_force(int kernel, int block_n, int splits);
 void ddpb_conv_plan(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int* out3);
+/* plan for a given call situation: with_tail = ddpb_conv_bn_relu_pool_fwd, with_sync = split_sync passed;
+ * out4 = {kernel, block_n, splits, 1 if the split-K sum happens inside the kernel} */
+void ddpb_conv_plan_ex(int N, int H, int W, int C_in, int C_out, int taps, int block_n, int with_tail, int with_sync,
+                       int* out4);
 void ddpb_conv_debug_timing(unsigned long long* per_cta_stamps);   /* 8 slots per CTA, see bench/conv_probe2.py */
 /* split_sync (optional, may be null): ddpb_conv_split_sync_words() uint32 words, zeroed ONCE by the caller and left
  * zero by every launch.  With it, split-K partial sums are added up inside the persistent kernel (the warp that

@@ -317,3 +317,28 @@ def test_device_augment_option_on_the_cpu_path():
     assert run(0) == run(0)
     assert run(0) != run(1)
     assert run(0) != run(0, device_augment=False)
+
+
+def test_conv_planner_picks_the_measured_best_plans_at_batch_256():
+    """The (tile width, split-K) planner is a cost model; profiles/r2_call37_conv_plan_sweep_in_kernel_split.txt is the
+    measured sweep it was calibrated against (batch 256, 148 SMs).  Host-only: pins its choices for the VGG-11 layers
+    to the measured best (or within 1 us of it), so a change of the cost terms that moves a layer shows up here."""
+    from ddpb200.ops import kernels as K
+
+    layers = [(32, 64, 64, 1), (16, 64, 128, 9), (8, 128, 256, 9), (8, 256, 256, 9), (4, 256, 512, 9), (4, 512, 512, 9),
+              (2, 512, 512, 9), (2, 512, 512, 9)]
+    fwd = [K.conv_plan_ex(256, s, s, ci, co, t, with_tail=True, with_sync=True)[1:] for s, ci, co, t in layers]
+    assert fwd == [(64, 1, 0), (128, 1, 0), (256, 1, 0), (256, 1, 0), (128, 1, 0), (128, 1, 0), (128, 4, 1), (128, 4, 1)]
+    dgrad = [K.conv_plan_ex(256, s, s, co, ci, 9)[1:] for s, ci, co, _ in layers[1:]]
+    assert dgrad == [(64, 1, 0), (128, 1, 0), (256, 1, 0), (256, 4, 0), (128, 1, 0), (128, 4, 0), (128, 4, 0)]
+    # the in-kernel sum is only planned with sync words, for the persistent kernel, with one item per CTA
+    assert K.conv_plan_ex(256, 2, 2, 512, 512, 9, with_tail=True, with_sync=False)[3] == 0
+    for n in (1, 24, 32, 85, 256, 1000):
+        for s, ci, co, t in layers:
+            kern, bn, splits, fused = K.conv_plan_ex(n, s, s, ci, co, t, with_tail=True, with_sync=True)
+            tiles = (n * s * s + 127) // 128 * (co // bn)
+            assert co % bn == 0 and 1 <= splits <= 8
+            assert not fused or (kern == 2 and splits > 1 and tiles * splits <= K.sm_count() and tiles * 16 <= K.conv_split_sync_words())
+            # the scratch query covers the plan with and without sync words / tail
+            need = K.conv_fprop_scratch_elems(n, s, s, ci, co, t)
+            assert need >= (splits * ((n * s * s + 127) // 128) * 128 * co if splits > 1 else 0)
