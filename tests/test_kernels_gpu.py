@@ -461,7 +461,8 @@ def test_batchnorm_tail_from_tmem_equals_the_tail_from_l2(shape, pool):
     assert torch.equal(out[0][0], out[2][0])                       # the conv output itself is deterministic
     assert torch.allclose(out[0][2], out[2][2], rtol=1e-5, atol=1e-6)
     diff = (out[0][1].float() - out[2][1].float()).abs()
-    assert float(diff.max()) <= 2 ** -6 * float(out[0][1].float().abs().max()) and float((diff > 0).float().mean()) < 1e-3
+    # (a last-bit difference of the statistics moves a few outputs by one bf16 ulp; a wrong tail would move most of them)
+    assert float(diff.max()) <= 2 ** -6 * float(out[0][1].float().abs().max()) and float((diff > 0).float().mean()) < 1e-2
     for mode in (0, 2):
         assert _rel_err(out[mode][1], R.bn_relu_pool_fwd(out[mode][0], gamma, beta, N, H, W, pool)) < 1e-2
 
