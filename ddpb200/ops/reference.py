@@ -142,3 +142,45 @@ def augment_normalize_u8(x_nhwc_u8: torch.Tensor, aug: torch.Tensor | None, pad:
     mean = CIFAR_MEAN.to(x.device).view(1, 3, 1, 1)
     std = CIFAR_STD.to(x.device).view(1, 3, 1, 1)
     return (x / 255.0 - mean) / std
+
+
+# ---- Philox4x32-10: the counter-based generator of the device-side augmentation draws ---------------
+_PHILOX_M0, _PHILOX_M1 = 0xD2511F53, 0xCD9E8D57
+_PHILOX_W0, _PHILOX_W1 = 0x9E3779B9, 0xBB67AE85
+
+
+def philox4x32_10(ctr, key):
+    """Philox4x32 with 10 rounds (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3") on numpy
+    arrays: ``ctr`` = four uint32 arrays of one shape, ``key`` = two uint32 scalars or arrays.  Restates
+    ``philox4x32_10`` of csrc/data_prep.cu word for word; checked against the published known-answer vectors
+    in tests/test_cpu_plumbing.py."""
+    import numpy as np
+
+    c = [np.asarray(v, dtype=np.uint64) & 0xFFFFFFFF for v in ctr]
+    k0 = np.asarray(key[0], dtype=np.uint64) & 0xFFFFFFFF
+    k1 = np.asarray(key[1], dtype=np.uint64) & 0xFFFFFFFF
+    for _ in range(10):
+        p0 = c[0] * np.uint64(_PHILOX_M0)          # 32 x 32 -> 64 bit products
+        p1 = c[2] * np.uint64(_PHILOX_M1)
+        c = [(p1 >> np.uint64(32)) ^ c[1] ^ k0, p1 & np.uint64(0xFFFFFFFF),
+             (p0 >> np.uint64(32)) ^ c[3] ^ k1, p0 & np.uint64(0xFFFFFFFF)]
+        k0 = (k0 + np.uint64(_PHILOX_W0)) & np.uint64(0xFFFFFFFF)
+        k1 = (k1 + np.uint64(_PHILOX_W1)) & np.uint64(0xFFFFFFFF)
+    return [v.astype(np.uint32) for v in c]
+
+
+def draw_augmentation(n: int, pad: int, seed: int, step: int) -> torch.Tensor:
+    """The crop / flip parameters ``ddpb_draw_augmentation`` draws for ``n`` images at step counter ``step``:
+    int8 [n][4] = {crop y, crop x in [0, 2 pad], flip, 0}; counter = (image, step, "AUG!", 0), key = seed."""
+    import numpy as np
+
+    seed &= 0xFFFFFFFFFFFFFFFF
+    img = np.arange(n, dtype=np.uint64)
+    zeros = np.zeros(n, dtype=np.uint64)
+    r = philox4x32_10([img, zeros + (step & 0xFFFFFFFF), zeros + 0x41554721, zeros], (seed & 0xFFFFFFFF, seed >> 32))
+    span = np.uint64(2 * pad + 1)
+    out = np.zeros((n, 4), dtype=np.int8)
+    out[:, 0] = ((r[0].astype(np.uint64) * span) >> np.uint64(32)).astype(np.int8)
+    out[:, 1] = ((r[1].astype(np.uint64) * span) >> np.uint64(32)).astype(np.int8)
+    out[:, 2] = (r[2] >> np.uint32(31)).astype(np.int8)
+    return torch.from_numpy(out)

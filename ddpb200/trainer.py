@@ -65,6 +65,7 @@ class Trainer:
         self.device_augment = device_augment
         self.augment_seed = (int(augment_seed) * 0x9E3779B97F4A7C15 + rank) & 0xFFFFFFFFFFFFFFFF
         self.augment_pad = augment_pad
+        self._aug_step_cpu = 0      # CPU path: the step counter the device keeps in _aug_step
         # CTA size of the reductions that overlap backward (mode 'ddp'): 32 CTAs of 256 threads -- the same
         # number of threads as round 1's 16 x 512, spread over twice as many SMs with half the footprint
         # each (2 GPUs, balanced buckets: 0.754 ms per step against 0.772 with 16 x 512, profiles/r2_call23_*)
@@ -563,12 +564,11 @@ class Trainer:
 
     def _step_cpu(self, data, target, aug=None):
         if aug is None and self.device_augment and data.dtype == torch.uint8:
-            g = torch.Generator().manual_seed((self.augment_seed + self.iteration) & 0x7FFFFFFFFFFFFFFF)
-            n, span = data.shape[0], 2 * self.augment_pad + 1
-            aug = torch.zeros(n, 4, dtype=torch.int8)
-            aug[:, 0] = torch.randint(0, span, (n,), generator=g).to(torch.int8)
-            aug[:, 1] = torch.randint(0, span, (n,), generator=g).to(torch.int8)
-            aug[:, 2] = torch.randint(0, 2, (n,), generator=g).to(torch.int8)
+            # the draws the device kernel makes for this seed and step counter (Philox restated in ops/reference.py)
+            from .ops.reference import draw_augmentation
+
+            aug = draw_augmentation(data.shape[0], self.augment_pad, self.augment_seed, self._aug_step_cpu)
+            self._aug_step_cpu += 1
         data = self._to_float_batch(data, aug)
         self.optimizer.zero_grad()
         loss = F.cross_entropy(self.model(data), target)

@@ -342,3 +342,30 @@ def test_conv_planner_picks_the_measured_best_plans_at_batch_256():
             # the scratch query covers the plan with and without sync words / tail
             need = K.conv_fprop_scratch_elems(n, s, s, ci, co, t)
             assert need >= (splits * ((n * s * s + 127) // 128) * 128 * co if splits > 1 else 0)
+
+
+def test_philox_reference_matches_the_published_vectors_and_draws_in_range():
+    """ops/reference.py restates the device generator (Philox4x32-10, csrc/data_prep.cu) in numpy: the Random123
+    known-answer vectors pin the algorithm; the crop / flip draws derived from it are in range, balanced,
+    deterministic in (seed, step) and different across steps, seeds and images."""
+    import numpy as np
+    from ddpb200.ops.reference import draw_augmentation, philox4x32_10
+
+    def kat(ctr, key):
+        return [int(v) for v in philox4x32_10([np.uint32(c) for c in ctr], [np.uint32(k) for k in key])]
+
+    assert kat([0, 0, 0, 0], [0, 0]) == [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]
+    assert kat([0xFFFFFFFF] * 4, [0xFFFFFFFF] * 2) == [0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD]
+    assert kat([0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344], [0xA4093822, 0x299F31D0]) == \
+        [0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1]
+    a = draw_augmentation(4096, 4, 1234, 0)
+    assert a.dtype == torch.int8 and a.shape == (4096, 4)
+    assert int(a[:, :2].min()) == 0 and int(a[:, :2].max()) == 8 and set(a[:, 2].unique().tolist()) == {0, 1}
+    assert int(a[:, 3].abs().max()) == 0
+    for col, k in ((0, 9), (1, 9), (2, 2)):
+        cnt = torch.bincount(a[:, col].long(), minlength=k).float()
+        assert float((cnt - 4096 / k).abs().max()) < 6 * (4096 * (1 / k) * (1 - 1 / k)) ** 0.5
+    assert torch.equal(a, draw_augmentation(4096, 4, 1234, 0))
+    assert not torch.equal(a, draw_augmentation(4096, 4, 1234, 1))
+    assert not torch.equal(a, draw_augmentation(4096, 4, 1235, 0))
+    assert torch.equal(a[:100], draw_augmentation(100, 4, 1234, 0))          # an image's draw does not depend on the batch size
