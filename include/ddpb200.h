@@ -182,6 +182,15 @@ int ddpb_allreduce_avg(const void* const* bufs, const void* mc, int rank, int wo
                        int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow, float lr,
                        float momentum, float weight_decay, long long sgd_off, long long sgd_n, int threads,
                        void* stream);
+/* Many ranges, one launch: the reference's 34 per-parameter all-reduces (part2/part2b/main.py:101-103) or a set of
+ * small buckets.  offs / ns: `count` (<= 64) pairwise disjoint ranges in floats (multiples of 4).  Ranges of at most
+ * small_max floats are reduced one-shot (every rank reduces every element itself and keeps the mean in registers
+ * across the closing barrier) while they fit in the threads' registers; the others two-shot.  p / m / shadow as
+ * above: the SGD update covers exactly the listed ranges. */
+int ddpb_allreduce_multi(const void* const* bufs, const void* mc, int rank, int world, const long long* offs,
+                         const long long* ns, int count, long long small_max, int blocks, int slot_base, int use_mc,
+                         float* p, float* m, void* shadow, float lr, float momentum, float weight_decay,
+                         void* stream);
 /* part2a gather -> mean on rank 0 -> scatter (part2/part2a/main.py:97-115). */
 int ddpb_reduce_root_bcast(const void* const* bufs, const void* mc, int rank, int world, int root, long long off,
                            long long n, int blocks, int slot_base, int use_mc, float* p, float* m, void* shadow,

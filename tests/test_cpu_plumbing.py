@@ -369,3 +369,53 @@ def test_philox_reference_matches_the_published_vectors_and_draws_in_range():
     assert not torch.equal(a, draw_augmentation(4096, 4, 1234, 1))
     assert not torch.equal(a, draw_augmentation(4096, 4, 1235, 0))
     assert torch.equal(a[:100], draw_augmentation(100, 4, 1234, 0))          # an image's draw does not depend on the batch size
+
+
+def test_c_header_library_and_ctypes_signatures_agree():
+    """include/ddpb200.h is the C ABI: it must compile as C99 and as C++, declare exactly the `ddpb_*` symbols the
+    library exports, and the ctypes signatures of ops/_native.py must have the declared number of parameters."""
+    import re
+    import shutil
+    import subprocess
+    from pathlib import Path
+
+    from ddpb200.ops import _native as nat
+    import ddpb200.parallel.comm  # noqa: F401  (registers its optional entry points)
+
+    header = Path(__file__).resolve().parent.parent / "include" / "ddpb200.h"
+    for cc, lang in (("gcc", ["-x", "c", "-std=c99"]), ("g++", ["-x", "c++"])):
+        if shutil.which(cc):
+            subprocess.run([cc, "-fsyntax-only", "-Wall", "-Werror", *lang, str(header)], check=True)
+    text = re.sub(r"/\*.*?\*/", " ", header.read_text(), flags=re.S)
+    declared = {}
+    for m in re.finditer(r"\b(ddpb_\w+)\s*\(([^;{}]*?)\)\s*;", text, flags=re.S):
+        params = m.group(2).strip()
+        declared[m.group(1)] = 0 if params in ("", "void") else params.count(",") + 1
+    nat.load()
+    if shutil.which("nm"):
+        out = subprocess.run(["nm", "-D", "--defined-only", str(nat.lib_path())], capture_output=True, text=True, check=True).stdout
+        exported = {ln.split()[-1] for ln in out.splitlines() if " T " in ln and ln.split()[-1].startswith("ddpb_")}
+        assert exported == set(declared), (sorted(exported - set(declared)), sorted(set(declared) - exported))
+    signatures = {**nat._SIGNATURES, **nat._OPTIONAL}
+    assert set(signatures) <= set(declared), sorted(set(signatures) - set(declared))
+    wrong = {k: (len(v), declared[k]) for k, v in signatures.items() if len(v) != declared[k]}
+    assert not wrong, wrong
+    # and the same kinds (32-bit int, 64-bit int, float, pointer) position by position
+    import ctypes as C
+
+    def header_kind(param):
+        if "*" in param:
+            return "ptr"
+        words = param.replace("const ", "").split()
+        return {"int": "i32", "unsigned int": "i32", "long long": "i64", "unsigned long long": "i64",
+                "float": "f32"}[" ".join(words[:-1])]
+
+    def ctypes_kind(t):
+        if t in (C.c_void_p, C.c_char_p) or issubclass(t, C._Pointer):
+            return "ptr"
+        return {C.c_int: "i32", C.c_uint: "i32", C.c_longlong: "i64", C.c_ulonglong: "i64", C.c_float: "f32"}[t]
+
+    for m in re.finditer(r"\b(ddpb_\w+)\s*\(([^;{}]*?)\)\s*;", text, flags=re.S):
+        name, params = m.group(1), m.group(2).strip()
+        if name in signatures and params not in ("", "void"):
+            assert [header_kind(q) for q in params.split(",")] == [ctypes_kind(t) for t in signatures[name]], name
