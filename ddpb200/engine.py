@@ -361,11 +361,12 @@ class VGGEngine:
         n = 0
         B = self.max_batch
         for li, L in enumerate(self.layers):
-            n += 1                  # fprop (BatchNorm forward fused in)
-            if K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps):
+            n += 1                  # fprop (BatchNorm forward fused in, also when split-K is summed in the kernel)
+            _, _, splits, fused = K.conv_plan_ex(B, L.H, L.W, L.c_in_eff, L.c_out, L.taps, with_tail=True, with_sync=True)
+            if splits > 1 and not fused:
                 n += 2              # split-K finalize + separate BatchNorm forward
-            if li > 0 and K.conv_fprop_scratch_elems(B, L.H, L.W, L.c_out, L.c_in, 9):
-                n += 1
+            if li > 0 and K.conv_plan_ex(B, L.H, L.W, L.c_out, L.c_in, 9)[2] > 1:
+                n += 1              # dgrad is called without sync words: its split-K is summed by the finalize kernel
             out_pix = B * L.H * L.W // (4 if L.pool else 1)
             owner = L.c_out // 8 >= 32 and out_pix * (5 if L.pool else 2) * 16 <= 48 * 1024
             n += 1 if owner else 2  # BatchNorm backward: channel-owner kernel, or reduce + apply

@@ -524,6 +524,7 @@ class Trainer:
         if self.device.type != "cuda":
             return 0
         n = 1 + self.engine.launches_per_train_step()  # input prep (+ first-layer filter pack)
+        n += 1                                          # the one-thread kernel that publishes the loss to the host
         if not self.distributed:
             n += len(self.groups) if (self.overlap_sgd and self.update_stream is not None) else 1
         elif self.mode == "ddp":
