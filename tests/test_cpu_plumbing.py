@@ -419,3 +419,19 @@ def test_c_header_library_and_ctypes_signatures_agree():
         name, params = m.group(1), m.group(2).strip()
         if name in signatures and params not in ("", "void"):
             assert [header_kind(q) for q in params.split(",")] == [ctypes_kind(t) for t in signatures[name]], name
+
+
+def test_launch_count_of_a_step_follows_the_planner():
+    """bench.py's gpu_launches is computed, not measured: VGGEngine.launches_per_train_step asks the planner which layers
+    need a finalize / separate BatchNorm kernel.  Host only (stub engine): 8 conv+BN, 14 BatchNorm backward, 8 + 5
+    wgrad (+ split reductions), 7 + 3 dgrad (+ split-K finalize), 2 classifier = 47 at batch 256."""
+    from types import SimpleNamespace
+
+    from ddpb200.engine import VGGEngine, _Layer
+
+    layers, hw = [], 32
+    for i, (ci, co, pool) in enumerate([(3, 64, True), (64, 128, True), (128, 256, False), (256, 256, True), (256, 512, False),
+                                        (512, 512, True), (512, 512, False), (512, 512, True)]):
+        layers.append(_Layer(hw, hw, ci, 64 if i == 0 else ci, co, 1 if i == 0 else 9, pool, 0, 0, 0, 0))
+        hw = hw // 2 if pool else hw
+    assert VGGEngine.launches_per_train_step(SimpleNamespace(max_batch=256, layers=layers)) == 47
