@@ -21,8 +21,6 @@ from __future__ import annotations
 
 from dataclasses import dataclass
 
-import os
-
 import torch
 import torch.nn as nn
 
