@@ -435,3 +435,24 @@ def test_launch_count_of_a_step_follows_the_planner():
         layers.append(_Layer(hw, hw, ci, 64 if i == 0 else ci, co, 1 if i == 0 else 9, pool, 0, 0, 0, 0))
         hw = hw // 2 if pool else hw
     assert VGGEngine.launches_per_train_step(SimpleNamespace(max_batch=256, layers=layers)) == 47
+
+
+def test_c_example_builds_against_the_header_and_runs(tmp_path):
+    """examples/c_api_plan.c: plain C99 against include/ddpb200.h, linked with the library; the host-side planner
+    entry points need no GPU."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+
+    from ddpb200.ops import _native as nat
+
+    if not shutil.which("gcc"):
+        pytest.skip("no C compiler")
+    nat.load()
+    root = Path(__file__).resolve().parent.parent
+    exe = tmp_path / "c_api_plan"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", f"-I{root / 'include'}", str(root / "examples" / "c_api_plan.c"), "-o",
+                    str(exe), str(nat.lib_path()), f"-Wl,-rpath,{nat.lib_path().parent}"], check=True)
+    out = subprocess.run([str(exe), "256"], capture_output=True, text=True, check=True).stdout
+    assert "ABI 5" in out and "L7  2x2  512->512 | fwd: 128-wide tile x4 (summed in the kernel)" in out
+    assert out.count("\n") == 9
