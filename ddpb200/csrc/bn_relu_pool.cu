@@ -432,7 +432,7 @@ __device__ __forceinline__ void grid_barrier_once(unsigned int* counter, unsigne
 // 256 threads x <=128 registers: small enough to share an SM with a gradient-sync CTA (512
 // threads, ~40 registers).  A cooperative launch needs ALL its CTAs resident at once, so a
 // fatter CTA would make every fused BatchNorm backward wait for the overlapped reductions of
-// mode 'ddp' to drain (measured: per-layer buckets got slower, profiles/r1_call18_*).
+// mode 'ddp' to drain (measured: per-layer buckets got slower; numbers in DESIGN.md par. 7).
 constexpr int kBnFusedThreads = 256;
 
 constexpr int kSliceGroups = 8;   // a CTA owns 8 channel groups = 64 channels ...
@@ -661,7 +661,7 @@ __device__ __forceinline__ uint4 sign_flip_mask(const float (&sc)[8]) {
 }
 
 // CTAs per SM the two kernels are compiled for / resident waves of the launch (measured: 3 / 2 / 2 is best,
-// more CTAs per SM spill and run 1.5-1.8x slower, profiles/r2_call18_*)
+// more CTAs per SM spill and run 1.5-1.8x slower: call 18, numbers in DESIGN.md par. 7)
 #ifndef DDPB_BN2_REDUCE_MINB
 #define DDPB_BN2_REDUCE_MINB 3
 #endif

@@ -405,7 +405,7 @@ static unsigned long long* g_dbg = nullptr;
 static int g_dbg_mode = 0;
 
 // Cycle estimates for the persistent kernel, calibrated on B200 with the in-kernel timeline
-// hook (profiles/r1_call11_conv_timeline.txt): a 64-deep k-step costs max(1.35 x tensor time,
+// hook (profiles/r1_call11_conv_timeline_persistent.txt): a 64-deep k-step costs max(1.35 x tensor time,
 // stage bytes / 55 B per clk of operand ingest); draining a tile costs ~30 cycles per column
 // with eight epilogue warps and overlaps the next tile's main loop.
 static double plan_cost(int bn, int splits, long long P, int C_out, int total_k, bool fused, bool with_tail) {
